@@ -1,0 +1,93 @@
+// fused cross-entropy over a (chunk of) logits: one block per row computes the
+// log-sum-exp online, the NLL for the target, and -- in the same launch --
+// overwrites the logits with d(loss)/d(logits) = (softmax - onehot) * gscale,
+// so the forward and the backward of log_softmax + nll_loss are a single pass
+// plus one re-read that hits L2.  ignore_index rows contribute zero loss and a
+// zero gradient.  The row losses and the count of non-ignored rows are
+// accumulated into a device fp32[2] (sum, count); no host sync.
+//
+// Used by ops.fused_linear_cross_entropy, which runs the vocabulary projection
+// in row chunks through gemm_tcgen05 and calls this on each chunk, so the full
+// [tokens, vocab] logits tensor (817 MB fp32 for the reference LM) never
+// exists.  Reference call sites: nn.Linear(emb, vocab) + nn.CrossEntropyLoss(
+// ignore_index=pad) at 02_development/distributed_utils.py:81, 162, 177, 335, 348.
+#include "common/ptx.cuh"
+#include "common/util.cuh"
+
+namespace hyp {
+
+template <typename T>
+__global__ void __launch_bounds__(512)
+ce_fwd_bwd_kernel(T* __restrict__ logits, long long ld, const long long* __restrict__ targets, int rows, int V,
+                  long long ignore_index, float* __restrict__ loss_sum_count, float* __restrict__ row_lse,
+                  const float* __restrict__ gscale_ptr, float gscale, int write_grad) {
+  __shared__ float red[32];
+  const int row = blockIdx.x;
+  T* lrow = logits + static_cast<long long>(row) * ld;
+  const long long tgt = targets[row];
+  const bool ignored = (tgt == ignore_index) || tgt < 0 || tgt >= V;
+
+  // pass 1: online max / sum-exp
+  float mx = -INFINITY, se = 0.f;
+  for (int c = threadIdx.x; c < V; c += blockDim.x) {
+    const float x = to_f32<T>(lrow[c]);
+    if (x > mx) { se = se * __expf(mx - x) + 1.f; mx = x; }
+    else se += __expf(x - mx);
+  }
+  const float bmx = block_max(mx, red);
+  se = (mx == -INFINITY) ? 0.f : se * __expf(mx - bmx);
+  se = block_sum(se, red);
+  const float lse = bmx + __logf(se);
+  if (threadIdx.x == 0) {
+    if (row_lse) row_lse[row] = lse;
+    if (!ignored) {
+      atomicAdd(loss_sum_count, lse - to_f32<T>(lrow[tgt]));
+      atomicAdd(loss_sum_count + 1, 1.f);
+    }
+  }
+  if (!write_grad) return;
+  __syncthreads();  // the target logit was read above; now overwrite the row
+  const float gs = ignored ? 0.f : (gscale_ptr ? *gscale_ptr * gscale : gscale);
+  for (int c = threadIdx.x; c < V; c += blockDim.x) {
+    const float x = to_f32<T>(lrow[c]);
+    float gr = __expf(x - lse);
+    if (c == tgt) gr -= 1.f;
+    lrow[c] = from_f32<T>(gr * gs);
+  }
+}
+
+// dlogits *= scale[0] ... used when the mean-reduction denominator (count of
+// non-ignored tokens) is only known after all chunks: out = 1 / max(count, 1)
+__global__ void ce_finalize_kernel(const float* __restrict__ sum_count, float* __restrict__ loss_out,
+                                   float* __restrict__ inv_count_out) {
+  const float cnt = fmaxf(sum_count[1], 1.f);
+  if (loss_out) *loss_out = sum_count[0] / cnt;
+  if (inv_count_out) *inv_count_out = 1.f / cnt;
+}
+
+}  // namespace hyp
+
+using namespace hyp;
+
+HYP_API int hyp_ce_fwd_bwd(void* logits, long long ld, const long long* targets, int rows, int V,
+                           long long ignore_index, float* loss_sum_count, float* row_lse, const float* gscale_ptr,
+                           float gscale, int write_grad, int dtype, void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  HYP_REQUIRE(rows > 0 && V > 0, "hyp_ce_fwd_bwd: empty input");
+  const int threads = V >= 8192 ? 512 : 256;
+  if (dtype == DT_F32)
+    ce_fwd_bwd_kernel<float><<<rows, threads, 0, st>>>((float*)logits, ld, targets, rows, V, ignore_index, loss_sum_count, row_lse, gscale_ptr, gscale, write_grad);
+  else if (dtype == DT_BF16)
+    ce_fwd_bwd_kernel<__nv_bfloat16><<<rows, threads, 0, st>>>((__nv_bfloat16*)logits, ld, targets, rows, V, ignore_index, loss_sum_count, row_lse, gscale_ptr, gscale, write_grad);
+  else
+    ce_fwd_bwd_kernel<__half><<<rows, threads, 0, st>>>((__half*)logits, ld, targets, rows, V, ignore_index, loss_sum_count, row_lse, gscale_ptr, gscale, write_grad);
+  HYP_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+HYP_API int hyp_ce_finalize(const float* sum_count, float* loss_out, float* inv_count_out, void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  ce_finalize_kernel<<<1, 1, 0, st>>>(sum_count, loss_out, inv_count_out);
+  HYP_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}

@@ -1,0 +1,253 @@
+// Streaming elementwise kernels: the HBM bandwidth probe (z = x + y, copy),
+// column sums for bias gradients, SwiGLU, dtype casts.  All are 128-bit
+// vectorised grid-stride loops sized to a multiple of the SM count.
+//
+// Reference call sites: `z = x + y` in the bandwidth sweep
+// (Phase 1/01_hardware_exploration.ipynb c1 L148), autocast casts
+// (02_development/distributed_utils.py:175).
+#include "common/ptx.cuh"
+#include "common/util.cuh"
+
+namespace hyp {
+
+template <typename T>
+__global__ void __launch_bounds__(512) stream_add_kernel(const T* __restrict__ x, const T* __restrict__ y,
+                                                         T* __restrict__ z, long long n) {
+  constexpr int V = 16 / sizeof(T);
+  const long long nv = n / V;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  const uint4* x4 = reinterpret_cast<const uint4*>(x);
+  const uint4* y4 = reinterpret_cast<const uint4*>(y);
+  uint4* z4 = reinterpret_cast<uint4*>(z);
+  long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  // two independent 16-byte loads per operand in flight per thread
+  for (; i + stride < nv; i += 2 * stride) {
+    const uint4 a0 = ld_nc_v4(x4 + i), b0 = ld_nc_v4(y4 + i);
+    const uint4 a1 = ld_nc_v4(x4 + i + stride), b1 = ld_nc_v4(y4 + i + stride);
+    uint4 r0, r1;
+    if constexpr (sizeof(T) == 4) {
+      const float* fa = reinterpret_cast<const float*>(&a0);
+      const float* fb = reinterpret_cast<const float*>(&b0);
+      float* fr = reinterpret_cast<float*>(&r0);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) fr[k] = fa[k] + fb[k];
+      fa = reinterpret_cast<const float*>(&a1);
+      fb = reinterpret_cast<const float*>(&b1);
+      fr = reinterpret_cast<float*>(&r1);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) fr[k] = fa[k] + fb[k];
+    } else {
+      float fa[8], fb[8];
+      unpack8<T>(a0, fa); unpack8<T>(b0, fb);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) fa[k] += fb[k];
+      r0 = pack8<T>(fa);
+      unpack8<T>(a1, fa); unpack8<T>(b1, fb);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) fa[k] += fb[k];
+      r1 = pack8<T>(fa);
+    }
+    z4[i] = r0;
+    z4[i + stride] = r1;
+  }
+  for (; i < nv; i += stride) {
+    const uint4 a0 = ld_nc_v4(x4 + i), b0 = ld_nc_v4(y4 + i);
+    uint4 r0;
+    if constexpr (sizeof(T) == 4) {
+      const float* fa = reinterpret_cast<const float*>(&a0);
+      const float* fb = reinterpret_cast<const float*>(&b0);
+      float* fr = reinterpret_cast<float*>(&r0);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) fr[k] = fa[k] + fb[k];
+    } else {
+      float fa[8], fb[8];
+      unpack8<T>(a0, fa); unpack8<T>(b0, fb);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) fa[k] += fb[k];
+      r0 = pack8<T>(fa);
+    }
+    z4[i] = r0;
+  }
+  // scalar tail
+  const long long t = nv * V + static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (t < n) z[t] = from_f32<T>(to_f32<T>(x[t]) + to_f32<T>(y[t]));
+}
+
+__global__ void __launch_bounds__(512) stream_copy_kernel(const uint4* __restrict__ x, uint4* __restrict__ z,
+                                                          long long nv) {
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  for (; i + 3 * stride < nv; i += 4 * stride) {
+    const uint4 a0 = ld_nc_v4(x + i), a1 = ld_nc_v4(x + i + stride), a2 = ld_nc_v4(x + i + 2 * stride),
+                a3 = ld_nc_v4(x + i + 3 * stride);
+    z[i] = a0; z[i + stride] = a1; z[i + 2 * stride] = a2; z[i + 3 * stride] = a3;
+  }
+  for (; i < nv; i += stride) z[i] = ld_nc_v4(x + i);
+}
+
+// out[c] (+)= sum_r x[r, c]  (fp32 atomics; out must be zeroed by the caller unless accumulating)
+template <typename T>
+__global__ void __launch_bounds__(256) colsum_kernel(const T* __restrict__ x, float* __restrict__ out, int M, int N,
+                                                     long long ld, int rows_per_block) {
+  __shared__ float red[8][64];
+  const int cx = threadIdx.x & 31, ry = threadIdx.x >> 5;
+  const int col = blockIdx.x * 64 + cx * 2;
+  const int r0 = blockIdx.y * rows_per_block;
+  const int r1 = min(M, r0 + rows_per_block);
+  float s0 = 0.f, s1 = 0.f;
+  if (col < N) {
+    const bool pair = (col + 1 < N);
+    for (int r = r0 + ry; r < r1; r += 8) {
+      const T* p = x + static_cast<long long>(r) * ld + col;
+      s0 += to_f32<T>(p[0]);
+      if (pair) s1 += to_f32<T>(p[1]);
+    }
+  }
+  red[ry][cx * 2] = s0;
+  red[ry][cx * 2 + 1] = s1;
+  __syncthreads();
+  if (threadIdx.x < 64) {
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) s += red[k][threadIdx.x];
+    const int c = blockIdx.x * 64 + threadIdx.x;
+    if (c < N) atomicAdd(out + c, s);
+  }
+}
+
+// SwiGLU: out = silu(gate) * up, and its backward.
+template <typename T>
+__global__ void swiglu_fwd_kernel(const T* __restrict__ gate, const T* __restrict__ up, T* __restrict__ out,
+                                  long long n) {
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x * 8;
+  for (long long i = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) * 8; i < n; i += stride) {
+    float g[8], u[8];
+    unpack8<T>(*reinterpret_cast<const uint4*>(gate + i), g);
+    unpack8<T>(*reinterpret_cast<const uint4*>(up + i), u);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) g[k] = silu(g[k]) * u[k];
+    *reinterpret_cast<uint4*>(out + i) = pack8<T>(g);
+  }
+}
+template <typename T>
+__global__ void swiglu_bwd_kernel(const T* __restrict__ gate, const T* __restrict__ up, const T* __restrict__ dout,
+                                  T* __restrict__ dgate, T* __restrict__ dup, long long n) {
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x * 8;
+  for (long long i = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) * 8; i < n; i += stride) {
+    float g[8], u[8], d[8], dg[8], du[8];
+    unpack8<T>(*reinterpret_cast<const uint4*>(gate + i), g);
+    unpack8<T>(*reinterpret_cast<const uint4*>(up + i), u);
+    unpack8<T>(*reinterpret_cast<const uint4*>(dout + i), d);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      dg[k] = d[k] * u[k] * dsilu(g[k]);
+      du[k] = d[k] * silu(g[k]);
+    }
+    *reinterpret_cast<uint4*>(dgate + i) = pack8<T>(dg);
+    *reinterpret_cast<uint4*>(dup + i) = pack8<T>(du);
+  }
+}
+
+template <typename TI, typename TO>
+__global__ void cast_kernel(const TI* __restrict__ x, TO* __restrict__ y, long long n, float scale) {
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride)
+    y[i] = from_f32<TO>(to_f32<TI>(x[i]) * scale);
+}
+
+static inline int stream_grid(long long work_items, int threads) {
+  long long b = (work_items + threads - 1) / threads;
+  const long long cap = static_cast<long long>(num_sms()) * 8;
+  return static_cast<int>(b < 1 ? 1 : (b > cap ? cap : b));
+}
+
+}  // namespace hyp
+
+using namespace hyp;
+
+HYP_API int hyp_stream_add(const void* x, const void* y, void* z, long long n, int dtype, void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  HYP_REQUIRE(n >= 0, "hyp_stream_add: negative size");
+  if (n == 0) return 0;
+  HYP_REQUIRE(((uintptr_t)x | (uintptr_t)y | (uintptr_t)z) % 16 == 0, "hyp_stream_add: pointers must be 16B aligned");
+  const int threads = 512;
+  if (dtype == DT_F32) {
+    stream_add_kernel<float><<<stream_grid(n / 8 + 1, threads), threads, 0, st>>>((const float*)x, (const float*)y, (float*)z, n);
+  } else if (dtype == DT_BF16) {
+    stream_add_kernel<__nv_bfloat16><<<stream_grid(n / 16 + 1, threads), threads, 0, st>>>(
+        (const __nv_bfloat16*)x, (const __nv_bfloat16*)y, (__nv_bfloat16*)z, n);
+  } else {
+    stream_add_kernel<__half><<<stream_grid(n / 16 + 1, threads), threads, 0, st>>>((const __half*)x, (const __half*)y, (__half*)z, n);
+  }
+  HYP_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+HYP_API int hyp_stream_copy(const void* x, void* z, long long nbytes, void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  HYP_REQUIRE(nbytes % 16 == 0 && ((uintptr_t)x | (uintptr_t)z) % 16 == 0, "hyp_stream_copy: needs 16B alignment/size");
+  if (nbytes == 0) return 0;
+  const long long nv = nbytes / 16;
+  stream_copy_kernel<<<stream_grid(nv / 4 + 1, 512), 512, 0, st>>>((const uint4*)x, (uint4*)z, nv);
+  HYP_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+HYP_API int hyp_colsum(const void* x, float* out, int M, int N, long long ld, int dtype, void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  HYP_REQUIRE(M > 0 && N > 0, "hyp_colsum: empty input");
+  const int gx = (N + 63) / 64;
+  int gy = (num_sms() * 4 + gx - 1) / gx;
+  if (gy > (M + 31) / 32) gy = (M + 31) / 32;
+  if (gy < 1) gy = 1;
+  const int rpb = (M + gy - 1) / gy;
+  gy = (M + rpb - 1) / rpb;
+  dim3 grid(gx, gy);
+  if (dtype == DT_F32) colsum_kernel<float><<<grid, 256, 0, st>>>((const float*)x, out, M, N, ld, rpb);
+  else if (dtype == DT_BF16) colsum_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>((const __nv_bfloat16*)x, out, M, N, ld, rpb);
+  else colsum_kernel<__half><<<grid, 256, 0, st>>>((const __half*)x, out, M, N, ld, rpb);
+  HYP_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+HYP_API int hyp_swiglu_fwd(const void* gate, const void* up, void* out, long long n, int dtype, void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  HYP_REQUIRE(n % 8 == 0 && dtype != DT_F32, "hyp_swiglu_fwd: n %% 8 == 0 and a 16-bit dtype are required");
+  const int g = stream_grid(n / 8, 256);
+  if (dtype == DT_BF16) swiglu_fwd_kernel<__nv_bfloat16><<<g, 256, 0, st>>>((const __nv_bfloat16*)gate, (const __nv_bfloat16*)up, (__nv_bfloat16*)out, n);
+  else swiglu_fwd_kernel<__half><<<g, 256, 0, st>>>((const __half*)gate, (const __half*)up, (__half*)out, n);
+  HYP_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+HYP_API int hyp_swiglu_bwd(const void* gate, const void* up, const void* dout, void* dgate, void* dup, long long n,
+                           int dtype, void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  HYP_REQUIRE(n % 8 == 0 && dtype != DT_F32, "hyp_swiglu_bwd: n %% 8 == 0 and a 16-bit dtype are required");
+  const int g = stream_grid(n / 8, 256);
+  if (dtype == DT_BF16)
+    swiglu_bwd_kernel<__nv_bfloat16><<<g, 256, 0, st>>>((const __nv_bfloat16*)gate, (const __nv_bfloat16*)up, (const __nv_bfloat16*)dout,
+                                                        (__nv_bfloat16*)dgate, (__nv_bfloat16*)dup, n);
+  else
+    swiglu_bwd_kernel<__half><<<g, 256, 0, st>>>((const __half*)gate, (const __half*)up, (const __half*)dout, (__half*)dgate, (__half*)dup, n);
+  HYP_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+HYP_API int hyp_cast(const void* x, void* y, long long n, int in_dtype, int out_dtype, float scale, void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  if (n == 0) return 0;
+  const int g = stream_grid(n, 256);
+#define HYP_CAST_CASE(TI, TO) cast_kernel<TI, TO><<<g, 256, 0, st>>>((const TI*)x, (TO*)y, n, scale)
+  if (in_dtype == DT_F32 && out_dtype == DT_BF16) HYP_CAST_CASE(float, __nv_bfloat16);
+  else if (in_dtype == DT_F32 && out_dtype == DT_F16) HYP_CAST_CASE(float, __half);
+  else if (in_dtype == DT_BF16 && out_dtype == DT_F32) HYP_CAST_CASE(__nv_bfloat16, float);
+  else if (in_dtype == DT_F16 && out_dtype == DT_F32) HYP_CAST_CASE(__half, float);
+  else if (in_dtype == DT_F32 && out_dtype == DT_F32) HYP_CAST_CASE(float, float);
+  else if (in_dtype == DT_BF16 && out_dtype == DT_BF16) HYP_CAST_CASE(__nv_bfloat16, __nv_bfloat16);
+  else if (in_dtype == DT_F16 && out_dtype == DT_F16) HYP_CAST_CASE(__half, __half);
+  else { set_error("hyp_cast: unsupported dtype pair %d -> %d", in_dtype, out_dtype); return -1; }
+#undef HYP_CAST_CASE
+  HYP_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}

@@ -1,0 +1,456 @@
+// gemm_tcgen05: persistent, warp-specialised GEMM for sm_100a.
+//
+//   D[M,N] = epilogue( alpha * A[M,K] . B[N,K]^T )       fp32 accumulation in TMEM
+//
+// * operands are staged by TMA (cp.async.bulk.tensor, SWIZZLE_128B) into a
+//   4..6 stage shared-memory ring; one elected thread issues tcgen05.mma
+//   (128 x BN x 16, cta_group::1); two TMEM accumulator stages let the
+//   epilogue of tile i overlap the main loop of tile i+1.
+// * either operand may be "MN-major" (its non-reduction dimension contiguous in
+//   global memory), which is what dgrad (dX = dY.W) and wgrad (dW = dY^T.X)
+//   need -- no transposed copies are ever made.
+// * dtypes: bf16 / fp16 (kind::f16) and fp32 run as tf32 (kind::tf32).
+// * epilogue functors: +bias, ReLU / GELU(erf|tanh), +residual, activation
+//   derivative (D = acc * act'(aux)), beta-accumulate, split-K fp32 reduction.
+//
+// Replaces the reference's library GEMM call sites: torch.matmul in the probe
+// (Phase 1/01_hardware_exploration.ipynb c1 L92) and every nn.Linear inside
+// the models (02_development/distributed_utils.py:75-88).
+#include "common/ptx.cuh"
+#include "common/util.cuh"
+
+namespace hyp {
+namespace gemm {
+
+constexpr int BM = 128;
+constexpr int ROW_BYTES = 128;  // one swizzle row: 64 x 16-bit or 32 x fp32
+constexpr int A_STAGE = BM * ROW_BYTES;
+constexpr int NUM_THREADS = 192;  // warp0 TMA, warp1 MMA, warps2-5 epilogue
+constexpr int GROUP_M = 8;
+
+struct Params {
+  int M, N, K;
+  int esize;       // 2 (f16/bf16) or 4 (tf32)
+  int a_mn, b_mn;  // operand majors
+  uint32_t idesc;
+  int splits;      // split-K factor (fp32 atomic epilogue when > 1)
+  // epilogue
+  void* D;
+  long long ldd;
+  int out_dtype;
+  const void* bias;
+  int bias_dtype;
+  const void* aux;  // residual (mode 0) or pre-activation (mode 1)
+  long long ld_aux;
+  int aux_dtype;
+  void* preact_out;  // optional: alpha*acc + bias before the activation (same ld / dtype as D)
+  int act;   // 0 none, 1 relu, 2 gelu(erf), 3 gelu(tanh), 4 silu
+  int mode;  // 0: D = act(alpha*acc + bias) + aux ; 1: D = alpha*acc * act'(aux)
+  float alpha, beta;
+  int vec_ok;  // D (and aux) rows are 16-byte aligned -> vector stores
+};
+
+template <int BN>
+struct Cfg {
+  static constexpr int STAGES = (BN == 256) ? 4 : 6;
+  static constexpr int B_STAGE = BN * ROW_BYTES;
+  static constexpr int TMEM_COLS = 2 * BN;
+  static constexpr int SMEM_BYTES = STAGES * (A_STAGE + B_STAGE) + 256 + 1024;
+};
+
+__device__ __forceinline__ float load_as_f32(const void* p, long long idx, int dt) {
+  if (dt == DT_F32) return reinterpret_cast<const float*>(p)[idx];
+  if (dt == DT_BF16) return __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(p)[idx]);
+  return __half2float(reinterpret_cast<const __half*>(p)[idx]);
+}
+__device__ __forceinline__ void store_from_f32(void* p, long long idx, int dt, float v) {
+  if (dt == DT_F32)
+    reinterpret_cast<float*>(p)[idx] = v;
+  else if (dt == DT_BF16)
+    reinterpret_cast<__nv_bfloat16*>(p)[idx] = __float2bfloat16_rn(v);
+  else
+    reinterpret_cast<__half*>(p)[idx] = __float2half_rn(v);
+}
+__device__ __forceinline__ float apply_act(float x, int act) {
+  switch (act) {
+    case 1: return fmaxf(x, 0.f);
+    case 2: return gelu_erf(x);
+    case 3: return gelu_tanh(x);
+    case 4: return silu(x);
+    default: return x;
+  }
+}
+__device__ __forceinline__ float apply_dact(float x, int act) {
+  switch (act) {
+    case 1: return x > 0.f ? 1.f : 0.f;
+    case 2: return dgelu_erf(x);
+    case 3: return dgelu_tanh(x);
+    case 4: return dsilu(x);
+    default: return 1.f;
+  }
+}
+
+// Epilogue for 8 consecutive columns of one output row.
+__device__ __forceinline__ void epilogue8(const Params& p, float (&v)[8], int row, int col) {
+  const int nvalid = min(8, p.N - col);
+  if (nvalid <= 0) return;
+  const long long doff = static_cast<long long>(row) * p.ldd + col;
+  const long long aoff = static_cast<long long>(row) * p.ld_aux + col;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) v[i] *= p.alpha;
+
+  if (p.splits > 1) {  // fp32 atomic reduction across K splits
+    float* d = reinterpret_cast<float*>(p.D) + doff;
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+      if (i < nvalid) atomicAdd(d + i, v[i]);
+    return;
+  }
+  const bool vec = p.vec_ok && nvalid == 8;
+  if (p.mode == 0) {
+    if (p.bias) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+        if (i < nvalid) v[i] += load_as_f32(p.bias, col + i, p.bias_dtype);
+    }
+    if (p.preact_out) {
+      if (vec && p.out_dtype == DT_BF16) {
+        *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.preact_out) + doff) = pack8<__nv_bfloat16>(v);
+      } else if (vec && p.out_dtype == DT_F16) {
+        *reinterpret_cast<uint4*>(reinterpret_cast<__half*>(p.preact_out) + doff) = pack8<__half>(v);
+      } else {
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+          if (i < nvalid) store_from_f32(p.preact_out, doff + i, p.out_dtype, v[i]);
+      }
+    }
+    if (p.act) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) v[i] = apply_act(v[i], p.act);
+    }
+  }
+  if (p.aux) {
+    float a[8];
+    if (vec && p.aux_dtype != DT_F32) {
+      const uint4 u = *reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(p.aux) + aoff);
+      if (p.aux_dtype == DT_BF16) unpack8<__nv_bfloat16>(u, a); else unpack8<__half>(u, a);
+    } else {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) a[i] = (i < nvalid) ? load_as_f32(p.aux, aoff + i, p.aux_dtype) : 0.f;
+    }
+    if (p.mode == 0) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) v[i] += a[i];
+    } else {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) v[i] *= apply_dact(a[i], p.act);
+    }
+  }
+  if (p.beta != 0.f) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+      if (i < nvalid) v[i] += p.beta * load_as_f32(p.D, doff + i, p.out_dtype);
+  }
+  if (vec) {
+    if (p.out_dtype == DT_BF16) {
+      *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.D) + doff) = pack8<__nv_bfloat16>(v);
+    } else if (p.out_dtype == DT_F16) {
+      *reinterpret_cast<uint4*>(reinterpret_cast<__half*>(p.D) + doff) = pack8<__half>(v);
+    } else {
+      float4* d = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.D) + doff);
+      d[0] = make_float4(v[0], v[1], v[2], v[3]);
+      d[1] = make_float4(v[4], v[5], v[6], v[7]);
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+      if (i < nvalid) store_from_f32(p.D, doff + i, p.out_dtype, v[i]);
+  }
+}
+
+struct TileCoord {
+  int m_blk, n_blk, kb0, kb1;
+};
+
+__device__ __forceinline__ TileCoord decode_tile(int tile, int tiles_m, int tiles_n, int nkb, int splits) {
+  const int per_split = tiles_m * tiles_n;
+  const int s = tile / per_split;
+  const int t = tile - s * per_split;
+  const int group_size = GROUP_M * tiles_n;
+  const int g = t / group_size;
+  const int first_m = g * GROUP_M;
+  const int gm = min(tiles_m - first_m, GROUP_M);
+  const int r = t - g * group_size;
+  TileCoord c;
+  c.m_blk = first_m + r % gm;
+  c.n_blk = r / gm;
+  const int per = (nkb + splits - 1) / splits;
+  c.kb0 = s * per;
+  c.kb1 = min(nkb, c.kb0 + per);
+  return c;
+}
+
+template <int BN>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const Params p) {
+  using C = Cfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + C::STAGES * A_STAGE;
+  uint64_t* full = reinterpret_cast<uint64_t*>(sB + C::STAGES * C::B_STAGE);
+  uint64_t* empty = full + C::STAGES;
+  uint64_t* tfull = empty + C::STAGES;
+  uint64_t* tempty = tfull + 2;
+  uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(tempty + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int epr = ROW_BYTES / p.esize;          // elements per 128-byte row == BK
+  const int nkb = (p.K + epr - 1) / epr;        // k blocks
+  const int tiles_m = (p.M + BM - 1) / BM;
+  const int tiles_n = (p.N + BN - 1) / BN;
+  const int total = tiles_m * tiles_n * p.splits;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      for (int i = 0; i < C::STAGES; ++i) {
+        mbar_init(&full[i], 1);
+        mbar_init(&empty[i], 1);
+      }
+      for (int i = 0; i < 2; ++i) {
+        mbar_init(&tfull[i], 1);
+        mbar_init(&tempty[i], 4);
+      }
+      mbar_fence_init();
+    }
+    __syncwarp();
+    tmem_alloc<C::TMEM_COLS>(tmem_holder);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_holder;
+
+  if (warp == 0) {
+    // ------------------------------------------------------- TMA producer
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < total; tile += gridDim.x) {
+        const TileCoord tc = decode_tile(tile, tiles_m, tiles_n, nkb, p.splits);
+        for (int kb = tc.kb0; kb < tc.kb1; ++kb) {
+          mbar_wait(&empty[stage], phase ^ 1);
+          mbar_expect_tx(&full[stage], A_STAGE + C::B_STAGE);
+          uint8_t* a_dst = sA + stage * A_STAGE;
+          uint8_t* b_dst = sB + stage * C::B_STAGE;
+          if (!p.a_mn) {
+            tma_load_2d(a_dst, &tmA, &full[stage], kb * epr, tc.m_blk * BM);
+          } else {
+            for (int j = 0; j < BM / epr; ++j)
+              tma_load_2d(a_dst + j * epr * ROW_BYTES, &tmA, &full[stage], tc.m_blk * BM + j * epr, kb * epr);
+          }
+          if (!p.b_mn) {
+            tma_load_2d(b_dst, &tmB, &full[stage], kb * epr, tc.n_blk * BN);
+          } else {
+            for (int j = 0; j < BN / epr; ++j)
+              tma_load_2d(b_dst + j * epr * ROW_BYTES, &tmB, &full[stage], tc.n_blk * BN + j * epr, kb * epr);
+          }
+          if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // --------------------------------------------------------- MMA issuer
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      // byte advance of the descriptor start address per UMMA_K step
+      const uint32_t a_kstep = p.a_mn ? (p.esize == 2 ? 16u : 8u) * ROW_BYTES : 32u;
+      const uint32_t b_kstep = p.b_mn ? (p.esize == 2 ? 16u : 8u) * ROW_BYTES : 32u;
+      const uint32_t a_lbo = p.a_mn ? epr * ROW_BYTES : 16u;
+      const uint32_t b_lbo = p.b_mn ? epr * ROW_BYTES : 16u;
+      for (int tile = blockIdx.x; tile < total; tile += gridDim.x) {
+        const TileCoord tc = decode_tile(tile, tiles_m, tiles_n, nkb, p.splits);
+        mbar_wait(&tempty[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * BN;
+        for (int kb = tc.kb0; kb < tc.kb1; ++kb) {
+          mbar_wait(&full[stage], phase);
+          tc_fence_after();
+          const uint32_t a_base = smem_u32(sA + stage * A_STAGE);
+          const uint32_t b_base = smem_u32(sB + stage * C::B_STAGE);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const uint64_t ad = make_smem_desc_sw128(a_base + k * a_kstep, a_lbo, 1024);
+            const uint64_t bd = make_smem_desc_sw128(b_base + k * b_kstep, b_lbo, 1024);
+            const uint32_t accum = (kb > tc.kb0 || k > 0) ? 1u : 0u;
+            if (p.esize == 2) umma_f16(d_tmem, ad, bd, p.idesc, accum);
+            else umma_tf32(d_tmem, ad, bd, p.idesc, accum);
+          }
+          umma_commit(&empty[stage]);
+          if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+        }
+        umma_commit(&tfull[acc]);
+        acc ^= 1;
+        if (acc == 0) acc_phase ^= 1;
+      }
+    }
+  } else {
+    // ----------------------------------------------------------- epilogue
+    const int quarter = warp & 3;  // TMEM lanes [32q, 32q+32) are visible to this warp
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = blockIdx.x; tile < total; tile += gridDim.x) {
+      const TileCoord tc = decode_tile(tile, tiles_m, tiles_n, nkb, p.splits);
+      mbar_wait(&tfull[acc], acc_phase);
+      tc_fence_after();
+      const int row = tc.m_blk * BM + quarter * 32 + lane;
+      const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * BN;
+      const bool has_k = tc.kb1 > tc.kb0;
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        const int col0 = tc.n_blk * BN + c * 32;
+        if (col0 >= p.N) break;  // warp-uniform
+        uint32_t r[32];
+        tmem_ld_32x32(t_row + c * 32, r);
+        tmem_ld_wait();
+        if (row < p.M && has_k) {
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            float v[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) v[i] = __uint_as_float(r[g * 8 + i]);
+            epilogue8(p, v, row, col0 + g * 8);
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty[acc]);
+      acc ^= 1;
+      if (acc == 0) acc_phase ^= 1;
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc<C::TMEM_COLS>(tmem_base);
+}
+
+// ------------------------------------------------------------------ host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* f = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(f);
+  }
+  return fn;
+}
+
+// 2D map over a row-major [outer, inner] matrix with leading dimension ld (elements).
+int make_tmap_2d(CUtensorMap* tm, const void* ptr, int dtype, long long inner, long long outer, long long ld,
+                 int box_inner, int box_outer) {
+  EncodeTiledFn enc = get_encode();
+  HYP_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled is unavailable (driver too old?)");
+  const int es = (dtype == DT_F32) ? 4 : 2;
+  const CUtensorMapDataType dt = (dtype == DT_F32)   ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32
+                                 : (dtype == DT_BF16) ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16
+                                                      : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+  HYP_REQUIRE((reinterpret_cast<uintptr_t>(ptr) & 15) == 0, "TMA operand pointer must be 16-byte aligned");
+  HYP_REQUIRE((ld * es) % 16 == 0, "TMA operand leading dimension must be a multiple of 16 bytes (ld=%lld)", ld);
+  cuuint64_t dims[2] = {static_cast<cuuint64_t>(inner), static_cast<cuuint64_t>(outer)};
+  cuuint64_t strides[1] = {static_cast<cuuint64_t>(ld) * es};
+  cuuint32_t box[2] = {static_cast<cuuint32_t>(box_inner), static_cast<cuuint32_t>(box_outer)};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(tm, dt, 2, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  HYP_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with CUresult %d", static_cast<int>(r));
+  return 0;
+}
+
+template <int BN>
+static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const Params& p, cudaStream_t stream) {
+  using C = Cfg<BN>;
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (!attr_set[dev & 63]) {
+    HYP_CHECK_CUDA(cudaFuncSetAttribute(gemm_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
+    attr_set[dev & 63] = true;
+  }
+  const int tiles = ((p.M + BM - 1) / BM) * ((p.N + BN - 1) / BN) * p.splits;
+  const int grid = tiles < num_sms() ? tiles : num_sms();
+  gemm_kernel<BN><<<grid, NUM_THREADS, C::SMEM_BYTES, stream>>>(ta, tb, p);
+  HYP_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace gemm
+}  // namespace hyp
+
+using namespace hyp;
+
+// See include/hyperion_b200.h for the contract.
+HYP_API int hyp_gemm(const void* A, const void* B, void* D, int M, int N, int K, long long lda, long long ldb,
+                     long long ldd, int in_dtype, int out_dtype, int a_mn_major, int b_mn_major, const void* bias,
+                     int bias_dtype, const void* aux, long long ld_aux, int aux_dtype, void* preact_out, int act, int mode,
+                     float alpha, float beta, int splits, void* stream_) {
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  HYP_REQUIRE(M > 0 && N > 0 && K > 0, "hyp_gemm: empty problem %dx%dx%d", M, N, K);
+  HYP_REQUIRE(in_dtype >= 0 && in_dtype <= 2 && out_dtype >= 0 && out_dtype <= 2, "hyp_gemm: bad dtype");
+  if (splits < 1) splits = 1;
+  HYP_REQUIRE(splits == 1 || (out_dtype == DT_F32 && !bias && !aux && !preact_out && act == 0 && beta == 0.f),
+              "hyp_gemm: split-K needs a zero-initialised fp32 output and a plain epilogue");
+  // tf32 operands must be K-major (the MN-major path needs the 32-bit-base swizzle, not built yet);
+  // callers transpose fp32 operands explicitly (ops.native.gemm does).
+  HYP_REQUIRE(in_dtype != DT_F32 || (!a_mn_major && !b_mn_major), "hyp_gemm: fp32/tf32 operands must be K-major");
+  const int es = (in_dtype == DT_F32) ? 4 : 2;
+  const int epr = gemm::ROW_BYTES / es;
+  const int BN = (N > 128) ? 256 : 128;
+
+  gemm::Params p;
+  p.M = M; p.N = N; p.K = K; p.esize = es; p.a_mn = a_mn_major; p.b_mn = b_mn_major;
+  const uint32_t fmt = (in_dtype == DT_F16) ? 0u : (in_dtype == DT_BF16 ? 1u : 2u);
+  p.idesc = make_idesc(fmt, gemm::BM, BN, a_mn_major != 0, b_mn_major != 0);
+  const int nkb = (K + epr - 1) / epr;
+  if (splits > nkb) splits = nkb;
+  const int per_split = (nkb + splits - 1) / splits;
+  p.splits = (nkb + per_split - 1) / per_split;  // no split is ever empty
+  p.D = D; p.ldd = ldd; p.out_dtype = out_dtype;
+  p.bias = bias; p.bias_dtype = bias_dtype;
+  p.aux = aux; p.ld_aux = ld_aux; p.aux_dtype = aux_dtype;
+  p.preact_out = preact_out;
+  HYP_REQUIRE(!preact_out || reinterpret_cast<uintptr_t>(preact_out) % 16 == 0, "hyp_gemm: preact_out must be 16B aligned");
+  p.act = act; p.mode = mode; p.alpha = alpha; p.beta = beta;
+  const int oes = (out_dtype == DT_F32) ? 4 : 2;
+  bool vec = (reinterpret_cast<uintptr_t>(D) % 16 == 0) && ((ldd * oes) % 16 == 0);
+  if (aux) {
+    const int aes = (aux_dtype == DT_F32) ? 4 : 2;
+    vec = vec && (reinterpret_cast<uintptr_t>(aux) % 16 == 0) && ((ld_aux * aes) % 16 == 0);
+  }
+  p.vec_ok = vec ? 1 : 0;
+
+  CUtensorMap ta, tb;
+  int rc;
+  if (!a_mn_major) rc = gemm::make_tmap_2d(&ta, A, in_dtype, K, M, lda, epr, gemm::BM);   // A: [M, K]
+  else             rc = gemm::make_tmap_2d(&ta, A, in_dtype, M, K, lda, epr, epr);        // A^T: [K, M]
+  if (rc) return rc;
+  if (!b_mn_major) rc = gemm::make_tmap_2d(&tb, B, in_dtype, K, N, ldb, epr, BN);         // B: [N, K]
+  else             rc = gemm::make_tmap_2d(&tb, B, in_dtype, N, K, ldb, epr, epr);        // B^T: [K, N]
+  if (rc) return rc;
+  return (BN == 256) ? gemm::launch<256>(ta, tb, p, stream) : gemm::launch<128>(ta, tb, p, stream);
+}

@@ -1,0 +1,294 @@
+// fused_norm: residual-add + LayerNorm / RMSNorm, forward and backward.
+//
+//   z = x (+ residual);  y = (z - mean) * rstd * gamma + beta        (LayerNorm)
+//   z = x (+ residual);  y = z * rsqrt(mean(z^2) + eps) * gamma      (RMSNorm)
+//
+// 16-bit or fp32 IO, fp32 math, one pass over the row held in registers.
+// Backward produces dz in the same pass and per-block partial dgamma/dbeta in a
+// caller-provided fp32 scratch, reduced by a second small kernel.
+//
+// Reference call sites: nn.LayerNorm inside nn.TransformerEncoderLayer
+// (02_development/distributed_utils.py:79; post-norm with residual) and the
+// HF LlamaRMSNorm reached through distributed_utils.py:465.
+#include "common/ptx.cuh"
+#include "common/util.cuh"
+
+namespace hyp {
+namespace norm {
+
+constexpr int MAXC = 4;  // 8-element chunks per thread -> d <= TPR * 32
+
+template <typename T>
+__device__ __forceinline__ void load8(const T* p, float (&f)[8]) {
+  if constexpr (sizeof(T) == 4) {
+    const float4 a = *reinterpret_cast<const float4*>(p);
+    const float4 b = *reinterpret_cast<const float4*>(p + 4);
+    f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w; f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
+  } else {
+    unpack8<T>(*reinterpret_cast<const uint4*>(p), f);
+  }
+}
+template <typename T>
+__device__ __forceinline__ void store8(T* p, const float (&f)[8]) {
+  if constexpr (sizeof(T) == 4) {
+    *reinterpret_cast<float4*>(p) = make_float4(f[0], f[1], f[2], f[3]);
+    *reinterpret_cast<float4*>(p + 4) = make_float4(f[4], f[5], f[6], f[7]);
+  } else {
+    *reinterpret_cast<uint4*>(p) = pack8<T>(f);
+  }
+}
+
+template <int TPR>
+__device__ __forceinline__ float group_sum(float v, float* red) {
+  if constexpr (TPR == 32) return warp_sum(v);
+  else return block_sum(v, red);
+}
+
+template <typename T, int TPR>
+__global__ void __launch_bounds__(TPR < 128 ? 128 : TPR)
+norm_fwd_kernel(const T* __restrict__ x, const T* __restrict__ residual, const T* __restrict__ gamma,
+                const T* __restrict__ beta, T* __restrict__ y, T* __restrict__ sum_out, float* __restrict__ mean_out,
+                float* __restrict__ rstd_out, int rows, int d, float eps, int rms) {
+  __shared__ float red[32];
+  constexpr int BLOCK = TPR < 128 ? 128 : TPR;
+  constexpr int RPB = BLOCK / TPR;
+  const int row = blockIdx.x * RPB + threadIdx.x / TPR;
+  const int t = threadIdx.x % TPR;
+  if (row >= rows) return;  // only reachable when TPR == 32 (whole warp exits)
+  const long long base = static_cast<long long>(row) * d;
+  float v[MAXC][8];
+  float s = 0.f;
+#pragma unroll
+  for (int k = 0; k < MAXC; ++k) {
+    const int c = (t + k * TPR) * 8;
+    if (c < d) {
+      load8<T>(x + base + c, v[k]);
+      if (residual) {
+        float r[8];
+        load8<T>(residual + base + c, r);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) v[k][i] += r[i];
+      }
+      if (sum_out) store8<T>(sum_out + base + c, v[k]);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) s += rms ? v[k][i] * v[k][i] : v[k][i];
+    }
+  }
+  s = group_sum<TPR>(s, red);
+  float mean = 0.f, rstd;
+  if (rms) {
+    rstd = rsqrtf(s / d + eps);
+  } else {
+    mean = s / d;
+    float q = 0.f;
+#pragma unroll
+    for (int k = 0; k < MAXC; ++k) {
+      const int c = (t + k * TPR) * 8;
+      if (c < d) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { const float u = v[k][i] - mean; q += u * u; }
+      }
+    }
+    q = group_sum<TPR>(q, red);
+    rstd = rsqrtf(q / d + eps);
+  }
+  if (t == 0) {
+    if (mean_out) mean_out[row] = mean;
+    if (rstd_out) rstd_out[row] = rstd;
+  }
+#pragma unroll
+  for (int k = 0; k < MAXC; ++k) {
+    const int c = (t + k * TPR) * 8;
+    if (c < d) {
+      float g[8], b[8], o[8];
+      load8<T>(gamma + c, g);
+      if (beta) load8<T>(beta + c, b);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) o[i] = (v[k][i] - mean) * rstd * g[i] + (beta ? b[i] : 0.f);
+      store8<T>(y + base + c, o);
+    }
+  }
+}
+
+// dz and per-(block,warp-row) partial dgamma / dbeta.
+// partial layout: [P][2][d] fp32 with P = gridDim.x * RPB.
+template <typename T, int TPR>
+__global__ void __launch_bounds__(TPR < 128 ? 128 : TPR)
+norm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ z, const T* __restrict__ gamma,
+                const float* __restrict__ mean_in, const float* __restrict__ rstd_in, T* __restrict__ dz,
+                float* __restrict__ partial, int rows, int d, int rms) {
+  __shared__ float red[32];
+  constexpr int BLOCK = TPR < 128 ? 128 : TPR;
+  constexpr int RPB = BLOCK / TPR;
+  const int sub = threadIdx.x / TPR;
+  const int t = threadIdx.x % TPR;
+  float dg[MAXC][8], db[MAXC][8], g[MAXC][8];
+#pragma unroll
+  for (int k = 0; k < MAXC; ++k) {
+    const int c = (t + k * TPR) * 8;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { dg[k][i] = 0.f; db[k][i] = 0.f; g[k][i] = 0.f; }
+    if (c < d) load8<T>(gamma + c, g[k]);
+  }
+  const float inv_d = 1.f / d;
+  for (int row = blockIdx.x * RPB + sub; row < rows; row += gridDim.x * RPB) {
+    const long long base = static_cast<long long>(row) * d;
+    const float mean = rms ? 0.f : mean_in[row];
+    const float rstd = rstd_in[row];
+    float xh[MAXC][8], wdy[MAXC][8];
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int k = 0; k < MAXC; ++k) {
+      const int c = (t + k * TPR) * 8;
+      if (c < d) {
+        float a[8], b[8];
+        load8<T>(dy + base + c, a);
+        load8<T>(z + base + c, b);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          xh[k][i] = (b[i] - mean) * rstd;
+          wdy[k][i] = a[i] * g[k][i];
+          dg[k][i] += a[i] * xh[k][i];
+          db[k][i] += a[i];
+          s1 += wdy[k][i];
+          s2 += wdy[k][i] * xh[k][i];
+        }
+      }
+    }
+    if (rms) s1 = 0.f; else s1 = group_sum<TPR>(s1, red) * inv_d;
+    s2 = group_sum<TPR>(s2, red) * inv_d;
+#pragma unroll
+    for (int k = 0; k < MAXC; ++k) {
+      const int c = (t + k * TPR) * 8;
+      if (c < d) {
+        float o[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) o[i] = rstd * (wdy[k][i] - s1 - xh[k][i] * s2);
+        store8<T>(dz + base + c, o);
+      }
+    }
+  }
+  float* pg = partial + static_cast<long long>(blockIdx.x * RPB + sub) * 2 * d;
+#pragma unroll
+  for (int k = 0; k < MAXC; ++k) {
+    const int c = (t + k * TPR) * 8;
+    if (c < d) {
+      store8<float>(pg + c, dg[k]);
+      store8<float>(pg + d + c, db[k]);
+    }
+  }
+}
+
+// Column reduce of the partials: out[0][c] = sum_p partial[p][0][c] etc.
+__global__ void __launch_bounds__(256) norm_bwd_reduce_kernel(const float* __restrict__ partial, int P, int d,
+                                                              float* __restrict__ dgamma, float* __restrict__ dbeta,
+                                                              int accumulate) {
+  __shared__ float red[2][8][32];
+  const int cx = threadIdx.x & 31, py = threadIdx.x >> 5;
+  const int col = blockIdx.x * 32 + cx;
+  float a = 0.f, b = 0.f;
+  if (col < d) {
+    for (int p = py; p < P; p += 8) {
+      const float* row = partial + static_cast<long long>(p) * 2 * d;
+      a += row[col];
+      b += row[d + col];
+    }
+  }
+  red[0][py][cx] = a;
+  red[1][py][cx] = b;
+  __syncthreads();
+  if (threadIdx.x < 64) {
+    const int which = threadIdx.x >> 5;
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) s += red[which][k][cx];
+    if (col < d) {
+      float* out = which ? dbeta : dgamma;
+      if (out) out[col] = accumulate ? out[col] + s : s;
+    }
+  }
+}
+
+inline int pick_tpr(int d) { return d <= 1024 ? 32 : (d <= 4096 ? 128 : 256); }
+inline int bwd_grid(int rows, int tpr) {
+  const int block = tpr < 128 ? 128 : tpr;
+  const int rpb = block / tpr;
+  int g = (rows + rpb - 1) / rpb;
+  const int cap = num_sms() * 2;
+  return g > cap ? cap : g;
+}
+
+}  // namespace norm
+}  // namespace hyp
+
+using namespace hyp;
+
+HYP_API int hyp_norm_fwd(const void* x, const void* residual, const void* gamma, const void* beta, void* y,
+                         void* sum_out, float* mean, float* rstd, int rows, int d, float eps, int rms, int dtype,
+                         void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  HYP_REQUIRE(rows > 0 && d > 0 && d % 8 == 0 && d <= 8192, "hyp_norm_fwd: need d %% 8 == 0 and d <= 8192 (d=%d)", d);
+  const int tpr = norm::pick_tpr(d);
+#define HYP_NORM_FWD(T, TPR)                                                                                         \
+  norm::norm_fwd_kernel<T, TPR><<<(rows + (TPR < 128 ? 128 / TPR : 1) - 1) / (TPR < 128 ? 128 / TPR : 1),            \
+                                  (TPR < 128 ? 128 : TPR), 0, st>>>((const T*)x, (const T*)residual, (const T*)gamma, \
+                                                                   (const T*)beta, (T*)y, (T*)sum_out, mean, rstd,    \
+                                                                   rows, d, eps, rms)
+#define HYP_NORM_FWD_T(T)            \
+  if (tpr == 32) HYP_NORM_FWD(T, 32); \
+  else if (tpr == 128) HYP_NORM_FWD(T, 128); \
+  else HYP_NORM_FWD(T, 256)
+  if (dtype == DT_F32) { HYP_NORM_FWD_T(float); }
+  else if (dtype == DT_BF16) { HYP_NORM_FWD_T(__nv_bfloat16); }
+  else { HYP_NORM_FWD_T(__half); }
+#undef HYP_NORM_FWD_T
+#undef HYP_NORM_FWD
+  HYP_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// Bytes of fp32 scratch hyp_norm_bwd needs for (rows, d).
+HYP_API long long hyp_norm_bwd_scratch_bytes(int rows, int d) {
+  const int tpr = norm::pick_tpr(d);
+  const int block = tpr < 128 ? 128 : tpr;
+  const long long P = static_cast<long long>(norm::bwd_grid(rows, tpr)) * (block / tpr);
+  return P * 2 * d * static_cast<long long>(sizeof(float));
+}
+
+namespace hyp { namespace norm {
+int launch_bwd(const void* dy, const void* z, const void* gamma, const float* mean, const float* rstd, void* dz,
+               float* dgamma, float* dbeta, float* scratch, int rows, int d, int rms, int dtype, int accumulate,
+               cudaStream_t st) {
+  const int tpr = pick_tpr(d);
+  const int grid = bwd_grid(rows, tpr);
+  const int block = tpr < 128 ? 128 : tpr;
+  const int P = grid * (block / tpr);
+#define HYP_NORM_BWD(T, TPR)                                                                                  \
+  norm_bwd_kernel<T, TPR><<<grid, block, 0, st>>>((const T*)dy, (const T*)z, (const T*)gamma, mean, rstd,     \
+                                                  (T*)dz, scratch, rows, d, rms)
+#define HYP_NORM_BWD_T(T)             \
+  if (tpr == 32) HYP_NORM_BWD(T, 32); \
+  else if (tpr == 128) HYP_NORM_BWD(T, 128); \
+  else HYP_NORM_BWD(T, 256)
+  if (dtype == DT_F32) { HYP_NORM_BWD_T(float); }
+  else if (dtype == DT_BF16) { HYP_NORM_BWD_T(__nv_bfloat16); }
+  else { HYP_NORM_BWD_T(__half); }
+#undef HYP_NORM_BWD_T
+#undef HYP_NORM_BWD
+  HYP_CHECK_CUDA(cudaGetLastError());
+  norm_bwd_reduce_kernel<<<(d + 31) / 32, 256, 0, st>>>(scratch, P, d, dgamma, dbeta, accumulate);
+  HYP_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+}}  // namespace hyp::norm
+
+HYP_API int hyp_norm_bwd(const void* dy, const void* z, const void* gamma, const float* mean, const float* rstd,
+                         void* dz, float* dgamma, float* dbeta, void* scratch, long long scratch_bytes, int rows, int d,
+                         int rms, int dtype, int accumulate, void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  HYP_REQUIRE(rows > 0 && d > 0 && d % 8 == 0 && d <= 8192, "hyp_norm_bwd: need d %% 8 == 0 and d <= 8192 (d=%d)", d);
+  HYP_REQUIRE(scratch != nullptr && scratch_bytes >= hyp_norm_bwd_scratch_bytes(rows, d),
+              "hyp_norm_bwd: scratch too small (%lld < %lld bytes)", scratch_bytes, hyp_norm_bwd_scratch_bytes(rows, d));
+  return norm::launch_bwd(dy, z, gamma, mean, rstd, dz, dgamma, dbeta, reinterpret_cast<float*>(scratch), rows, d, rms,
+                          dtype, accumulate, st);
+}
