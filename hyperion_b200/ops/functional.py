@@ -1,0 +1,454 @@
+"""Autograd-aware ops.  On a CUDA tensor they run the hand-written sm_100a kernels
+(``libhyperion_b200.so``); on a CPU tensor they run the plain PyTorch formulation
+of the same maths, which is both the oracle of the GPU tests and the code path of
+the gloo/CPU configuration (BASELINE config 1).
+
+There is no silent GPU fallback: a CUDA tensor with the native library missing
+raises (see :func:`_native`).
+"""
+from __future__ import annotations
+
+import math
+
+import torch
+import torch.nn.functional as F
+
+from . import _lib, native
+
+_SUPPORTED = (torch.float32, torch.float16, torch.bfloat16)
+
+
+def _native(*tensors) -> bool:
+    """True -> run the sm_100a kernels.  CUDA tensors without the library are an error."""
+    t0 = next(t for t in tensors if t is not None)
+    if not t0.is_cuda:
+        return False
+    if not _lib.available():
+        if torch.cuda.is_available() and _lib.raw() is None:
+            raise RuntimeError("CUDA tensor given but libhyperion_b200.so is not built; run `python -m hyperion_b200.build`")
+        return False
+    return t0.dtype in _SUPPORTED
+
+
+def _as2d(t: torch.Tensor) -> torch.Tensor:
+    """2-D row-major view usable as a TMA operand (16-byte aligned rows), copying only if needed."""
+    t2 = t.reshape(-1, t.shape[-1])
+    es = t2.element_size()
+    ok = t2.stride(1) == 1 and (t2.stride(0) * es) % 16 == 0 and t2.data_ptr() % 16 == 0
+    if ok:
+        return t2
+    return _padded_copy(t2)
+
+
+def _padded_empty(rows: int, cols: int, dtype, device) -> torch.Tensor:
+    """[rows, cols] view of a buffer whose leading dimension is padded to 16 bytes."""
+    per = 16 // torch.empty((), dtype=dtype).element_size()
+    ld = (cols + per - 1) // per * per
+    if ld == cols:
+        return torch.empty((rows, cols), dtype=dtype, device=device)
+    return torch.empty((rows, ld), dtype=dtype, device=device)[:, :cols]
+
+
+def _padded_copy(t2: torch.Tensor) -> torch.Tensor:
+    out = _padded_empty(t2.shape[0], t2.shape[1], t2.dtype, t2.device)
+    out.copy_(t2)
+    return out
+
+
+def _act_ref(x, act):
+    if act in (None, "none"):
+        return x
+    if act == "relu":
+        return F.relu(x)
+    if act in ("gelu", "gelu_erf"):
+        return F.gelu(x)
+    if act == "gelu_tanh":
+        return F.gelu(x, approximate="tanh")
+    if act == "silu":
+        return F.silu(x)
+    raise ValueError(act)
+
+
+# --------------------------------------------------------------------------- linear
+class _LinearFn(torch.autograd.Function):
+    """y = act(x @ W^T + b) (+ residual) on gemm_tcgen05; dgrad / wgrad use the MN-major operand paths."""
+
+    @staticmethod
+    def forward(ctx, x, w, b, residual, act):
+        x2 = _as2d(x)
+        w2 = _as2d(w)
+        M, N = x2.shape[0], w2.shape[0]
+        out = _padded_empty(M, N, x.dtype, x.device)
+        res2 = _as2d(residual) if residual is not None else None
+        pre = _padded_empty(M, N, x.dtype, x.device) if act not in (None, "none", "relu") else None
+        native.gemm(x2, w2, out=out, bias=b, aux=res2, act=act, preact_out=pre)
+        ctx.act = act
+        ctx.has_bias = b is not None
+        ctx.has_res = residual is not None
+        ctx.x_shape = x.shape
+        # relu'(h) is recoverable from the output only when no residual was added
+        if act == "relu":
+            if residual is not None:
+                raise NotImplementedError("relu + residual in one linear epilogue is not differentiable from the output")
+            ctx.save_for_backward(x2, w2, out)
+        else:
+            ctx.save_for_backward(x2, w2, pre)
+        return out.reshape(*x.shape[:-1], N)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, w2, h = ctx.saved_tensors
+        dy2 = _as2d(dy)
+        act = ctx.act
+        if act not in (None, "none"):
+            # dh = dy * act'(h)   (one elementwise pass; the fused two-layer MLP op avoids it)
+            dh = _dact_mul(dy2, h, act)
+        else:
+            dh = dy2
+        dx = dw = db = dres = None
+        if ctx.needs_input_grad[0]:
+            dx = native.gemm(dh, w2, b_mn_major=True, out=_padded_empty(dh.shape[0], w2.shape[1], dh.dtype, dh.device))
+            dx = dx.reshape(ctx.x_shape)
+        if ctx.needs_input_grad[1]:
+            dw = native.gemm(dh, x2, a_mn_major=True, b_mn_major=True,
+                             out=_padded_empty(w2.shape[0], w2.shape[1], w2.dtype, w2.device))
+            if not dw.is_contiguous():
+                dw = dw.contiguous()
+        if ctx.has_bias and ctx.needs_input_grad[2]:
+            db = native.colsum(dh).to(dy.dtype)
+        if ctx.has_res and ctx.needs_input_grad[3]:
+            dres = dy
+        return dx, dw, db, dres, None
+
+
+def _dact_mul(dy2, h, act):
+    """dy * act'(h) elementwise (torch ops; only used by the un-fused single linear+activation)."""
+    hf = h.float()
+    if act == "relu":
+        g = (hf > 0).float()
+    elif act in ("gelu", "gelu_erf"):
+        g = 0.5 * (1 + torch.erf(hf * 0.7071067811865476)) + hf * torch.exp(-0.5 * hf * hf) * 0.3989422804014327
+    elif act == "gelu_tanh":
+        u = 0.7978845608028654 * (hf + 0.044715 * hf ** 3)
+        t = torch.tanh(u)
+        g = 0.5 * (1 + t) + 0.5 * hf * (1 - t * t) * 0.7978845608028654 * (1 + 3 * 0.044715 * hf * hf)
+    elif act == "silu":
+        s = torch.sigmoid(hf)
+        g = s * (1 + hf * (1 - s))
+    else:
+        raise ValueError(act)
+    return (dy2.float() * g).to(dy2.dtype)
+
+
+def linear(x, w, b=None, act: str | None = None, residual=None):
+    """``act(x @ w.T + b) + residual`` with the bias / activation / residual fused into the GEMM epilogue."""
+    if _native(x, w) and x.shape[-1] % (16 // x.element_size()) == 0:
+        return _LinearFn.apply(x, w, b, residual, act)
+    y = _act_ref(F.linear(x, w, b), act)
+    return y if residual is None else y + residual
+
+
+# --------------------------------------------------------------------------- fused MLP
+class _MlpFn(torch.autograd.Function):
+    """y = act(x W1^T + b1) W2^T + b2 (+ residual); backward fuses act' into the dgrad GEMM epilogue."""
+
+    @staticmethod
+    def forward(ctx, x, w1, b1, w2, b2, residual, act):
+        x2 = _as2d(x)
+        M = x2.shape[0]
+        h = torch.empty((M, w1.shape[0]), dtype=x.dtype, device=x.device)
+        a = torch.empty_like(h)
+        native.gemm(x2, w1, out=a, bias=b1, act=act, preact_out=h)
+        y = torch.empty((M, w2.shape[0]), dtype=x.dtype, device=x.device)
+        native.gemm(a, w2, out=y, bias=b2, aux=_as2d(residual) if residual is not None else None)
+        ctx.save_for_backward(x2, w1, w2, h, a)
+        ctx.act = act
+        ctx.flags = (b1 is not None, b2 is not None, residual is not None)
+        ctx.x_shape = x.shape
+        return y.reshape(*x.shape[:-1], w2.shape[0])
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, w1, w2, h, a = ctx.saved_tensors
+        dy2 = _as2d(dy)
+        has_b1, has_b2, has_res = ctx.flags
+        # dh = (dy @ W2) * act'(h): activation derivative applied in the GEMM epilogue
+        dh = native.gemm(dy2, w2, b_mn_major=True, aux=h, act=ctx.act, mode=1)
+        dw2 = native.gemm(dy2, a, a_mn_major=True, b_mn_major=True)
+        dw1 = native.gemm(dh, x2, a_mn_major=True, b_mn_major=True)
+        dx = native.gemm(dh, w1, b_mn_major=True).reshape(ctx.x_shape) if ctx.needs_input_grad[0] else None
+        db1 = native.colsum(dh).to(dy.dtype) if has_b1 else None
+        db2 = native.colsum(dy2).to(dy.dtype) if has_b2 else None
+        return dx, dw1, db1, dw2, db2, (dy if has_res else None), None
+
+
+def mlp(x, w1, b1, w2, b2, act: str = "relu", residual=None):
+    """Two-layer feed-forward block (the FFN of every transformer in the model zoo)."""
+    es = x.element_size()
+    if _native(x, w1) and x.shape[-1] % (16 // es) == 0 and w1.shape[0] % (16 // es) == 0 and w2.shape[0] % (16 // es) == 0:
+        return _MlpFn.apply(x, w1, b1, w2, b2, residual, act)
+    y = F.linear(_act_ref(F.linear(x, w1, b1), act), w2, b2)
+    return y if residual is None else y + residual
+
+
+# --------------------------------------------------------------------------- norms
+class _NormFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, gamma, beta, residual, eps, rms):
+        xc = x.contiguous()
+        rc = residual.contiguous() if residual is not None else None
+        y, z, mean, rstd = native.norm_fwd(xc, gamma, beta, residual=rc, eps=eps, rms=rms)
+        ctx.save_for_backward(z, gamma, mean, rstd)
+        ctx.rms = rms
+        ctx.has_beta = beta is not None
+        ctx.has_res = residual is not None
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        z, gamma, mean, rstd = ctx.saved_tensors
+        dz, dgamma, dbeta = native.norm_bwd(dy.contiguous(), z, gamma, mean, rstd, rms=ctx.rms, need_beta=ctx.has_beta)
+        return (dz, dgamma.to(gamma.dtype), dbeta.to(gamma.dtype) if dbeta is not None else None,
+                dz if ctx.has_res else None, None, None)
+
+
+def layer_norm(x, gamma, beta, eps: float = 1e-5, residual=None):
+    """LayerNorm(x + residual) in one pass (post-norm residual add fused)."""
+    d = x.shape[-1]
+    if _native(x, gamma) and d % 8 == 0 and d <= 8192:
+        return _NormFn.apply(x, gamma, beta, residual, eps, False)
+    z = x if residual is None else x + residual
+    return F.layer_norm(z, (d,), gamma, beta, eps)
+
+
+def rms_norm(x, gamma, eps: float = 1e-6, residual=None):
+    d = x.shape[-1]
+    if _native(x, gamma) and d % 8 == 0 and d <= 8192:
+        return _NormFn.apply(x, gamma, None, residual, eps, True)
+    z = x if residual is None else x + residual
+    zf = z.float()
+    return (zf * torch.rsqrt(zf.pow(2).mean(-1, keepdim=True) + eps)).to(x.dtype) * gamma
+
+
+# --------------------------------------------------------------------------- embedding
+class _EmbeddingFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, idx, table, padding_idx):
+        ctx.save_for_backward(idx)
+        ctx.shape = table.shape
+        ctx.dtype = table.dtype
+        ctx.padding_idx = -1 if padding_idx is None else padding_idx
+        return native.embedding_fwd(table, idx.contiguous())
+
+    @staticmethod
+    def backward(ctx, dout):
+        (idx,) = ctx.saved_tensors
+        dt = torch.zeros(ctx.shape, device=dout.device, dtype=torch.float32)
+        native.embedding_bwd(dout.contiguous(), idx.contiguous(), dt, ctx.padding_idx)
+        return None, dt.to(ctx.dtype), None
+
+
+def embedding(idx, table, padding_idx=None):
+    if _native(table) and (table.shape[1] * table.element_size()) % 16 == 0:
+        return _EmbeddingFn.apply(idx, table, padding_idx)
+    return F.embedding(idx, table, padding_idx)
+
+
+# --------------------------------------------------------------------------- linear + cross-entropy
+class _LinearCEFn(torch.autograd.Function):
+    """mean CE(x @ W^T + b, targets) without ever holding the [tokens, vocab] logits.
+
+    The vocabulary projection runs in row chunks; each chunk's logits are turned
+    into their gradient in place by the fused CE kernel and immediately consumed
+    by the dgrad / wgrad GEMMs (wgrad accumulates across chunks in fp32).
+    """
+
+    @staticmethod
+    def forward(ctx, x, w, b, targets, ignore_index, chunk_rows):
+        x2 = _as2d(x)
+        w2 = _as2d(w)
+        M, K = x2.shape
+        V = w2.shape[0]
+        dev = x.device
+        tgt = targets.reshape(-1).contiguous()
+        sum_count = torch.zeros(2, device=dev, dtype=torch.float32)
+        inv_cnt = (tgt != ignore_index).sum().clamp(min=1).to(torch.float32).reciprocal().reshape(1)
+        dx = torch.empty_like(x2)
+        dw = torch.zeros((V, K), device=dev, dtype=torch.float32)
+        db = torch.zeros(V, device=dev, dtype=torch.float32) if b is not None else None
+        for r0 in range(0, M, chunk_rows):
+            r1 = min(M, r0 + chunk_rows)
+            logits = _padded_empty(r1 - r0, V, x.dtype, dev)
+            native.gemm(x2[r0:r1], w2, out=logits, bias=b)
+            native.ce_fwd_bwd(logits, tgt[r0:r1], ignore_index, sum_count, gscale_ptr=inv_cnt, n_classes=V)
+            native.gemm(logits, w2, b_mn_major=True, out=dx[r0:r1])
+            native.gemm(logits, x2[r0:r1], a_mn_major=True, b_mn_major=True, out=dw, beta=1.0)
+            if db is not None:
+                native.colsum(logits, out=db)
+        loss = torch.empty((), device=dev, dtype=torch.float32)
+        native.ce_finalize(sum_count, loss)
+        ctx.save_for_backward(dx, dw, db)
+        ctx.x_shape, ctx.w_dtype = x.shape, w.dtype
+        return loss
+
+    @staticmethod
+    def backward(ctx, dloss):
+        dx, dw, db = ctx.saved_tensors
+        s = dloss.to(torch.float32)
+        gx = (dx * s.to(dx.dtype)).reshape(ctx.x_shape)
+        gw = (dw * s).to(ctx.w_dtype)
+        gb = (db * s).to(ctx.w_dtype) if db is not None else None
+        return gx, gw, gb, None, None, None
+
+
+def linear_cross_entropy(x, w, b, targets, ignore_index: int = -100, chunk_rows: int = 4096):
+    """Mean cross-entropy of ``x @ w.T + b`` against ``targets`` (fp32 scalar)."""
+    if _native(x, w) and x.shape[-1] % (16 // x.element_size()) == 0:
+        return _LinearCEFn.apply(x, w, b, targets, ignore_index, chunk_rows)
+    logits = F.linear(x, w, b)
+    return F.cross_entropy(logits.reshape(-1, logits.shape[-1]).float(), targets.reshape(-1), ignore_index=ignore_index)
+
+
+class _CEFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logits, targets, ignore_index):
+        l2 = _padded_copy(logits.reshape(-1, logits.shape[-1]))
+        tgt = targets.reshape(-1).contiguous()
+        sc = torch.zeros(2, device=logits.device, dtype=torch.float32)
+        inv_cnt = (tgt != ignore_index).sum().clamp(min=1).to(torch.float32).reciprocal().reshape(1)
+        native.ce_fwd_bwd(l2, tgt, ignore_index, sc, gscale_ptr=inv_cnt, n_classes=logits.shape[-1])
+        loss = torch.empty((), device=logits.device, dtype=torch.float32)
+        native.ce_finalize(sc, loss)
+        ctx.save_for_backward(l2)
+        ctx.shape = logits.shape
+        return loss
+
+    @staticmethod
+    def backward(ctx, dloss):
+        (g,) = ctx.saved_tensors
+        return (g * dloss.to(g.dtype)).reshape(ctx.shape), None, None
+
+
+def cross_entropy(logits, targets, ignore_index: int = -100):
+    if _native(logits):
+        return _CEFn.apply(logits, targets, ignore_index)
+    return F.cross_entropy(logits.reshape(-1, logits.shape[-1]).float(), targets.reshape(-1), ignore_index=ignore_index)
+
+
+# --------------------------------------------------------------------------- rope / swiglu
+class _RopeFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, theta, positions, layout):
+        ctx.theta, ctx.layout = theta, layout
+        ctx.save_for_backward(positions) if positions is not None else None
+        ctx.has_pos = positions is not None
+        y = x.contiguous().clone()
+        return native.rope_(y, theta, positions, inverse=False, layout=layout)
+
+    @staticmethod
+    def backward(ctx, dy):
+        pos = ctx.saved_tensors[0] if ctx.has_pos else None
+        g = dy.contiguous().clone()
+        return native.rope_(g, ctx.theta, pos, inverse=True, layout=ctx.layout), None, None, None
+
+
+def rope(x, theta: float = 10000.0, positions=None, layout: str = "bshd"):
+    """Rotate-half rotary position embedding on ``[B,S,H,D]`` (``bshd``) or ``[B,H,S,D]`` (``bhsd``)."""
+    if _native(x):
+        return _RopeFn.apply(x, theta, positions, layout)
+    D = x.shape[-1]
+    S = x.shape[1] if layout == "bshd" else x.shape[2]
+    inv_freq = 1.0 / (theta ** (torch.arange(0, D, 2, device=x.device, dtype=torch.float32) / D))
+    if positions is None:
+        pos = torch.arange(S, device=x.device, dtype=torch.float32)[None, :].expand(x.shape[0], S)
+    else:
+        pos = positions.float()
+    ang = pos[..., None] * inv_freq  # [B,S,D/2]
+    cos = torch.cat([ang, ang], -1).cos()
+    sin = torch.cat([ang, ang], -1).sin()
+    if layout == "bshd":
+        cos, sin = cos[:, :, None, :], sin[:, :, None, :]
+    else:
+        cos, sin = cos[:, None, :, :], sin[:, None, :, :]
+    xf = x.float()
+    rot = torch.cat([-xf[..., D // 2:], xf[..., : D // 2]], -1)
+    return (xf * cos + rot * sin).to(x.dtype)
+
+
+class _SwigluFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, gate, up):
+        g, u = gate.contiguous(), up.contiguous()
+        ctx.save_for_backward(g, u)
+        return native.swiglu_fwd(g, u)
+
+    @staticmethod
+    def backward(ctx, dout):
+        g, u = ctx.saved_tensors
+        return native.swiglu_bwd(g, u, dout.contiguous())
+
+
+def swiglu(gate, up):
+    if _native(gate) and gate.dtype != torch.float32 and gate.numel() % 8 == 0:
+        return _SwigluFn.apply(gate, up)
+    return F.silu(gate) * up
+
+
+# --------------------------------------------------------------------------- attention
+def attention(q, k, v, causal: bool = False, key_padding_mask=None, dropout_p: float = 0.0, scale: float | None = None):
+    """softmax(q k^T * scale + mask) v for ``[B, H, S, D]`` tensors.
+
+    key_padding_mask: bool ``[B, S_k]``, True = attend.  Dispatches to the
+    tcgen05 flash kernel (:mod:`hyperion_b200.ops.attn`) when it applies.
+    """
+    from . import attn as _attn
+
+    return _attn.attention(q, k, v, causal=causal, key_padding_mask=key_padding_mask, dropout_p=dropout_p, scale=scale)
+
+
+# --------------------------------------------------------------------------- LoRA
+class _LoraLinearFn(torch.autograd.Function):
+    """y = x W^T + b + scaling * (xd A^T) B^T (+ residual); W is usually frozen."""
+
+    @staticmethod
+    def forward(ctx, x, xd, w, b, A, B, scaling, residual):
+        x2, xd2 = _as2d(x), _as2d(xd)
+        same = xd is x
+        t = native.gemm(xd2, A, alpha=scaling)  # [M, r], scaling folded in
+        y = torch.empty((x2.shape[0], w.shape[0]), dtype=x.dtype, device=x.device)
+        native.gemm(x2, w, out=y, bias=b, aux=_as2d(residual) if residual is not None else None)
+        native.gemm(t, B, out=y, beta=1.0)  # rank-r update accumulated into the same output tile
+        ctx.save_for_backward(x2, xd2, w, A, B, t)
+        ctx.scaling, ctx.same = scaling, same
+        ctx.has_bias, ctx.has_res = b is not None, residual is not None
+        ctx.x_shape = x.shape
+        return y.reshape(*x.shape[:-1], w.shape[0])
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, xd2, w, A, B, t = ctx.saved_tensors
+        dy2 = _as2d(dy)
+        need_x, need_xd, need_w = ctx.needs_input_grad[0], ctx.needs_input_grad[1], ctx.needs_input_grad[2]
+        dt = native.gemm(dy2, B, b_mn_major=True, alpha=ctx.scaling)        # [M, r]
+        dB = native.gemm(dy2, t, a_mn_major=True, b_mn_major=True)          # [out, r]
+        dA = native.gemm(dt, xd2, a_mn_major=True, b_mn_major=True)         # [r, in]
+        dx = dxd = None
+        if need_x or (ctx.same and need_xd):
+            dx = native.gemm(dy2, w, b_mn_major=True)
+            if ctx.same:
+                native.gemm(dt, A, b_mn_major=True, out=dx, beta=1.0)
+            dx = dx.reshape(ctx.x_shape)
+        if not ctx.same and need_xd:
+            dxd = native.gemm(dt, A, b_mn_major=True).reshape(ctx.x_shape)
+        dw = native.gemm(dy2, x2, a_mn_major=True, b_mn_major=True) if need_w else None
+        db = native.colsum(dy2).to(dy.dtype) if (ctx.has_bias and ctx.needs_input_grad[3]) else None
+        return dx, dxd, dw, db, dA, dB, None, (dy if ctx.has_res else None)
+
+
+def lora_linear(x, xd, w, b, A, B, scaling: float, residual=None):
+    """LoRA projection. ``xd`` is ``dropout(x)`` (pass ``x`` itself when dropout is off)."""
+    per = 16 // x.element_size()
+    if _native(x, w) and x.shape[-1] % per == 0 and w.shape[0] % per == 0 and A.shape[0] % per == 0:
+        return _LoraLinearFn.apply(x, xd, w, b, A, B, scaling, residual)
+    y = F.linear(x, w, b) + scaling * F.linear(F.linear(xd, A), B)
+    return y if residual is None else y + residual

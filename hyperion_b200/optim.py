@@ -1,0 +1,103 @@
+"""FusedAdamW: AdamW over :class:`FlatParams` in one kernel launch (``csrc/optim.cu``).
+
+* fp32 master weights + exp_avg / exp_avg_sq live here; the module's parameters are the 16-bit
+  compute copy, rewritten by the same kernel (so AMP needs no per-op weight casts).
+* ``max_norm`` (global-norm clipping), ``inv_scale`` (AMP unscale) and ``found_inf`` (skip on
+  overflow) are device scalars read by the kernel -- the step never syncs the host.
+* Without the native library (CPU tests) the identical update runs as torch ops.
+
+Reference: ``torch.optim.AdamW(model.parameters(), lr=...)`` + ``GradScaler.step`` +
+``clip_grad_norm_`` (02_development/distributed_utils.py:161, 179, 231, 334, 351-352, 503, 522-523).
+"""
+from __future__ import annotations
+
+import torch
+
+from .ops import _lib, native
+from .parallel.flat import FlatParams
+
+
+class FusedAdamW:
+    def __init__(self, flat: FlatParams, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8,
+                 weight_decay: float = 0.01, max_norm: float = 0.0, shard: tuple[int, int] | None = None):
+        """``shard=(start, end)``: keep optimizer state only for that element range (FSDP)."""
+        self.flat = flat
+        self.lr, self.betas, self.eps, self.weight_decay, self.max_norm = lr, betas, eps, weight_decay, max_norm
+        self.step_count = 0
+        self.start, self.end = shard if shard is not None else (0, flat.numel)
+        n = self.end - self.start
+        dev = flat.device
+        self.master = flat.data[self.start:self.end].to(torch.float32).clone() if flat.dtype != torch.float32 else None
+        self.exp_avg = torch.zeros(n, device=dev, dtype=torch.float32)
+        self.exp_avg_sq = torch.zeros(n, device=dev, dtype=torch.float32)
+        self._norm_buf = torch.zeros(2, device=dev, dtype=torch.float32)
+
+    # -- norms ---------------------------------------------------------------------------------
+    def grad_sumsq(self, grad: torch.Tensor | None = None) -> torch.Tensor:
+        """fp32[2] = (sum of squares, non-finite flag) of the (local) gradient, computed on device."""
+        g = grad if grad is not None else self.flat.grad[self.start:self.end]
+        self._norm_buf.zero_()
+        if g.is_cuda and _lib.available():
+            native.sumsq(g, self._norm_buf)
+        else:
+            gf = g.float()
+            self._norm_buf[0] = (gf * gf).sum()
+            self._norm_buf[1] = (~torch.isfinite(gf)).any().float()
+        return self._norm_buf
+
+    # -- step ----------------------------------------------------------------------------------
+    @torch.no_grad()
+    def step(self, grad: torch.Tensor | None = None, sumsq: torch.Tensor | None = None,
+             inv_scale: torch.Tensor | None = None, found_inf: torch.Tensor | None = None) -> None:
+        self.step_count += 1
+        g = grad if grad is not None else self.flat.grad[self.start:self.end]
+        p16 = self.flat.data[self.start:self.end]
+        b1, b2 = self.betas
+        if self.max_norm > 0 and sumsq is None:
+            sumsq = self.grad_sumsq(g)
+        if g.is_cuda and _lib.available():
+            if self.master is not None:
+                native.adamw_step(self.master, g, self.exp_avg, self.exp_avg_sq, p16, lr=self.lr, beta1=b1, beta2=b2,
+                                  eps=self.eps, weight_decay=self.weight_decay, step=self.step_count,
+                                  max_norm=self.max_norm, sumsq=sumsq, inv_scale=inv_scale, found_inf=found_inf)
+            else:
+                native.adamw_step(p16, g, self.exp_avg, self.exp_avg_sq, None, lr=self.lr, beta1=b1, beta2=b2,
+                                  eps=self.eps, weight_decay=self.weight_decay, step=self.step_count,
+                                  max_norm=self.max_norm, sumsq=sumsq, inv_scale=inv_scale, found_inf=found_inf)
+            return
+        # ---- torch formulation of the same update (CPU / oracle) ----
+        if found_inf is not None and float(found_inf.reshape(-1)[0]) != 0.0:
+            return
+        gf = g.float()
+        scale = float(inv_scale.reshape(-1)[0]) if inv_scale is not None else 1.0
+        if self.max_norm > 0:
+            norm = float(sumsq[0]) ** 0.5 * scale
+            coef = self.max_norm / (norm + 1e-6)
+            if coef < 1.0:
+                scale *= coef
+        gf = gf * scale
+        p = self.master if self.master is not None else p16
+        self.exp_avg.mul_(b1).add_(gf, alpha=1 - b1)
+        self.exp_avg_sq.mul_(b2).addcmul_(gf, gf, value=1 - b2)
+        c1 = 1 - b1 ** self.step_count
+        c2 = 1 - b2 ** self.step_count
+        denom = (self.exp_avg_sq.sqrt() / (c2 ** 0.5)).add_(self.eps)
+        p.mul_(1 - self.lr * self.weight_decay).addcdiv_(self.exp_avg, denom, value=-self.lr / c1)
+        if self.master is not None:
+            p16.copy_(p.to(p16.dtype))
+
+    def zero_grad(self, set_to_none: bool = False) -> None:
+        self.flat.zero_grad()
+
+    # -- checkpointing ---------------------------------------------------------------------------
+    def state_dict(self) -> dict:
+        return {"step": self.step_count, "exp_avg": self.exp_avg, "exp_avg_sq": self.exp_avg_sq, "master": self.master,
+                "lr": self.lr, "betas": self.betas, "eps": self.eps, "weight_decay": self.weight_decay}
+
+    def load_state_dict(self, sd: dict) -> None:
+        self.step_count = int(sd["step"])
+        self.exp_avg.copy_(sd["exp_avg"])
+        self.exp_avg_sq.copy_(sd["exp_avg_sq"])
+        if self.master is not None and sd.get("master") is not None:
+            self.master.copy_(sd["master"])
+            self.flat.data[self.start:self.end].copy_(self.master.to(self.flat.dtype))

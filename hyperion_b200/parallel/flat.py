@@ -1,0 +1,101 @@
+"""Flat parameter storage.
+
+Trainable parameters of a module are re-pointed at views of ONE flat buffer (``data``), and
+their ``.grad`` at views of a second one (``grad``), so that
+
+* AdamW is a single streaming kernel over the flat buffers (``optim.FusedAdamW``),
+* a DDP bucket or an FSDP shard is a contiguous byte range that a communication kernel can
+  address on every peer with the same offset (the buffers can live in symmetric memory).
+
+Order: parameters are laid out in REVERSE registration order, which is (approximately) the order
+their gradients become ready in backward -- so bucket k of the flat gradient is complete before
+bucket k+1 and can be reduced while backward is still running.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+
+import torch
+import torch.nn as nn
+
+ALIGN_BYTES = 256
+
+
+@dataclass
+class ParamSpec:
+    name: str
+    param: nn.Parameter
+    offset: int   # element offset into the flat buffers
+    numel: int
+
+
+class FlatParams:
+    def __init__(self, named_params, dtype: torch.dtype | None = None, device=None, reverse: bool = True,
+                 pad_to: int = 1, allocator=None):
+        """``named_params``: iterable of (name, Parameter); only ``requires_grad`` ones are taken.
+        ``allocator(numel, dtype, device)`` lets callers place the buffers in symmetric memory."""
+        items = [(n, p) for n, p in named_params if p.requires_grad]
+        seen, uniq = set(), []
+        for n, p in items:  # tied parameters appear once
+            if id(p) not in seen:
+                seen.add(id(p))
+                uniq.append((n, p))
+        if reverse:
+            uniq = uniq[::-1]
+        if not uniq:
+            raise ValueError("no trainable parameters")
+        self.dtype = dtype or uniq[0][1].dtype
+        self.device = device or uniq[0][1].device
+        es = torch.empty((), dtype=self.dtype).element_size()
+        align = ALIGN_BYTES // es
+        self.specs: list[ParamSpec] = []
+        off = 0
+        for n, p in uniq:
+            self.specs.append(ParamSpec(n, p, off, p.numel()))
+            off += (p.numel() + align - 1) // align * align
+        self.numel = (off + pad_to - 1) // pad_to * pad_to
+        alloc = allocator or (lambda n, dt, dev: torch.zeros(n, dtype=dt, device=dev))
+        self.data = alloc(self.numel, self.dtype, self.device)
+        self.grad = alloc(self.numel, self.dtype, self.device)
+        self.data.zero_()
+        self.grad.zero_()
+        with torch.no_grad():
+            for s in self.specs:
+                view = self.data[s.offset:s.offset + s.numel].view(s.param.shape)
+                view.copy_(s.param.data.to(self.dtype))
+                s.param.data = view
+                s.param.grad = self.grad[s.offset:s.offset + s.numel].view(s.param.shape)
+
+    def zero_grad(self) -> None:
+        self.grad.zero_()
+        for s in self.specs:  # re-attach in case something set .grad to None
+            if s.param.grad is None or s.param.grad.data_ptr() != self.grad.data_ptr() + s.offset * self.grad.element_size():
+                s.param.grad = self.grad[s.offset:s.offset + s.numel].view(s.param.shape)
+
+    def rebind(self, data: torch.Tensor | None = None, grad: torch.Tensor | None = None) -> None:
+        """Point parameters / grads at new flat buffers of the same size (contents are copied)."""
+        with torch.no_grad():
+            if data is not None:
+                data.copy_(self.data)
+                self.data = data
+                for s in self.specs:
+                    s.param.data = data[s.offset:s.offset + s.numel].view(s.param.shape)
+            if grad is not None:
+                grad.copy_(self.grad)
+                self.grad = grad
+                for s in self.specs:
+                    s.param.grad = grad[s.offset:s.offset + s.numel].view(s.param.shape)
+
+    def buckets(self, cap_bytes: int, first_cap_bytes: int | None = None) -> list[tuple[int, int, list[int]]]:
+        """Contiguous (start, end, [spec indices]) element ranges of at most ``cap_bytes`` (whole parameters)."""
+        es = self.data.element_size()
+        out, cur_start, cur_idx = [], 0, []
+        cap = first_cap_bytes or cap_bytes
+        for i, s in enumerate(self.specs):
+            end = self.specs[i + 1].offset if i + 1 < len(self.specs) else self.numel
+            if cur_idx and (end - cur_start) * es > cap:
+                out.append((cur_start, s.offset, cur_idx))
+                cur_start, cur_idx, cap = s.offset, [], cap_bytes
+            cur_idx.append(i)
+        out.append((cur_start, self.numel, cur_idx))
+        return out
