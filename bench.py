@@ -1,0 +1,142 @@
+#!/usr/bin/env python3
+"""Headline benchmark (driver contract; see the task statement and BASELINE.json).
+
+    python bench.py --gpus 1 --steps 10 --warmup 3
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port P \
+        bench.py --gpus 8 --steps 10 --warmup 3
+
+Flagship = BASELINE config 4: GPT-2 medium (354.8 M parameters), FSDP full-shard state, bf16, WikiText-2-shaped
+synthetic tokens, sequence length 1024, weak scaling (fixed per-GPU batch); metric = whole-job tokens/s, device-timed
+with CUDA events, max over ranks.  ``--config resnet50_ddp | vit_ddp | lm_ddp | llama_lora`` select the other
+BASELINE configs.  Prints ONE JSON line on rank 0.
+
+``--impl reference`` must run the unmodified reference from ``baseline/_ref``; the reference is a set of notebooks
+and scripts without ``setup.py`` / ``pyproject.toml`` and pip refuses to install it, so that arm prints
+``{"impl": "reference", "unavailable": ...}``.  ``--impl torch`` runs the stock-PyTorch restatement
+(torch FSDP/DDP + NCCL + cuBLAS, ``baseline/torch_baseline.py``) for the same config -- the operative baseline of
+BASELINE.md section 3.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=8)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", choices=["hyperion", "reference", "torch"], default="hyperion")
+    ap.add_argument("--config", default="gpt2_fsdp", choices=["gpt2_fsdp", "resnet50_ddp", "vit_ddp", "lm_ddp", "llama_lora"])
+    ap.add_argument("--batch", type=int, default=None, help="per-GPU batch")
+    ap.add_argument("--seq", type=int, default=None)
+    ap.add_argument("--size", default=None, help="model size override (gpt2: medium/small/tiny; llama: 7b/tiny)")
+    ap.add_argument("--no-fused-comm", dest="fused_comm", action="store_false", default=None)
+    ap.add_argument("--no-e2e", dest="e2e", action="store_false", default=True)
+    return ap.parse_args()
+
+
+def main() -> int:
+    args = parse()
+    if args.impl == "reference":
+        print(json.dumps({"impl": "reference", "unavailable":
+                          "pip cannot install /root/reference (no setup.py/pyproject.toml; notebooks + scripts that "
+                          "import matplotlib/peft and download from the network); see DESIGN.md"}))
+        return 0
+    if args.impl == "torch":
+        from baseline.torch_baseline import run as run_torch
+
+        return run_torch(args)
+
+    import torch
+    import torch.distributed as dist
+
+    from hyperion_b200.ops import _lib
+    from hyperion_b200.parallel.runtime import max_over_ranks, setup
+    from hyperion_b200.utils.timing import ClockSampler
+
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    if world != args.gpus and rank == 0:
+        print(f"[bench] warning: --gpus {args.gpus} but WORLD_SIZE={world}; using {world}", file=sys.stderr)
+    if not torch.cuda.is_available():
+        print(json.dumps({"error": "no CUDA device", "metric": "tokens/s"}))
+        return 1
+    if world > 1:
+        dev = setup(rank, world, "nccl")
+    else:
+        dev = torch.device("cuda", 0)
+        torch.cuda.set_device(dev)
+        torch.manual_seed(0)
+    assert _lib.available(), "libhyperion_b200.so must be built (python -m hyperion_b200.build)"
+
+    from hyperion_b200.bench.cases import make_case
+
+    case = make_case(args.config, dev, rank, world, batch=args.batch, seq=args.seq, size=args.size,
+                     fused_comm=args.fused_comm)
+
+    def sync_all():
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize(dev)
+
+    # ---------------- device-timed region: inputs resident on the device
+    for _ in range(args.warmup):
+        case.step(case.device_batch())
+    sync_all()
+    sampler = ClockSampler(dev.index or 0).start() if rank == 0 else None
+    launches0 = _lib.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        case.step(case.device_batch())
+    e1.record()
+    sync_all()
+    launches = _lib.launch_count() - launches0
+    ms = max_over_ranks(e0.elapsed_time(e1), dev)
+    clocks = sampler.stop() if sampler is not None else None
+    ms_per_step = ms / args.steps
+    value = case.items_per_step * world / (ms_per_step / 1e3)
+
+    # ---------------- end-to-end region: pinned host batch -> H2D every step, loss D2H every step
+    e2e = None
+    if args.e2e:
+        host_batches = [case.host_batch(i) for i in range(max(2, min(args.steps, 4)))]
+        for i in range(2):
+            case.step_e2e(host_batches[i % len(host_batches)])
+        sync_all()
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        f0.record()
+        for i in range(args.steps):
+            case.step_e2e(host_batches[i % len(host_batches)])
+        f1.record()
+        sync_all()
+        ms2 = max_over_ranks(f0.elapsed_time(f1), dev) / args.steps
+        e2e = {"value": case.items_per_step * world / (ms2 / 1e3), "unit": case.unit, "ms_per_step": ms2,
+               "h2d_bytes_per_step": case.h2d_bytes, "d2h_bytes_per_step": case.d2h_bytes}
+
+    if rank == 0:
+        out = {
+            "metric": case.metric, "value": value, "unit": case.unit, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": case.dtype, "data": "synthetic", "impl": "hyperion",
+            "config": case.config, "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
+            "peak_mem_gb": torch.cuda.max_memory_allocated(dev) / 2 ** 30,
+        }
+        print(json.dumps(out), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

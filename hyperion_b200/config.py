@@ -10,20 +10,22 @@ from pathlib import Path
 
 @dataclass
 class HardwareConfig:
-    gpu_type: str = "NVIDIA B200"
+    gpu_type: str = "B200"
     num_gpus: int = 8
-    memory_per_gpu: str = "180GB"
+    memory_per_gpu_gb: int = 180
 
 
 @dataclass
 class OptimizationConfig:
-    use_amp: bool = True
-    amp_dtype: str = "bf16"          # addition: the reference only had a boolean
-    use_torch_compile: bool = False  # the hot path is hand-written kernels, never torch.compile
+    enable_amp: bool = True
+    amp_dtype: str = "bf16"          # addition: the reference only had the boolean
+    enable_compile: bool = False     # kept for schema parity; the hot path is hand-written kernels, never torch.compile
     compile_mode: str = "reduce-overhead"
-    use_channels_last: bool = True
+    optimize_dataloader: bool = True
+    set_omp_threads: bool = True
+    enable_channels_last: bool = True
     gradient_accumulation_steps: int = 1
-    gradient_checkpointing: bool = False
+    enable_gradient_checkpointing: bool = False
     distributed_strategy: str = "ddp"
 
 
@@ -32,7 +34,7 @@ class BenchmarkingConfig:
     batch_sizes: list = field(default_factory=lambda: [1, 2, 4, 8, 16, 32, 64, 128])
     models: list = field(default_factory=lambda: ["resnet50", "vit_small", "transformer"])
     precision_formats: list = field(default_factory=lambda: ["fp32", "fp16", "bf16"])
-    iterations: int = 50
+    num_iterations: int = 50
     warmup_iterations: int = 10
 
 
@@ -40,8 +42,6 @@ class BenchmarkingConfig:
 class DistributedConfig:
     backend: str = "nccl"
     init_method: str = "env://"
-    world_size: int = -1
-    rank: int = -1
 
 
 @dataclass

@@ -114,10 +114,12 @@ def stream_ptr(device=None) -> int:
 
 
 _launches = 0
+# kernels launched per entry-point call (everything not listed launches exactly one)
+_KERNELS_PER_CALL = {"hyp_norm_bwd": 2, "hyp_ipc_alloc": 0, "hyp_ipc_open": 0, "hyp_ipc_close": 0, "hyp_ipc_free": 0}
 
 
 def launch_count() -> int:
-    """Number of native entry-point calls made so far (bench.py reports the delta)."""
+    """Number of sm_100a kernels of this library launched so far (bench.py reports the delta)."""
     return _launches
 
 
@@ -126,7 +128,7 @@ def call(name: str, *args) -> None:
     global _launches
     lib = require()
     rc = getattr(lib, name)(*args)
-    _launches += 1
+    _launches += _KERNELS_PER_CALL.get(name, 1)
     if rc != 0:
         msg = lib.hyp_last_error().decode(errors="replace")
         raise RuntimeError(f"{name} failed (rc={rc}): {msg}")

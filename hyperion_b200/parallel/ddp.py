@@ -165,3 +165,9 @@ class HyperionDDP(nn.Module):
 
     def load_state_dict(self, sd, *args, **kwargs):
         return self.module.load_state_dict(sd, *args, **kwargs)
+
+    def loss(self, *args, **kwargs):
+        """Forward through ``module.loss`` (fused LM-head + cross-entropy) with DDP's buffer sync."""
+        if self.broadcast_buffers and self.world_size > 1 and self.training:
+            self._sync_buffers()
+        return self.module.loss(*args, **kwargs)

@@ -31,7 +31,7 @@ class ParamSpec:
 
 class FlatParams:
     def __init__(self, named_params, dtype: torch.dtype | None = None, device=None, reverse: bool = True,
-                 pad_to: int = 1, allocator=None):
+                 pad_to: int = 1, allocator=None, unit_key=None, unit_align: int = 1, grad_allocator=None):
         """``named_params``: iterable of (name, Parameter); only ``requires_grad`` ones are taken.
         ``allocator(numel, dtype, device)`` lets callers place the buffers in symmetric memory."""
         items = [(n, p) for n, p in named_params if p.requires_grad]
@@ -49,14 +49,29 @@ class FlatParams:
         es = torch.empty((), dtype=self.dtype).element_size()
         align = ALIGN_BYTES // es
         self.specs: list[ParamSpec] = []
+        # ``unit_key(name)`` groups consecutive parameters into units (FSDP); a unit starts at a multiple of
+        # ``unit_align`` elements so it splits evenly over the ranks in 16-byte multiples.
+        self.units: list[list] = []  # [start, end, key]
         off = 0
+        prev_key = object()
         for n, p in uniq:
+            key = unit_key(n) if unit_key is not None else None
+            if unit_key is not None and key != prev_key:
+                off = (off + unit_align - 1) // unit_align * unit_align
+                if self.units:
+                    self.units[-1][1] = off
+                self.units.append([off, off, key])
+                prev_key = key
             self.specs.append(ParamSpec(n, p, off, p.numel()))
             off += (p.numel() + align - 1) // align * align
+        pad_to = max(pad_to, unit_align)
         self.numel = (off + pad_to - 1) // pad_to * pad_to
+        if self.units:
+            self.units[-1][1] = self.numel
         alloc = allocator or (lambda n, dt, dev: torch.zeros(n, dtype=dt, device=dev))
+        galloc = grad_allocator or alloc
         self.data = alloc(self.numel, self.dtype, self.device)
-        self.grad = alloc(self.numel, self.dtype, self.device)
+        self.grad = galloc(self.numel, self.dtype, self.device)
         self.data.zero_()
         self.grad.zero_()
         with torch.no_grad():

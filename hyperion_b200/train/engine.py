@@ -1,0 +1,95 @@
+"""Training engine shared by every trainer: precision policy + parallel wrapper + fused optimizer.
+
+    eng = build_engine(model, strategy="ddp", precision="bf16", lr=2e-4, device=dev)
+    loss = eng.model.loss(x, y); eng.backward_and_step(loss)
+
+One ``backward_and_step`` = scale loss -> backward (communication kernels fire from autograd hooks and
+overlap) -> fused AdamW (unscale / clip / skip-on-overflow read from device scalars) -> scaler update ->
+zero the flat gradient.  Nothing in it synchronises the host.
+"""
+from __future__ import annotations
+
+import torch
+import torch.nn as nn
+
+from ..amp import DynamicLossScaler, policy
+from ..optim import FusedAdamW
+from ..parallel.ddp import HyperionDDP
+from ..parallel.flat import FlatParams
+from ..parallel.fsdp import HyperionFSDP
+from ..parallel.runtime import world
+
+
+def cast_trainable(model: nn.Module, dtype: torch.dtype) -> nn.Module:
+    """Move floating-point parameters and buffers to the compute dtype (BatchNorm statistics stay fp32)."""
+    if dtype == torch.float32:
+        return model
+    for m in model.modules():
+        for name, p in m.named_parameters(recurse=False):
+            if p.is_floating_point():
+                p.data = p.data.to(dtype)
+        for name, b in m.named_buffers(recurse=False):
+            if b.is_floating_point() and not isinstance(m, nn.modules.batchnorm._BatchNorm):
+                setattr(m, name, b.to(dtype))
+    return model
+
+
+class Engine:
+    def __init__(self, model, wrapped, flat, optimizer, scaler, strategy: str, precision, clip: float):
+        self.raw_model, self.model, self.flat, self.optimizer, self.scaler = model, wrapped, flat, optimizer, scaler
+        self.strategy, self.precision, self.clip = strategy, precision, clip
+        self.rank, self.world_size = world()
+
+    def backward_and_step(self, loss: torch.Tensor) -> None:
+        scaler = self.scaler
+        (scaler.scale_loss(loss) if scaler is not None else loss).backward()
+        if self.strategy == "fsdp":
+            self.model.step()
+            return
+        inv_scale = found_inf = sumsq = None
+        fused_ddp = self.strategy == "ddp" and getattr(self.model, "fused", False)
+        if scaler is not None and scaler.enabled:
+            if fused_ddp:
+                found_inf = self.model.symm.found_inf  # raised on every rank by the all-reduce kernel; grads already unscaled
+                scaler.found_inf = found_inf
+            else:
+                sumsq = self.optimizer.grad_sumsq()
+                scaler.note_overflow(sumsq)
+                inv_scale, found_inf = scaler.inv_scale, scaler.found_inf
+        if self.clip > 0 and sumsq is None:
+            sumsq = self.optimizer.grad_sumsq()
+        self.optimizer.step(sumsq=sumsq if self.clip > 0 else None, inv_scale=inv_scale, found_inf=found_inf)
+        if scaler is not None:
+            scaler.update()
+        self.optimizer.zero_grad()
+
+    def state_for_checkpoint(self):
+        return self.optimizer if self.strategy != "fsdp" else None
+
+
+def build_engine(model: nn.Module, *, strategy: str = "single", precision: str = "bf16", lr: float = 1e-3,
+                 betas=(0.9, 0.999), eps: float = 1e-8, weight_decay: float = 0.01, clip: float = 0.0, device=None,
+                 fused_comm: bool | None = None, bucket_cap_mb: float = 25.0, fsdp_units=None,
+                 fsdp_min_num_params: int = 100_000, broadcast_buffers: bool = True) -> Engine:
+    rank, W = world()
+    pol = policy(precision)
+    device = torch.device(device) if device is not None else next(model.parameters()).device
+    if device.type != "cuda":
+        pol = policy("fp32") if precision != "fp32" and not torch.cuda.is_available() and precision == "fp16" else pol
+    model = model.to(device)
+    cast_trainable(model, pol.dtype)
+    scaler = DynamicLossScaler(device, enabled=True) if pol.needs_scaler else None
+    if strategy == "fsdp":
+        wrapped = HyperionFSDP(model, units=fsdp_units, min_num_params=fsdp_min_num_params, lr=lr, betas=betas, eps=eps,
+                               weight_decay=weight_decay, max_norm=clip, fused=fused_comm, loss_scaler=scaler)
+        return Engine(model, wrapped, wrapped.flat, None, scaler, strategy, pol, clip)
+    if strategy == "ddp" and W > 1:
+        wrapped = HyperionDDP(model, bucket_cap_mb=bucket_cap_mb, fused=fused_comm, loss_scaler=scaler,
+                              broadcast_buffers=broadcast_buffers)
+        flat = wrapped.flat
+    else:
+        wrapped = model
+        flat = FlatParams(model.named_parameters(), device=device)
+        strategy = "single" if strategy != "ddp" else "ddp"
+    opt = FusedAdamW(flat, lr=lr, betas=betas, eps=eps, weight_decay=weight_decay, max_norm=clip)
+    return Engine(model, wrapped, flat, opt, scaler, strategy, pol, clip)

@@ -1,0 +1,288 @@
+"""CPU-only tests of the framework layer (tests/cpu): config, CLI, data formats, CSV schemas,
+scaling-report arithmetic against the reference's shipped CSVs, checkpoint key compatibility, LoRA maths, optimizer
+parity.  Oracles are the PyTorch classes / numbers the reference itself uses."""
+import copy
+import csv
+import json
+import os
+from pathlib import Path
+
+import pytest
+import torch
+import torch.nn as nn
+
+REF = Path("/root/reference")
+
+
+def test_config_roundtrip_and_reference_keys(tmp_path):
+    from hyperion_b200.config import HyperionConfig, load_default
+
+    cfg = load_default()
+    d = cfg.to_dict()
+    assert set(d) == {"hardware", "optimization", "benchmarking", "distributed"}
+    ref_cfg = REF / "Phase 1/default_config.json"
+    if ref_cfg.exists():
+        ref = json.loads(ref_cfg.read_text())
+        for section, keys in ref.items():
+            assert section in d
+            for k in keys:
+                assert k in d[section], f"{section}.{k} missing"
+        loaded = HyperionConfig.from_dict(ref)
+        assert loaded.benchmarking.num_iterations == 50 and loaded.benchmarking.warmup_iterations == 10
+    p = tmp_path / "c.json"
+    cfg.save(p)
+    assert HyperionConfig.load(p).to_dict() == d
+
+
+def test_cli_flags_match_reference():
+    import run_distributed
+
+    p = run_distributed.build_parser()
+    a = p.parse_args([])
+    assert a.model == "language_ddp" and a.epochs == 5 and a.scaling_gpus == "1,2,4,8" and a.progress_every == 50
+    assert a.model_id == "NousResearch/Llama-2-7b-hf"
+    for m in ["language_ddp", "cifar", "language_fsdp", "llama", "all", "scaling", "resnet50", "vit", "gpt2"]:
+        assert p.parse_args(["--model", m]).model == m
+    assert p.parse_args(["--lora", "--batch_size", "2"]).lora
+
+
+def test_synthetic_wikitext_format(tmp_path):
+    from hyperion_b200.data import WikiText2TorchDataset, synth
+
+    ds = synth.write_wikitext2_like(tmp_path / "wikitext2_tokenized", rows={"train": 50, "validation": 7, "test": 9})
+    from datasets import load_from_disk
+
+    back = load_from_disk(str(tmp_path / "wikitext2_tokenized"))
+    assert set(back.keys()) == {"train", "validation", "test"} and len(back["train"]) == 50
+    assert set(back["train"].column_names) == {"input_ids", "attention_mask"}
+    row = back["train"][0]
+    assert len(row["input_ids"]) == 128 and len(row["attention_mask"]) == 128
+    t = WikiText2TorchDataset(back, "train")
+    ids, mask = t[3]
+    assert ids.dtype == torch.long and ids.shape == (128,) and mask.shape == (128,)
+    assert bool(((ids == synth.GPT2_PAD) == (mask == 0)).all())
+    assert synth.WIKITEXT2_ROWS == {"train": 23767, "validation": 2461, "test": 2891}
+
+
+def test_synthetic_cifar_format(tmp_path):
+    from hyperion_b200.data import CIFAR10TorchDataset, synth
+
+    synth.write_cifar10_like(tmp_path, rows={"train": 20, "test": 5})
+    data = torch.load(tmp_path / "cifar10_train.pt", weights_only=False)
+    assert isinstance(data, list) and len(data) == 20
+    img, lbl = CIFAR10TorchDataset(data)[0]
+    assert img.shape == (3, 32, 32) and img.dtype == torch.float32 and -1 <= img.min() and img.max() <= 1
+    assert isinstance(lbl, int) and 0 <= lbl < 10
+
+
+def test_device_resident_loader_shards_like_distributed_sampler():
+    from hyperion_b200.data import DeviceResidentLoader
+
+    x = torch.arange(103)
+    seen = []
+    for r in range(4):
+        ld = DeviceResidentLoader((x,), 8, r, 4, shuffle=True, seed=3)
+        ld.set_epoch(1)
+        got = torch.cat([b[0] for b in ld])
+        assert got.numel() == 26
+        seen.append(got)
+    allv = torch.cat(seen)
+    assert set(allv.tolist()) == set(range(103))  # every sample seen, padding only repeats
+
+
+def test_csv_logger_headers(tmp_path):
+    from hyperion_b200.utils.metrics import HEADERS, CsvLogger
+
+    assert HEADERS["language_ddp"] == ["epoch", "loss", "duration", "gpus"]
+    assert HEADERS["cifar_ddp"] == ["epoch", "loss", "accuracy", "duration", "gpus"]
+    assert HEADERS["llama"] == ["epoch", "loss", "duration_s", "gpus", "mode"]
+    lg = CsvLogger(tmp_path, "cifar_ddp", 4, rank=0)
+    lg.log(1, 0.5, 91.2, 3.3, 4)
+    rows = list(csv.reader(open(lg.path)))
+    assert rows[0] == HEADERS["cifar_ddp"] and rows[1][0] == "1"
+    assert lg.run_id.startswith("cifar_ddp_4gpus_") and lg.path.name.endswith("_metrics.csv")
+
+
+@pytest.mark.skipif(not (REF / "data/distributed").exists(), reason="reference CSVs not mounted")
+def test_scaling_report_reproduces_reference_numbers(tmp_path):
+    """The reference publishes 3.42x (LM DDP) and 2.93x (ResNet-18) at 4 GPUs (data/distributed/scaling_analysis.csv:3)."""
+    import shutil
+
+    from hyperion_b200.utils.report import create_scaling_report
+
+    for f in (REF / "data/distributed").glob("*_metrics.csv"):
+        shutil.copy(f, tmp_path / f.name)
+    table = create_scaling_report(tmp_path, plot=False)
+    row4 = table[table.gpus == 4].iloc[0]
+    assert abs(row4["language_ddp_speedup"] - 3.4223) < 2e-3
+    assert abs(row4["cifar_speedup"] - 2.9274) < 2e-3
+    assert abs(row4["language_ddp_efficiency"] - 3.4223 / 4) < 1e-3
+    out = (tmp_path / "scaling_analysis.csv").read_text().splitlines()[0]
+    assert out.startswith("gpus,ideal,")
+
+
+def test_scaling_report_never_fabricates(tmp_path):
+    from hyperion_b200.utils.report import create_scaling_report
+
+    assert create_scaling_report(tmp_path, plot=False) is None
+    assert not list(tmp_path.glob("scaling_analysis*"))
+
+
+def test_scaling_orchestrator_commands():
+    from hyperion_b200.utils.scaling import run_scaling_experiment
+
+    cmds = run_scaling_experiment("cifar", [1, 2], epochs=1, base_dir="/tmp/x", dry_run=True)
+    assert len(cmds) == 2 and "--nproc-per-node=2" in cmds[1] and "--model=cifar" in cmds[1]
+    assert "127.0.0.1" in cmds[0]
+
+
+def test_model_state_dict_keys_match_reference_classes():
+    import torchvision
+
+    from hyperion_b200 import models
+
+    class RefLM(nn.Module):  # 02_development/distributed_utils.py:75-88
+        def __init__(self, vocab_size, emb_dim=256, n_heads=4, n_layers=2):
+            super().__init__()
+            self.embed = nn.Embedding(vocab_size, emb_dim)
+            self.tr = nn.TransformerEncoder(nn.TransformerEncoderLayer(d_model=emb_dim, nhead=n_heads), num_layers=n_layers)
+            self.fc = nn.Linear(emb_dim, vocab_size)
+
+    ref, mine = RefLM(1000), models.SimpleTransformerLM(1000)
+    a, b = ref.state_dict(), mine.state_dict()
+    assert set(a) == set(b) and all(a[k].shape == b[k].shape for k in a)
+    assert sum(p.numel() for p in models.SimpleTransformerLM(50257).parameters()) == 28_411_985
+    nb = models.NotebookTransformerLM(1000).state_dict()
+    assert {k.split(".")[0] for k in nb} == {"embedding", "transformer", "fc"}
+    for m, tv in [(models.resnet18(10), torchvision.models.resnet18(num_classes=10)),
+                  (models.resnet50(), torchvision.models.resnet50())]:
+        a, b = m.state_dict(), tv.state_dict()
+        assert set(a) == set(b) and all(a[k].shape == b[k].shape for k in a)
+    assert sum(p.numel() for p in models.FallbackCNN().parameters()) == 212_328
+    assert sum(p.numel() for p in models.create_custom_transformer().parameters()) == 18_914_304
+
+
+def test_lm_forward_matches_torch_encoder_numerically():
+    """Loading the reference class's weights into our module reproduces its eval-mode output."""
+    from hyperion_b200.models import SimpleTransformerLM
+
+    torch.manual_seed(0)
+
+    class RefLM(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.embed = nn.Embedding(500, 64)
+            self.tr = nn.TransformerEncoder(nn.TransformerEncoderLayer(d_model=64, nhead=4, dim_feedforward=128), num_layers=2,
+                                            enable_nested_tensor=False)
+            self.fc = nn.Linear(64, 500)
+
+        def forward(self, x):
+            return self.fc(self.tr(self.embed(x).permute(1, 0, 2)).permute(1, 0, 2))
+
+    ref = RefLM().eval()
+    mine = SimpleTransformerLM(500, 64, 4, 2, 128).eval()
+    mine.load_state_dict(ref.state_dict())
+    x = torch.randint(0, 500, (3, 17))
+    with torch.no_grad():
+        assert torch.allclose(mine(x), ref(x), atol=1e-4, rtol=1e-4)
+
+
+def test_lora_math_and_peft_export(tmp_path):
+    from hyperion_b200.lora import LoRALinear, inject_lora, load_adapter, lora_state_dict, save_pretrained, trainable_parameters
+    from hyperion_b200.models import LlamaConfig, LlamaForCausalLM
+
+    torch.manual_seed(0)
+    base = nn.Linear(32, 48, bias=False)
+    l = LoRALinear(base, r=4, alpha=8, dropout=0.0).eval()
+    nn.init.normal_(l.lora_B.weight, std=0.1)
+    x = torch.randn(5, 32)
+    want = x @ (base.weight + (8 / 4) * l.lora_B.weight @ l.lora_A.weight).t()
+    assert torch.allclose(l(x), want, atol=1e-5)
+    assert torch.allclose(x @ l.merged_weight().t(), want, atol=1e-5)
+    cfg = LlamaConfig.tiny()
+    m = inject_lora(LlamaForCausalLM(cfg))
+    per_layer = 4 * 2 * cfg.hidden_size * 16
+    assert trainable_parameters(m) == cfg.num_hidden_layers * per_layer
+    # the 7B count the reference reports: 32 layers * 4 proj * 2 mats * 4096 * 16
+    assert 32 * 4 * 2 * 4096 * 16 == 16_777_216
+    out = save_pretrained(m, tmp_path / "adapter", "NousResearch/Llama-2-7b-hf")
+    cfgj = json.loads((out / "adapter_config.json").read_text())
+    assert cfgj["r"] == 16 and cfgj["lora_alpha"] == 32 and cfgj["target_modules"] == ["q_proj", "k_proj", "v_proj", "o_proj"]
+    sd = lora_state_dict(m)
+    assert "base_model.model.model.layers.0.self_attn.q_proj.lora_A.weight" in sd
+    m2 = inject_lora(LlamaForCausalLM(cfg))
+    load_adapter(m2, out)
+    k = "base_model.model.model.layers.1.self_attn.v_proj.lora_A.weight"
+    assert torch.equal(lora_state_dict(m2)[k], sd[k])
+
+
+def test_fused_adamw_cpu_path_matches_torch():
+    from hyperion_b200.optim import FusedAdamW
+    from hyperion_b200.parallel.flat import FlatParams
+
+    torch.manual_seed(0)
+    m = nn.Sequential(nn.Linear(16, 32), nn.ReLU(), nn.Linear(32, 4))
+    ref = copy.deepcopy(m)
+    flat = FlatParams(m.named_parameters())
+    opt = FusedAdamW(flat, lr=1e-2, weight_decay=0.01, max_norm=0.5)
+    ropt = torch.optim.AdamW(ref.parameters(), lr=1e-2, weight_decay=0.01)
+    x, y = torch.randn(8, 16), torch.randn(8, 4)
+    for _ in range(4):
+        opt.zero_grad(); ropt.zero_grad()
+        ((m(x) - y) ** 2).mean().backward(); opt.step()
+        ((ref(x) - y) ** 2).mean().backward(); torch.nn.utils.clip_grad_norm_(ref.parameters(), 0.5); ropt.step()
+    for a, b in zip(m.parameters(), ref.parameters()):
+        assert torch.allclose(a, b, atol=1e-5)
+
+
+def test_loss_scaler_update_rule():
+    from hyperion_b200.amp import DynamicLossScaler
+
+    s = DynamicLossScaler("cpu", init_scale=1024.0, growth_interval=2)
+    s.found_inf.fill_(1.0); s.update()
+    assert s.scale.item() == 512.0 and s.found_inf.item() == 0
+    s.update(); s.update()
+    assert s.scale.item() == 1024.0
+    sd = s.state_dict()
+    assert {"scale", "growth_factor", "backoff_factor", "growth_interval", "_growth_tracker"} <= set(sd)
+
+
+def test_checkpoint_formats(tmp_path):
+    from hyperion_b200.models import SimpleTransformerLM
+    from hyperion_b200.utils.checkpoint import load_model, save_model, verify
+
+    m = SimpleTransformerLM(100, 32, 2, 1, 64)
+    save_model(m, tmp_path / "x_model.pt")
+    obj = torch.load(tmp_path / "x_model.pt", weights_only=False)
+    assert list(obj) == ["model_state_dict"] and not any(k.startswith("module.") for k in obj["model_state_dict"])
+    assert verify(tmp_path / "x_model.pt")
+    m2 = SimpleTransformerLM(100, 32, 2, 1, 64)
+    load_model(m2, tmp_path / "x_model.pt")
+    assert all(torch.equal(a, b) for a, b in zip(m.state_dict().values(), m2.state_dict().values()))
+
+
+def test_activation_checkpointing_same_grads_and_memory_api():
+    from hyperion_b200.memory import MemoryStats, enable_checkpointing
+    from hyperion_b200.models import NotebookTransformerLM
+
+    torch.manual_seed(0)
+    a = NotebookTransformerLM(200, 32, 2, 2, dropout=0.0)
+    b = copy.deepcopy(a)
+    assert enable_checkpointing(b, True) >= 1 and b.use_checkpoint
+    x = torch.randint(0, 200, (2, 9))
+    a.loss(x, x).backward(); b.loss(x, x).backward()
+    for p, q in zip(a.parameters(), b.parameters()):
+        assert torch.allclose(p.grad, q.grad, atol=1e-6)
+    s = MemoryStats().sample()
+    assert s.allocated_mb >= 0 and s.peak_mb >= 0
+
+
+def test_fsdp_unit_policy_matches_reference_wrap():
+    """size_based_auto_wrap_policy(min_num_params=100_000) gives 8 units for the LM."""
+    from hyperion_b200.models import SimpleTransformerLM
+    from hyperion_b200.parallel.fsdp import size_based_units
+
+    units = size_based_units(SimpleTransformerLM(50257), 100_000)
+    assert len(units) == 8
+    sizes = sorted(sum(p.numel() for p in u.parameters()) for u in units)
+    assert sizes[-1] == 12_916_049 and sizes[-2] == 12_865_792
