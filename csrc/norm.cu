@@ -292,3 +292,64 @@ HYP_API int hyp_norm_bwd(const void* dy, const void* z, const void* gamma, const
   return norm::launch_bwd(dy, z, gamma, mean, rstd, dz, dgamma, dbeta, reinterpret_cast<float*>(scratch), rows, d, rms,
                           dtype, accumulate, st);
 }
+
+// ---------------------------------------------------------------------------------------------------------
+// hyp_norm_bwd_noalloc: the same backward as hyp_norm_bwd for callers that have no way to obtain scratch.
+//
+// Who needs this: code that calls the library from a place where device memory cannot be allocated -- a
+// plugin running inside another runtime's execution callback (an inference-server backend, a custom-call
+// hook of a graph executor), a real-time loop with a fixed memory budget, or a thin C wrapper that owns no
+// allocator at all.  Such callers can pass their inputs and outputs, but they cannot call cudaMalloc (the
+// host runtime forbids it, or it would synchronise the device at a bad moment) and they have nobody to ask
+// for a temporary buffer.
+//
+// The partial dgamma/dbeta sums therefore live in a fixed array compiled into the library.  Every GPU that
+// loads the library holds HYP_NORM_BWD_NOALLOC_SCRATCH_BYTES (16 MiB) of device memory for it until the
+// process exits.  Shapes whose partial sums do not fit (hyp_norm_bwd_scratch_bytes(rows, d) > 16 MiB, which
+// only happens for d > 4096 with many rows) are refused with an error; use hyp_norm_bwd for those.
+//
+// Set-up: the first call on each device looks up the device address of the array (cudaGetSymbolAddress,
+// with that device current) and caches it; make that first call outside any stream capture.  After that a
+// call only launches the two kernels.  No call allocates or frees anything.
+//
+// Sharing: all calls on a device use the same array, and it keeps whatever the previous call left in it.
+// Nothing has to be cleared -- every word the reduce kernel reads is written by the backward kernel of the
+// same call first -- but two calls that overlap on the GPU (different streams, no dependency) would write
+// the same words and corrupt each other's dgamma/dbeta: serialise them.
+namespace hyp { namespace norm {
+constexpr long long kNoAllocScratchBytes = 16ll << 20;
+static __device__ __align__(256) unsigned char g_bwd_scratch[kNoAllocScratchBytes];
+// device address of g_bwd_scratch per device ordinal; the symbol itself is only a host-side stand-in
+static void* g_bwd_scratch_addr[64] = {nullptr};
+
+static int resolve_scratch(float** out) {
+  int dev = 0;
+  HYP_CHECK_CUDA(cudaGetDevice(&dev));
+  HYP_REQUIRE(dev >= 0 && dev < 64, "hyp_norm_bwd_noalloc: device ordinal %d out of range", dev);
+  if (g_bwd_scratch_addr[dev] == nullptr) {
+    void* p = nullptr;
+    HYP_CHECK_CUDA(cudaGetSymbolAddress(&p, g_bwd_scratch));
+    g_bwd_scratch_addr[dev] = p;
+  }
+  *out = reinterpret_cast<float*>(g_bwd_scratch_addr[dev]);
+  return 0;
+}
+}}  // namespace hyp::norm
+
+HYP_API long long hyp_norm_bwd_noalloc_max_scratch_bytes() { return norm::kNoAllocScratchBytes; }
+
+HYP_API int hyp_norm_bwd_noalloc(const void* dy, const void* z, const void* gamma, const float* mean,
+                                 const float* rstd, void* dz, float* dgamma, float* dbeta, int rows, int d, int rms,
+                                 int dtype, int accumulate, void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  HYP_REQUIRE(rows > 0 && d > 0 && d % 8 == 0 && d <= 8192,
+              "hyp_norm_bwd_noalloc: need d %% 8 == 0 and d <= 8192 (d=%d)", d);
+  const long long need = hyp_norm_bwd_scratch_bytes(rows, d);
+  HYP_REQUIRE(need <= norm::kNoAllocScratchBytes,
+              "hyp_norm_bwd_noalloc: rows=%d d=%d needs %lld bytes of partial sums but the built-in scratch holds %lld; "
+              "call hyp_norm_bwd with your own scratch for this shape", rows, d, need, norm::kNoAllocScratchBytes);
+  float* scratch = nullptr;
+  const int rc = norm::resolve_scratch(&scratch);
+  if (rc) return rc;
+  return norm::launch_bwd(dy, z, gamma, mean, rstd, dz, dgamma, dbeta, scratch, rows, d, rms, dtype, accumulate, st);
+}

@@ -68,6 +68,18 @@ int hyp_norm_bwd(const void* dy, const void* z, const void* gamma, const float* 
                  float* dgamma, float* dbeta, void* scratch, long long scratch_bytes, int rows, int d, int rms,
                  int dtype, int accumulate, void* stream);
 
+/* hyp_norm_bwd without caller scratch.  It has no counterpart in the reference: it exists for callers that
+ * cannot allocate device memory at the point where they call us -- a plugin inside another runtime's callback,
+ * a fixed-budget real-time loop, a C wrapper with no allocator.  The partial sums go to a 16 MiB array built
+ * into the library (held on every GPU that loads it, until exit); shapes needing more
+ * (hyp_norm_bwd_scratch_bytes(rows, d) > hyp_norm_bwd_noalloc_max_scratch_bytes()) are refused with an error.
+ * The first call on a device resolves the array's device address -- make it before any stream capture.  All calls
+ * share the array: calls that overlap on the GPU race; serialise them.  Never allocates or frees. */
+long long hyp_norm_bwd_noalloc_max_scratch_bytes(void);
+int hyp_norm_bwd_noalloc(const void* dy, const void* z, const void* gamma, const float* mean, const float* rstd,
+                         void* dz, float* dgamma, float* dbeta, int rows, int d, int rms, int dtype, int accumulate,
+                         void* stream);
+
 /* ---- fused_adamw (csrc/optim.cu) --------------------------------------------
  * One pass over a flat fp32 parameter buffer; optionally writes a 16-bit compute
  * copy.  sumsq / inv_scale / found_inf are optional DEVICE scalars (global-norm
