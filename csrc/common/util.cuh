@@ -176,4 +176,42 @@ __device__ __forceinline__ float dsilu(float x) {
   return s * (1.f + x * (1.f - s));
 }
 
+
+// ---- fast activation variants for GEMM epilogues (outputs are rounded to 16 bits anyway) -------------
+__device__ __forceinline__ float tanh_fast(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+// erf via Abramowitz-Stegun 7.1.26 (|err| < 1.5e-7), one MUFU.EX2 + one MUFU.RCP
+__device__ __forceinline__ float erf_fast(float x) {
+  const float ax = fabsf(x);
+  const float t = __frcp_rn(1.f + 0.3275911f * ax);
+  const float poly = t * (0.254829592f + t * (-0.284496736f + t * (1.421413741f + t * (-1.453152027f + t * 1.061405429f))));
+  const float y = 1.f - poly * __expf(-ax * ax);
+  return copysignf(y, x);
+}
+template <int ACT>
+__device__ __forceinline__ float act_fast(float x) {
+  if constexpr (ACT == 1) return fmaxf(x, 0.f);
+  else if constexpr (ACT == 2) return 0.5f * x * (1.f + erf_fast(x * 0.70710678118654752f));
+  else if constexpr (ACT == 3) return 0.5f * x * (1.f + tanh_fast(0.7978845608028654f * (x + 0.044715f * x * x * x)));
+  else if constexpr (ACT == 4) return x * __frcp_rn(1.f + __expf(-x));
+  else return x;
+}
+template <int ACT>
+__device__ __forceinline__ float dact_fast(float x) {
+  if constexpr (ACT == 1) return x > 0.f ? 1.f : 0.f;
+  else if constexpr (ACT == 2) {
+    const float cdf = 0.5f * (1.f + erf_fast(x * 0.70710678118654752f));
+    return cdf + x * 0.39894228040143268f * __expf(-0.5f * x * x);
+  } else if constexpr (ACT == 3) {
+    const float t = tanh_fast(0.7978845608028654f * (x + 0.044715f * x * x * x));
+    return 0.5f * (1.f + t) + 0.5f * x * (1.f - t * t) * 0.7978845608028654f * (1.f + 0.134145f * x * x);
+  } else if constexpr (ACT == 4) {
+    const float s = __frcp_rn(1.f + __expf(-x));
+    return s * (1.f + x * (1.f - s));
+  } else return 1.f;
+}
+
 }  // namespace hyp

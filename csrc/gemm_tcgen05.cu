@@ -48,6 +48,7 @@ struct Params {
   int mode;  // 0: D = act(alpha*acc + bias) + aux ; 1: D = alpha*acc * act'(aux)
   float alpha, beta;
   int vec_ok;  // D (and aux) rows are 16-byte aligned -> vector stores
+  int simple;  // plain epilogue (alpha, optional 16-bit bias) -> branch-free fast path
 };
 
 template <int BN>
@@ -91,7 +92,12 @@ __device__ __forceinline__ float apply_dact(float x, int act) {
 }
 
 // Epilogue for 8 consecutive columns of one output row.
-__device__ __forceinline__ void epilogue8(const Params& p, float (&v)[8], int row, int col) {
+// General (rare-variant) epilogue; deliberately NOT inlined: inlining 32 copies of this body per tile blew the
+// kernel up to ~170 KB of SASS and left the epilogue warps stalled on instruction fetch (ncu: stall_no_inst).
+__device__ __noinline__ void epilogue8(const Params* pp, float v0, float v1, float v2, float v3, float v4, float v5,
+                                       float v6, float v7, int row, int col) {
+  const Params& p = *pp;
+  float v[8] = {v0, v1, v2, v3, v4, v5, v6, v7};
   const int nvalid = min(8, p.N - col);
   if (nvalid <= 0) return;
   const long long doff = static_cast<long long>(row) * p.ldd + col;
@@ -190,9 +196,86 @@ __device__ __forceinline__ TileCoord decode_tile(int tile, int tiles_m, int tile
   return c;
 }
 
-template <int BN>
+// 32 consecutive columns of one output row, compile-time epilogue kind:
+//   EPI 0: D = alpha*acc (+bias)                              (plain)
+//   EPI 1: D = ACT(alpha*acc + bias) (+ residual aux); optional pre-activation side output
+//   EPI 2: D = alpha*acc * ACT'(aux)                          (activation backward)
+// Requires 16-byte aligned rows (vec_ok), a full 32-column chunk, 16-bit aux / preact.
+template <int EPI, int ACT>
+__device__ __forceinline__ void epilogue32(const Params& p, const uint32_t (&r)[32], int row, int col0) {
+  const long long doff = static_cast<long long>(row) * p.ldd + col0;
+  float v[32];
+#pragma unroll
+  for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]) * p.alpha;
+  if (EPI != 2 && p.bias) {
+    if (p.bias_dtype == DT_F32) {
+      const float4* b4 = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.bias) + col0);
+#pragma unroll
+      for (int g = 0; g < 8; ++g) {
+        const float4 t = __ldg(b4 + g);
+        v[4 * g] += t.x; v[4 * g + 1] += t.y; v[4 * g + 2] += t.z; v[4 * g + 3] += t.w;
+      }
+    } else {
+      const uint4* b4 = reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(p.bias) + col0);
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {
+        float t[8];
+        const uint4 u = __ldg(b4 + g);
+        if (p.bias_dtype == DT_BF16) unpack8<__nv_bfloat16>(u, t); else unpack8<__half>(u, t);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) v[g * 8 + i] += t[i];
+      }
+    }
+  }
+  if (EPI == 1 && p.preact_out) {
+    uint4* d = reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(p.preact_out) + doff);
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+      float t[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) t[i] = v[g * 8 + i];
+      d[g] = (p.out_dtype == DT_BF16) ? pack8<__nv_bfloat16>(t) : pack8<__half>(t);
+    }
+  }
+  if (EPI == 1) {
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = act_fast<ACT>(v[i]);
+  }
+  if (EPI != 0 && p.aux) {
+    const uint4* a4 = reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(p.aux) +
+                                                     static_cast<long long>(row) * p.ld_aux + col0);
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+      float t[8];
+      const uint4 u = a4[g];
+      if (p.aux_dtype == DT_BF16) unpack8<__nv_bfloat16>(u, t); else unpack8<__half>(u, t);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        if (EPI == 1) v[g * 8 + i] += t[i];
+        else v[g * 8 + i] *= dact_fast<ACT>(t[i]);
+      }
+    }
+  }
+  if (p.out_dtype == DT_F32) {
+    float4* d = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.D) + doff);
+#pragma unroll
+    for (int g = 0; g < 8; ++g) d[g] = make_float4(v[4 * g], v[4 * g + 1], v[4 * g + 2], v[4 * g + 3]);
+  } else {
+    uint4* d = reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(p.D) + doff);
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+      float t[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) t[i] = v[g * 8 + i];
+      d[g] = (p.out_dtype == DT_BF16) ? pack8<__nv_bfloat16>(t) : pack8<__half>(t);
+    }
+  }
+}
+
+template <int BN, int EPI, int ACT>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
-gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const Params p) {
+gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+            const __grid_constant__ Params p) {
   using C = Cfg<BN>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -322,12 +405,14 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         tmem_ld_32x32(t_row + c * 32, r);
         tmem_ld_wait();
         if (row < p.M && has_k) {
+          if (EPI != 3 && col0 + 32 <= p.N) {
+            epilogue32<EPI, ACT>(p, r, row, col0);
+          } else {
 #pragma unroll
-          for (int g = 0; g < 4; ++g) {
-            float v[8];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) v[i] = __uint_as_float(r[g * 8 + i]);
-            epilogue8(p, v, row, col0 + g * 8);
+            for (int g = 0; g < 4; ++g)
+              epilogue8(&p, __uint_as_float(r[g * 8]), __uint_as_float(r[g * 8 + 1]), __uint_as_float(r[g * 8 + 2]),
+                        __uint_as_float(r[g * 8 + 3]), __uint_as_float(r[g * 8 + 4]), __uint_as_float(r[g * 8 + 5]),
+                        __uint_as_float(r[g * 8 + 6]), __uint_as_float(r[g * 8 + 7]), row, col0 + g * 8);
           }
         }
       }
@@ -382,21 +467,46 @@ int make_tmap_2d(CUtensorMap* tm, const void* ptr, int dtype, long long inner, l
   return 0;
 }
 
-template <int BN>
+template <int BN, int EPI, int ACT>
 static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const Params& p, cudaStream_t stream) {
   using C = Cfg<BN>;
   static bool attr_set[64] = {false};
   int dev = 0;
   cudaGetDevice(&dev);
   if (!attr_set[dev & 63]) {
-    HYP_CHECK_CUDA(cudaFuncSetAttribute(gemm_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
+    HYP_CHECK_CUDA(cudaFuncSetAttribute(gemm_kernel<BN, EPI, ACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
     attr_set[dev & 63] = true;
   }
   const int tiles = ((p.M + BM - 1) / BM) * ((p.N + BN - 1) / BN) * p.splits;
   const int grid = tiles < num_sms() ? tiles : num_sms();
-  gemm_kernel<BN><<<grid, NUM_THREADS, C::SMEM_BYTES, stream>>>(ta, tb, p);
+  gemm_kernel<BN, EPI, ACT><<<grid, NUM_THREADS, C::SMEM_BYTES, stream>>>(ta, tb, p);
   HYP_CHECK_CUDA(cudaGetLastError());
   return 0;
+}
+
+// epilogue kind -> kernel instantiation
+template <int BN>
+static int dispatch(const CUtensorMap& ta, const CUtensorMap& tb, const Params& p, int epi, cudaStream_t st) {
+  if (epi == 0) return launch<BN, 0, 0>(ta, tb, p, st);
+  if (epi == 1) {
+    switch (p.act) {
+      case 0: return launch<BN, 1, 0>(ta, tb, p, st);
+      case 1: return launch<BN, 1, 1>(ta, tb, p, st);
+      case 2: return launch<BN, 1, 2>(ta, tb, p, st);
+      case 3: return launch<BN, 1, 3>(ta, tb, p, st);
+      default: return launch<BN, 1, 4>(ta, tb, p, st);
+    }
+  }
+  if (epi == 2) {
+    switch (p.act) {
+      case 1: return launch<BN, 2, 1>(ta, tb, p, st);
+      case 2: return launch<BN, 2, 2>(ta, tb, p, st);
+      case 3: return launch<BN, 2, 3>(ta, tb, p, st);
+      case 4: return launch<BN, 2, 4>(ta, tb, p, st);
+      default: break;
+    }
+  }
+  return launch<BN, 3, 0>(ta, tb, p, st);
 }
 
 }  // namespace gemm
@@ -443,6 +553,14 @@ HYP_API int hyp_gemm(const void* A, const void* B, void* D, int M, int N, int K,
     vec = vec && (reinterpret_cast<uintptr_t>(aux) % 16 == 0) && ((ld_aux * aes) % 16 == 0);
   }
   p.vec_ok = vec ? 1 : 0;
+  // pick the compile-time epilogue: 0 plain, 1 bias/act/residual/preact, 2 act', 3 general (split-K, beta, unaligned)
+  const bool fast = vec && p.splits == 1 && beta == 0.f && (!bias || reinterpret_cast<uintptr_t>(bias) % 16 == 0) &&
+                    (!aux || aux_dtype != DT_F32) && (!preact_out || out_dtype != DT_F32);
+  int epi = 3;
+  if (fast && mode == 0 && act == 0 && !aux && !preact_out) epi = 0;
+  else if (fast && mode == 0) epi = 1;
+  else if (fast && mode == 1 && aux && act != 0) epi = 2;
+  p.simple = epi;
 
   CUtensorMap ta, tb;
   int rc;
@@ -452,5 +570,5 @@ HYP_API int hyp_gemm(const void* A, const void* B, void* D, int M, int N, int K,
   if (!b_mn_major) rc = gemm::make_tmap_2d(&tb, B, in_dtype, K, N, ldb, epr, BN);         // B: [N, K]
   else             rc = gemm::make_tmap_2d(&tb, B, in_dtype, N, K, ldb, epr, epr);        // B^T: [K, N]
   if (rc) return rc;
-  return (BN == 256) ? gemm::launch<256>(ta, tb, p, stream) : gemm::launch<128>(ta, tb, p, stream);
+  return (BN == 256) ? gemm::dispatch<256>(ta, tb, p, epi, stream) : gemm::dispatch<128>(ta, tb, p, epi, stream);
 }
