@@ -25,7 +25,7 @@ namespace gemm {
 constexpr int BM = 128;
 constexpr int ROW_BYTES = 128;  // one swizzle row: 64 x 16-bit or 32 x fp32
 constexpr int A_STAGE = BM * ROW_BYTES;
-constexpr int NUM_THREADS = 192;  // warp0 TMA, warp1 MMA, warps2-5 epilogue
+constexpr int NUM_THREADS = 320;  // warp0 TMA, warp1 MMA, warps2-9 epilogue (two warps per TMEM lane quarter)
 constexpr int GROUP_M = 8;
 
 struct Params {
@@ -200,6 +200,7 @@ __device__ __forceinline__ TileCoord decode_tile(int tile, int tiles_m, int tile
 //   EPI 0: D = alpha*acc (+bias)                              (plain)
 //   EPI 1: D = ACT(alpha*acc + bias) (+ residual aux); optional pre-activation side output
 //   EPI 2: D = alpha*acc * ACT'(aux)                          (activation backward)
+//   EPI 4: D += alpha*acc with red.global.add.v4.f32           (split-K partial tiles, fp32 output)
 // Requires 16-byte aligned rows (vec_ok), a full 32-column chunk, 16-bit aux / preact.
 template <int EPI, int ACT>
 __device__ __forceinline__ void epilogue32(const Params& p, const uint32_t (&r)[32], int row, int col0) {
@@ -207,6 +208,12 @@ __device__ __forceinline__ void epilogue32(const Params& p, const uint32_t (&r)[
   float v[32];
 #pragma unroll
   for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]) * p.alpha;
+  if (EPI == 4) {  // split-K: vector fp32 reductions into the (zero-initialised) output
+    float4* d = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.D) + doff);
+#pragma unroll
+    for (int g = 0; g < 8; ++g) atomicAdd(d + g, make_float4(v[4 * g], v[4 * g + 1], v[4 * g + 2], v[4 * g + 3]));
+    return;
+  }
   if (EPI != 2 && p.bias) {
     if (p.bias_dtype == DT_F32) {
       const float4* b4 = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.bias) + col0);
@@ -307,7 +314,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       }
       for (int i = 0; i < 2; ++i) {
         mbar_init(&tfull[i], 1);
-        mbar_init(&tempty[i], 4);
+        mbar_init(&tempty[i], 8);
       }
       mbar_fence_init();
     }
@@ -388,6 +395,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   } else {
     // ----------------------------------------------------------- epilogue
     const int quarter = warp & 3;  // TMEM lanes [32q, 32q+32) are visible to this warp
+    const int chalf = (warp - 2) >> 2;  // which half of the tile's column chunks this warp drains
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int tile = blockIdx.x; tile < total; tile += gridDim.x) {
@@ -398,7 +406,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * BN;
       const bool has_k = tc.kb1 > tc.kb0;
 #pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
+      for (int c = chalf * (BN / 64); c < (chalf + 1) * (BN / 64); ++c) {
         const int col0 = tc.n_blk * BN + c * 32;
         if (col0 >= p.N) break;  // warp-uniform
         uint32_t r[32];
@@ -506,6 +514,7 @@ static int dispatch(const CUtensorMap& ta, const CUtensorMap& tb, const Params& 
       default: break;
     }
   }
+  if (epi == 4) return launch<BN, 4, 0>(ta, tb, p, st);
   return launch<BN, 3, 0>(ta, tb, p, st);
 }
 
@@ -560,6 +569,7 @@ HYP_API int hyp_gemm(const void* A, const void* B, void* D, int M, int N, int K,
   if (fast && mode == 0 && act == 0 && !aux && !preact_out) epi = 0;
   else if (fast && mode == 0) epi = 1;
   else if (fast && mode == 1 && aux && act != 0) epi = 2;
+  else if (vec && p.splits > 1) epi = 4;
   p.simple = epi;
 
   CUtensorMap ta, tb;

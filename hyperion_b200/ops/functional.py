@@ -55,6 +55,27 @@ def _padded_copy(t2: torch.Tensor) -> torch.Tensor:
     return out
 
 
+_SM_COUNT = 148
+
+
+def _wgrad(dy2: torch.Tensor, x2: torch.Tensor, out_dtype) -> torch.Tensor:
+    """dW[N, K] = dy2[M, N]^T @ x2[M, K] (both operands MN-major).  The output has few tiles (N*K is small next to
+    the token count M), so the reduction is split across SMs: split-K partial tiles are reduced with vector fp32
+    atomics, then rounded to the parameter dtype."""
+    N, K = dy2.shape[1], x2.shape[1]
+    tiles = ((N + 127) // 128) * ((K + 255) // 256 if K > 128 else 1)
+    splits = 1
+    if tiles < 120 and dy2.shape[0] >= 2048:
+        splits = min(8, max(1, (2 * _SM_COUNT) // tiles), dy2.shape[0] // 512)
+    if splits > 1 and (K * 4) % 16 == 0:
+        acc = torch.zeros((N, K), device=dy2.device, dtype=torch.float32)
+        native.gemm(dy2, x2, a_mn_major=True, b_mn_major=True, out=acc, splits=splits)
+        return acc if out_dtype == torch.float32 else native.cast(acc, out_dtype)
+    out = _padded_empty(N, K, out_dtype, dy2.device)
+    native.gemm(dy2, x2, a_mn_major=True, b_mn_major=True, out=out)
+    return out if out.is_contiguous() else out.contiguous()
+
+
 def _act_ref(x, act):
     if act in (None, "none"):
         return x
@@ -110,10 +131,7 @@ class _LinearFn(torch.autograd.Function):
             dx = native.gemm(dh, w2, b_mn_major=True, out=_padded_empty(dh.shape[0], w2.shape[1], dh.dtype, dh.device))
             dx = dx.reshape(ctx.x_shape)
         if ctx.needs_input_grad[1]:
-            dw = native.gemm(dh, x2, a_mn_major=True, b_mn_major=True,
-                             out=_padded_empty(w2.shape[0], w2.shape[1], w2.dtype, w2.device))
-            if not dw.is_contiguous():
-                dw = dw.contiguous()
+            dw = _wgrad(dh, x2, w2.dtype)
         if ctx.has_bias and ctx.needs_input_grad[2]:
             db = native.colsum(dh).to(dy.dtype)
         if ctx.has_res and ctx.needs_input_grad[3]:
@@ -174,8 +192,8 @@ class _MlpFn(torch.autograd.Function):
         has_b1, has_b2, has_res = ctx.flags
         # dh = (dy @ W2) * act'(h): activation derivative applied in the GEMM epilogue
         dh = native.gemm(dy2, w2, b_mn_major=True, aux=h, act=ctx.act, mode=1)
-        dw2 = native.gemm(dy2, a, a_mn_major=True, b_mn_major=True)
-        dw1 = native.gemm(dh, x2, a_mn_major=True, b_mn_major=True)
+        dw2 = _wgrad(dy2, a, w2.dtype)
+        dw1 = _wgrad(dh, x2, w1.dtype)
         dx = native.gemm(dh, w1, b_mn_major=True).reshape(ctx.x_shape) if ctx.needs_input_grad[0] else None
         db1 = native.colsum(dh).to(dy.dtype) if has_b1 else None
         db2 = native.colsum(dy2).to(dy.dtype) if has_b2 else None
