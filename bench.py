@@ -95,9 +95,13 @@ def main() -> int:
     sampler = ClockSampler(dev.index or 0).start() if rank == 0 else None
     launches0 = _lib.launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    import time as _time
+
     e0.record()
+    h0 = _time.perf_counter()
     for _ in range(args.steps):
         case.step(case.device_batch())
+    host_ms = (_time.perf_counter() - h0) * 1e3 / args.steps  # CPU time to ENQUEUE one step (launch-bound check)
     e1.record()
     sync_all()
     launches = _lib.launch_count() - launches0
@@ -128,7 +132,7 @@ def main() -> int:
             "metric": case.metric, "value": value, "unit": case.unit, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": case.dtype, "data": "synthetic", "impl": "hyperion",
-            "config": case.config, "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
+            "config": case.config, "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "host_enqueue_ms_per_step": host_ms,
             "peak_mem_gb": torch.cuda.max_memory_allocated(dev) / 2 ** 30,
         }
         print(json.dumps(out), flush=True)

@@ -27,9 +27,24 @@ ce_fwd_bwd_kernel(T* __restrict__ logits, long long ld, const long long* __restr
   const long long tgt = targets[row];
   const bool ignored = (tgt == ignore_index) || tgt < 0 || tgt >= V;
 
-  // pass 1: online max / sum-exp
+  // pass 1: online max / sum-exp (16-byte vector loads when the row is aligned)
   float mx = -INFINITY, se = 0.f;
-  for (int c = threadIdx.x; c < V; c += blockDim.x) {
+  constexpr int VE = 16 / sizeof(T);
+  const bool vec = (sizeof(T) == 2) && ((ld * sizeof(T)) % 16 == 0) && (reinterpret_cast<uintptr_t>(logits) % 16 == 0);
+  const int Vv = vec ? (V / VE) * VE : 0;
+  if (vec) {
+    for (int c = threadIdx.x * VE; c < Vv; c += blockDim.x * VE) {
+      float f[8];
+      unpack8<T>(*reinterpret_cast<const uint4*>(lrow + c), f);
+      float cm = f[0];
+#pragma unroll
+      for (int i = 1; i < 8; ++i) cm = fmaxf(cm, f[i]);
+      if (cm > mx) { se *= __expf(mx - cm); mx = cm; }
+#pragma unroll
+      for (int i = 0; i < 8; ++i) se += __expf(f[i] - mx);
+    }
+  }
+  for (int c = Vv + threadIdx.x; c < V; c += blockDim.x) {
     const float x = to_f32<T>(lrow[c]);
     if (x > mx) { se = se * __expf(mx - x) + 1.f; mx = x; }
     else se += __expf(x - mx);
@@ -48,7 +63,20 @@ ce_fwd_bwd_kernel(T* __restrict__ logits, long long ld, const long long* __restr
   if (!write_grad) return;
   __syncthreads();  // the target logit was read above; now overwrite the row
   const float gs = ignored ? 0.f : (gscale_ptr ? *gscale_ptr * gscale : gscale);
-  for (int c = threadIdx.x; c < V; c += blockDim.x) {
+  if (vec) {
+    for (int c = threadIdx.x * VE; c < Vv; c += blockDim.x * VE) {
+      float f[8];
+      unpack8<T>(*reinterpret_cast<const uint4*>(lrow + c), f);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        float gr = __expf(f[i] - lse);
+        if (c + i == tgt) gr -= 1.f;
+        f[i] = gr * gs;
+      }
+      *reinterpret_cast<uint4*>(lrow + c) = pack8<T>(f);
+    }
+  }
+  for (int c = Vv + threadIdx.x; c < V; c += blockDim.x) {
     const float x = to_f32<T>(lrow[c]);
     float gr = __expf(x - lse);
     if (c == tgt) gr -= 1.f;

@@ -201,6 +201,7 @@ __device__ __forceinline__ TileCoord decode_tile(int tile, int tiles_m, int tile
 //   EPI 1: D = ACT(alpha*acc + bias) (+ residual aux); optional pre-activation side output
 //   EPI 2: D = alpha*acc * ACT'(aux)                          (activation backward)
 //   EPI 4: D += alpha*acc with red.global.add.v4.f32           (split-K partial tiles, fp32 output)
+//   EPI 5: D = alpha*acc + beta*D                              (gradient accumulation)
 // Requires 16-byte aligned rows (vec_ok), a full 32-column chunk, 16-bit aux / preact.
 template <int EPI, int ACT>
 __device__ __forceinline__ void epilogue32(const Params& p, const uint32_t (&r)[32], int row, int col0) {
@@ -214,7 +215,7 @@ __device__ __forceinline__ void epilogue32(const Params& p, const uint32_t (&r)[
     for (int g = 0; g < 8; ++g) atomicAdd(d + g, make_float4(v[4 * g], v[4 * g + 1], v[4 * g + 2], v[4 * g + 3]));
     return;
   }
-  if (EPI != 2 && p.bias) {
+  if (EPI != 2 && EPI != 5 && p.bias) {
     if (p.bias_dtype == DT_F32) {
       const float4* b4 = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.bias) + col0);
 #pragma unroll
@@ -248,7 +249,7 @@ __device__ __forceinline__ void epilogue32(const Params& p, const uint32_t (&r)[
 #pragma unroll
     for (int i = 0; i < 32; ++i) v[i] = act_fast<ACT>(v[i]);
   }
-  if (EPI != 0 && p.aux) {
+  if ((EPI == 1 || EPI == 2) && p.aux) {
     const uint4* a4 = reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(p.aux) +
                                                      static_cast<long long>(row) * p.ld_aux + col0);
 #pragma unroll
@@ -260,6 +261,26 @@ __device__ __forceinline__ void epilogue32(const Params& p, const uint32_t (&r)[
       for (int i = 0; i < 8; ++i) {
         if (EPI == 1) v[g * 8 + i] += t[i];
         else v[g * 8 + i] *= dact_fast<ACT>(t[i]);
+      }
+    }
+  }
+  if (EPI == 5) {  // D = alpha*acc + beta*D
+    if (p.out_dtype == DT_F32) {
+      const float4* d = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.D) + doff);
+#pragma unroll
+      for (int g = 0; g < 8; ++g) {
+        const float4 t = d[g];
+        v[4 * g] += p.beta * t.x; v[4 * g + 1] += p.beta * t.y; v[4 * g + 2] += p.beta * t.z; v[4 * g + 3] += p.beta * t.w;
+      }
+    } else {
+      const uint4* d = reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(p.D) + doff);
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {
+        float t[8];
+        const uint4 u = d[g];
+        if (p.out_dtype == DT_BF16) unpack8<__nv_bfloat16>(u, t); else unpack8<__half>(u, t);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) v[g * 8 + i] += p.beta * t[i];
       }
     }
   }
@@ -515,6 +536,7 @@ static int dispatch(const CUtensorMap& ta, const CUtensorMap& tb, const Params& 
     }
   }
   if (epi == 4) return launch<BN, 4, 0>(ta, tb, p, st);
+  if (epi == 5) return launch<BN, 5, 0>(ta, tb, p, st);
   return launch<BN, 3, 0>(ta, tb, p, st);
 }
 
@@ -570,6 +592,7 @@ HYP_API int hyp_gemm(const void* A, const void* B, void* D, int M, int N, int K,
   else if (fast && mode == 0) epi = 1;
   else if (fast && mode == 1 && aux && act != 0) epi = 2;
   else if (vec && p.splits > 1) epi = 4;
+  else if (vec && p.splits == 1 && beta != 0.f && mode == 0 && act == 0 && !bias && !aux && !preact_out) epi = 5;
   p.simple = epi;
 
   CUtensorMap ta, tb;

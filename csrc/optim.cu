@@ -87,7 +87,23 @@ __global__ void __launch_bounds__(256) sumsq_kernel(const T* __restrict__ x, lon
   float s = 0.f;
   bool bad = false;
   const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
-  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride) {
+  constexpr int VE = 16 / sizeof(T);
+  const bool vec = (reinterpret_cast<uintptr_t>(x) % 16) == 0;
+  const long long nv = vec ? n / VE : 0;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < nv; i += stride) {
+    const uint4 u = ld_nc_v4(reinterpret_cast<const uint4*>(x) + i);
+    if constexpr (sizeof(T) == 4) {
+      const float* f = reinterpret_cast<const float*>(&u);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) { s += f[k] * f[k]; bad |= !isfinite(f[k]); }
+    } else {
+      float f[8];
+      unpack8<T>(u, f);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) { s += f[k] * f[k]; bad |= !isfinite(f[k]); }
+    }
+  }
+  for (long long i = nv * VE + static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride) {
     const float f = to_f32<T>(x[i]);
     s += f * f;
     bad |= !isfinite(f);
@@ -136,8 +152,8 @@ HYP_API int hyp_adamw(float* p, const void* g, float* m, float* v, void* p_copy,
 HYP_API int hyp_sumsq(const void* x, long long n, int dtype, float* out2, void* stream_) {
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
   if (n == 0) return 0;
-  long long blocks = (n + 1023) / 1024;
-  const long long cap = (long long)num_sms() * 4;
+  long long blocks = (n + 2047) / 2048;
+  const long long cap = (long long)num_sms() * 8;
   if (blocks > cap) blocks = cap;
   const int grid = (int)blocks;
   if (dtype == DT_F32) sumsq_kernel<float><<<grid, 256, 0, st>>>((const float*)x, n, out2);
