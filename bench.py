@@ -40,6 +40,7 @@ def parse():
     ap.add_argument("--size", default=None, help="model size override (gpt2: medium/small/tiny; llama: 7b/tiny)")
     ap.add_argument("--no-fused-comm", dest="fused_comm", action="store_false", default=None)
     ap.add_argument("--no-e2e", dest="e2e", action="store_false", default=True)
+    ap.add_argument("--no-graph", dest="graph", action="store_false", default=True, help="do not capture the step in a CUDA graph")
     return ap.parse_args()
 
 
@@ -81,6 +82,11 @@ def main() -> int:
 
     case = make_case(args.config, dev, rank, world, batch=args.batch, seq=args.seq, size=args.size,
                      fused_comm=args.fused_comm)
+
+    graphed = False
+    if args.graph and world == 1:
+        graphed = case.enable_graph()
+    case.config["cuda_graph"] = graphed
 
     def sync_all():
         torch.cuda.synchronize(dev)

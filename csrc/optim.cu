@@ -21,6 +21,7 @@ struct AdamArgs {
   const float* sumsq;      // device: sum of squares of the (unscaled) global gradient, or null
   const float* inv_scale;  // device: 1 / loss_scale, or null
   const float* found_inf;  // device: != 0 -> skip the step, or null
+  const float* step_ptr;   // device: step count (>= 1) when the step number must not be baked into the launch (CUDA graphs)
 };
 
 template <typename TG, typename TC>
@@ -34,8 +35,14 @@ adamw_kernel(float* __restrict__ p, const TG* __restrict__ g, float* __restrict_
     const float coef = a.max_norm / (norm + 1e-6f);
     if (coef < 1.f) gscale *= coef;
   }
-  const float step_size = a.lr / a.bias_c1;
-  const float inv_sqrt_c2 = rsqrtf(a.bias_c2);
+  float c1 = a.bias_c1, c2 = a.bias_c2;
+  if (a.step_ptr) {
+    const float t = fmaxf(*a.step_ptr, 1.f);
+    c1 = 1.f - powf(a.beta1, t);
+    c2 = 1.f - powf(a.beta2, t);
+  }
+  const float step_size = a.lr / c1;
+  const float inv_sqrt_c2 = rsqrtf(c2);
   const float decay = 1.f - a.lr * a.weight_decay;
   const long long stride = static_cast<long long>(gridDim.x) * blockDim.x * 4;
   long long i = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) * 4;
@@ -120,17 +127,18 @@ using namespace hyp;
 HYP_API int hyp_adamw(float* p, const void* g, float* m, float* v, void* p_copy, long long n, int grad_dtype,
                       int copy_dtype, float lr, float beta1, float beta2, float eps, float weight_decay, int step,
                       float max_norm, const float* sumsq, const float* inv_scale, const float* found_inf,
-                      void* stream_) {
+                      const float* step_ptr, void* stream_) {
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
   if (n == 0) return 0;
-  HYP_REQUIRE(step >= 1, "hyp_adamw: step counts from 1");
+  HYP_REQUIRE(step >= 1 || step_ptr, "hyp_adamw: step counts from 1");
+  if (step < 1) step = 1;
   HYP_REQUIRE(((uintptr_t)p | (uintptr_t)m | (uintptr_t)v) % 16 == 0, "hyp_adamw: state pointers must be 16B aligned");
   HYP_REQUIRE(grad_dtype != DT_F32 || (uintptr_t)g % 16 == 0, "hyp_adamw: fp32 grad pointer must be 16B aligned");
   AdamArgs a;
   a.lr = lr; a.beta1 = beta1; a.beta2 = beta2; a.eps = eps; a.weight_decay = weight_decay;
   a.bias_c1 = 1.f - powf(beta1, (float)step);
   a.bias_c2 = 1.f - powf(beta2, (float)step);
-  a.max_norm = max_norm; a.sumsq = sumsq; a.inv_scale = inv_scale; a.found_inf = found_inf;
+  a.max_norm = max_norm; a.sumsq = sumsq; a.inv_scale = inv_scale; a.found_inf = found_inf; a.step_ptr = step_ptr;
   long long blocks = (n / 4 + 255) / 256;
   const long long cap = (long long)num_sms() * 8;
   if (blocks > cap) blocks = cap;

@@ -41,7 +41,26 @@ class Case:
     def loss_fn(self, batch):
         raise NotImplementedError
 
+    graphed = None
+
+    def enable_graph(self) -> bool:
+        """Capture the whole step in a CUDA graph (falls back to eager and says so if capture fails)."""
+        from ..train.engine import GraphedStep
+
+        try:
+            self.graphed = GraphedStep(self.eng, self.loss_fn, self.batches[0])
+            return True
+        except Exception as e:  # noqa: BLE001
+            import sys
+
+            print(f"[bench] CUDA-graph capture failed, running eager: {e!r}", file=sys.stderr)
+            torch.cuda.synchronize()
+            self.graphed = None
+            return False
+
     def step(self, batch):
+        if self.graphed is not None:
+            return self.graphed(batch)
         loss = self.loss_fn(batch)
         self.eng.backward_and_step(loss)
         return loss

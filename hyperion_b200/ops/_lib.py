@@ -32,7 +32,7 @@ _SIGS = {
     "hyp_cast": "ppliifp",
     "hyp_norm_fwd": "ppppppppiifiip",
     "hyp_norm_bwd": "pppppppppliiiiip",
-    "hyp_adamw": "ppppplii" + "fffff" + "i" + "f" + "pppp",
+    "hyp_adamw": "ppppplii" + "fffff" + "i" + "f" + "ppppp",
     "hyp_sumsq": "plipp",
     "hyp_ce_fwd_bwd": "plpiilpppfiip",
     "hyp_ce_finalize": "pppp",
@@ -121,6 +121,12 @@ _KERNELS_PER_CALL = {"hyp_norm_bwd": 2, "hyp_ipc_alloc": 0, "hyp_ipc_open": 0, "
 def launch_count() -> int:
     """Number of sm_100a kernels of this library launched so far (bench.py reports the delta)."""
     return _launches
+
+
+def add_launches(n: int) -> None:
+    """Account for kernels launched by a CUDA-graph replay (they do not pass through :func:`call`)."""
+    global _launches
+    _launches += n
 
 
 def call(name: str, *args) -> None:

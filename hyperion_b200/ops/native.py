@@ -139,10 +139,11 @@ def norm_bwd(dy, z, gamma, mean, rstd, rms: bool = False, need_beta: bool = True
 
 
 def adamw_step(p, g, m, v, p_copy, *, lr, beta1, beta2, eps, weight_decay, step, max_norm=0.0, sumsq=None,
-               inv_scale=None, found_inf=None) -> None:
+               inv_scale=None, found_inf=None, step_t=None) -> None:
     call("hyp_adamw", ptr(p), ptr(g), ptr(m), ptr(v), ptr(p_copy), p.numel(), DT[g.dtype],
          DT[p_copy.dtype] if p_copy is not None else 2, float(lr), float(beta1), float(beta2), float(eps),
-         float(weight_decay), int(step), float(max_norm), ptr(sumsq), ptr(inv_scale), ptr(found_inf), stream_ptr())
+         float(weight_decay), int(step), float(max_norm), ptr(sumsq), ptr(inv_scale), ptr(found_inf), ptr(step_t),
+         stream_ptr())
 
 
 def sumsq(x: torch.Tensor, out2: torch.Tensor | None = None) -> torch.Tensor:

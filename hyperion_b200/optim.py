@@ -31,6 +31,7 @@ class FusedAdamW:
         self.exp_avg = torch.zeros(n, device=dev, dtype=torch.float32)
         self.exp_avg_sq = torch.zeros(n, device=dev, dtype=torch.float32)
         self._norm_buf = torch.zeros(2, device=dev, dtype=torch.float32)
+        self.step_t = torch.zeros(1, device=dev, dtype=torch.float32)  # device-side step count (CUDA-graph safe)
 
     # -- norms ---------------------------------------------------------------------------------
     def grad_sumsq(self, grad: torch.Tensor | None = None) -> torch.Tensor:
@@ -50,6 +51,7 @@ class FusedAdamW:
     def step(self, grad: torch.Tensor | None = None, sumsq: torch.Tensor | None = None,
              inv_scale: torch.Tensor | None = None, found_inf: torch.Tensor | None = None) -> None:
         self.step_count += 1
+        self.step_t += 1
         g = grad if grad is not None else self.flat.grad[self.start:self.end]
         p16 = self.flat.data[self.start:self.end]
         b1, b2 = self.betas
@@ -59,11 +61,13 @@ class FusedAdamW:
             if self.master is not None:
                 native.adamw_step(self.master, g, self.exp_avg, self.exp_avg_sq, p16, lr=self.lr, beta1=b1, beta2=b2,
                                   eps=self.eps, weight_decay=self.weight_decay, step=self.step_count,
-                                  max_norm=self.max_norm, sumsq=sumsq, inv_scale=inv_scale, found_inf=found_inf)
+                                  max_norm=self.max_norm, sumsq=sumsq, inv_scale=inv_scale, found_inf=found_inf,
+                                  step_t=self.step_t)
             else:
                 native.adamw_step(p16, g, self.exp_avg, self.exp_avg_sq, None, lr=self.lr, beta1=b1, beta2=b2,
                                   eps=self.eps, weight_decay=self.weight_decay, step=self.step_count,
-                                  max_norm=self.max_norm, sumsq=sumsq, inv_scale=inv_scale, found_inf=found_inf)
+                                  max_norm=self.max_norm, sumsq=sumsq, inv_scale=inv_scale, found_inf=found_inf,
+                                  step_t=self.step_t)
             return
         # ---- torch formulation of the same update (CPU / oracle) ----
         if found_inf is not None and float(found_inf.reshape(-1)[0]) != 0.0:
@@ -91,11 +95,12 @@ class FusedAdamW:
 
     # -- checkpointing ---------------------------------------------------------------------------
     def state_dict(self) -> dict:
-        return {"step": self.step_count, "exp_avg": self.exp_avg, "exp_avg_sq": self.exp_avg_sq, "master": self.master,
+        return {"step": int(self.step_t.item()), "exp_avg": self.exp_avg, "exp_avg_sq": self.exp_avg_sq, "master": self.master,
                 "lr": self.lr, "betas": self.betas, "eps": self.eps, "weight_decay": self.weight_decay}
 
     def load_state_dict(self, sd: dict) -> None:
         self.step_count = int(sd["step"])
+        self.step_t.fill_(float(self.step_count))
         self.exp_avg.copy_(sd["exp_avg"])
         self.exp_avg_sq.copy_(sd["exp_avg_sq"])
         if self.master is not None and sd.get("master") is not None:

@@ -107,6 +107,7 @@ class HyperionFSDP(nn.Module):
         self.gshard = torch.zeros(self.shard_numel, device=self.device, dtype=torch.float32) if (W > 1) else None
         self.sumsq = torch.zeros(2, device=self.device, dtype=torch.float32)
         self.step_count = 0
+        self.step_t = torch.zeros(1, device=self.device, dtype=torch.float32)  # device-side step count (CUDA-graph safe)
         # ---- schedule
         self.comm_stream = torch.cuda.Stream(self.device) if self.device.type == "cuda" else None
         self._spec_unit = {}
@@ -267,13 +268,15 @@ class HyperionFSDP(nn.Module):
                 self.loss_scaler.note_overflow(self.sumsq)
                 found_inf = self.loss_scaler.found_inf
             self.step_count += 1
+            self.step_t += 1
             p16 = self.shard16 if W > 1 else self.flat.data
             master = self.master if self.master is not None else p16
             if native_ok:
                 native.adamw_step(master, g, self.exp_avg, self.exp_avg_sq, p16 if self.master is not None else None,
                                   lr=self.lr, beta1=self.betas[0], beta2=self.betas[1], eps=self.eps,
                                   weight_decay=self.weight_decay, step=self.step_count, max_norm=self.max_norm,
-                                  sumsq=sumsq if self.max_norm > 0 else None, inv_scale=inv_scale, found_inf=found_inf)
+                                  sumsq=sumsq if self.max_norm > 0 else None, inv_scale=inv_scale, found_inf=found_inf,
+                                  step_t=self.step_t)
             else:
                 self._adamw_torch(master, g, p16, sumsq, inv_scale, found_inf)
             self.sumsq.zero_()

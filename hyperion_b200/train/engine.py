@@ -93,3 +93,50 @@ def build_engine(model: nn.Module, *, strategy: str = "single", precision: str =
         strategy = "single" if strategy != "ddp" else "ddp"
     opt = FusedAdamW(flat, lr=lr, betas=betas, eps=eps, weight_decay=weight_decay, max_norm=clip)
     return Engine(model, wrapped, flat, opt, scaler, strategy, pol, clip)
+
+
+class GraphedStep:
+    """One whole training step (forward, backward, communication kernels, optimizer, scaler update) captured in a
+    CUDA graph and replayed with a single launch.
+
+    A GPT-2-medium step is ~1000 kernel launches; enqueueing them from Python takes about as long as the GPU needs
+    to run them, so the step is launch-bound once the kernels are fast.  Capturing removes that: every launch made
+    through the C ABI lands on the capturing stream, tensors come from the graph's private pool (fixed addresses, so
+    the TMA descriptors baked into the launches stay valid), and everything that varies per step lives in device
+    memory (AdamW step count, loss scale, found_inf, communication epochs).
+
+        step = GraphedStep(eng, lambda batch: eng.model.loss(batch[0]), example_batch)
+        loss = step(batch)            # copies the batch into the static input, replays, returns the static loss tensor
+
+    ``warmup`` eager steps run first (they are real optimizer steps).  Shapes are fixed by ``example_batch``.
+    """
+
+    def __init__(self, eng: Engine, loss_fn, example_batch, warmup: int = 2):
+        assert torch.cuda.is_available()
+        self.eng = eng
+        self.static_batch = tuple(t.clone() for t in example_batch)
+        dev = self.static_batch[0].device
+        side = torch.cuda.Stream(dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):
+            for _ in range(max(1, warmup)):
+                eng.backward_and_step(loss_fn(self.static_batch))
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+        from ..ops import _lib
+
+        n0 = _lib.launch_count()
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self.loss = loss_fn(self.static_batch)
+            eng.backward_and_step(self.loss)
+        self.loss = self.loss.detach()
+        self.kernels_per_replay = _lib.launch_count() - n0  # library kernels recorded in the graph
+        self._add_launches = _lib.add_launches
+
+    def __call__(self, batch):
+        for dst, src in zip(self.static_batch, batch):
+            dst.copy_(src, non_blocking=True)
+        self.graph.replay()
+        self._add_launches(self.kernels_per_replay)
+        return self.loss

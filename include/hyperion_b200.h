@@ -83,12 +83,13 @@ int hyp_norm_bwd_noalloc(const void* dy, const void* z, const void* gamma, const
 /* ---- fused_adamw (csrc/optim.cu) --------------------------------------------
  * One pass over a flat fp32 parameter buffer; optionally writes a 16-bit compute
  * copy.  sumsq / inv_scale / found_inf are optional DEVICE scalars (global-norm
- * clipping, AMP unscale, skip-on-overflow) so the step needs no host sync.
+ * clipping, AMP unscale, skip-on-overflow) so the step needs no host sync.  step_ptr (optional device fp32)
+ * overrides `step` so a captured CUDA graph can be replayed with an advancing step count.
  * Reference: torch.optim.AdamW.step (distributed_utils.py:161, 231, 334, 503),
  * GradScaler.step (:179), clip_grad_norm_ (:351, 522). */
 int hyp_adamw(float* p, const void* g, float* m, float* v, void* p_copy, long long n, int grad_dtype, int copy_dtype,
               float lr, float beta1, float beta2, float eps, float weight_decay, int step, float max_norm,
-              const float* sumsq, const float* inv_scale, const float* found_inf, void* stream);
+              const float* sumsq, const float* inv_scale, const float* found_inf, const float* step_ptr, void* stream);
 /* out2[0] += sum(x^2); out2[1] = 1 if a non-finite value was seen. */
 int hyp_sumsq(const void* x, long long n, int dtype, float* out2, void* stream);
 
