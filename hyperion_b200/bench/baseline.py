@@ -1,0 +1,143 @@
+"""Baseline model benchmarks: ``Phase 1/baseline_performance.ipynb`` (c0) as a module + CLI.
+
+    python -m hyperion_b200 baseline [--out results/benchmarks] [--precision fp32|bf16] [--batch 32]
+
+``benchmark_model(model_fn, input_shape, target_shape)`` times three loops like the reference (c0 L70-176): forward only,
+forward+backward, full step with Adam(1e-3) and ``MSELoss`` against random targets; derives
+``backward = (fwd+bwd) - fwd`` and ``optimizer = full - fwd - bwd``; records peak memory and ``throughput = batch/total``.
+``run_baseline_benchmarks`` covers ResNet-50 ``(32,3,224,224)->(32,1000)``, ViT ``(32,3,224,224)->(32,1000)`` and the
+custom Transformer ``(32,16,512)->(32,16,512)`` (L179-224); ``test_batch_size_scaling`` sweeps ResNet-50 over 1..64
+(L295-340).  CSV columns equal the reference's: ``Model, Forward Time (ms), Backward Time (ms), Optimizer Time (ms),
+Total Time (ms), Memory Usage (MB), Throughput (samples/s)`` (+ ``Batch Size``).
+
+The "ViT" row is the real ViT-B/16 here; the reference's published row was its silent CNN fallback, which
+is benchmarked too and labelled as what it is.
+"""
+from __future__ import annotations
+
+import argparse
+import os
+import sys
+
+import pandas as pd
+import torch
+import torch.nn as nn
+
+from ..memory import MemoryStats
+from ..models import FallbackCNN, create_custom_transformer, create_resnet50, create_vit_model
+from ..train.engine import build_engine
+
+COLUMNS = ["Model", "Forward Time (ms)", "Backward Time (ms)", "Optimizer Time (ms)", "Total Time (ms)",
+           "Memory Usage (MB)", "Throughput (samples/s)"]
+
+
+def _loop_ms(fn, iters: int, device) -> float:
+    if device.type == "cuda":
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(iters):
+            fn()
+        e1.record()
+        torch.cuda.synchronize(device)
+        return e0.elapsed_time(e1) / iters
+    import time
+
+    t0 = time.time()
+    for _ in range(iters):
+        fn()
+    return (time.time() - t0) * 1e3 / iters
+
+
+def benchmark_model(model_fn, input_shape, target_shape, num_iterations: int = 50, warmup_iterations: int = 10,
+                    precision: str = "fp32", device=None, name: str | None = None) -> dict:
+    device = torch.device(device or ("cuda" if torch.cuda.is_available() else "cpu"))
+    model = model_fn()
+    eng = build_engine(model, strategy="single", precision=precision if device.type == "cuda" else "fp32", lr=1e-3,
+                       weight_decay=0.0, device=device)
+    dt = eng.precision.dtype
+    inputs = torch.rand(*input_shape, device=device).to(dt)
+    targets = torch.rand(*target_shape, device=device)
+    crit = nn.MSELoss()
+    model.train()
+
+    def fwd():
+        return eng.model(inputs)
+
+    def fwd_bwd():
+        eng.flat.zero_grad()
+        crit(eng.model(inputs).float(), targets).backward()
+
+    def full():
+        eng.backward_and_step(crit(eng.model(inputs).float(), targets))
+
+    for _ in range(warmup_iterations):
+        full()
+    f = _loop_ms(fwd, num_iterations, device)
+    fb = _loop_ms(fwd_bwd, num_iterations, device)
+    t = _loop_ms(full, num_iterations, device)
+    mem = MemoryStats(device)
+    mem.reset_peak()
+    fwd_bwd()
+    if device.type == "cuda":
+        torch.cuda.synchronize(device)
+    bwd = max(fb - f, 0.0)
+    opt = max(t - fb, 0.0)
+    total = f + bwd + opt
+    return {"Model": name or getattr(model_fn, "__name__", "model"), "Forward Time (ms)": f, "Backward Time (ms)": bwd,
+            "Optimizer Time (ms)": opt, "Total Time (ms)": total, "Memory Usage (MB)": mem.sample().peak_mb,
+            "Throughput (samples/s)": input_shape[0] / (total / 1e3)}
+
+
+def run_baseline_benchmarks(batch: int = 32, precision: str = "fp32", out_dir: str | None = None, iters: int = 50,
+                            warmup: int = 10, device=None) -> pd.DataFrame:
+    cases = [
+        ("ResNet-50", create_resnet50, (batch, 3, 224, 224), (batch, 1000)),
+        ("Vision Transformer (ViT-B/16)", create_vit_model, (batch, 3, 224, 224), (batch, 1000)),
+        ("Fallback CNN (what the reference published as 'ViT')", FallbackCNN, (batch, 3, 224, 224), (batch, 1000)),
+        ("Custom Transformer", create_custom_transformer, (batch, 16, 512), (batch, 16, 512)),
+    ]
+    rows = [benchmark_model(fn, i, t, iters, warmup, precision, device, name) for name, fn, i, t in cases]
+    df = pd.DataFrame(rows, columns=COLUMNS)
+    if out_dir:
+        d = os.path.join(out_dir, "baseline")
+        os.makedirs(d, exist_ok=True)
+        df.to_csv(os.path.join(d, "model_benchmarks.csv"), index=False)
+    return df
+
+
+def test_batch_size_scaling(model_fn=create_resnet50, input_hw=(3, 224, 224), out_features: int = 1000,
+                            batch_sizes=(1, 2, 4, 8, 16, 32, 64), precision: str = "fp32", out_dir: str | None = None,
+                            iters: int = 20, warmup: int = 5, device=None) -> pd.DataFrame:
+    rows = []
+    for bs in batch_sizes:
+        r = benchmark_model(model_fn, (bs, *input_hw), (bs, out_features), iters, warmup, precision, device,
+                            getattr(model_fn, "__name__", "model"))
+        r["Batch Size"] = bs
+        rows.append(r)
+    df = pd.DataFrame(rows, columns=COLUMNS + ["Batch Size"])
+    if out_dir:
+        d = os.path.join(out_dir, "scaling")
+        os.makedirs(d, exist_ok=True)
+        df.to_csv(os.path.join(d, f"{getattr(model_fn, '__name__', 'model')}_batch_scaling.csv"), index=False)
+    return df
+
+
+def main(argv=None) -> int:
+    ap = argparse.ArgumentParser(prog="hyperion baseline")
+    ap.add_argument("--out", default="results/benchmarks")
+    ap.add_argument("--precision", default="fp32", choices=["fp32", "fp16", "bf16"])
+    ap.add_argument("--batch", type=int, default=32)
+    ap.add_argument("--iters", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--no-scaling", action="store_true")
+    a = ap.parse_args(argv)
+    df = run_baseline_benchmarks(a.batch, a.precision, a.out, a.iters, a.warmup)
+    print(df.to_string(index=False))
+    if not a.no_scaling:
+        sc = test_batch_size_scaling(precision=a.precision, out_dir=a.out)
+        print(sc.to_string(index=False))
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())
