@@ -1,0 +1,323 @@
+// flash_attn_sm100: scaled-dot-product attention on the 5th-gen tensor cores.
+//
+//   O = softmax(Q K^T * scale + mask) V        per (batch, head), never materialising the S x S scores
+//
+// One CTA owns a 128-row query block of one (batch, head) and streams 128-key blocks:
+//   warp 0     TMA producer: Q once, then a 2-stage ring of K/V tiles (4-D tensor maps over [D, S, H, B] with
+//              arbitrary strides, so the packed [B, S, 3, H, D] projection output is consumed in place)
+//   warp 1     one thread issues tcgen05.mma:  S = Q K^T  (128x128xD, accumulator in TMEM columns [0,128))
+//                                              O_blk = P V (128xDx128, accumulator in TMEM columns [128,128+D))
+//   warps 2-5  softmax: thread r owns query row r; two passes over the S row in TMEM (row max, then exp2 / row sum),
+//              P is rounded to 16 bits and written to shared memory in the 128B-swizzled K-major layout the PV
+//              MMA reads; the running output is rescaled and accumulated in registers (online softmax)
+// S_{j+1} = Q K_{j+1}^T is issued right behind P_j V_j, so it overlaps the softmax threads' accumulation, and two
+// CTAs fit per SM at D = 64 so one CTA's softmax overlaps the other's MMAs.
+// Masks: none / causal / causal + key padding (bool [B, Sk]); keys beyond Sk are masked, rows with no visible key
+// produce zeros.  The per-row log-sum-exp is saved for the backward.
+//
+// Reference call sites: nn.MultiheadAttention inside nn.TransformerEncoderLayer (02_development/
+// distributed_utils.py:79; the reference ran the *math* SDPA path that materialises the scores)
+// and HF Llama SDPA with causal + padding mask (distributed_utils.py:465).
+#include "common/ptx.cuh"
+#include "common/tmap.cuh"
+#include "common/util.cuh"
+
+namespace hyp {
+namespace attn {
+
+constexpr int BQ = 128, BKV = 128;
+constexpr int THREADS = 192;
+constexpr float LOG2E = 1.4426950408889634f;
+
+struct FwdParams {
+  int B, H, Sq, Sk, D;
+  int causal;
+  float scale_log2;          // softmax scale * log2(e)
+  const uint8_t* kpm;        // [B, Sk] 1 = attend, or null
+  void* o;                   // output, element strides below
+  long long o_sb, o_sh, o_ss;
+  float* lse;                // [B, H, Sq] natural-log LSE, or null
+  int dtype;
+};
+
+template <int D>
+struct Smem {
+  static constexpr int TILE = 128 * D * 2;        // one [128 x D] 16-bit tile
+  static constexpr int P_BYTES = 128 * 128 * 2;
+  static constexpr int Q_OFF = 0;
+  static constexpr int K_OFF = TILE;               // 2 stages
+  static constexpr int V_OFF = 3 * TILE;           // 2 stages
+  static constexpr int P_OFF = 5 * TILE;
+  static constexpr int BAR_OFF = P_OFF + P_BYTES;
+  static constexpr int TOTAL = BAR_OFF + 256 + 1024;
+};
+
+template <typename T, int D>
+__global__ void __launch_bounds__(THREADS, (D == 64) ? 2 : 1)
+flash_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                 const __grid_constant__ CUtensorMap tmV, const __grid_constant__ FwdParams p) {
+  using L = Smem<D>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sQ = smem + L::Q_OFF;
+  uint8_t* sK = smem + L::K_OFF;
+  uint8_t* sV = smem + L::V_OFF;
+  uint8_t* sP = smem + L::P_OFF;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::BAR_OFF);
+  uint64_t* q_full = bars;          // 1
+  uint64_t* kv_full = bars + 1;     // 2
+  uint64_t* kv_empty = bars + 3;    // 2
+  uint64_t* s_full = bars + 5;
+  uint64_t* p_full = bars + 6;
+  uint64_t* o_full = bars + 7;
+  uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(bars + 8);
+  uint8_t* s_kpm = reinterpret_cast<uint8_t*>(bars + 10);  // 128 bytes of key-padding mask for the current block
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nq_blk = (p.Sq + BQ - 1) / BQ;
+  const int q_blk = nq_blk - 1 - blockIdx.x;  // heavy (late) causal blocks first
+  const int h = blockIdx.y, b = blockIdx.z;
+  const int q0 = q_blk * BQ;
+  const int shift = p.Sk - p.Sq;  // causal alignment: query i sees keys <= i + shift
+  int kv_end = p.Sk;
+  if (p.causal) kv_end = min(p.Sk, q0 + BQ + shift);
+  const int nblk = max(0, (kv_end + BKV - 1) / BKV);
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV);
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      mbar_init(q_full, 1);
+      for (int i = 0; i < 2; ++i) { mbar_init(&kv_full[i], 1); mbar_init(&kv_empty[i], 1); }
+      mbar_init(s_full, 1);
+      mbar_init(p_full, 128);
+      mbar_init(o_full, 1);
+      mbar_fence_init();
+    }
+    __syncwarp();
+    tmem_alloc<256>(tmem_holder);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_holder;
+  const uint32_t tS = tmem_base, tO = tmem_base + 128;
+
+  if (warp == 0) {
+    if (lane == 0 && nblk > 0) {
+      mbar_expect_tx(q_full, L::TILE);
+      for (int c = 0; c < D / 64; ++c) tma_load_4d(sQ + c * 16384, &tmQ, q_full, c * 64, q0, h, b);
+      for (int j = 0; j < nblk; ++j) {
+        const int st = j & 1;
+        mbar_wait(&kv_empty[st], ((j >> 1) & 1) ^ 1);
+        mbar_expect_tx(&kv_full[st], 2 * L::TILE);
+        for (int c = 0; c < D / 64; ++c) {
+          tma_load_4d(sK + st * L::TILE + c * 16384, &tmK, &kv_full[st], c * 64, j * BKV, h, b);
+          tma_load_4d(sV + st * L::TILE + c * 16384, &tmV, &kv_full[st], c * 64, j * BKV, h, b);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0 && nblk > 0) {
+      const uint32_t fmt = (p.dtype == DT_F16) ? 0u : 1u;
+      const uint32_t idesc_s = make_idesc(fmt, 128, 128, false, false);
+      const uint32_t idesc_o = make_idesc(fmt, 128, D, false, true);  // B = V is N(=D)-major
+      const uint32_t q_base = smem_u32(sQ), p_base = smem_u32(sP);
+      auto issue_s = [&](int j) {
+        const uint32_t k_base = smem_u32(sK + (j & 1) * L::TILE);
+#pragma unroll
+        for (int k = 0; k < D / 16; ++k) {
+          const uint32_t off = (k >> 2) * 16384 + (k & 3) * 32;
+          umma_f16(tS, make_smem_desc_sw128(q_base + off, 16, 1024), make_smem_desc_sw128(k_base + off, 16, 1024),
+                   idesc_s, k > 0 ? 1u : 0u);
+        }
+        umma_commit(s_full);
+      };
+      mbar_wait(q_full, 0);
+      mbar_wait(&kv_full[0], 0);
+      tc_fence_after();
+      issue_s(0);
+      for (int j = 0; j < nblk; ++j) {
+        const int st = j & 1;
+        if (j + 1 < nblk) mbar_wait(&kv_full[(j + 1) & 1], ((j + 1) >> 1) & 1);
+        mbar_wait(p_full, j & 1);
+        tc_fence_after();
+        const uint32_t v_base = smem_u32(sV + st * L::TILE);
+#pragma unroll
+        for (int k = 0; k < BKV / 16; ++k) {
+          const uint64_t ad = make_smem_desc_sw128(p_base + (k >> 2) * 16384 + (k & 3) * 32, 16, 1024);
+          const uint64_t bd = make_smem_desc_sw128(v_base + k * 2048, 16384, 1024);
+          umma_f16(tO, ad, bd, idesc_o, k > 0 ? 1u : 0u);
+        }
+        umma_commit(o_full);
+        umma_commit(&kv_empty[st]);
+        if (j + 1 < nblk) issue_s(j + 1);
+      }
+    }
+  } else {
+    // ------------------------------------------------------------ softmax + output
+    const int quarter = warp & 3;
+    const int r = quarter * 32 + lane;         // row inside the query block == TMEM lane
+    const int tid128 = (warp - 2) * 32 + lane; // 0..127 among the softmax threads
+    const int qi = q0 + r;
+    const uint32_t lane_off = static_cast<uint32_t>(quarter * 32) << 16;
+    float o_acc[D];
+#pragma unroll
+    for (int i = 0; i < D; ++i) o_acc[i] = 0.f;
+    float m_run = -INFINITY, l_run = 0.f;
+    for (int j = 0; j < nblk; ++j) {
+      const int k0 = j * BKV;
+      const bool need_mask = (k0 + BKV > p.Sk) || (p.causal && (k0 + BKV - 1 > q0 + shift)) || (p.kpm != nullptr);
+      if (p.kpm) {
+        named_bar_sync(1, 128);  // previous block's readers are done with s_kpm
+        const int kk = k0 + tid128;
+        s_kpm[tid128] = (kk < p.Sk) ? p.kpm[static_cast<long long>(b) * p.Sk + kk] : 0;
+        named_bar_sync(1, 128);
+      }
+      mbar_wait(s_full, j & 1);
+      tc_fence_after();
+      // pass 1: row maximum
+      float mx = -INFINITY;
+#pragma unroll 1
+      for (int c = 0; c < 4; ++c) {
+        uint32_t v[32];
+        tmem_ld_32x32(tS + lane_off + c * 32, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          float s = __uint_as_float(v[i]) * p.scale_log2;
+          if (need_mask) {
+            const int kj = k0 + c * 32 + i;
+            const bool ok = (kj < p.Sk) && (!p.causal || kj <= qi + shift) && (!p.kpm || s_kpm[c * 32 + i]);
+            s = ok ? s : -INFINITY;
+          }
+          mx = fmaxf(mx, s);
+        }
+      }
+      const float m_new = fmaxf(m_run, mx);
+      const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
+      const float alpha = exp2f(m_run - m_use);  // m_run = -inf -> 0
+      // pass 2: probabilities -> shared memory (K-major, 128B swizzle), row sum
+      float l_blk = 0.f;
+#pragma unroll 1
+      for (int c = 0; c < 4; ++c) {
+        uint32_t v[32];
+        tmem_ld_32x32(tS + lane_off + c * 32, v);
+        tmem_ld_wait();
+        float pr[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          float s = __uint_as_float(v[i]) * p.scale_log2;
+          if (need_mask) {
+            const int kj = k0 + c * 32 + i;
+            const bool ok = (kj < p.Sk) && (!p.causal || kj <= qi + shift) && (!p.kpm || s_kpm[c * 32 + i]);
+            s = ok ? s : -INFINITY;
+          }
+          pr[i] = exp2f(s - m_use);
+          l_blk += pr[i];
+        }
+        uint8_t* prow = sP + (c >> 1) * 16384 + r * 128;
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+          float f[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) f[i] = pr[t * 8 + i];
+          const int cc = (c & 1) * 4 + t;
+          *reinterpret_cast<uint4*>(prow + ((cc ^ (r & 7)) << 4)) = pack8<T>(f);
+        }
+      }
+      l_run = l_run * alpha + l_blk;
+      m_run = m_new;
+      tc_fence_before();          // our tcgen05.ld of S are complete before the MMA warp may overwrite S
+      fence_proxy_async_smem();   // P (generic-proxy stores) visible to the tensor core (async proxy)
+      mbar_arrive(p_full);
+      // accumulate O_blk
+      mbar_wait(o_full, j & 1);
+      tc_fence_after();
+#pragma unroll
+      for (int c = 0; c < D / 32; ++c) {
+        uint32_t v[32];
+        tmem_ld_32x32(tO + lane_off + c * 32, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) o_acc[c * 32 + i] = o_acc[c * 32 + i] * alpha + __uint_as_float(v[i]);
+      }
+      tc_fence_before();
+    }
+    if (qi < p.Sq) {
+      const float inv_l = l_run > 0.f ? 1.f / l_run : 0.f;
+      T* orow = reinterpret_cast<T*>(p.o) + b * p.o_sb + h * p.o_sh + static_cast<long long>(qi) * p.o_ss;
+#pragma unroll
+      for (int g = 0; g < D / 8; ++g) {
+        float f[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) f[i] = o_acc[g * 8 + i] * inv_l;
+        *reinterpret_cast<uint4*>(orow + g * 8) = pack8<T>(f);
+      }
+      if (p.lse) {
+        const float lse = (l_run > 0.f) ? (m_run + log2f(l_run)) * 0.6931471805599453f : -INFINITY;
+        p.lse[(static_cast<long long>(b) * p.H + h) * p.Sq + qi] = lse;
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc<256>(tmem_base);
+}
+
+// 4-D map over a [B, H, S, D]-indexed tensor with element strides (sb, sh, ss), unit stride in D.
+static int make_qkv_map(CUtensorMap* tm, const void* ptr, int dtype, int B, int H, int S, int D, long long sb, long long sh,
+                        long long ss) {
+  const unsigned long long dims[4] = {(unsigned long long)D, (unsigned long long)S, (unsigned long long)H, (unsigned long long)B};
+  const unsigned long long strides[3] = {(unsigned long long)ss * 2, (unsigned long long)sh * 2, (unsigned long long)sb * 2};
+  const unsigned box[4] = {64, 128, 1, 1};
+  return make_tmap_nd(tm, ptr, dtype, 4, dims, strides, box);
+}
+
+template <typename T, int D>
+static int launch_fwd(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const FwdParams& p, cudaStream_t st) {
+  using L = Smem<D>;
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (!attr_set[dev & 63]) {
+    HYP_CHECK_CUDA(cudaFuncSetAttribute(flash_fwd_kernel<T, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
+    attr_set[dev & 63] = true;
+  }
+  dim3 grid((p.Sq + BQ - 1) / BQ, p.H, p.B);
+  flash_fwd_kernel<T, D><<<grid, THREADS, L::TOTAL, st>>>(tq, tk, tv, p);
+  HYP_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace attn
+}  // namespace hyp
+
+using namespace hyp;
+
+// q/k/v/o are indexed [b, h, s, d] through element strides (unit stride in d); see include/hyperion_b200.h.
+HYP_API int hyp_flash_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse, int B, int H, int Sq, int Sk,
+                               int D, long long q_sb, long long q_sh, long long q_ss, long long k_sb, long long k_sh,
+                               long long k_ss, long long v_sb, long long v_sh, long long v_ss, long long o_sb,
+                               long long o_sh, long long o_ss, const unsigned char* key_padding_mask, int causal,
+                               float scale, int dtype, void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  HYP_REQUIRE(dtype == DT_F16 || dtype == DT_BF16, "hyp_flash_attn_fwd: 16-bit dtypes only");
+  HYP_REQUIRE(D == 64 || D == 128, "hyp_flash_attn_fwd: head dim must be 64 or 128 (got %d)", D);
+  HYP_REQUIRE(B > 0 && H > 0 && Sq > 0 && Sk > 0, "hyp_flash_attn_fwd: empty problem");
+  HYP_REQUIRE(reinterpret_cast<uintptr_t>(o) % 16 == 0 && (o_sb % 8 | o_sh % 8 | o_ss % 8) == 0,
+              "hyp_flash_attn_fwd: output rows must be 16-byte aligned");
+  CUtensorMap tq, tk, tv;
+  int rc;
+  if ((rc = attn::make_qkv_map(&tq, q, dtype, B, H, Sq, D, q_sb, q_sh, q_ss))) return rc;
+  if ((rc = attn::make_qkv_map(&tk, k, dtype, B, H, Sk, D, k_sb, k_sh, k_ss))) return rc;
+  if ((rc = attn::make_qkv_map(&tv, v, dtype, B, H, Sk, D, v_sb, v_sh, v_ss))) return rc;
+  attn::FwdParams p;
+  p.B = B; p.H = H; p.Sq = Sq; p.Sk = Sk; p.D = D; p.causal = causal;
+  p.scale_log2 = scale * attn::LOG2E;
+  p.kpm = key_padding_mask;
+  p.o = o; p.o_sb = o_sb; p.o_sh = o_sh; p.o_ss = o_ss; p.lse = lse; p.dtype = dtype;
+  if (dtype == DT_BF16) return D == 64 ? attn::launch_fwd<__nv_bfloat16, 64>(tq, tk, tv, p, st) : attn::launch_fwd<__nv_bfloat16, 128>(tq, tk, tv, p, st);
+  return D == 64 ? attn::launch_fwd<__half, 64>(tq, tk, tv, p, st) : attn::launch_fwd<__half, 128>(tq, tk, tv, p, st);
+}

@@ -1,0 +1,87 @@
+"""Autograd wrapper of the tcgen05 flash-attention kernels (``csrc/attention.cu``).
+
+Inputs are ``[B, H, S, D]`` *views* with unit stride in D (e.g. slices of the packed ``[B, S, 3, H, D]`` projection
+output); the kernels read them in place through 4-D TMA descriptors.  The output is produced in ``[B, S, H, D]`` memory
+order and returned as a ``[B, H, S, D]`` view, so the usual ``transpose(1, 2).reshape(B, S, E)`` that follows is free.
+"""
+from __future__ import annotations
+
+import math
+
+import torch
+
+from . import _lib
+from ._lib import DT, call, ptr, stream_ptr
+
+_declared = False
+
+
+def _declare():
+    global _declared
+    if _declared:
+        return
+    _lib.declare("hyp_flash_attn_fwd", "ppppp" + "iiiii" + "l" * 12 + "p" + "i" + "f" + "i" + "p")
+    lib = _lib.require()
+    if hasattr(lib, "hyp_flash_attn_bwd"):
+        _lib.declare("hyp_flash_attn_bwd", "pppppp" + "ppp" + "pp" + "iiiii" + "l" * 12 + "lll" + "p" + "i" + "f" + "i" + "p")
+    _declared = True
+
+
+def _strides_bhs(t: torch.Tensor):
+    assert t.dim() == 4 and t.stride(3) == 1, "expected [B, H, S, D] with unit stride in D"
+    return t.stride(0), t.stride(1), t.stride(2)
+
+
+def _tma_ok(t: torch.Tensor) -> bool:
+    return t.data_ptr() % 16 == 0 and all(s % 8 == 0 for s in t.stride()[:3])
+
+
+def flash_fwd(q, k, v, causal: bool, key_padding_mask, scale: float):
+    """Returns (o as [B,H,S,D] view over [B,S,H,D] memory, lse [B,H,Sq] fp32)."""
+    _declare()
+    B, H, Sq, D = q.shape
+    Sk = k.shape[2]
+    q, k, v = (t if _tma_ok(t) else t.contiguous() for t in (q, k, v))
+    o_mem = torch.empty((B, Sq, H, D), device=q.device, dtype=q.dtype)
+    o = o_mem.permute(0, 2, 1, 3)
+    lse = torch.empty((B, H, Sq), device=q.device, dtype=torch.float32)
+    kpm = None
+    if key_padding_mask is not None:
+        kpm = key_padding_mask.to(torch.uint8).contiguous()
+    call("hyp_flash_attn_fwd", ptr(q), ptr(k), ptr(v), ptr(o_mem), ptr(lse), B, H, Sq, Sk, D, *_strides_bhs(q),
+         *_strides_bhs(k), *_strides_bhs(v), *_strides_bhs(o), ptr(kpm), int(causal), float(scale), DT[q.dtype],
+         stream_ptr())
+    return o, lse, (q, k, v, kpm)
+
+
+class _FlashFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, q, k, v, causal, key_padding_mask, scale):
+        o, lse, (qc, kc, vc, kpm) = flash_fwd(q, k, v, causal, key_padding_mask, scale)
+        ctx.save_for_backward(qc, kc, vc, o, lse, kpm if kpm is not None else torch.empty(0, device=q.device))
+        ctx.causal, ctx.scale, ctx.has_kpm = causal, scale, kpm is not None
+        return o
+
+    @staticmethod
+    def backward(ctx, do):
+        q, k, v, o, lse, kpm = ctx.saved_tensors
+        kpm = kpm if ctx.has_kpm else None
+        lib = _lib.require()
+        if hasattr(lib, "hyp_flash_attn_bwd"):
+            from .flash_bwd import flash_bwd
+
+            dq, dk, dv = flash_bwd(q, k, v, o, lse, do, ctx.causal, kpm, ctx.scale)
+            return dq, dk, dv, None, None, None
+        # recompute-based backward in plain PyTorch (only used when the backward kernel is not built)
+        from .attn import attention_reference
+
+        with torch.enable_grad():
+            qq, kk, vv = (t.detach().requires_grad_(True) for t in (q, k, v))
+            out = attention_reference(qq, kk, vv, ctx.causal, kpm.bool() if kpm is not None else None, 0.0, ctx.scale)
+            dq, dk, dv = torch.autograd.grad(out, (qq, kk, vv), do)
+        return dq, dk, dv, None, None, None
+
+
+def flash_attention(q, k, v, causal: bool = False, key_padding_mask=None, scale: float | None = None):
+    scale = scale if scale is not None else 1.0 / math.sqrt(q.shape[-1])
+    return _FlashFn.apply(q, k, v, causal, key_padding_mask, scale)

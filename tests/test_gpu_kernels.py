@@ -231,3 +231,46 @@ def test_rope(nat):
     assert _rel_err(y, ref) < 1e-2
     back = nat.rope_(y.clone(), inverse=True)
     assert _rel_err(back, xf) < 2e-2
+
+
+ATTN_CASES = [
+    # B, H, Sq, Sk, D, causal, padded
+    (2, 4, 127, 127, 64, False, False),   # reference LM: no mask, ragged S
+    (2, 8, 16, 16, 64, False, False),     # custom transformer
+    (1, 12, 197, 197, 64, False, False),  # ViT
+    (2, 16, 1024, 1024, 64, True, False), # GPT-2 medium
+    (2, 4, 128, 128, 128, True, True),    # Llama: causal + key padding, d 128
+    (1, 2, 300, 300, 128, True, False),
+    (1, 3, 256, 384, 64, True, False),    # Sk > Sq (causal alignment at the end)
+]
+
+
+@pytest.mark.parametrize("B,H,Sq,Sk,D,causal,padded", ATTN_CASES)
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_flash_attention_forward(nat, B, H, Sq, Sk, D, causal, padded, dtype):
+    from hyperion_b200.ops.attn import attention_reference
+    from hyperion_b200.ops.flash import flash_fwd
+
+    torch.manual_seed(10)
+    # packed projection layout [B, S, 3, H, D] like the models produce (strided q/k/v views)
+    if Sq == Sk:
+        qkv = torch.randn(B, Sq, 3, H, D, device="cuda", dtype=dtype)
+        q, k, v = (qkv[:, :, i].permute(0, 2, 1, 3) for i in range(3))
+    else:
+        q = torch.randn(B, H, Sq, D, device="cuda", dtype=dtype)
+        k = torch.randn(B, H, Sk, D, device="cuda", dtype=dtype)
+        v = torch.randn(B, H, Sk, D, device="cuda", dtype=dtype)
+    kpm = None
+    if padded:
+        lens = torch.randint(Sk // 2, Sk + 1, (B,), device="cuda")
+        kpm = torch.arange(Sk, device="cuda")[None] < lens[:, None]
+    o, lse, _ = flash_fwd(q, k, v, causal, kpm, 1.0 / D ** 0.5)
+    ref = attention_reference(q, k, v, causal, kpm, 0.0, None)
+    assert o.shape == ref.shape
+    assert _rel_err(o, ref) < 2e-2, _rel_err(o, ref)
+    s = torch.matmul(q.float(), k.float().transpose(-1, -2)) / D ** 0.5
+    if causal:
+        s = s.masked_fill(~torch.ones(Sq, Sk, dtype=torch.bool, device="cuda").tril(Sk - Sq), float("-inf"))
+    if kpm is not None:
+        s = s.masked_fill(~kpm[:, None, None, :], float("-inf"))
+    assert torch.allclose(lse, torch.logsumexp(s, -1), atol=2e-2, rtol=1e-3)
