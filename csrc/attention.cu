@@ -321,3 +321,362 @@ HYP_API int hyp_flash_attn_fwd(const void* q, const void* k, const void* v, void
   if (dtype == DT_BF16) return D == 64 ? attn::launch_fwd<__nv_bfloat16, 64>(tq, tk, tv, p, st) : attn::launch_fwd<__nv_bfloat16, 128>(tq, tk, tv, p, st);
   return D == 64 ? attn::launch_fwd<__half, 64>(tq, tk, tv, p, st) : attn::launch_fwd<__half, 128>(tq, tk, tv, p, st);
 }
+
+// =====================================================================================================
+// Backward.  One CTA owns a 128-key block of one (batch, head), keeps K_j / V_j in shared memory and dK_j / dV_j in
+// tensor memory, and streams the query blocks that can see it:
+//     S  = Q_i K_j^T            dP = dO_i V_j^T                     (two 128x128xD MMAs into TMEM)
+//     P  = exp(S*scale - lse)   dS = P o (dP - delta) * scale        (softmax threads; P, dS -> smem, 16-bit)
+//     dV += P^T dO_i            dK += dS^T Q_i                       (A operand = the same smem tile read MN-major)
+//     dQ_i = dS K_j             -> fp32 red.global.add into the dQ accumulator
+// delta = rowsum(dO o O) comes from a small pre-kernel.  TMEM columns: [0,128) S then dQ_i, [128,256) dP,
+// [256,256+D) dV, [256+D,256+2D) dK.
+namespace hyp {
+namespace attn {
+
+struct BwdParams {
+  int B, H, Sq, Sk, D;
+  int causal;
+  float scale, scale_log2;
+  const uint8_t* kpm;
+  const float* lse;    // [B,H,Sq]
+  const float* delta;  // [B,H,Sq]
+  float* dq_acc;       // [B,H,Sq,D] fp32, zero-initialised
+  void* dk; void* dv;  // element strides below (unit stride in D)
+  long long dk_sb, dk_sh, dk_ss, dv_sb, dv_sh, dv_ss;
+  int dtype;
+};
+
+template <int D>
+struct BwdSmem {
+  static constexpr int TILE = 128 * D * 2;
+  static constexpr int NST = (D == 64) ? 2 : 1;
+  static constexpr int K_OFF = 0, V_OFF = TILE;
+  static constexpr int Q_OFF = 2 * TILE;                 // NST stages
+  static constexpr int DO_OFF = Q_OFF + NST * TILE;      // NST stages
+  static constexpr int P_OFF = DO_OFF + NST * TILE;
+  static constexpr int DS_OFF = P_OFF + 32768;
+  static constexpr int BAR_OFF = DS_OFF + 32768;
+  static constexpr int TOTAL = BAR_OFF + 384 + 1024;
+};
+
+template <typename T, int D>
+__global__ void __launch_bounds__(THREADS, 1)
+flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                 const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmDO,
+                 const __grid_constant__ BwdParams p) {
+  using L = BwdSmem<D>;
+  constexpr int NST = L::NST;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sK = smem + L::K_OFF;
+  uint8_t* sV = smem + L::V_OFF;
+  uint8_t* sQ = smem + L::Q_OFF;
+  uint8_t* sDO = smem + L::DO_OFF;
+  uint8_t* sP = smem + L::P_OFF;
+  uint8_t* sDS = smem + L::DS_OFF;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::BAR_OFF);
+  uint64_t* kv_full = bars;            // 1
+  uint64_t* qdo_full = bars + 1;       // 2
+  uint64_t* qdo_empty = bars + 3;      // 2
+  uint64_t* sdp_full = bars + 5;
+  uint64_t* pds_full = bars + 6;       // 128 arrivals
+  uint64_t* dq_full = bars + 7;
+  uint64_t* dq_read = bars + 8;        // 128 arrivals
+  uint64_t* done = bars + 9;
+  uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(bars + 10);
+  uint8_t* s_kpm = reinterpret_cast<uint8_t*>(bars + 12);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int j = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
+  const int k0 = j * BKV;
+  const int shift = p.Sk - p.Sq;
+  const int nq_blk = (p.Sq + BQ - 1) / BQ;
+  int i_start = 0;
+  if (p.causal) i_start = max(0, (k0 - shift) / BQ);  // first query block with a row that sees key k0
+  const int niter = max(0, nq_blk - i_start);
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV); tma_prefetch_desc(&tmDO);
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      mbar_init(kv_full, 1);
+      for (int s = 0; s < 2; ++s) { mbar_init(&qdo_full[s], 1); mbar_init(&qdo_empty[s], 1); }
+      mbar_init(sdp_full, 1);
+      mbar_init(pds_full, 128);
+      mbar_init(dq_full, 1);
+      mbar_init(dq_read, 128);
+      mbar_init(done, 1);
+      mbar_fence_init();
+    }
+    __syncwarp();
+    tmem_alloc<512>(tmem_holder);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_holder;
+  const uint32_t tS = tmem_base, tDP = tmem_base + 128, tDV = tmem_base + 256, tDK = tmem_base + 256 + D;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      mbar_expect_tx(kv_full, 2 * L::TILE);
+      for (int c = 0; c < D / 64; ++c) {
+        tma_load_4d(sK + c * 16384, &tmK, kv_full, c * 64, k0, h, b);
+        tma_load_4d(sV + c * 16384, &tmV, kv_full, c * 64, k0, h, b);
+      }
+      for (int it = 0; it < niter; ++it) {
+        const int st = it % NST;
+        mbar_wait(&qdo_empty[st], ((it / NST) & 1) ^ 1);
+        mbar_expect_tx(&qdo_full[st], 2 * L::TILE);
+        const int q0 = (i_start + it) * BQ;
+        for (int c = 0; c < D / 64; ++c) {
+          tma_load_4d(sQ + st * L::TILE + c * 16384, &tmQ, &qdo_full[st], c * 64, q0, h, b);
+          tma_load_4d(sDO + st * L::TILE + c * 16384, &tmDO, &qdo_full[st], c * 64, q0, h, b);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t fmt = (p.dtype == DT_F16) ? 0u : 1u;
+      const uint32_t idesc_s = make_idesc(fmt, 128, 128, false, false);
+      const uint32_t idesc_t = make_idesc(fmt, 128, D, true, true);    // dV, dK: A = P^T / dS^T (MN-major), B MN-major
+      const uint32_t idesc_q = make_idesc(fmt, 128, D, false, true);   // dQ: A = dS (K-major), B = K (MN-major)
+      const uint32_t k_base = smem_u32(sK), v_base = smem_u32(sV), p_base = smem_u32(sP), ds_base = smem_u32(sDS);
+      mbar_wait(kv_full, 0);
+      for (int it = 0; it < niter; ++it) {
+        const int st = it % NST;
+        const uint32_t q_base = smem_u32(sQ + st * L::TILE), do_base = smem_u32(sDO + st * L::TILE);
+        mbar_wait(&qdo_full[st], (it / NST) & 1);
+        if (it > 0) mbar_wait(dq_read, (it - 1) & 1);  // dQ_{i-1} has been drained from the columns S reuses
+        tc_fence_after();
+#pragma unroll
+        for (int k = 0; k < D / 16; ++k) {
+          const uint32_t off = (k >> 2) * 16384 + (k & 3) * 32;
+          umma_f16(tS, make_smem_desc_sw128(q_base + off, 16, 1024), make_smem_desc_sw128(k_base + off, 16, 1024),
+                   idesc_s, k > 0 ? 1u : 0u);
+        }
+#pragma unroll
+        for (int k = 0; k < D / 16; ++k) {
+          const uint32_t off = (k >> 2) * 16384 + (k & 3) * 32;
+          umma_f16(tDP, make_smem_desc_sw128(do_base + off, 16, 1024), make_smem_desc_sw128(v_base + off, 16, 1024),
+                   idesc_s, k > 0 ? 1u : 0u);
+        }
+        umma_commit(sdp_full);
+        mbar_wait(pds_full, it & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int k = 0; k < BQ / 16; ++k) {  // reduction over the 128 query rows
+          umma_f16(tDV, make_smem_desc_sw128(p_base + k * 2048, 16384, 1024),
+                   make_smem_desc_sw128(do_base + k * 2048, 16384, 1024), idesc_t, (it > 0 || k > 0) ? 1u : 0u);
+        }
+#pragma unroll
+        for (int k = 0; k < BQ / 16; ++k) {
+          umma_f16(tDK, make_smem_desc_sw128(ds_base + k * 2048, 16384, 1024),
+                   make_smem_desc_sw128(q_base + k * 2048, 16384, 1024), idesc_t, (it > 0 || k > 0) ? 1u : 0u);
+        }
+#pragma unroll
+        for (int k = 0; k < BKV / 16; ++k) {  // reduction over the 128 keys
+          umma_f16(tS, make_smem_desc_sw128(ds_base + (k >> 2) * 16384 + (k & 3) * 32, 16, 1024),
+                   make_smem_desc_sw128(k_base + k * 2048, 16384, 1024), idesc_q, k > 0 ? 1u : 0u);
+        }
+        umma_commit(dq_full);
+        umma_commit(&qdo_empty[st]);
+      }
+      if (niter > 0) umma_commit(done);
+    }
+  } else {
+    const int quarter = warp & 3;
+    const int r = quarter * 32 + lane;
+    const int tid128 = (warp - 2) * 32 + lane;
+    const uint32_t lane_off = static_cast<uint32_t>(quarter * 32) << 16;
+    if (p.kpm) {
+      const int kk = k0 + tid128;
+      s_kpm[tid128] = (kk < p.Sk) ? p.kpm[static_cast<long long>(b) * p.Sk + kk] : 0;
+      named_bar_sync(1, 128);
+    }
+    const long long bh = static_cast<long long>(b) * p.H + h;
+    for (int it = 0; it < niter; ++it) {
+      const int q0 = (i_start + it) * BQ;
+      const int qi = q0 + r;
+      const bool row_ok = qi < p.Sq;
+      float lse2 = 0.f, delta = 0.f;
+      if (row_ok) {
+        lse2 = p.lse[bh * p.Sq + qi] * LOG2E;
+        delta = p.delta[bh * p.Sq + qi];
+      }
+      const bool dead = !row_ok || lse2 == -INFINITY;
+      const bool need_mask = (k0 + BKV > p.Sk) || (p.causal && (k0 + BKV - 1 > q0 + shift)) || (p.kpm != nullptr);
+      mbar_wait(sdp_full, it & 1);
+      tc_fence_after();
+#pragma unroll 1
+      for (int c = 0; c < 4; ++c) {
+        uint32_t vs[32], vd[32];
+        tmem_ld_32x32(tS + lane_off + c * 32, vs);
+        tmem_ld_32x32(tDP + lane_off + c * 32, vd);
+        tmem_ld_wait();
+        float pr[32], ds[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          bool ok = !dead;
+          if (need_mask) {
+            const int kj = k0 + c * 32 + i;
+            ok = ok && (kj < p.Sk) && (!p.causal || kj <= qi + shift) && (!p.kpm || s_kpm[c * 32 + i]);
+          }
+          const float pv = ok ? exp2f(__uint_as_float(vs[i]) * p.scale_log2 - lse2) : 0.f;
+          pr[i] = pv;
+          ds[i] = pv * (__uint_as_float(vd[i]) - delta) * p.scale;
+        }
+        uint8_t* prow = sP + (c >> 1) * 16384 + r * 128;
+        uint8_t* drow = sDS + (c >> 1) * 16384 + r * 128;
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+          float f[8], g[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) { f[i] = pr[t * 8 + i]; g[i] = ds[t * 8 + i]; }
+          const int cc = ((c & 1) * 4 + t) ^ (r & 7);
+          *reinterpret_cast<uint4*>(prow + (cc << 4)) = pack8<T>(f);
+          *reinterpret_cast<uint4*>(drow + (cc << 4)) = pack8<T>(g);
+        }
+      }
+      tc_fence_before();
+      fence_proxy_async_smem();
+      mbar_arrive(pds_full);
+      // dQ_i tile -> fp32 accumulator in global memory
+      mbar_wait(dq_full, it & 1);
+      tc_fence_after();
+      float* dq_row = p.dq_acc + (bh * p.Sq + qi) * D;
+#pragma unroll
+      for (int c = 0; c < D / 32; ++c) {
+        uint32_t v[32];
+        tmem_ld_32x32(tS + lane_off + c * 32, v);
+        tmem_ld_wait();
+        if (row_ok) {
+#pragma unroll
+          for (int g = 0; g < 8; ++g)
+            atomicAdd(reinterpret_cast<float4*>(dq_row + c * 32) + g,
+                      make_float4(__uint_as_float(v[4 * g]), __uint_as_float(v[4 * g + 1]), __uint_as_float(v[4 * g + 2]),
+                                  __uint_as_float(v[4 * g + 3])));
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(dq_read);
+    }
+    // dV_j, dK_j: thread r owns key row k0 + r
+    if (niter > 0) mbar_wait(done, 0);
+    tc_fence_after();
+    const int kj = k0 + r;
+    T* dv_row = reinterpret_cast<T*>(p.dv) + b * p.dv_sb + h * p.dv_sh + static_cast<long long>(kj) * p.dv_ss;
+    T* dk_row = reinterpret_cast<T*>(p.dk) + b * p.dk_sb + h * p.dk_sh + static_cast<long long>(kj) * p.dk_ss;
+#pragma unroll
+    for (int c = 0; c < D / 32; ++c) {
+      uint32_t v[32];
+      tmem_ld_32x32(tDV + lane_off + c * 32, v);
+      tmem_ld_wait();
+      if (kj < p.Sk) {
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          float f[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) f[i] = niter > 0 ? __uint_as_float(v[g * 8 + i]) : 0.f;
+          *reinterpret_cast<uint4*>(dv_row + c * 32 + g * 8) = pack8<T>(f);
+        }
+      }
+      tmem_ld_32x32(tDK + lane_off + c * 32, v);
+      tmem_ld_wait();
+      if (kj < p.Sk) {
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          float f[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) f[i] = niter > 0 ? __uint_as_float(v[g * 8 + i]) : 0.f;
+          *reinterpret_cast<uint4*>(dk_row + c * 32 + g * 8) = pack8<T>(f);
+        }
+      }
+    }
+    tc_fence_before();
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc<512>(tmem_base);
+}
+
+// delta[b,h,q] = sum_d dO[b,h,q,d] * O[b,h,q,d]; one thread per row, 16-byte loads.
+template <typename T>
+__global__ void __launch_bounds__(256)
+attn_delta_kernel(const T* __restrict__ o, const T* __restrict__ d_o, float* __restrict__ delta, int B, int H, int S, int D,
+                  long long o_sb, long long o_sh, long long o_ss, long long g_sb, long long g_sh, long long g_ss) {
+  const long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const long long total = static_cast<long long>(B) * H * S;
+  if (idx >= total) return;
+  const int s = static_cast<int>(idx % S);
+  const int h = static_cast<int>((idx / S) % H);
+  const int b = static_cast<int>(idx / (static_cast<long long>(S) * H));
+  const T* po = o + b * o_sb + h * o_sh + static_cast<long long>(s) * o_ss;
+  const T* pg = d_o + b * g_sb + h * g_sh + static_cast<long long>(s) * g_ss;
+  float acc = 0.f;
+  for (int c = 0; c < D; c += 8) {
+    float a[8], g[8];
+    unpack8<T>(*reinterpret_cast<const uint4*>(po + c), a);
+    unpack8<T>(*reinterpret_cast<const uint4*>(pg + c), g);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc += a[i] * g[i];
+  }
+  delta[idx] = acc;
+}
+
+template <typename T, int D>
+static int launch_bwd(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const CUtensorMap& tdo,
+                      const BwdParams& p, cudaStream_t st) {
+  using L = BwdSmem<D>;
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (!attr_set[dev & 63]) {
+    HYP_CHECK_CUDA(cudaFuncSetAttribute(flash_bwd_kernel<T, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
+    attr_set[dev & 63] = true;
+  }
+  dim3 grid((p.Sk + BKV - 1) / BKV, p.H, p.B);
+  flash_bwd_kernel<T, D><<<grid, THREADS, L::TOTAL, st>>>(tq, tk, tv, tdo, p);
+  HYP_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace attn
+}  // namespace hyp
+
+// dq_acc: fp32 [B,H,Sq,D] zero-initialised by the caller (accumulated with reductions); delta: fp32 [B,H,Sq] scratch
+// written here; dk / dv are written in full.  All tensors are indexed [b,h,s,d] through element strides.
+HYP_API int hyp_flash_attn_bwd(const void* q, const void* k, const void* v, const void* o, const void* d_o, const float* lse,
+                               float* dq_acc, void* dk, void* dv, float* delta, const unsigned char* key_padding_mask,
+                               int B, int H, int Sq, int Sk, int D, long long q_sb, long long q_sh, long long q_ss,
+                               long long k_sb, long long k_sh, long long k_ss, long long v_sb, long long v_sh, long long v_ss,
+                               long long o_sb, long long o_sh, long long o_ss, long long g_sb, long long g_sh, long long g_ss,
+                               long long dkv_sb, long long dkv_sh, long long dkv_ss, int causal, float scale, int dtype,
+                               void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  HYP_REQUIRE(dtype == DT_F16 || dtype == DT_BF16, "hyp_flash_attn_bwd: 16-bit dtypes only");
+  HYP_REQUIRE(D == 64 || D == 128, "hyp_flash_attn_bwd: head dim must be 64 or 128 (got %d)", D);
+  const long long rows = static_cast<long long>(B) * H * Sq;
+  const int dgrid = static_cast<int>((rows + 255) / 256);
+  if (dtype == DT_BF16)
+    attn::attn_delta_kernel<__nv_bfloat16><<<dgrid, 256, 0, st>>>((const __nv_bfloat16*)o, (const __nv_bfloat16*)d_o, delta, B, H, Sq, D, o_sb, o_sh, o_ss, g_sb, g_sh, g_ss);
+  else
+    attn::attn_delta_kernel<__half><<<dgrid, 256, 0, st>>>((const __half*)o, (const __half*)d_o, delta, B, H, Sq, D, o_sb, o_sh, o_ss, g_sb, g_sh, g_ss);
+  HYP_CHECK_CUDA(cudaGetLastError());
+  CUtensorMap tq, tk, tv, tdo;
+  int rc;
+  if ((rc = attn::make_qkv_map(&tq, q, dtype, B, H, Sq, D, q_sb, q_sh, q_ss))) return rc;
+  if ((rc = attn::make_qkv_map(&tk, k, dtype, B, H, Sk, D, k_sb, k_sh, k_ss))) return rc;
+  if ((rc = attn::make_qkv_map(&tv, v, dtype, B, H, Sk, D, v_sb, v_sh, v_ss))) return rc;
+  if ((rc = attn::make_qkv_map(&tdo, d_o, dtype, B, H, Sq, D, g_sb, g_sh, g_ss))) return rc;
+  attn::BwdParams p;
+  p.B = B; p.H = H; p.Sq = Sq; p.Sk = Sk; p.D = D; p.causal = causal;
+  p.scale = scale; p.scale_log2 = scale * attn::LOG2E;
+  p.kpm = key_padding_mask; p.lse = lse; p.delta = delta; p.dq_acc = dq_acc; p.dk = dk; p.dv = dv;
+  p.dk_sb = dkv_sb; p.dk_sh = dkv_sh; p.dk_ss = dkv_ss; p.dv_sb = dkv_sb; p.dv_sh = dkv_sh; p.dv_ss = dkv_ss;
+  p.dtype = dtype;
+  if (dtype == DT_BF16) return D == 64 ? attn::launch_bwd<__nv_bfloat16, 64>(tq, tk, tv, tdo, p, st) : attn::launch_bwd<__nv_bfloat16, 128>(tq, tk, tv, tdo, p, st);
+  return D == 64 ? attn::launch_bwd<__half, 64>(tq, tk, tv, tdo, p, st) : attn::launch_bwd<__half, 128>(tq, tk, tv, tdo, p, st);
+}

@@ -23,7 +23,7 @@ def _declare():
     _lib.declare("hyp_flash_attn_fwd", "ppppp" + "iiiii" + "l" * 12 + "p" + "i" + "f" + "i" + "p")
     lib = _lib.require()
     if hasattr(lib, "hyp_flash_attn_bwd"):
-        _lib.declare("hyp_flash_attn_bwd", "pppppp" + "ppp" + "pp" + "iiiii" + "l" * 12 + "lll" + "p" + "i" + "f" + "i" + "p")
+        _lib.declare("hyp_flash_attn_bwd", "pppppp" + "ppp" + "pp" + "iiiii" + "l" * 18 + "ifip")
     _declared = True
 
 

@@ -274,3 +274,27 @@ def test_flash_attention_forward(nat, B, H, Sq, Sk, D, causal, padded, dtype):
     if kpm is not None:
         s = s.masked_fill(~kpm[:, None, None, :], float("-inf"))
     assert torch.allclose(lse, torch.logsumexp(s, -1), atol=2e-2, rtol=1e-3)
+
+
+@pytest.mark.parametrize("B,H,Sq,Sk,D,causal,padded", ATTN_CASES)
+def test_flash_attention_backward(nat, B, H, Sq, Sk, D, causal, padded):
+    from hyperion_b200.ops.attn import attention_reference
+    from hyperion_b200.ops.flash import flash_attention
+
+    torch.manual_seed(11)
+    dtype = torch.bfloat16
+    q = torch.randn(B, H, Sq, D, device="cuda", dtype=dtype, requires_grad=True)
+    k = torch.randn(B, H, Sk, D, device="cuda", dtype=dtype, requires_grad=True)
+    v = torch.randn(B, H, Sk, D, device="cuda", dtype=dtype, requires_grad=True)
+    kpm = None
+    if padded:
+        lens = torch.randint(Sk // 2, Sk + 1, (B,), device="cuda")
+        kpm = torch.arange(Sk, device="cuda")[None] < lens[:, None]
+    do = torch.randn(B, H, Sq, D, device="cuda", dtype=dtype)
+    o = flash_attention(q, k, v, causal=causal, key_padding_mask=kpm)
+    dq, dk, dv = torch.autograd.grad(o, (q, k, v), do)
+    qf, kf, vf = (t.detach().float().requires_grad_(True) for t in (q, k, v))
+    ref = attention_reference(qf, kf, vf, causal, kpm, 0.0, None)
+    rq, rk, rv = torch.autograd.grad(ref, (qf, kf, vf), do.float())
+    for got, want, name in ((dq, rq, "dq"), (dk, rk, "dk"), (dv, rv, "dv")):
+        assert _rel_err(got, want) < 3e-2, (name, _rel_err(got, want))
