@@ -49,7 +49,7 @@ struct Smem {
   static constexpr int V_OFF = 3 * TILE;           // 2 stages
   static constexpr int P_OFF = 5 * TILE;
   static constexpr int BAR_OFF = P_OFF + P_BYTES;
-  static constexpr int TOTAL = BAR_OFF + 256 + 1024;
+  static constexpr int TOTAL = BAR_OFF + 256;  // no alignment slack: the dynamic window is declared 1024-aligned
 };
 
 template <typename T, int D>
@@ -57,8 +57,9 @@ __global__ void __launch_bounds__(THREADS, (D == 64) ? 2 : 1)
 flash_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                  const __grid_constant__ CUtensorMap tmV, const __grid_constant__ FwdParams p) {
   using L = Smem<D>;
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  extern __shared__ __align__(1024) uint8_t smem_fwd[];
+  uint8_t* smem = smem_fwd;
+  if (threadIdx.x == 0 && (smem_u32(smem) & 1023u)) __trap();  // SWIZZLE_128B tiles need a 1024-byte aligned base
   uint8_t* sQ = smem + L::Q_OFF;
   uint8_t* sK = smem + L::K_OFF;
   uint8_t* sV = smem + L::V_OFF;
@@ -177,45 +178,53 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
       }
       mbar_wait(s_full, j & 1);
       tc_fence_after();
-      // pass 1: row maximum
+      // pass 1: row maximum of the raw scores (scale > 0, so it commutes with max)
       float mx = -INFINITY;
 #pragma unroll 1
       for (int c = 0; c < 4; ++c) {
         uint32_t v[32];
         tmem_ld_32x32(tS + lane_off + c * 32, v);
         tmem_ld_wait();
+        if (need_mask) {
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          float s = __uint_as_float(v[i]) * p.scale_log2;
-          if (need_mask) {
+          for (int i = 0; i < 32; ++i) {
             const int kj = k0 + c * 32 + i;
-            const bool ok = (kj < p.Sk) && (!p.causal || kj <= qi + shift) && (!p.kpm || s_kpm[c * 32 + i]);
-            s = ok ? s : -INFINITY;
+            bool ok = (kj < p.Sk) & (!p.causal | (kj <= qi + shift));
+            if (p.kpm) ok = ok & (s_kpm[c * 32 + i] != 0);
+            mx = fmaxf(mx, ok ? __uint_as_float(v[i]) : -INFINITY);
           }
-          mx = fmaxf(mx, s);
+        } else {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(v[i]));
         }
       }
-      const float m_new = fmaxf(m_run, mx);
+      const float m_new = fmaxf(m_run, mx * p.scale_log2);
       const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
-      const float alpha = exp2f(m_run - m_use);  // m_run = -inf -> 0
+      const float alpha = ex2_fast(m_run - m_use);  // m_run = -inf -> 0
       // pass 2: probabilities -> shared memory (K-major, 128B swizzle), row sum
       float l_blk = 0.f;
+      const float neg_m = -m_use;
 #pragma unroll 1
       for (int c = 0; c < 4; ++c) {
         uint32_t v[32];
         tmem_ld_32x32(tS + lane_off + c * 32, v);
         tmem_ld_wait();
         float pr[32];
+        if (need_mask) {
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          float s = __uint_as_float(v[i]) * p.scale_log2;
-          if (need_mask) {
+          for (int i = 0; i < 32; ++i) {
             const int kj = k0 + c * 32 + i;
-            const bool ok = (kj < p.Sk) && (!p.causal || kj <= qi + shift) && (!p.kpm || s_kpm[c * 32 + i]);
-            s = ok ? s : -INFINITY;
+            bool ok = (kj < p.Sk) & (!p.causal | (kj <= qi + shift));
+            if (p.kpm) ok = ok & (s_kpm[c * 32 + i] != 0);
+            pr[i] = ok ? ex2_fast(fmaf(__uint_as_float(v[i]), p.scale_log2, neg_m)) : 0.f;
+            l_blk += pr[i];
           }
-          pr[i] = exp2f(s - m_use);
-          l_blk += pr[i];
+        } else {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            pr[i] = ex2_fast(fmaf(__uint_as_float(v[i]), p.scale_log2, neg_m));
+            l_blk += pr[i];
+          }
         }
         uint8_t* prow = sP + (c >> 1) * 16384 + r * 128;
 #pragma unroll
@@ -522,9 +531,10 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
           bool ok = !dead;
           if (need_mask) {
             const int kj = k0 + c * 32 + i;
-            ok = ok && (kj < p.Sk) && (!p.causal || kj <= qi + shift) && (!p.kpm || s_kpm[c * 32 + i]);
+            ok = ok & (kj < p.Sk) & (!p.causal | (kj <= qi + shift));
+            if (p.kpm) ok = ok & (s_kpm[c * 32 + i] != 0);
           }
-          const float pv = ok ? exp2f(__uint_as_float(vs[i]) * p.scale_log2 - lse2) : 0.f;
+          const float pv = ok ? ex2_fast(fmaf(__uint_as_float(vs[i]), p.scale_log2, -lse2)) : 0.f;
           pr[i] = pv;
           ds[i] = pv * (__uint_as_float(vd[i]) - delta) * p.scale;
         }

@@ -177,6 +177,12 @@ __device__ __forceinline__ float dsilu(float x) {
 }
 
 
+__device__ __forceinline__ float ex2_fast(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 // ---- fast activation variants for GEMM epilogues (outputs are rounded to 16 bits anyway) -------------
 __device__ __forceinline__ float tanh_fast(float x) {
   float y;
