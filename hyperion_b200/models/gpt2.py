@@ -51,8 +51,7 @@ class _Attn(nn.Module):
     def forward(self, x, residual):
         B, S, E = x.shape
         qkv = ops.linear(x, self.c_attn.weight, self.c_attn.bias)
-        qkv = qkv.reshape(B, S, 3, self.n_head, E // self.n_head).permute(2, 0, 3, 1, 4)
-        o = ops.attention(qkv[0], qkv[1], qkv[2], causal=True)
+        o = ops.attention_qkvpacked(qkv.reshape(B, S, 3, self.n_head, E // self.n_head), causal=True)
         o = o.transpose(1, 2).reshape(B, S, E)
         return ops.linear(o, self.c_proj.weight, self.c_proj.bias, residual=residual)
 

@@ -35,9 +35,9 @@ class MultiheadSelfAttention(nn.Module):
     def forward(self, x, causal: bool = False, key_padding_mask=None, residual=None):
         B, S, E = x.shape
         qkv = ops.linear(x, self.in_proj_weight, self.in_proj_bias)
-        qkv = qkv.reshape(B, S, 3, self.num_heads, self.head_dim).permute(2, 0, 3, 1, 4)
+        qkv = qkv.reshape(B, S, 3, self.num_heads, self.head_dim)
         p = self.dropout if self.training else 0.0
-        o = ops.attention(qkv[0], qkv[1], qkv[2], causal=causal, key_padding_mask=key_padding_mask, dropout_p=p)
+        o = ops.attention_qkvpacked(qkv, causal=causal, key_padding_mask=key_padding_mask, dropout_p=p)
         o = o.transpose(1, 2).reshape(B, S, E)
         return ops.linear(o, self.out_proj.weight, self.out_proj.bias, residual=residual)
 

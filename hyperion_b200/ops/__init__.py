@@ -1,9 +1,9 @@
 """Hot ops of the framework: autograd functions over the sm_100a kernels (see functional.py)."""
 from . import _lib
-from .functional import (attention, cross_entropy, embedding, layer_norm, linear, linear_cross_entropy, lora_linear,
+from .functional import (attention, attention_qkvpacked, cross_entropy, embedding, layer_norm, linear, linear_cross_entropy, lora_linear,
                          mlp, rms_norm, rope, swiglu)
 
-__all__ = ["attention", "cross_entropy", "embedding", "layer_norm", "linear", "linear_cross_entropy", "lora_linear", "mlp",
+__all__ = ["attention", "attention_qkvpacked", "cross_entropy", "embedding", "layer_norm", "linear", "linear_cross_entropy", "lora_linear", "mlp",
            "rms_norm", "rope", "swiglu", "native_available"]
 
 

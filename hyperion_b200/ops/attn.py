@@ -47,8 +47,23 @@ def _flash_supported(q, k, v, dropout_p) -> bool:
     return q.dtype in (torch.float16, torch.bfloat16) and q.shape[-1] in (64, 128) and dropout_p == 0.0
 
 
+def attention_qkvpacked(qkv, causal=False, key_padding_mask=None, dropout_p=0.0, scale=None):
+    """Attention over the packed projection output ``qkv[B, S, 3, H, D]``; returns ``[B, H, S, D]``."""
+    import os
+
+    if (qkv.is_contiguous() and _flash_supported(qkv, qkv, qkv, dropout_p) and qkv.data_ptr() % 16 == 0
+            and os.environ.get("HYPERION_ATTN", "flash") == "flash"):
+        from .flash import flash_attention_qkvpacked
+
+        return flash_attention_qkvpacked(qkv, causal=causal, key_padding_mask=key_padding_mask, scale=scale)
+    q, k, v = (qkv[:, :, i].permute(0, 2, 1, 3) for i in range(3))
+    return attention(q, k, v, causal, key_padding_mask, dropout_p, scale)
+
+
 def attention(q, k, v, causal=False, key_padding_mask=None, dropout_p=0.0, scale=None):
-    if _flash_supported(q, k, v, dropout_p):
+    import os
+
+    if _flash_supported(q, k, v, dropout_p) and os.environ.get("HYPERION_ATTN", "flash") == "flash":
         from .flash import flash_attention
 
         return flash_attention(q, k, v, causal=causal, key_padding_mask=key_padding_mask, scale=scale)

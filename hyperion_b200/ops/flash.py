@@ -85,3 +85,41 @@ class _FlashFn(torch.autograd.Function):
 def flash_attention(q, k, v, causal: bool = False, key_padding_mask=None, scale: float | None = None):
     scale = scale if scale is not None else 1.0 / math.sqrt(q.shape[-1])
     return _FlashFn.apply(q, k, v, causal, key_padding_mask, scale)
+
+
+class _FlashPackedFn(torch.autograd.Function):
+    """Attention over the packed projection output ``qkv[B, S, 3, H, D]``; the backward writes dq / dk / dv straight
+    into one ``[B, S, 3, H, D]`` gradient buffer (no per-slice zero-fill + copy + add in autograd)."""
+
+    @staticmethod
+    def forward(ctx, qkv, causal, key_padding_mask, scale):
+        q, k, v = (qkv[:, :, i].permute(0, 2, 1, 3) for i in range(3))
+        o, lse, (_, _, _, kpm) = flash_fwd(q, k, v, causal, key_padding_mask, scale)
+        ctx.save_for_backward(qkv, o, lse, kpm if kpm is not None else torch.empty(0, device=qkv.device))
+        ctx.causal, ctx.scale, ctx.has_kpm = causal, scale, kpm is not None
+        return o
+
+    @staticmethod
+    def backward(ctx, do):
+        qkv, o, lse, kpm = ctx.saved_tensors
+        kpm = kpm if ctx.has_kpm else None
+        _declare()
+        B, S, _, H, D = qkv.shape
+        q, k, v = (qkv[:, :, i].permute(0, 2, 1, 3) for i in range(3))
+        if not (do.stride(3) == 1 and _tma_ok(do)):
+            do = do.permute(0, 2, 1, 3).contiguous().permute(0, 2, 1, 3)
+        dqkv = torch.empty_like(qkv)
+        dk, dv = dqkv[:, :, 1].permute(0, 2, 1, 3), dqkv[:, :, 2].permute(0, 2, 1, 3)
+        dq_acc = torch.zeros((B, H, S, D), device=qkv.device, dtype=torch.float32)
+        delta = torch.empty((B, H, S), device=qkv.device, dtype=torch.float32)
+        call("hyp_flash_attn_bwd", ptr(q), ptr(k), ptr(v), ptr(o), ptr(do), ptr(lse), ptr(dq_acc), ptr(dk), ptr(dv),
+             ptr(delta), ptr(kpm), B, H, S, S, D, *_strides_bhs(q), *_strides_bhs(k), *_strides_bhs(v), *_strides_bhs(o),
+             *_strides_bhs(do), *_strides_bhs(dk), int(ctx.causal), float(ctx.scale), DT[qkv.dtype], stream_ptr())
+        dqkv[:, :, 0].copy_(dq_acc.permute(0, 2, 1, 3))
+        return dqkv, None, None, None
+
+
+def flash_attention_qkvpacked(qkv, causal: bool = False, key_padding_mask=None, scale: float | None = None):
+    """``qkv``: ``[B, S, 3, H, D]`` (contiguous).  Returns ``[B, H, S, D]`` (a view over ``[B, S, H, D]`` memory)."""
+    scale = scale if scale is not None else 1.0 / math.sqrt(qkv.shape[-1])
+    return _FlashPackedFn.apply(qkv, causal, key_padding_mask, scale)

@@ -470,3 +470,11 @@ def lora_linear(x, xd, w, b, A, B, scaling: float, residual=None):
         return _LoraLinearFn.apply(x, xd, w, b, A, B, scaling, residual)
     y = F.linear(x, w, b) + scaling * F.linear(F.linear(xd, A), B)
     return y if residual is None else y + residual
+
+
+def attention_qkvpacked(qkv, causal: bool = False, key_padding_mask=None, dropout_p: float = 0.0, scale: float | None = None):
+    """Attention over the packed projection output ``qkv[B, S, 3, H, D]`` -> ``[B, H, S, D]`` (no q/k/v copies; the
+    backward fills one packed gradient buffer)."""
+    from . import attn as _attn
+
+    return _attn.attention_qkvpacked(qkv, causal=causal, key_padding_mask=key_padding_mask, dropout_p=dropout_p, scale=scale)
