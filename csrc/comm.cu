@@ -36,7 +36,8 @@ namespace comm {
 constexpr int MAX_W = 8;
 constexpr int MAX_BLOCKS = 64;
 constexpr int THREADS = 512;
-constexpr int INF_WORD = MAX_BLOCKS * MAX_W;  // float word: 1.0 when any rank saw a non-finite gradient
+constexpr int BARRIER_SLOTS = 256 * MAX_W;     // per-block barrier slots; the all-gather-fused GEMM uses up to 148 blocks
+constexpr int INF_WORD = BARRIER_SLOTS;        // float word: 1.0 when any rank saw a non-finite gradient
 constexpr long long SPIN_LIMIT = 1ll << 31;   // ~ several seconds, then trap instead of hanging the GPU
 
 struct Peers {

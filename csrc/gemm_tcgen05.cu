@@ -18,6 +18,7 @@
 // the models (02_development/distributed_utils.py:75-88).
 #include "common/ptx.cuh"
 #include "common/util.cuh"
+#include <string.h>
 
 namespace hyp {
 namespace gemm {
@@ -27,6 +28,24 @@ constexpr int ROW_BYTES = 128;  // one swizzle row: 64 x 16-bit or 32 x fp32
 constexpr int A_STAGE = BM * ROW_BYTES;
 constexpr int NUM_THREADS = 320;  // warp0 TMA, warp1 MMA, warps2-9 epilogue (two warps per TMEM lane quarter)
 constexpr int GROUP_M = 8;
+
+// All-gather fusion (FSDP K-C3): the B operand (a weight) lives in a flat "unit" buffer whose W equal slices are
+// owned by W ranks.  Four extra warps per CTA pull every rank's slice from peer memory into the local unit buffer
+// while the GEMM runs; the TMA producer only waits for the slices that cover the B tile it is about to load, so
+// tiles whose weights are local (or have already landed) start immediately.
+struct AgParams {
+  int enabled, W, rank;
+  unsigned epoch;                 // cross-rank barrier epoch (uses epoch and epoch + 1)
+  const char* src[8];             // peer r's shard of this unit (already offset to the unit's shard)
+  uint32_t* peer_flags[8];        // symmetric flag regions (per-block barrier slots)
+  char* dst;                      // local unit buffer (W * per_bytes)
+  long long per_bytes;            // bytes of one rank's slice
+  long long b_off_bytes;          // offset of the B matrix inside the unit buffer
+  long long bias_off_bytes;       // offset of the bias inside the unit buffer, or -1
+  long long row_bytes;            // bytes of one B row (K * elem)
+  uint32_t* arrived;              // local uint32[W]: chunks of rank q copied so far (monotonic across launches)
+  unsigned target;                // value arrived[q] reaches when rank q's slice is complete for THIS launch
+};
 
 struct Params {
   int M, N, K;
@@ -49,6 +68,7 @@ struct Params {
   float alpha, beta;
   int vec_ok;  // D (and aux) rows are 16-byte aligned -> vector stores
   int simple;  // plain epilogue (alpha, optional 16-bit bias) -> branch-free fast path
+  AgParams ag;
 };
 
 template <int BN>
@@ -220,7 +240,7 @@ __device__ __forceinline__ void epilogue32(const Params& p, const uint32_t (&r)[
       const float4* b4 = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.bias) + col0);
 #pragma unroll
       for (int g = 0; g < 8; ++g) {
-        const float4 t = __ldg(b4 + g);
+        const float4 t = b4[g];
         v[4 * g] += t.x; v[4 * g + 1] += t.y; v[4 * g + 2] += t.z; v[4 * g + 3] += t.w;
       }
     } else {
@@ -228,7 +248,7 @@ __device__ __forceinline__ void epilogue32(const Params& p, const uint32_t (&r)[
 #pragma unroll
       for (int g = 0; g < 4; ++g) {
         float t[8];
-        const uint4 u = __ldg(b4 + g);
+        const uint4 u = b4[g];
         if (p.bias_dtype == DT_BF16) unpack8<__nv_bfloat16>(u, t); else unpack8<__half>(u, t);
 #pragma unroll
         for (int i = 0; i < 8; ++i) v[g * 8 + i] += t[i];
@@ -300,8 +320,36 @@ __device__ __forceinline__ void epilogue32(const Params& p, const uint32_t (&r)[
   }
 }
 
-template <int BN, int EPI, int ACT>
-__global__ void __launch_bounds__(NUM_THREADS, 1)
+constexpr int AG_THREADS = 128;     // 4 gather warps (warps 10-13) in the all-gather-fused variant
+constexpr int AG_CHUNK = 32768;     // bytes copied per work item
+constexpr long long AG_SPIN_LIMIT = 1ll << 31;
+
+__device__ __forceinline__ void ag_wait(const uint32_t* ctr, unsigned target) {
+  long long spins = 0;
+  unsigned v;
+  do {
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory");
+    if (++spins > AG_SPIN_LIMIT) { printf("hyperion gemm_ag: timed out waiting for a gathered slice\n"); __trap(); }
+  } while (static_cast<int>(v - target) < 0);
+}
+
+// Barrier between the gather warps of block b on every rank (same protocol as csrc/comm.cu).
+__device__ __forceinline__ void ag_rank_barrier(const AgParams& g, int tid, unsigned epoch) {
+  named_bar_sync(2, AG_THREADS);
+  if (tid < g.W) {
+    __threadfence_system();
+    st_release_sys(g.peer_flags[tid] + blockIdx.x * g.W + g.rank, epoch);
+    const uint32_t* mine = g.peer_flags[g.rank] + blockIdx.x * g.W + tid;
+    long long spins = 0;
+    while (static_cast<int32_t>(ld_acquire_sys(mine) - epoch) < 0) {
+      if (++spins > AG_SPIN_LIMIT) { printf("hyperion gemm_ag: rank %d timed out waiting for rank %d\n", g.rank, tid); __trap(); }
+    }
+  }
+  named_bar_sync(2, AG_THREADS);
+}
+
+template <int BN, int EPI, int ACT, bool AG = false>
+__global__ void __launch_bounds__(NUM_THREADS + (AG ? AG_THREADS : 0), 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
             const __grid_constant__ Params p) {
   using C = Cfg<BN>;
@@ -322,6 +370,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   const int tiles_m = (p.M + BM - 1) / BM;
   const int tiles_n = (p.N + BN - 1) / BN;
   const int total = tiles_m * tiles_n * p.splits;
+  int ag_rot = 0;
+  if (AG && p.ag.enabled) {
+    const long long first = static_cast<long long>(p.ag.rank) * p.ag.per_bytes - p.ag.b_off_bytes;
+    if (first > 0) ag_rot = static_cast<int>(min(static_cast<long long>(tiles_n - 1), first / (p.ag.row_bytes * BN)));
+  }
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
@@ -353,7 +406,18 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < total; tile += gridDim.x) {
-        const TileCoord tc = decode_tile(tile, tiles_m, tiles_n, nkb, p.splits);
+        TileCoord tc = decode_tile(tile, tiles_m, tiles_n, nkb, p.splits);
+        if (AG && p.ag.enabled) {
+          // rotate the column-block order so this rank's own rows come first, then wait for the slices
+          // (one counter per owner rank) that cover rows [n0, n0 + BN) of the weight
+          tc.n_blk = (tc.n_blk + ag_rot) % tiles_n;
+          const long long lo = p.ag.b_off_bytes + static_cast<long long>(tc.n_blk) * BN * p.ag.row_bytes;
+          long long hi = p.ag.b_off_bytes + static_cast<long long>(min(p.N, (tc.n_blk + 1) * BN)) * p.ag.row_bytes;
+          const int q_lo = static_cast<int>(lo / p.ag.per_bytes);
+          const int q_hi = static_cast<int>((hi - 1) / p.ag.per_bytes);
+          for (int q = q_lo; q <= q_hi && q < p.ag.W; ++q) ag_wait(p.ag.arrived + q, p.ag.target);
+          asm volatile("fence.proxy.async.global;" ::: "memory");
+        }
         for (int kb = tc.kb0; kb < tc.kb1; ++kb) {
           mbar_wait(&empty[stage], phase ^ 1);
           mbar_expect_tx(&full[stage], A_STAGE + C::B_STAGE);
@@ -388,7 +452,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       const uint32_t a_lbo = p.a_mn ? epr * ROW_BYTES : 16u;
       const uint32_t b_lbo = p.b_mn ? epr * ROW_BYTES : 16u;
       for (int tile = blockIdx.x; tile < total; tile += gridDim.x) {
-        const TileCoord tc = decode_tile(tile, tiles_m, tiles_n, nkb, p.splits);
+        const TileCoord tc = decode_tile(tile, tiles_m, tiles_n, nkb, p.splits);  // n_blk unused here
         mbar_wait(&tempty[acc], acc_phase ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * BN;
@@ -413,14 +477,54 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         if (acc == 0) acc_phase ^= 1;
       }
     }
+  } else if (AG && warp >= NUM_THREADS / 32) {
+    // ----------------------------------------------------------- all-gather warps (K-C3)
+    if (p.ag.enabled) {
+      const AgParams& g = p.ag;
+      const int tid = threadIdx.x - NUM_THREADS;
+      ag_rank_barrier(g, tid, g.epoch);  // every rank's shard holds this step's parameters
+      const long long nch = (g.per_bytes + AG_CHUNK - 1) / AG_CHUNK;
+      for (int pi = 0; pi < g.W; ++pi) {
+        const int q = (g.rank + pi) % g.W;
+        const char* src = g.src[q];
+        char* dst = g.dst + static_cast<long long>(q) * g.per_bytes;
+        for (long long c = blockIdx.x; c < nch; c += gridDim.x) {
+          const long long b0 = c * AG_CHUNK;
+          const long long nvec = (min(static_cast<long long>(AG_CHUNK), g.per_bytes - b0)) / 16;
+          long long i = tid;
+          for (; i + 3 * AG_THREADS < nvec; i += 4 * AG_THREADS) {
+            const uint4 a0 = ld_volatile_v4(src + b0 + i * 16), a1 = ld_volatile_v4(src + b0 + (i + AG_THREADS) * 16),
+                        a2 = ld_volatile_v4(src + b0 + (i + 2 * AG_THREADS) * 16), a3 = ld_volatile_v4(src + b0 + (i + 3 * AG_THREADS) * 16);
+            *reinterpret_cast<uint4*>(dst + b0 + i * 16) = a0;
+            *reinterpret_cast<uint4*>(dst + b0 + (i + AG_THREADS) * 16) = a1;
+            *reinterpret_cast<uint4*>(dst + b0 + (i + 2 * AG_THREADS) * 16) = a2;
+            *reinterpret_cast<uint4*>(dst + b0 + (i + 3 * AG_THREADS) * 16) = a3;
+          }
+          for (; i < nvec; i += AG_THREADS) *reinterpret_cast<uint4*>(dst + b0 + i * 16) = ld_volatile_v4(src + b0 + i * 16);
+          named_bar_sync(2, AG_THREADS);
+          if (tid == 0) {
+            __threadfence();
+            atomicAdd(g.arrived + q, 1u);
+          }
+        }
+      }
+      ag_rank_barrier(g, tid, g.epoch + 1);  // peers are done reading my shard
+    }
   } else {
     // ----------------------------------------------------------- epilogue
     const int quarter = warp & 3;  // TMEM lanes [32q, 32q+32) are visible to this warp
     const int chalf = (warp - 2) >> 2;  // which half of the tile's column chunks this warp drains
     int acc = 0;
     uint32_t acc_phase = 0;
+    if (AG && p.ag.enabled && p.bias && p.ag.bias_off_bytes >= 0) {
+      // the bias read in this epilogue lives in the same unit: wait for its owner slice(s)
+      const long long hi = p.ag.bias_off_bytes + static_cast<long long>(p.N) * (p.bias_dtype == DT_F32 ? 4 : 2) - 1;
+      for (int q = static_cast<int>(p.ag.bias_off_bytes / p.ag.per_bytes); q <= static_cast<int>(hi / p.ag.per_bytes) && q < p.ag.W; ++q)
+        ag_wait(p.ag.arrived + q, p.ag.target);
+    }
     for (int tile = blockIdx.x; tile < total; tile += gridDim.x) {
-      const TileCoord tc = decode_tile(tile, tiles_m, tiles_n, nkb, p.splits);
+      TileCoord tc = decode_tile(tile, tiles_m, tiles_n, nkb, p.splits);
+      if (AG && p.ag.enabled) tc.n_blk = (tc.n_blk + ag_rot) % tiles_n;
       mbar_wait(&tfull[acc], acc_phase);
       tc_fence_after();
       const int row = tc.m_blk * BM + quarter * 32 + lane;
@@ -496,21 +600,38 @@ int make_tmap_2d(CUtensorMap* tm, const void* ptr, int dtype, long long inner, l
   return 0;
 }
 
-template <int BN, int EPI, int ACT>
+template <int BN, int EPI, int ACT, bool AG = false>
 static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const Params& p, cudaStream_t stream) {
   using C = Cfg<BN>;
   static bool attr_set[64] = {false};
   int dev = 0;
   cudaGetDevice(&dev);
   if (!attr_set[dev & 63]) {
-    HYP_CHECK_CUDA(cudaFuncSetAttribute(gemm_kernel<BN, EPI, ACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
+    HYP_CHECK_CUDA(cudaFuncSetAttribute(gemm_kernel<BN, EPI, ACT, AG>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
     attr_set[dev & 63] = true;
   }
   const int tiles = ((p.M + BM - 1) / BM) * ((p.N + BN - 1) / BN) * p.splits;
-  const int grid = tiles < num_sms() ? tiles : num_sms();
-  gemm_kernel<BN, EPI, ACT><<<grid, NUM_THREADS, C::SMEM_BYTES, stream>>>(ta, tb, p);
+  int grid = tiles < num_sms() ? tiles : num_sms();
+  if (AG) grid = num_sms();  // the same grid on every rank: gather warps pair up with their peer blocks
+  gemm_kernel<BN, EPI, ACT, AG><<<grid, NUM_THREADS + (AG ? AG_THREADS : 0), C::SMEM_BYTES, stream>>>(ta, tb, p);
   HYP_CHECK_CUDA(cudaGetLastError());
   return 0;
+}
+
+template <int BN>
+static int dispatch_ag(const CUtensorMap& ta, const CUtensorMap& tb, const Params& p, int epi, cudaStream_t st) {
+  if (epi == 0) return launch<BN, 0, 0, true>(ta, tb, p, st);
+  if (epi == 1) {
+    switch (p.act) {
+      case 0: return launch<BN, 1, 0, true>(ta, tb, p, st);
+      case 1: return launch<BN, 1, 1, true>(ta, tb, p, st);
+      case 2: return launch<BN, 1, 2, true>(ta, tb, p, st);
+      case 3: return launch<BN, 1, 3, true>(ta, tb, p, st);
+      default: return launch<BN, 1, 4, true>(ta, tb, p, st);
+    }
+  }
+  set_error("hyp_gemm_ag: the all-gather fusion supports the forward epilogues only (plain / bias / activation / residual)");
+  return -1;
 }
 
 // epilogue kind -> kernel instantiation
@@ -546,10 +667,10 @@ static int dispatch(const CUtensorMap& ta, const CUtensorMap& tb, const Params& 
 using namespace hyp;
 
 // See include/hyperion_b200.h for the contract.
-HYP_API int hyp_gemm(const void* A, const void* B, void* D, int M, int N, int K, long long lda, long long ldb,
+static int gemm_impl(const void* A, const void* B, void* D, int M, int N, int K, long long lda, long long ldb,
                      long long ldd, int in_dtype, int out_dtype, int a_mn_major, int b_mn_major, const void* bias,
                      int bias_dtype, const void* aux, long long ld_aux, int aux_dtype, void* preact_out, int act, int mode,
-                     float alpha, float beta, int splits, void* stream_) {
+                     float alpha, float beta, int splits, const gemm::AgParams* ag, void* stream_) {
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
   HYP_REQUIRE(M > 0 && N > 0 && K > 0, "hyp_gemm: empty problem %dx%dx%d", M, N, K);
   HYP_REQUIRE(in_dtype >= 0 && in_dtype <= 2 && out_dtype >= 0 && out_dtype <= 2, "hyp_gemm: bad dtype");
@@ -584,6 +705,8 @@ HYP_API int hyp_gemm(const void* A, const void* B, void* D, int M, int N, int K,
     vec = vec && (reinterpret_cast<uintptr_t>(aux) % 16 == 0) && ((ld_aux * aes) % 16 == 0);
   }
   p.vec_ok = vec ? 1 : 0;
+  memset(&p.ag, 0, sizeof(p.ag));
+  if (ag) p.ag = *ag;
   // pick the compile-time epilogue: 0 plain, 1 bias/act/residual/preact, 2 act', 3 general (split-K, beta, unaligned)
   const bool fast = vec && p.splits == 1 && beta == 0.f && (!bias || reinterpret_cast<uintptr_t>(bias) % 16 == 0) &&
                     (!aux || aux_dtype != DT_F32) && (!preact_out || out_dtype != DT_F32);
@@ -603,5 +726,53 @@ HYP_API int hyp_gemm(const void* A, const void* B, void* D, int M, int N, int K,
   if (!b_mn_major) rc = gemm::make_tmap_2d(&tb, B, in_dtype, K, N, ldb, epr, BN);         // B: [N, K]
   else             rc = gemm::make_tmap_2d(&tb, B, in_dtype, N, K, ldb, epr, epr);        // B^T: [K, N]
   if (rc) return rc;
+  if (ag) {
+    HYP_REQUIRE(!b_mn_major && splits <= 1, "hyp_gemm_ag: B must be the [N, K] weight layout and split-K is not supported");
+    return (BN == 256) ? gemm::dispatch_ag<256>(ta, tb, p, epi, stream) : gemm::dispatch_ag<128>(ta, tb, p, epi, stream);
+  }
   return (BN == 256) ? gemm::dispatch<256>(ta, tb, p, epi, stream) : gemm::dispatch<128>(ta, tb, p, epi, stream);
+}
+
+HYP_API int hyp_gemm(const void* A, const void* B, void* D, int M, int N, int K, long long lda, long long ldb,
+                     long long ldd, int in_dtype, int out_dtype, int a_mn_major, int b_mn_major, const void* bias,
+                     int bias_dtype, const void* aux, long long ld_aux, int aux_dtype, void* preact_out, int act, int mode,
+                     float alpha, float beta, int splits, void* stream_) {
+  return gemm_impl(A, B, D, M, N, K, lda, ldb, ldd, in_dtype, out_dtype, a_mn_major, b_mn_major, bias, bias_dtype, aux,
+                   ld_aux, aux_dtype, preact_out, act, mode, alpha, beta, splits, nullptr, stream_);
+}
+
+// K-C3: D = epilogue(A . B^T) where B (and the optional bias) live in a flat FSDP unit buffer `unit_dst` of W equal
+// slices; slice q is pulled from peer_src[q] (peer q's shard, mapped through NVLink) by gather warps inside the same
+// kernel, and the GEMM consumes tiles as their weights land.  peer_src / peer_flags: HOST arrays of W device addresses.
+// `arrived`: device uint32[W], zero at creation, never reset; `target` = launches so far (incl. this one) * number of
+// 32 KiB chunks per slice.  Every rank must launch this with the same shapes and epoch (uses epoch, epoch + 1).
+HYP_API int hyp_gemm_ag(const void* A, const void* B, void* D, int M, int N, int K, long long lda, long long ldb,
+                        long long ldd, int in_dtype, int out_dtype, const void* bias, int bias_dtype, const void* aux,
+                        long long ld_aux, int aux_dtype, void* preact_out, int act, float alpha,
+                        const long long* peer_src, const long long* peer_flags, int rank, int W, unsigned epoch,
+                        void* unit_dst, long long per_bytes, unsigned* arrived, unsigned target, void* stream_) {
+  HYP_REQUIRE(W >= 1 && W <= 8, "hyp_gemm_ag: world size %d not in [1, 8]", W);
+  HYP_REQUIRE(per_bytes > 0 && per_bytes % 16 == 0, "hyp_gemm_ag: slice size must be a positive multiple of 16 bytes");
+  gemm::AgParams g;
+  memset(&g, 0, sizeof(g));
+  g.enabled = 1; g.W = W; g.rank = rank; g.epoch = epoch;
+  for (int i = 0; i < W; ++i) {
+    g.src[i] = reinterpret_cast<const char*>(peer_src[i]);
+    g.peer_flags[i] = reinterpret_cast<uint32_t*>(peer_flags[i]);
+  }
+  g.dst = static_cast<char*>(unit_dst);
+  g.per_bytes = per_bytes;
+  const long long unit_bytes = per_bytes * W;
+  const long long b_off = static_cast<const char*>(B) - static_cast<const char*>(unit_dst);
+  HYP_REQUIRE(b_off >= 0 && b_off < unit_bytes, "hyp_gemm_ag: B does not live inside the unit buffer");
+  g.b_off_bytes = b_off;
+  g.row_bytes = ldb * (in_dtype == DT_F32 ? 4 : 2);
+  g.bias_off_bytes = -1;
+  if (bias) {
+    const long long o = static_cast<const char*>(bias) - static_cast<const char*>(unit_dst);
+    if (o >= 0 && o < unit_bytes) g.bias_off_bytes = o;
+  }
+  g.arrived = arrived; g.target = target;
+  return gemm_impl(A, B, D, M, N, K, lda, ldb, ldd, in_dtype, out_dtype, 0, 0, bias, bias_dtype, aux, ld_aux, aux_dtype,
+                   preact_out, act, 0, alpha, 0.f, 1, &g, stream_);
 }

@@ -128,6 +128,36 @@ def run(bench: bool = False, out_json: str | None = None) -> int:
     check("allgather", torch.equal(dst, torch.cat(ref_list)))
     check("allgather_flags", bool((flags > 0).all()))
 
+    # ---- K-C3 fused: all-gather inside the consumer GEMM vs (NCCL all-gather, then matmul)
+    torch.manual_seed(99)  # identical on every rank
+    Nw, Kw, Mx = 1536, 1024, 2048
+    unit_elems = ((Nw * Kw + Nw + world * 128 - 1) // (world * 128)) * (world * 128)
+    per_u = unit_elems // world
+    full_ref = torch.zeros(unit_elems, device=dev, dtype=torch.bfloat16)
+    full_ref[:Nw * Kw + Nw].copy_((torch.randn(Nw * Kw + Nw, device=dev) * 0.05).to(torch.bfloat16))
+    shard16[:per_u].copy_(full_ref[rank * per_u:(rank + 1) * per_u])
+    unit_local = torch.zeros(unit_elems, device=dev, dtype=torch.bfloat16)   # stale local copy, filled by the kernel
+    w_view = unit_local[:Nw * Kw].view(Nw, Kw)
+    b_view = unit_local[Nw * Kw:Nw * Kw + Nw]
+    torch.manual_seed(100 + rank)
+    x2 = torch.randn(Mx, Kw, device=dev, dtype=torch.bfloat16)
+    out = torch.empty(Mx, Nw, device=dev, dtype=torch.bfloat16)
+    arrived = torch.zeros(world, device=dev, dtype=torch.int32)
+    nch = (per_u * 2 + 32767) // 32768
+    torch.cuda.synchronize()
+    dist.barrier()
+    for gen in (1, 2):  # twice: the arrival counters are monotonic across launches
+        if gen == 2:
+            unit_local.zero_()
+        arena.gemm_allgather(x2, w_view, out, shard_buf=shard16, shard_start=0, per_elems=per_u, unit_dst=unit_local,
+                             arrived=arrived, target=gen * nch, bias=b_view, act="gelu_tanh")
+        torch.cuda.synchronize()
+        ref = torch.nn.functional.gelu(x2.float() @ full_ref[:Nw * Kw].view(Nw, Kw).float().t() + full_ref[Nw * Kw:Nw * Kw + Nw].float(),
+                                       approximate="tanh")
+        check(f"gemm_allgather[{gen}]", _rel(out, ref) < 2e-2, _rel(out, ref))
+        check(f"gemm_allgather_unit[{gen}]", torch.equal(unit_local, full_ref))
+        dist.barrier()
+
     # ---- bandwidth (device-timed, max over ranks)
     if bench:
         from hyperion_b200.parallel.runtime import max_over_ranks

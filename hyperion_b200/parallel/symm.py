@@ -42,6 +42,7 @@ def _declare():
     _lib.declare("hyp_comm_allreduce", "pplii" + "lli" + "i" + "pf" + "ip")
     _lib.declare("hyp_comm_reduce_scatter", "pplii" + "lli" + "i" + "f" + "pp" + "i" + "pppp" + "i" + "fffff" + "i" + "ip")
     _lib.declare("hyp_comm_allgather", "ppii" + "ll" + "p" + "i" + "p" + "ip")
+    _lib.declare("hyp_gemm_ag", "ppp" + "iii" + "lll" + "ii" + "pi" + "pli" + "p" + "if" + "pp" + "iii" + "pl" + "pi" + "p")
     _lib.declare("hyp_ipc_alloc", "lpp")
     _lib.declare("hyp_ipc_open", "pp")
     _lib.declare("hyp_ipc_close", "l")
@@ -229,6 +230,26 @@ class SymmetricArena:
         _lib.call("hyp_comm_allgather", ctypes.addressof(sb.c_ptrs()), ctypes.addressof(self._flags_sb.c_ptrs()),
                   self.rank, self.world_size, off + shard_start * es, per_elems * es, _lib.ptr(dst), self._next_epoch(),
                   _lib.ptr(chunk_flags), self.max_blocks, _lib.stream_ptr(self.device))
+
+    def gemm_allgather(self, x2: torch.Tensor, w: torch.Tensor, out: torch.Tensor, *, shard_buf: torch.Tensor,
+                       shard_start: int, per_elems: int, unit_dst: torch.Tensor, arrived: torch.Tensor, target: int,
+                       bias=None, aux=None, act=None, preact_out=None, alpha: float = 1.0) -> None:
+        """K-C3 fused: ``out = epilogue(x2 @ w.T)`` where ``w`` (and ``bias``) are views into ``unit_dst`` (the local,
+        full-size unit buffer) whose W slices are pulled from every rank's ``shard_buf[shard_start:+per_elems]``
+        by gather warps inside the GEMM kernel."""
+        from ..ops.native import ACT, _ld
+
+        sb, off = self.lookup(shard_buf)
+        es = shard_buf.element_size()
+        srcs = (ctypes.c_longlong * self.world_size)(*[p + off + shard_start * es for p in sb.peer_ptrs])
+        M, K = x2.shape
+        N = w.shape[0]
+        _lib.call("hyp_gemm_ag", _lib.ptr(x2), _lib.ptr(w), _lib.ptr(out), M, N, K, _ld(x2), _ld(w), _ld(out), DT[x2.dtype],
+                  DT[out.dtype], _lib.ptr(bias), DT[bias.dtype] if bias is not None else 0, _lib.ptr(aux),
+                  _ld(aux) if aux is not None else 0, DT[aux.dtype] if aux is not None else 0, _lib.ptr(preact_out), ACT[act],
+                  float(alpha), ctypes.addressof(srcs), ctypes.addressof(self._flags_sb.c_ptrs()), self.rank, self.world_size,
+                  self._next_epoch(), _lib.ptr(unit_dst), per_elems * es, _lib.ptr(arrived), int(target),
+                  _lib.stream_ptr(self.device))
 
     def close(self) -> None:
         torch.cuda.synchronize(self.device)
