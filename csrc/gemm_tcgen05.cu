@@ -338,8 +338,9 @@ __device__ __forceinline__ void ag_rank_barrier(const AgParams& g, int tid, unsi
   named_bar_sync(2, AG_THREADS);
   if (tid < g.W) {
     __threadfence_system();
-    st_release_sys(g.peer_flags[tid] + blockIdx.x * g.W + g.rank, epoch);
-    const uint32_t* mine = g.peer_flags[g.rank] + blockIdx.x * g.W + tid;
+    // slots [64*W, ...) : disjoint from the ones csrc/comm.cu kernels (<= 64 blocks) use on the communication stream
+    st_release_sys(g.peer_flags[tid] + (64 + blockIdx.x) * g.W + g.rank, epoch);
+    const uint32_t* mine = g.peer_flags[g.rank] + (64 + blockIdx.x) * g.W + tid;
     long long spins = 0;
     while (static_cast<int32_t>(ld_acquire_sys(mine) - epoch) < 0) {
       if (++spins > AG_SPIN_LIMIT) { printf("hyperion gemm_ag: rank %d timed out waiting for rank %d\n", g.rank, tid); __trap(); }

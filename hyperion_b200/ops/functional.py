@@ -95,14 +95,17 @@ class _LinearFn(torch.autograd.Function):
     """y = act(x @ W^T + b) (+ residual) on gemm_tcgen05; dgrad / wgrad use the MN-major operand paths."""
 
     @staticmethod
-    def forward(ctx, x, w, b, residual, act):
+    def forward(ctx, x, w, b, residual, act, ag=None):
         x2 = _as2d(x)
         w2 = _as2d(w)
         M, N = x2.shape[0], w2.shape[0]
         out = _padded_empty(M, N, x.dtype, x.device)
         res2 = _as2d(residual) if residual is not None else None
         pre = _padded_empty(M, N, x.dtype, x.device) if act not in (None, "none", "relu") else None
-        native.gemm(x2, w2, out=out, bias=b, aux=res2, act=act, preact_out=pre)
+        if ag is not None and ag.pending:
+            ag.run(x2, w2, out, bias=b, aux=res2, act=act, preact_out=pre)  # K-C3: the unit is gathered inside this GEMM
+        else:
+            native.gemm(x2, w2, out=out, bias=b, aux=res2, act=act, preact_out=pre)
         ctx.act = act
         ctx.has_bias = b is not None
         ctx.has_res = residual is not None
@@ -136,7 +139,7 @@ class _LinearFn(torch.autograd.Function):
             db = native.colsum(dh).to(dy.dtype)
         if ctx.has_res and ctx.needs_input_grad[3]:
             dres = dy
-        return dx, dw, db, dres, None
+        return dx, dw, db, dres, None, None
 
 
 def _dact_mul(dy2, h, act):
@@ -161,7 +164,7 @@ def _dact_mul(dy2, h, act):
 def linear(x, w, b=None, act: str | None = None, residual=None):
     """``act(x @ w.T + b) + residual`` with the bias / activation / residual fused into the GEMM epilogue."""
     if _native(x, w) and x.shape[-1] % (16 // x.element_size()) == 0:
-        return _LinearFn.apply(x, w, b, residual, act)
+        return _LinearFn.apply(x, w, b, residual, act, getattr(w, "_hyp_ag", None))
     y = _act_ref(F.linear(x, w, b), act)
     return y if residual is None else y + residual
 
@@ -171,14 +174,21 @@ class _MlpFn(torch.autograd.Function):
     """y = act(x W1^T + b1) W2^T + b2 (+ residual); backward fuses act' into the dgrad GEMM epilogue."""
 
     @staticmethod
-    def forward(ctx, x, w1, b1, w2, b2, residual, act):
+    def forward(ctx, x, w1, b1, w2, b2, residual, act, ag1=None, ag2=None):
         x2 = _as2d(x)
         M = x2.shape[0]
         h = torch.empty((M, w1.shape[0]), dtype=x.dtype, device=x.device)
         a = torch.empty_like(h)
-        native.gemm(x2, w1, out=a, bias=b1, act=act, preact_out=h)
+        if ag1 is not None and ag1.pending:
+            ag1.run(x2, w1, a, bias=b1, act=act, preact_out=h)
+        else:
+            native.gemm(x2, w1, out=a, bias=b1, act=act, preact_out=h)
         y = torch.empty((M, w2.shape[0]), dtype=x.dtype, device=x.device)
-        native.gemm(a, w2, out=y, bias=b2, aux=_as2d(residual) if residual is not None else None)
+        res2 = _as2d(residual) if residual is not None else None
+        if ag2 is not None and ag2.pending:
+            ag2.run(a, w2, y, bias=b2, aux=res2)
+        else:
+            native.gemm(a, w2, out=y, bias=b2, aux=res2)
         ctx.save_for_backward(x2, w1, w2, h, a)
         ctx.act = act
         ctx.flags = (b1 is not None, b2 is not None, residual is not None)
@@ -197,14 +207,14 @@ class _MlpFn(torch.autograd.Function):
         dx = native.gemm(dh, w1, b_mn_major=True).reshape(ctx.x_shape) if ctx.needs_input_grad[0] else None
         db1 = native.colsum(dh).to(dy.dtype) if has_b1 else None
         db2 = native.colsum(dy2).to(dy.dtype) if has_b2 else None
-        return dx, dw1, db1, dw2, db2, (dy if has_res else None), None
+        return dx, dw1, db1, dw2, db2, (dy if has_res else None), None, None, None
 
 
 def mlp(x, w1, b1, w2, b2, act: str = "relu", residual=None):
     """Two-layer feed-forward block (the FFN of every transformer in the model zoo)."""
     es = x.element_size()
     if _native(x, w1) and x.shape[-1] % (16 // es) == 0 and w1.shape[0] % (16 // es) == 0 and w2.shape[0] % (16 // es) == 0:
-        return _MlpFn.apply(x, w1, b1, w2, b2, residual, act)
+        return _MlpFn.apply(x, w1, b1, w2, b2, residual, act, getattr(w1, "_hyp_ag", None), getattr(w2, "_hyp_ag", None))
     y = F.linear(_act_ref(F.linear(x, w1, b1), act), w2, b2)
     return y if residual is None else y + residual
 
@@ -294,10 +304,14 @@ class _LinearCEFn(torch.autograd.Function):
         dx = torch.empty_like(x2)
         dw = torch.zeros((V, K), device=dev, dtype=torch.float32)
         db = torch.zeros(V, device=dev, dtype=torch.float32) if b is not None else None
+        ag = getattr(w, "_hyp_ag", None)
         for r0 in range(0, M, chunk_rows):
             r1 = min(M, r0 + chunk_rows)
             logits = _padded_empty(r1 - r0, V, x.dtype, dev)
-            native.gemm(x2[r0:r1], w2, out=logits, bias=b)
+            if ag is not None and ag.pending:
+                ag.run(x2[r0:r1], w2, logits, bias=b)  # first chunk gathers the head's unit inside its GEMM
+            else:
+                native.gemm(x2[r0:r1], w2, out=logits, bias=b)
             native.ce_fwd_bwd(logits, tgt[r0:r1], ignore_index, sum_count, gscale_ptr=inv_cnt, n_classes=V)
             native.gemm(logits, w2, b_mn_major=True, out=dx[r0:r1])
             native.gemm(logits, x2[r0:r1], a_mn_major=True, b_mn_major=True, out=dw, beta=1.0)

@@ -52,11 +52,34 @@ def class_based_units(module: nn.Module, cls) -> list[nn.Module]:
     return [m for m in module.modules() if isinstance(m, cls)]
 
 
+class _AgHandle:
+    """Attached to the first-consumed weight of a GEMM-first unit (``weight._hyp_ag``): while ``pending`` the
+    unit's parameters are stale locally, and the next GEMM on that weight gathers the whole unit from the peers'
+    shards *inside* the GEMM kernel (K-C3, ``hyp_gemm_ag``)."""
+
+    def __init__(self, fsdp: "HyperionFSDP", ui: int):
+        self.fsdp, self.ui = fsdp, ui
+        self.pending = False
+        self.gen = 0
+        self.arrived = torch.zeros(fsdp.world_size, device=fsdp.device, dtype=torch.int32)
+
+    def run(self, x2, w2, out, bias=None, aux=None, act=None, preact_out=None) -> None:
+        f = self.fsdp
+        s, e, _ = f.units[self.ui]
+        a, b = f._shard_range(self.ui)
+        self.gen += 1
+        nch = ((b - a) * f.shard16.element_size() + 32767) // 32768
+        f.arena.gemm_allgather(x2, w2, out, shard_buf=f.shard16, shard_start=a, per_elems=b - a,
+                               unit_dst=f.flat.data[s:e], arrived=self.arrived, target=self.gen * nch, bias=bias,
+                               aux=aux, act=act, preact_out=preact_out)
+        self.pending = False
+
+
 class HyperionFSDP(nn.Module):
     def __init__(self, module: nn.Module, units: list[nn.Module] | None = None, min_num_params: int = 100_000,
                  lr: float = 1e-4, betas=(0.9, 0.999), eps: float = 1e-8, weight_decay: float = 0.01,
                  max_norm: float = 0.0, fused: bool | None = None, process_group=None, loss_scaler=None,
-                 sync_params: bool = True):
+                 sync_params: bool = True, fuse_allgather_gemm: bool = True):
         super().__init__()
         self.module = module
         self.rank, self.world_size = world()
@@ -131,6 +154,23 @@ class HyperionFSDP(nn.Module):
             sp.param.register_post_accumulate_grad_hook(self._make_grad_hook(i))
         for k, um in enumerate(unit_modules):
             um.register_forward_pre_hook(self._make_fwd_hook(k))
+        # ---- K-C3: units whose first consumer is a GEMM on a known weight gather inside that GEMM
+        self._ag_handles: dict[int, _AgHandle] = {}
+        if self.fused and fuse_allgather_gemm and self.flat.dtype in (torch.bfloat16, torch.float16):
+            from ..models.transformer import MultiheadSelfAttention
+
+            flat_ids = {id(sp.param) for sp in self.flat.specs}
+            for k, um in enumerate(unit_modules):
+                target = None
+                if isinstance(um, nn.Linear):
+                    target = um.weight
+                elif isinstance(um, MultiheadSelfAttention):
+                    target = um.in_proj_weight
+                uis = self._key_to_units.get(k, [])
+                if target is not None and id(target) in flat_ids and len(uis) == 1 and target.shape[1] % 8 == 0:
+                    h = _AgHandle(self, uis[0])
+                    target._hyp_ag = h
+                    self._ag_handles[uis[0]] = h
 
     # ------------------------------------------------------------------ shard <-> flat index helpers
     def _shard_range(self, ui: int) -> tuple[int, int]:
@@ -317,6 +357,10 @@ class HyperionFSDP(nn.Module):
             self.comm_stream.wait_event(ev)
             with torch.cuda.stream(self.comm_stream):
                 for ui in order:
+                    if ui in self._ag_handles:  # gathered later, inside the unit's first GEMM (K-C3)
+                        self._ag_handles[ui].pending = True
+                        self._gather_events[ui] = None
+                        continue
                     s, e, _ = self.units[ui]
                     a, b = self._shard_range(ui)
                     self.arena.allgather(self.shard16, a, b - a, self.flat.data[s:e])

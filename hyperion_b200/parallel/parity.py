@@ -30,6 +30,8 @@ def run(strategy: str, precision: str, steps: int) -> int:
         eng = build_engine(model, strategy=strategy, precision=precision, lr=1e-3, clip=1.0 if strategy == "fsdp" else 0.0,
                            device=dev, fused_comm=fused)
         assert getattr(eng.model, "fused", None) == fused, "requested comm path was not taken"
+        if strategy == "fsdp" and fused:
+            assert len(eng.model._ag_handles) > 0, "no unit uses the all-gather-fused GEMM"
         losses = []
         for s in range(steps):
             b = data[s, rank]
