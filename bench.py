@@ -84,7 +84,7 @@ def main() -> int:
                      fused_comm=args.fused_comm)
 
     graphed = False
-    if args.graph and world == 1:
+    if args.graph:
         graphed = case.enable_graph()
     case.config["cuda_graph"] = graphed
 

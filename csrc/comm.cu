@@ -131,8 +131,9 @@ __device__ __forceinline__ void raise_inf(const Peers& P, int W) {
 // In-place average of buf[off_bytes : off_bytes + n*sizeof(T)] across ranks.
 template <typename T>
 __global__ void __launch_bounds__(THREADS, 1)
-allreduce_kernel(Peers P, char* mc, int rank, int W, long long off_bytes, long long n, uint32_t epoch,
-                 const float* __restrict__ inv_scale, float extra_scale) {
+allreduce_kernel(Peers P, char* mc, int rank, int W, long long off_bytes, long long n, uint32_t epoch_arg,
+                 const uint32_t* __restrict__ epoch_base, const float* __restrict__ inv_scale, float extra_scale) {
+  const uint32_t epoch = epoch_arg + (epoch_base ? *epoch_base : 0u);
   constexpr int N = Vec<T>::N;
   const long long nvec = (n + N - 1) / N;                 // region is padded to 16 bytes by the caller
   const long long per = (nvec + W - 1) / W;               // vectors per rank slice
@@ -198,6 +199,7 @@ struct AdamShard {
   float* v;
   void* p16;      // 16-bit parameter shard written for the next all-gather (may be null)
   float lr, beta1, beta2, eps, weight_decay, bias_c1, bias_c2;
+  const float* step_ptr;  // device step count (CUDA-graph safe) or null
 };
 
 // Rank r reduces slice r of the gradient region across ranks (average).
@@ -205,15 +207,23 @@ struct AdamShard {
 //   fused_adam = 0: write the fp32 reduced shard to `gshard` and add its sum of squares to sumsq[0]
 template <typename T, typename TP>
 __global__ void __launch_bounds__(THREADS, 1)
-reduce_scatter_kernel(Peers P, char* mc, int rank, int W, long long off_bytes, long long per_vec, uint32_t epoch,
-                      float scale, float* __restrict__ gshard, float* __restrict__ sumsq, int fused_adam, AdamShard A) {
+reduce_scatter_kernel(Peers P, char* mc, int rank, int W, long long off_bytes, long long per_vec, uint32_t epoch_arg,
+                      const uint32_t* __restrict__ epoch_base, float scale, float* __restrict__ gshard,
+                      float* __restrict__ sumsq, int fused_adam, AdamShard A) {
+  const uint32_t epoch = epoch_arg + (epoch_base ? *epoch_base : 0u);
   constexpr int N = Vec<T>::N;
   __shared__ float red[32];
   block_barrier(P, rank, W, epoch);
   float ss = 0.f;
   bool bad = false;
-  const float step_size = A.lr / A.bias_c1;
-  const float inv_sqrt_c2 = rsqrtf(A.bias_c2);
+  float c1 = A.bias_c1, c2 = A.bias_c2;
+  if (A.step_ptr) {
+    const float t = fmaxf(*A.step_ptr, 1.f);
+    c1 = 1.f - powf(A.beta1, t);
+    c2 = 1.f - powf(A.beta2, t);
+  }
+  const float step_size = A.lr / c1;
+  const float inv_sqrt_c2 = rsqrtf(c2);
   const float decay = 1.f - A.lr * A.weight_decay;
   for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < per_vec;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
@@ -260,7 +270,8 @@ reduce_scatter_kernel(Peers P, char* mc, int rank, int W, long long off_bytes, l
 // memory) so a consumer kernel can start on weights that have landed.
 __global__ void __launch_bounds__(THREADS, 1)
 allgather_kernel(Peers P, int rank, int W, long long shard_off_bytes, long long per_vec, char* __restrict__ dst,
-                 uint32_t epoch, uint32_t* __restrict__ chunk_flags) {
+                 uint32_t epoch_arg, const uint32_t* __restrict__ epoch_base, uint32_t* __restrict__ chunk_flags) {
+  const uint32_t epoch = epoch_arg + (epoch_base ? *epoch_base : 0u);
   block_barrier(P, rank, W, epoch);  // every rank's shard holds this step's parameters
   for (int p = 0; p < W; ++p) {
     const int q = (rank + p) % W;
@@ -320,8 +331,8 @@ HYP_API int hyp_comm_max_blocks() { return MAX_BLOCKS; }
 // [off_bytes, off_bytes + n*elem) must be 16-byte aligned and padded to 16 bytes.  `epoch` must be the
 // same on every rank and grow by 4 per launch.  Uses 3 barrier epochs.
 HYP_API int hyp_comm_allreduce(const long long* peer_bufs, const long long* peer_flags, long long mc_ptr, int rank, int W,
-                               long long off_bytes, long long n, int dtype, unsigned epoch, const float* inv_scale,
-                               float extra_scale, int max_blocks, void* stream_) {
+                               long long off_bytes, long long n, int dtype, unsigned epoch, const unsigned* epoch_base,
+                               const float* inv_scale, float extra_scale, int max_blocks, void* stream_) {
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
   Peers P;
   if (fill_peers(P, peer_bufs, peer_flags, W)) return -1;
@@ -332,9 +343,9 @@ HYP_API int hyp_comm_allreduce(const long long* peer_bufs, const long long* peer
   const long long nvec = (n * es + 15) / 16;
   const int grid = pick_grid((nvec + W - 1) / W, max_blocks);
   char* mc = reinterpret_cast<char*>(mc_ptr);
-  if (dtype == DT_F32) allreduce_kernel<float><<<grid, THREADS, 0, st>>>(P, mc, rank, W, off_bytes, n, epoch, inv_scale, extra_scale);
-  else if (dtype == DT_BF16) allreduce_kernel<__nv_bfloat16><<<grid, THREADS, 0, st>>>(P, mc, rank, W, off_bytes, n, epoch, inv_scale, extra_scale);
-  else allreduce_kernel<__half><<<grid, THREADS, 0, st>>>(P, mc, rank, W, off_bytes, n, epoch, inv_scale, extra_scale);
+  if (dtype == DT_F32) allreduce_kernel<float><<<grid, THREADS, 0, st>>>(P, mc, rank, W, off_bytes, n, epoch, epoch_base, inv_scale, extra_scale);
+  else if (dtype == DT_BF16) allreduce_kernel<__nv_bfloat16><<<grid, THREADS, 0, st>>>(P, mc, rank, W, off_bytes, n, epoch, epoch_base, inv_scale, extra_scale);
+  else allreduce_kernel<__half><<<grid, THREADS, 0, st>>>(P, mc, rank, W, off_bytes, n, epoch, epoch_base, inv_scale, extra_scale);
   HYP_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -343,15 +354,16 @@ HYP_API int hyp_comm_allreduce(const long long* peer_bufs, const long long* peer
 // fused_adam: master/m/v/p16 describe the local shard (per_elems elements). Uses 2 barrier epochs.
 HYP_API int hyp_comm_reduce_scatter(const long long* peer_bufs, const long long* peer_flags, long long mc_ptr, int rank,
                                     int W, long long off_bytes, long long per_elems, int dtype, unsigned epoch,
-                                    float scale, float* gshard, float* sumsq, int fused_adam, float* master, float* m,
-                                    float* v, void* p16, int p16_dtype, float lr, float beta1, float beta2, float eps,
-                                    float weight_decay, int step, int max_blocks, void* stream_) {
+                                    const unsigned* epoch_base, float scale, float* gshard, float* sumsq, int fused_adam,
+                                    float* master, float* m, float* v, void* p16, int p16_dtype, float lr, float beta1,
+                                    float beta2, float eps, float weight_decay, int step, const float* step_ptr,
+                                    int max_blocks, void* stream_) {
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
   Peers P;
   if (fill_peers(P, peer_bufs, peer_flags, W)) return -1;
   const int es = dtype == DT_F32 ? 4 : 2;
   HYP_REQUIRE(off_bytes % 16 == 0 && (per_elems * es) % 16 == 0, "hyp_comm_reduce_scatter: slices must be 16-byte multiples");
-  HYP_REQUIRE(fused_adam ? (master && m && v && step >= 1) : gshard != nullptr, "hyp_comm_reduce_scatter: missing outputs");
+  HYP_REQUIRE(fused_adam ? (master && m && v && (step >= 1 || step_ptr)) : gshard != nullptr, "hyp_comm_reduce_scatter: missing outputs");
   if (per_elems <= 0) return 0;
   if (max_blocks <= 0 || max_blocks > MAX_BLOCKS) max_blocks = MAX_BLOCKS;
   const long long per_vec = per_elems * es / 16;
@@ -361,8 +373,9 @@ HYP_API int hyp_comm_reduce_scatter(const long long* peer_bufs, const long long*
   A.lr = lr; A.beta1 = beta1; A.beta2 = beta2; A.eps = eps; A.weight_decay = weight_decay;
   A.bias_c1 = 1.f - powf(beta1, (float)(step > 0 ? step : 1));
   A.bias_c2 = 1.f - powf(beta2, (float)(step > 0 ? step : 1));
+  A.step_ptr = step_ptr;
   char* mc = reinterpret_cast<char*>(mc_ptr);
-#define HYP_RS(T, TP) reduce_scatter_kernel<T, TP><<<grid, THREADS, 0, st>>>(P, mc, rank, W, off_bytes, per_vec, epoch, scale, gshard, sumsq, fused_adam, A)
+#define HYP_RS(T, TP) reduce_scatter_kernel<T, TP><<<grid, THREADS, 0, st>>>(P, mc, rank, W, off_bytes, per_vec, epoch, epoch_base, scale, gshard, sumsq, fused_adam, A)
   if (dtype == DT_F32) { if (p16_dtype == DT_F16) HYP_RS(float, __half); else HYP_RS(float, __nv_bfloat16); }
   else if (dtype == DT_BF16) { if (p16_dtype == DT_F16) HYP_RS(__nv_bfloat16, __half); else HYP_RS(__nv_bfloat16, __nv_bfloat16); }
   else { if (p16_dtype == DT_F16) HYP_RS(__half, __half); else HYP_RS(__half, __nv_bfloat16); }
@@ -374,7 +387,7 @@ HYP_API int hyp_comm_reduce_scatter(const long long* peer_bufs, const long long*
 // dst (local, W*per_bytes) <- every rank's shard bytes [shard_off_bytes, +per_bytes). Uses 2 barrier epochs.
 HYP_API int hyp_comm_allgather(const long long* peer_bufs, const long long* peer_flags, int rank, int W,
                                long long shard_off_bytes, long long per_bytes, void* dst, unsigned epoch,
-                               unsigned* chunk_flags, int max_blocks, void* stream_) {
+                               const unsigned* epoch_base, unsigned* chunk_flags, int max_blocks, void* stream_) {
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
   Peers P;
   if (fill_peers(P, peer_bufs, peer_flags, W)) return -1;
@@ -384,7 +397,7 @@ HYP_API int hyp_comm_allgather(const long long* peer_bufs, const long long* peer
   if (max_blocks <= 0 || max_blocks > MAX_BLOCKS) max_blocks = MAX_BLOCKS;
   const long long per_vec = per_bytes / 16;
   const int grid = pick_grid(per_vec / 4 + 1, max_blocks);
-  allgather_kernel<<<grid, THREADS, 0, st>>>(P, rank, W, shard_off_bytes, per_vec, static_cast<char*>(dst), epoch, chunk_flags);
+  allgather_kernel<<<grid, THREADS, 0, st>>>(P, rank, W, shard_off_bytes, per_vec, static_cast<char*>(dst), epoch, epoch_base, chunk_flags);
   HYP_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

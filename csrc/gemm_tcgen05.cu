@@ -36,6 +36,7 @@ constexpr int GROUP_M = 8;
 struct AgParams {
   int enabled, W, rank;
   unsigned epoch;                 // cross-rank barrier epoch (uses epoch and epoch + 1)
+  const unsigned* epoch_base;     // optional device word added to `epoch` (CUDA-graph replays)
   const char* src[8];             // peer r's shard of this unit (already offset to the unit's shard)
   uint32_t* peer_flags[8];        // symmetric flag regions (per-block barrier slots)
   char* dst;                      // local unit buffer (W * per_bytes)
@@ -45,6 +46,7 @@ struct AgParams {
   long long row_bytes;            // bytes of one B row (K * elem)
   uint32_t* arrived;              // local uint32[W]: chunks of rank q copied so far (monotonic across launches)
   unsigned target;                // value arrived[q] reaches when rank q's slice is complete for THIS launch
+  const unsigned* target_base;    // optional device word: target = *target_base + target (graph replays)
 };
 
 struct Params {
@@ -416,7 +418,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           long long hi = p.ag.b_off_bytes + static_cast<long long>(min(p.N, (tc.n_blk + 1) * BN)) * p.ag.row_bytes;
           const int q_lo = static_cast<int>(lo / p.ag.per_bytes);
           const int q_hi = static_cast<int>((hi - 1) / p.ag.per_bytes);
-          for (int q = q_lo; q <= q_hi && q < p.ag.W; ++q) ag_wait(p.ag.arrived + q, p.ag.target);
+          for (int q = q_lo; q <= q_hi && q < p.ag.W; ++q) ag_wait(p.ag.arrived + q, p.ag.target + (p.ag.target_base ? *p.ag.target_base : 0u));
           asm volatile("fence.proxy.async.global;" ::: "memory");
         }
         for (int kb = tc.kb0; kb < tc.kb1; ++kb) {
@@ -483,7 +485,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     if (p.ag.enabled) {
       const AgParams& g = p.ag;
       const int tid = threadIdx.x - NUM_THREADS;
-      ag_rank_barrier(g, tid, g.epoch);  // every rank's shard holds this step's parameters
+      const unsigned ep = g.epoch + (g.epoch_base ? *g.epoch_base : 0u);
+      ag_rank_barrier(g, tid, ep);  // every rank's shard holds this step's parameters
       const long long nch = (g.per_bytes + AG_CHUNK - 1) / AG_CHUNK;
       for (int pi = 0; pi < g.W; ++pi) {
         const int q = (g.rank + pi) % g.W;
@@ -509,7 +512,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           }
         }
       }
-      ag_rank_barrier(g, tid, g.epoch + 1);  // peers are done reading my shard
+      ag_rank_barrier(g, tid, ep + 1);  // peers are done reading my shard
     }
   } else {
     // ----------------------------------------------------------- epilogue
@@ -521,7 +524,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       // the bias read in this epilogue lives in the same unit: wait for its owner slice(s)
       const long long hi = p.ag.bias_off_bytes + static_cast<long long>(p.N) * (p.bias_dtype == DT_F32 ? 4 : 2) - 1;
       for (int q = static_cast<int>(p.ag.bias_off_bytes / p.ag.per_bytes); q <= static_cast<int>(hi / p.ag.per_bytes) && q < p.ag.W; ++q)
-        ag_wait(p.ag.arrived + q, p.ag.target);
+        ag_wait(p.ag.arrived + q, p.ag.target + (p.ag.target_base ? *p.ag.target_base : 0u));
     }
     for (int tile = blockIdx.x; tile < total; tile += gridDim.x) {
       TileCoord tc = decode_tile(tile, tiles_m, tiles_n, nkb, p.splits);
@@ -751,12 +754,13 @@ HYP_API int hyp_gemm_ag(const void* A, const void* B, void* D, int M, int N, int
                         long long ldd, int in_dtype, int out_dtype, const void* bias, int bias_dtype, const void* aux,
                         long long ld_aux, int aux_dtype, void* preact_out, int act, float alpha,
                         const long long* peer_src, const long long* peer_flags, int rank, int W, unsigned epoch,
-                        void* unit_dst, long long per_bytes, unsigned* arrived, unsigned target, void* stream_) {
+                        const unsigned* epoch_base, void* unit_dst, long long per_bytes, unsigned* arrived,
+                        unsigned target, const unsigned* target_base, void* stream_) {
   HYP_REQUIRE(W >= 1 && W <= 8, "hyp_gemm_ag: world size %d not in [1, 8]", W);
   HYP_REQUIRE(per_bytes > 0 && per_bytes % 16 == 0, "hyp_gemm_ag: slice size must be a positive multiple of 16 bytes");
   gemm::AgParams g;
   memset(&g, 0, sizeof(g));
-  g.enabled = 1; g.W = W; g.rank = rank; g.epoch = epoch;
+  g.enabled = 1; g.W = W; g.rank = rank; g.epoch = epoch; g.epoch_base = epoch_base; g.target_base = target_base;
   for (int i = 0; i < W; ++i) {
     g.src[i] = reinterpret_cast<const char*>(peer_src[i]);
     g.peer_flags[i] = reinterpret_cast<uint32_t*>(peer_flags[i]);

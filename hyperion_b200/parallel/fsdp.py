@@ -60,18 +60,18 @@ class _AgHandle:
     def __init__(self, fsdp: "HyperionFSDP", ui: int):
         self.fsdp, self.ui = fsdp, ui
         self.pending = False
-        self.gen = 0
         self.arrived = torch.zeros(fsdp.world_size, device=fsdp.device, dtype=torch.int32)
+        self.done = torch.zeros(1, device=fsdp.device, dtype=torch.int32)  # chunks per slice gathered by past launches
 
     def run(self, x2, w2, out, bias=None, aux=None, act=None, preact_out=None) -> None:
         f = self.fsdp
         s, e, _ = f.units[self.ui]
         a, b = f._shard_range(self.ui)
-        self.gen += 1
         nch = ((b - a) * f.shard16.element_size() + 32767) // 32768
         f.arena.gemm_allgather(x2, w2, out, shard_buf=f.shard16, shard_start=a, per_elems=b - a,
-                               unit_dst=f.flat.data[s:e], arrived=self.arrived, target=self.gen * nch, bias=bias,
-                               aux=aux, act=act, preact_out=preact_out)
+                               unit_dst=f.flat.data[s:e], arrived=self.arrived, target=nch, target_base=self.done,
+                               bias=bias, aux=aux, act=act, preact_out=preact_out)
+        self.done += nch  # device-side, so a captured graph replays with advancing targets
         self.pending = False
 
 
@@ -128,9 +128,12 @@ class HyperionFSDP(nn.Module):
         self.exp_avg = torch.zeros(self.shard_numel, device=self.device, dtype=torch.float32)
         self.exp_avg_sq = torch.zeros(self.shard_numel, device=self.device, dtype=torch.float32)
         self.gshard = torch.zeros(self.shard_numel, device=self.device, dtype=torch.float32) if (W > 1) else None
-        self.sumsq = torch.zeros(2, device=self.device, dtype=torch.float32)
+        # (sum of squares, non-finite flag); lives in symmetric memory when fused so the global-norm reduction is
+        # one tiny launch of the all-reduce kernel instead of an NCCL call (K-C4)
+        self.sumsq = (self.arena.alloc(4, torch.float32, self.device) if self.fused else
+                      torch.zeros(4, device=self.device, dtype=torch.float32))
         self.step_count = 0
-        self.step_t = torch.zeros(1, device=self.device, dtype=torch.float32)  # device-side step count (CUDA-graph safe)
+        self.step_t = torch.ones(1, device=self.device, dtype=torch.float32)  # device-side number of the step in flight
         # ---- schedule
         self.comm_stream = torch.cuda.Stream(self.device) if self.device.type == "cuda" else None
         self._spec_unit = {}
@@ -242,7 +245,8 @@ class HyperionFSDP(nn.Module):
 
     def _adam_args(self, a: int, b: int) -> dict:
         return dict(master=self.master[a:b], m=self.exp_avg[a:b], v=self.exp_avg_sq[a:b], p16=self.shard16[a:b],
-                    lr=self.lr, betas=self.betas, eps=self.eps, weight_decay=self.weight_decay, step=self.step_count + 1)
+                    lr=self.lr, betas=self.betas, eps=self.eps, weight_decay=self.weight_decay, step=self.step_count + 1,
+                    step_t=self.step_t)
 
     def _unscale(self) -> float:
         return 1.0 / self.world_size
@@ -302,13 +306,17 @@ class HyperionFSDP(nn.Module):
                     self.sumsq[0] = (g * g).sum()
                     self.sumsq[1] = (~torch.isfinite(g)).any().float()
                 if self.max_norm > 0 or self.loss_scaler is not None:
-                    dist.all_reduce(self.sumsq, group=self.group)  # scalar all-reduce: exact GLOBAL norm
+                    if self.fused:  # scalar all-reduce on the comm stream: exact GLOBAL norm, no NCCL in the step
+                        with torch.cuda.stream(self.comm_stream):
+                            self.arena.allreduce_avg_(self.sumsq, 0, 4, extra_scale=1.0)
+                        torch.cuda.current_stream(self.device).wait_stream(self.comm_stream)
+                    else:
+                        dist.all_reduce(self.sumsq, group=self.group)
                 sumsq = self.sumsq
             if self.loss_scaler is not None:
                 self.loss_scaler.note_overflow(self.sumsq)
                 found_inf = self.loss_scaler.found_inf
             self.step_count += 1
-            self.step_t += 1
             p16 = self.shard16 if W > 1 else self.flat.data
             master = self.master if self.master is not None else p16
             if native_ok:
@@ -322,11 +330,14 @@ class HyperionFSDP(nn.Module):
             self.sumsq.zero_()
         else:
             self.step_count += 1  # AdamW already applied inside the reduce-scatter kernels
+        self.step_t += 1
         if self.loss_scaler is not None:
             self.loss_scaler.update()
         self.flat.grad.zero_()
         if W > 1:
             self._queue_gathers()
+        if self.arena is not None:
+            self.arena.end_step(self.comm_stream)
 
     def _adamw_torch(self, master, g, p16, sumsq, inv_scale, found_inf) -> None:
         if found_inf is not None and float(found_inf.reshape(-1)[0]) != 0.0:
@@ -367,6 +378,10 @@ class HyperionFSDP(nn.Module):
                     gev = torch.cuda.Event()
                     gev.record(self.comm_stream)
                     self._gather_events[ui] = gev
+            if torch.cuda.is_current_stream_capturing():
+                # a captured step must re-join every forked stream before the capture ends
+                torch.cuda.current_stream(self.device).wait_stream(self.comm_stream)
+                self._gather_events = [None] * len(self.units)
         else:
             for ui in order:
                 s, e, _ = self.units[ui]

@@ -151,6 +151,7 @@ def run(bench: bool = False, out_json: str | None = None) -> int:
             unit_local.zero_()
         arena.gemm_allgather(x2, w_view, out, shard_buf=shard16, shard_start=0, per_elems=per_u, unit_dst=unit_local,
                              arrived=arrived, target=gen * nch, bias=b_view, act="gelu_tanh")
+        arena.end_step()
         torch.cuda.synchronize()
         ref = torch.nn.functional.gelu(x2.float() @ full_ref[:Nw * Kw].view(Nw, Kw).float().t() + full_ref[Nw * Kw:Nw * Kw + Nw].float(),
                                        approximate="tanh")

@@ -39,10 +39,10 @@ def _declare():
     if _SIGS_DECLARED:
         return
     lib = _lib.require()
-    _lib.declare("hyp_comm_allreduce", "pplii" + "lli" + "i" + "pf" + "ip")
-    _lib.declare("hyp_comm_reduce_scatter", "pplii" + "lli" + "i" + "f" + "pp" + "i" + "pppp" + "i" + "fffff" + "i" + "ip")
-    _lib.declare("hyp_comm_allgather", "ppii" + "ll" + "p" + "i" + "p" + "ip")
-    _lib.declare("hyp_gemm_ag", "ppp" + "iii" + "lll" + "ii" + "pi" + "pli" + "p" + "if" + "pp" + "iii" + "pl" + "pi" + "p")
+    _lib.declare("hyp_comm_allreduce", "pplii" + "lli" + "i" + "p" + "pf" + "ip")
+    _lib.declare("hyp_comm_reduce_scatter", "pplii" + "lli" + "i" + "p" + "f" + "pp" + "i" + "pppp" + "i" + "fffff" + "i" + "p" + "ip")
+    _lib.declare("hyp_comm_allgather", "ppii" + "ll" + "p" + "i" + "p" + "p" + "ip")
+    _lib.declare("hyp_gemm_ag", "ppp" + "iii" + "lll" + "ii" + "pi" + "pli" + "p" + "if" + "pp" + "iii" + "p" + "pl" + "pi" + "p" + "p")
     _lib.declare("hyp_ipc_alloc", "lpp")
     _lib.declare("hyp_ipc_open", "pp")
     _lib.declare("hyp_ipc_close", "l")
@@ -77,7 +77,8 @@ class SymmetricArena:
         self.buffers: list[SymmetricBuffer] = []
         self._by_ptr: dict[int, SymmetricBuffer] = {}
         self._ready = False
-        self.epoch = 1
+        self.epoch = 0          # offset of the next kernel's epoch within the current step (host side)
+        self.epoch_base = None  # device uint32: epoch of the step's first kernel; advanced by end_step()
         lib = _lib.require()
         self.flag_words = lib.hyp_comm_flag_words()
         self.inf_word = lib.hyp_comm_inf_word()
@@ -87,6 +88,9 @@ class SymmetricArena:
         self._ipc_opened: list[int] = []
         self._symm_ok = None
         self.flags = self.alloc(self.flag_words, torch.int32, self.device)
+        self.epoch_base = torch.ones(1, device=self.device, dtype=torch.int32)       # kernels on the comm stream
+        self.epoch_base_main = torch.ones(1, device=self.device, dtype=torch.int32)  # gemm_ag kernels (main stream)
+        self.epoch_main = 0
 
     # -- allocation ------------------------------------------------------------------------------
     def _try_symm_alloc(self, numel, dtype):
@@ -186,9 +190,32 @@ class SymmetricArena:
         return any(sb.multicast_ptr for sb in self.buffers)
 
     def _next_epoch(self, n: int = 4) -> int:
+        """Epoch offset of the next kernel.  The kernel adds the device word ``epoch_base`` to it, so a captured
+        CUDA graph (which bakes the offset) stays in lock-step with the other ranks when it is replayed."""
         e = self.epoch
         self.epoch += n
         return e
+
+    def _next_epoch_main(self, n: int = 2) -> int:
+        e = self.epoch_main
+        self.epoch_main += n
+        return e
+
+    def end_step(self, comm_stream=None) -> None:
+        """Advance the device epoch bases past every kernel launched since the last call; call it at the same point
+        of the step on every rank.  Each base is only touched on the stream whose kernels read it (``comm_stream``
+        for the collectives, the current stream for the all-gather-fused GEMMs), so stream order keeps it
+        consistent; during graph capture all streams are joined and the current stream is used for both."""
+        if self.epoch:
+            if comm_stream is not None and not torch.cuda.is_current_stream_capturing():
+                with torch.cuda.stream(comm_stream):
+                    self.epoch_base += self.epoch
+            else:
+                self.epoch_base += self.epoch
+            self.epoch = 0
+        if self.epoch_main:
+            self.epoch_base_main += self.epoch_main
+            self.epoch_main = 0
 
     # -- kernels ---------------------------------------------------------------------------------
     def allreduce_avg_(self, flat: torch.Tensor, start: int, end: int, inv_scale=None, found_inf=None,
@@ -200,7 +227,8 @@ class SymmetricArena:
         scale = (1.0 / self.world_size) if extra_scale is None else extra_scale
         _lib.call("hyp_comm_allreduce", ctypes.addressof(sb.c_ptrs()), ctypes.addressof(self._flags_sb.c_ptrs()),
                   sb.multicast_ptr, self.rank, self.world_size, off + start * es, end - start, DT[flat.dtype],
-                  self._next_epoch(), _lib.ptr(inv_scale), float(scale), self.max_blocks, _lib.stream_ptr(self.device))
+                  self._next_epoch(), _lib.ptr(self.epoch_base), _lib.ptr(inv_scale), float(scale), self.max_blocks,
+                  _lib.stream_ptr(self.device))
 
     def reduce_scatter(self, grad_flat: torch.Tensor, start: int, per_elems: int, *, gshard=None, sumsq=None,
                        adam=None, scale: float | None = None) -> None:
@@ -213,12 +241,14 @@ class SymmetricArena:
             p16 = adam.get("p16")
             args = (1, _lib.ptr(adam["master"]), _lib.ptr(adam["m"]), _lib.ptr(adam["v"]), _lib.ptr(p16),
                     DT[p16.dtype] if p16 is not None else 2, float(adam["lr"]), float(adam["betas"][0]),
-                    float(adam["betas"][1]), float(adam["eps"]), float(adam["weight_decay"]), int(adam["step"]))
+                    float(adam["betas"][1]), float(adam["eps"]), float(adam["weight_decay"]), int(adam["step"]),
+                    _lib.ptr(adam.get("step_t")))
         else:
-            args = (0, None, None, None, None, 2, 0.0, 0.9, 0.999, 1e-8, 0.0, 1)
+            args = (0, None, None, None, None, 2, 0.0, 0.9, 0.999, 1e-8, 0.0, 1, None)
         _lib.call("hyp_comm_reduce_scatter", ctypes.addressof(sb.c_ptrs()), ctypes.addressof(self._flags_sb.c_ptrs()),
                   sb.multicast_ptr, self.rank, self.world_size, off + start * es, per_elems, DT[grad_flat.dtype],
-                  self._next_epoch(), float(scale), _lib.ptr(gshard), _lib.ptr(sumsq), *args, self.max_blocks,
+                  self._next_epoch(), _lib.ptr(self.epoch_base), float(scale), _lib.ptr(gshard), _lib.ptr(sumsq), *args,
+                  self.max_blocks,
                   _lib.stream_ptr(self.device))
 
     def allgather(self, shard_buf: torch.Tensor, shard_start: int, per_elems: int, dst: torch.Tensor,
@@ -229,11 +259,12 @@ class SymmetricArena:
         assert dst.numel() >= per_elems * self.world_size and dst.dtype == shard_buf.dtype
         _lib.call("hyp_comm_allgather", ctypes.addressof(sb.c_ptrs()), ctypes.addressof(self._flags_sb.c_ptrs()),
                   self.rank, self.world_size, off + shard_start * es, per_elems * es, _lib.ptr(dst), self._next_epoch(),
-                  _lib.ptr(chunk_flags), self.max_blocks, _lib.stream_ptr(self.device))
+                  _lib.ptr(self.epoch_base), _lib.ptr(chunk_flags), self.max_blocks, _lib.stream_ptr(self.device))
 
     def gemm_allgather(self, x2: torch.Tensor, w: torch.Tensor, out: torch.Tensor, *, shard_buf: torch.Tensor,
                        shard_start: int, per_elems: int, unit_dst: torch.Tensor, arrived: torch.Tensor, target: int,
-                       bias=None, aux=None, act=None, preact_out=None, alpha: float = 1.0) -> None:
+                       target_base: torch.Tensor | None = None, bias=None, aux=None, act=None, preact_out=None,
+                       alpha: float = 1.0) -> None:
         """K-C3 fused: ``out = epilogue(x2 @ w.T)`` where ``w`` (and ``bias``) are views into ``unit_dst`` (the local,
         full-size unit buffer) whose W slices are pulled from every rank's ``shard_buf[shard_start:+per_elems]``
         by gather warps inside the GEMM kernel."""
@@ -248,8 +279,8 @@ class SymmetricArena:
                   DT[out.dtype], _lib.ptr(bias), DT[bias.dtype] if bias is not None else 0, _lib.ptr(aux),
                   _ld(aux) if aux is not None else 0, DT[aux.dtype] if aux is not None else 0, _lib.ptr(preact_out), ACT[act],
                   float(alpha), ctypes.addressof(srcs), ctypes.addressof(self._flags_sb.c_ptrs()), self.rank, self.world_size,
-                  self._next_epoch(), _lib.ptr(unit_dst), per_elems * es, _lib.ptr(arrived), int(target),
-                  _lib.stream_ptr(self.device))
+                  self._next_epoch_main(), _lib.ptr(self.epoch_base_main), _lib.ptr(unit_dst), per_elems * es, _lib.ptr(arrived),
+                  int(target), _lib.ptr(target_base), _lib.stream_ptr(self.device))
 
     def close(self) -> None:
         torch.cuda.synchronize(self.device)

@@ -62,6 +62,9 @@ class Engine:
         if scaler is not None:
             scaler.update()
         self.optimizer.zero_grad()
+        symm = getattr(self.model, "symm", None)
+        if symm is not None:
+            symm.end_step(getattr(self.model, "comm_stream", None))
 
     def state_for_checkpoint(self):
         return self.optimizer if self.strategy != "fsdp" else None
@@ -123,11 +126,15 @@ class GraphedStep:
                 eng.backward_and_step(loss_fn(self.static_batch))
         torch.cuda.current_stream(dev).wait_stream(side)
         torch.cuda.synchronize(dev)
+        # events recorded by the eager warm-up steps (pending parameter gathers) are complete after the synchronize;
+        # waiting on them from the capturing stream would be a dependency on uncaptured work
+        if hasattr(eng.model, "_gather_events"):
+            eng.model._gather_events = [None] * len(eng.model._gather_events)
         from ..ops import _lib
 
         n0 = _lib.launch_count()
         self.graph = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(self.graph):
+        with torch.cuda.graph(self.graph, capture_error_mode="thread_local"):  # other threads (NCCL watchdog) may poll events
             self.loss = loss_fn(self.static_batch)
             eng.backward_and_step(self.loss)
         self.loss = self.loss.detach()
