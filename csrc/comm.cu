@@ -144,26 +144,37 @@ allreduce_kernel(Peers P, char* mc, int rank, int W, long long off_bytes, long l
 
   block_barrier(P, rank, W, epoch);  // every rank's bucket is complete
   bool bad = false;
-  for (long long v = v0 + static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; v < v1;
-       v += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const long long off = off_bytes + v * 16;
-    float acc[8];
-    reduce_vec<T>(P, mc, rank, W, off, acc);
+  // UNR independent 16-byte vectors per thread are in flight at a time (NVLink round trips are ~2 us)
+  constexpr int UNR = 4;
+  const long long tstride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long vb = v0 + static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; vb < v1; vb += UNR * tstride) {
+    float acc[UNR][8];
 #pragma unroll
-    for (int i = 0; i < N; ++i) {
-      acc[i] *= scale;
-      bad |= !isfinite(acc[i]);
+    for (int u = 0; u < UNR; ++u) {
+      const long long v = vb + u * tstride;
+      if (v < v1) reduce_vec<T>(P, mc, rank, W, off_bytes + v * 16, acc[u]);
     }
-    if (mc) {
-      uint4 u;
-      float tmp[8];
 #pragma unroll
-      for (int i = 0; i < 8; ++i) tmp[i] = i < N ? acc[i] : 0.f;
-      if constexpr (sizeof(T) == 4) u = make_uint4(__float_as_uint(tmp[0]), __float_as_uint(tmp[1]), __float_as_uint(tmp[2]), __float_as_uint(tmp[3]));
-      else u = pack8<T>(tmp);
-      multimem_st_u32x4(mc + off, u);  // the switch broadcasts the reduced vector to every rank
-    } else {
-      Vec<T>::store(mine + off, acc);
+    for (int u = 0; u < UNR; ++u) {
+      const long long v = vb + u * tstride;
+      if (v >= v1) continue;
+      const long long off = off_bytes + v * 16;
+#pragma unroll
+      for (int i = 0; i < N; ++i) {
+        acc[u][i] *= scale;
+        bad |= !isfinite(acc[u][i]);
+      }
+      if (mc) {
+        uint4 q;
+        float tmp[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) tmp[i] = i < N ? acc[u][i] : 0.f;
+        if constexpr (sizeof(T) == 4) q = make_uint4(__float_as_uint(tmp[0]), __float_as_uint(tmp[1]), __float_as_uint(tmp[2]), __float_as_uint(tmp[3]));
+        else q = pack8<T>(tmp);
+        multimem_st_u32x4(mc + off, q);  // the switch broadcasts the reduced vector to every rank
+      } else {
+        Vec<T>::store(mine + off, acc[u]);
+      }
     }
   }
   if (bad) raise_inf(P, W);
@@ -225,34 +236,52 @@ reduce_scatter_kernel(Peers P, char* mc, int rank, int W, long long off_bytes, l
   const float step_size = A.lr / c1;
   const float inv_sqrt_c2 = rsqrtf(c2);
   const float decay = 1.f - A.lr * A.weight_decay;
-  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < per_vec;
-       i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const long long off = off_bytes + (static_cast<long long>(rank) * per_vec + i) * 16;
-    float g[8];
-    reduce_vec<T>(P, mc, rank, W, off, g);
-    const long long e0 = i * N;  // element index inside the shard
+  constexpr int UNR = 2;
+  const long long tstride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long ib = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; ib < per_vec; ib += UNR * tstride) {
+    float gg[UNR][8];
 #pragma unroll
-    for (int k = 0; k < N; ++k) {
-      g[k] *= scale;
-      ss += g[k] * g[k];
-      bad |= !isfinite(g[k]);
+    for (int u = 0; u < UNR; ++u) {
+      const long long i = ib + u * tstride;
+      if (i < per_vec) reduce_vec<T>(P, mc, rank, W, off_bytes + (static_cast<long long>(rank) * per_vec + i) * 16, gg[u]);
     }
-    if (!fused_adam) {
 #pragma unroll
-      for (int k = 0; k < N; ++k) gshard[e0 + k] = g[k];
-    } else {
-      float out[8];
+    for (int u = 0; u < UNR; ++u) {
+      const long long i = ib + u * tstride;
+      if (i >= per_vec) continue;
+      float (&g)[8] = gg[u];
+      const long long e0 = i * N;  // element index inside the shard
 #pragma unroll
       for (int k = 0; k < N; ++k) {
-        const float mk = A.beta1 * A.m[e0 + k] + (1.f - A.beta1) * g[k];
-        const float vk = A.beta2 * A.v[e0 + k] + (1.f - A.beta2) * g[k] * g[k];
-        const float pk = A.master[e0 + k] * decay - step_size * mk / (sqrtf(vk) * inv_sqrt_c2 + A.eps);
-        A.m[e0 + k] = mk; A.v[e0 + k] = vk; A.master[e0 + k] = pk;
-        out[k] = pk;
+        g[k] *= scale;
+        ss += g[k] * g[k];
+        bad |= !isfinite(g[k]);
       }
-      if (A.p16) {
+      if (!fused_adam) {
 #pragma unroll
-        for (int k = 0; k < N; ++k) reinterpret_cast<TP*>(A.p16)[e0 + k] = from_f32<TP>(out[k]);
+        for (int k = 0; k < N; k += 4) *reinterpret_cast<float4*>(gshard + e0 + k) = make_float4(g[k], g[k + 1], g[k + 2], g[k + 3]);
+      } else {
+        float out[8];
+#pragma unroll
+        for (int k = 0; k < N; k += 4) {
+          float4 mm = *reinterpret_cast<float4*>(A.m + e0 + k), vv = *reinterpret_cast<float4*>(A.v + e0 + k),
+                 pp = *reinterpret_cast<float4*>(A.master + e0 + k);
+          float* mf = reinterpret_cast<float*>(&mm); float* vf = reinterpret_cast<float*>(&vv); float* pf = reinterpret_cast<float*>(&pp);
+#pragma unroll
+          for (int t = 0; t < 4; ++t) {
+            mf[t] = A.beta1 * mf[t] + (1.f - A.beta1) * g[k + t];
+            vf[t] = A.beta2 * vf[t] + (1.f - A.beta2) * g[k + t] * g[k + t];
+            pf[t] = pf[t] * decay - step_size * mf[t] / (sqrtf(vf[t]) * inv_sqrt_c2 + A.eps);
+            out[k + t] = pf[t];
+          }
+          *reinterpret_cast<float4*>(A.m + e0 + k) = mm;
+          *reinterpret_cast<float4*>(A.v + e0 + k) = vv;
+          *reinterpret_cast<float4*>(A.master + e0 + k) = pp;
+        }
+        if (A.p16) {
+#pragma unroll
+          for (int k = 0; k < N; ++k) reinterpret_cast<TP*>(A.p16)[e0 + k] = from_f32<TP>(out[k]);
+        }
       }
     }
   }

@@ -82,7 +82,7 @@ class SymmetricArena:
         lib = _lib.require()
         self.flag_words = lib.hyp_comm_flag_words()
         self.inf_word = lib.hyp_comm_inf_word()
-        self.max_blocks = int(os.environ.get("HYPERION_COMM_BLOCKS", "32"))
+        self.max_blocks = int(os.environ.get("HYPERION_COMM_BLOCKS", "48"))
         self.use_multicast = os.environ.get("HYPERION_NVLS", "1") == "1"
         self._ipc_allocs: list[int] = []
         self._ipc_opened: list[int] = []
