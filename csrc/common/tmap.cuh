@@ -29,6 +29,10 @@ inline int make_tmap_nd(CUtensorMap* tm, const void* ptr, int dtype, int rank, c
                         const unsigned long long* strides_bytes, const unsigned* box) {
   EncodeTiledFn enc = tmap_encode_fn();
   HYP_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled is unavailable (driver too old?)");
+  // The encoder is a driver-API call: make sure the primary context is bound to THIS thread first (a fresh autograd
+  // worker thread has only had cudaSetDevice, which binds lazily) -- otherwise it fails with CUDA_ERROR_INVALID_CONTEXT.
+  static thread_local bool ctx_bound = false;
+  if (!ctx_bound) { cudaFree(nullptr); ctx_bound = true; }
   const CUtensorMapDataType dt = (dtype == DT_F32)   ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32
                                  : (dtype == DT_BF16) ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16
                                                       : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;

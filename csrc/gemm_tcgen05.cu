@@ -588,6 +588,10 @@ int make_tmap_2d(CUtensorMap* tm, const void* ptr, int dtype, long long inner, l
                  int box_inner, int box_outer) {
   EncodeTiledFn enc = get_encode();
   HYP_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled is unavailable (driver too old?)");
+  // The encoder is a driver-API call: make sure the primary context is bound to THIS thread first (a fresh autograd
+  // worker thread has only had cudaSetDevice, which binds lazily) -- otherwise it fails with CUDA_ERROR_INVALID_CONTEXT.
+  static thread_local bool ctx_bound = false;
+  if (!ctx_bound) { cudaFree(nullptr); ctx_bound = true; }
   const int es = (dtype == DT_F32) ? 4 : 2;
   const CUtensorMapDataType dt = (dtype == DT_F32)   ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32
                                  : (dtype == DT_BF16) ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16

@@ -37,8 +37,62 @@ def _conv(x, conv: nn.Conv2d):
     return F.conv2d(x, conv.weight, conv.bias, conv.stride, conv.padding, conv.dilation, conv.groups)
 
 
+_bn_declared = False
+
+
+def _declare_bn():
+    global _bn_declared
+    if not _bn_declared:
+        _lib.declare("hyp_bn_act_fwd", "pppppppppp" + "li" + "ff" + "ii" + "p")
+        _lib.declare("hyp_bn_act_bwd", "ppppppppp" + "li" + "ii" + "p")
+        _bn_declared = True
+
+
+class _BnActFn(torch.autograd.Function):
+    """Training-mode BatchNorm2d + (residual add) + ReLU on a channels-last tensor: csrc/bn_act.cu."""
+
+    @staticmethod
+    def forward(ctx, x, gamma, beta, residual, running_mean, running_var, eps, momentum, relu):
+        _declare_bn()
+        N, C, H, W = x.shape
+        rows = N * H * W
+        y = torch.empty_like(x, memory_format=torch.channels_last)
+        sums = torch.zeros(2 * C, device=x.device, dtype=torch.float32)
+        mean = torch.empty(C, device=x.device, dtype=torch.float32)
+        rstd = torch.empty(C, device=x.device, dtype=torch.float32)
+        gf, bf = gamma.float(), beta.float()
+        _lib.call("hyp_bn_act_fwd", _lib.ptr(x), _lib.ptr(residual), _lib.ptr(gf), _lib.ptr(bf), _lib.ptr(y), _lib.ptr(sums),
+                  _lib.ptr(mean), _lib.ptr(rstd), _lib.ptr(running_mean), _lib.ptr(running_var), rows, C, float(eps),
+                  float(momentum), int(relu), _lib.DT[x.dtype], _lib.stream_ptr())
+        ctx.save_for_backward(x, y, mean, rstd, gf)
+        ctx.relu, ctx.has_res, ctx.pdtype = relu, residual is not None, gamma.dtype
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, y, mean, rstd, gf = ctx.saved_tensors
+        N, C, H, W = x.shape
+        dy = dy.contiguous(memory_format=torch.channels_last)
+        dx = torch.empty_like(x, memory_format=torch.channels_last)
+        dres = torch.empty_like(x, memory_format=torch.channels_last) if ctx.has_res else None
+        dsums = torch.zeros(2 * C, device=x.device, dtype=torch.float32)
+        _lib.call("hyp_bn_act_bwd", _lib.ptr(dy), _lib.ptr(x), _lib.ptr(y), _lib.ptr(mean), _lib.ptr(rstd), _lib.ptr(gf),
+                  _lib.ptr(dsums), _lib.ptr(dx), _lib.ptr(dres), N * H * W, C, int(ctx.relu), _lib.DT[x.dtype], _lib.stream_ptr())
+        return dx, dsums[C:].to(ctx.pdtype), dsums[:C].to(ctx.pdtype), dres, None, None, None, None, None
+
+
+def _bn_native_ok(y, bn, residual) -> bool:
+    return (bn.training and y.is_cuda and _lib.available() and y.dtype in (torch.float16, torch.bfloat16)
+            and y.dim() == 4 and y.shape[1] % 8 == 0 and y.is_contiguous(memory_format=torch.channels_last)
+            and bn.track_running_stats and bn.momentum is not None
+            and (residual is None or (residual.shape == y.shape and residual.is_contiguous(memory_format=torch.channels_last))))
+
+
 def conv_bn_act(x, conv: nn.Conv2d, bn: nn.BatchNorm2d, relu: bool = True, residual=None):
     y = _conv(x, conv)
+    if _bn_native_ok(y, bn, residual):
+        bn.num_batches_tracked.add_(1)
+        return _BnActFn.apply(y, bn.weight, bn.bias, residual, bn.running_mean, bn.running_var, bn.eps, bn.momentum, relu)
     if bn.training:
         if bn.num_batches_tracked is not None:
             bn.num_batches_tracked.add_(1)

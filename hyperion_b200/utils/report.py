@@ -67,7 +67,7 @@ def scaling_table(durations: dict) -> pd.DataFrame:
         row = {"gpus": g, "ideal": float(g)}
         for model, d in durations.items():
             base = d.get(1)
-            if base is None or g not in d:
+            if base is None or g not in d or d[g] <= 0 or base <= 0:  # Llama logs integer seconds: 0 is possible
                 row[f"{model}_speedup"] = None
                 row[f"{model}_efficiency"] = None
             else:

@@ -116,6 +116,74 @@ int hyp_embedding_bwd(const void* dout, const long long* idx, float* dtable, lon
 int hyp_rope(void* x, int B, int S, int H, int D, long long stride_b, long long stride_s, long long stride_h,
              const long long* positions, float theta, int inverse, int dtype, void* stream);
 
+/* ---- flash_attn_sm100 (csrc/attention.cu) -------------------------------------------
+ * softmax(Q K^T * scale + mask) V on tcgen05 with TMEM accumulators; head dim 64 or 128, fp16 / bf16.
+ * q/k/v/o (and d_o, dk, dv) are indexed [b, h, s, d] through ELEMENT strides (unit stride in d; strides multiples of 8),
+ * read in place by 4-D TMA descriptors.  key_padding_mask: uint8 [B, Sk], 1 = attend, or NULL.  lse: fp32 [B, H, Sq].
+ * Backward: dq_acc is fp32 [B, H, Sq, D], ZEROED by the caller (accumulated with vector reductions); delta is fp32
+ * [B, H, Sq] scratch; dk / dv are written in full.
+ * Reference: nn.MultiheadAttention in nn.TransformerEncoderLayer (distributed_utils.py:79), HF Llama SDPA (:465). */
+int hyp_flash_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse, int B, int H, int Sq, int Sk, int D,
+                       long long q_sb, long long q_sh, long long q_ss, long long k_sb, long long k_sh, long long k_ss,
+                       long long v_sb, long long v_sh, long long v_ss, long long o_sb, long long o_sh, long long o_ss,
+                       const unsigned char* key_padding_mask, int causal, float scale, int dtype, void* stream);
+int hyp_flash_attn_bwd(const void* q, const void* k, const void* v, const void* o, const void* d_o, const float* lse,
+                       float* dq_acc, void* dk, void* dv, float* delta, const unsigned char* key_padding_mask, int B, int H,
+                       int Sq, int Sk, int D, long long q_sb, long long q_sh, long long q_ss, long long k_sb, long long k_sh,
+                       long long k_ss, long long v_sb, long long v_sh, long long v_ss, long long o_sb, long long o_sh,
+                       long long o_ss, long long g_sb, long long g_sh, long long g_ss, long long dkv_sb, long long dkv_sh,
+                       long long dkv_ss, int causal, float scale, int dtype, void* stream);
+
+/* ---- NVLink communication kernels (csrc/comm.cu) ------------------------------------
+ * peer_bufs / peer_flags are HOST arrays of W device addresses: this rank's mapping of every rank's symmetric data
+ * buffer / flag region (hyp_comm_flag_words() uint32 words, zero-initialised).  mc_ptr: multicast (NVLS) address of
+ * the data buffer or 0.  The kernels spin on flags written by peer GPUs: every rank must launch the same sequence, on
+ * one stream, with at most hyp_comm_max_blocks() co-resident blocks.  The barrier epoch of a launch is
+ * epoch + (epoch_base ? *epoch_base : 0); it must be equal on all ranks and grow by >= 4 per launch.
+ * Reference: the implicit DDP all-reduce / FSDP reduce-scatter + all-gather of distributed_utils.py:159, 328-332. */
+int hyp_comm_flag_words(void);
+int hyp_comm_inf_word(void);   /* index (as float) of the word raised to 1.0 on every rank when a non-finite value is reduced */
+int hyp_comm_max_blocks(void);
+/* K-C1: in-place average (x extra_scale, x *inv_scale) of n elements at off_bytes, all ranks. */
+int hyp_comm_allreduce(const long long* peer_bufs, const long long* peer_flags, long long mc_ptr, int rank, int W,
+                       long long off_bytes, long long n, int dtype, unsigned epoch, const unsigned* epoch_base,
+                       const float* inv_scale, float extra_scale, int max_blocks, void* stream);
+/* K-C2: rank r reduces slice r (per_elems elements) of the region; fused_adam != 0 applies AdamW to the local fp32
+ * shard (master, m, v; optional 16-bit copy p16) in the same pass, else the fp32 slice goes to gshard and its sum of
+ * squares is added to sumsq[0]. */
+int hyp_comm_reduce_scatter(const long long* peer_bufs, const long long* peer_flags, long long mc_ptr, int rank, int W,
+                            long long off_bytes, long long per_elems, int dtype, unsigned epoch, const unsigned* epoch_base,
+                            float scale, float* gshard, float* sumsq, int fused_adam, float* master, float* m, float* v,
+                            void* p16, int p16_dtype, float lr, float beta1, float beta2, float eps, float weight_decay,
+                            int step, const float* step_ptr, int max_blocks, void* stream);
+/* K-C3 (gather only): dst[q*per_bytes ...] = rank q's bytes [shard_off_bytes, +per_bytes) for every q. */
+int hyp_comm_allgather(const long long* peer_bufs, const long long* peer_flags, int rank, int W, long long shard_off_bytes,
+                       long long per_bytes, void* dst, unsigned epoch, const unsigned* epoch_base, unsigned* chunk_flags,
+                       int max_blocks, void* stream);
+/* K-C3 fused: D = epilogue(A . B^T) where B (and bias) live in the flat unit buffer `unit_dst` (W slices of per_bytes);
+ * gather warps inside the GEMM kernel pull slice q from peer_src[q] while tiles whose weights have landed are computed.
+ * arrived: device uint32[W], zero at creation; a launch completes when arrived[q] == target + (target_base ? *target_base : 0). */
+int hyp_gemm_ag(const void* A, const void* B, void* D, int M, int N, int K, long long lda, long long ldb, long long ldd,
+                int in_dtype, int out_dtype, const void* bias, int bias_dtype, const void* aux, long long ld_aux,
+                int aux_dtype, void* preact_out, int act, float alpha, const long long* peer_src,
+                const long long* peer_flags, int rank, int W, unsigned epoch, const unsigned* epoch_base, void* unit_dst,
+                long long per_bytes, unsigned* arrived, unsigned target, const unsigned* target_base, void* stream);
+/* Plain CUDA IPC provider of peer memory (set-up time only; hyp_ipc_alloc calls cudaMalloc). */
+int hyp_ipc_alloc(long long bytes, long long* out_ptr, unsigned char* out_handle64);
+int hyp_ipc_open(const unsigned char* handle64, long long* out_ptr);
+int hyp_ipc_close(long long ptr);
+int hyp_ipc_free(long long ptr);
+
+/* ---- bn_act (csrc/bn_act.cu) ------------------------------------------------------
+ * Training-mode BatchNorm2d + residual add + ReLU on NHWC-contiguous [rows = N*H*W, C] 16-bit tensors.
+ * sums / dsums: fp32 [2*C] scratch ZEROED by the caller (batch statistics / dbeta,dgamma on return).
+ * Reference: torchvision ResNet Conv2d->BatchNorm2d->ReLU(+residual) (distributed_utils.py:229). */
+int hyp_bn_act_fwd(const void* x, const void* res, const float* gamma, const float* beta, void* y, float* sums, float* mean,
+                   float* rstd, float* running_mean, float* running_var, long long rows, int C, float eps, float momentum,
+                   int relu, int dtype, void* stream);
+int hyp_bn_act_bwd(const void* dy, const void* x, const void* y, const float* mean, const float* rstd, const float* gamma,
+                   float* dsums, void* dx, void* dres, long long rows, int C, int relu, int dtype, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

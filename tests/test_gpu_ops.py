@@ -1,0 +1,237 @@
+"""GPU tests of the autograd ops and models: forward AND backward of each fused op against plain PyTorch fp32 on the
+same (16-bit-rounded) inputs, then whole models (loss + parameter gradients) against their CPU/fp32 execution."""
+import copy
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def _rel(a, b):
+    a, b = a.float(), b.float()
+    return ((a - b).norm() / (b.norm() + 1e-12)).item()
+
+
+@pytest.fixture(scope="module")
+def ops():
+    from hyperion_b200 import ops as o
+
+    assert o.native_available()
+    return o
+
+
+def _leaf(*shape, scale=1.0, dtype=torch.bfloat16):
+    return (torch.randn(*shape, device="cuda") * scale).to(dtype).requires_grad_(True)
+
+
+def _ref_copy(*ts):
+    return [t.detach().float().requires_grad_(True) for t in ts]
+
+
+@pytest.mark.parametrize("act", [None, "relu", "gelu", "gelu_tanh", "silu"])
+@pytest.mark.parametrize("with_res", [False, True])
+def test_linear_op(ops, act, with_res):
+    if act == "relu" and with_res:
+        pytest.skip("relu + residual is rejected by design")
+    torch.manual_seed(0)
+    x, w, b = _leaf(4, 96, 256), _leaf(520, 256, scale=0.05), _leaf(520)
+    res = _leaf(4, 96, 520) if with_res else None
+    y = ops.linear(x, w, b, act=act, residual=res)
+    dy = torch.randn_like(y)
+    grads = torch.autograd.grad(y, [x, w, b] + ([res] if with_res else []), dy)
+    xr, wr, br = _ref_copy(x, w, b)
+    rr = _ref_copy(res)[0] if with_res else None
+    fn = {None: lambda t: t, "relu": F.relu, "gelu": F.gelu, "gelu_tanh": lambda t: F.gelu(t, approximate="tanh"), "silu": F.silu}[act]
+    yr = fn(F.linear(xr, wr, br)) + (rr if with_res else 0)
+    gr = torch.autograd.grad(yr, [xr, wr, br] + ([rr] if with_res else []), dy.float())
+    assert _rel(y, yr) < 2e-2
+    for g, r in zip(grads, gr):
+        assert _rel(g, r) < 3e-2
+
+
+@pytest.mark.parametrize("act", ["relu", "gelu", "gelu_tanh"])
+def test_mlp_op(ops, act):
+    torch.manual_seed(1)
+    x, w1, b1, w2, b2 = _leaf(8, 127, 256), _leaf(2048, 256, scale=0.05), _leaf(2048), _leaf(256, 2048, scale=0.02), _leaf(256)
+    y = ops.mlp(x, w1, b1, w2, b2, act=act, residual=x)
+    dy = torch.randn_like(y)
+    grads = torch.autograd.grad(y, [x, w1, b1, w2, b2], dy)
+    xr, w1r, b1r, w2r, b2r = _ref_copy(x, w1, b1, w2, b2)
+    fn = {"relu": F.relu, "gelu": F.gelu, "gelu_tanh": lambda t: F.gelu(t, approximate="tanh")}[act]
+    yr = F.linear(fn(F.linear(xr, w1r, b1r)), w2r, b2r) + xr
+    gr = torch.autograd.grad(yr, [xr, w1r, b1r, w2r, b2r], dy.float())
+    assert _rel(y, yr) < 2e-2
+    for g, r in zip(grads, gr):
+        assert _rel(g, r) < 4e-2
+
+
+@pytest.mark.parametrize("rms", [False, True])
+def test_norm_op(ops, rms):
+    torch.manual_seed(2)
+    x, r, g, b = _leaf(6, 50, 768), _leaf(6, 50, 768), _leaf(768), _leaf(768)
+    y = ops.rms_norm(x, g, 1e-5, residual=r) if rms else ops.layer_norm(x, g, b, 1e-5, residual=r)
+    dy = torch.randn_like(y)
+    ins = [x, r, g] + ([] if rms else [b])
+    grads = torch.autograd.grad(y, ins, dy)
+    xr, rr, gr_, br = _ref_copy(x, r, g, b)
+    z = xr + rr
+    yr = z * torch.rsqrt(z.pow(2).mean(-1, keepdim=True) + 1e-5) * gr_ if rms else F.layer_norm(z, (768,), gr_, br, 1e-5)
+    gref = torch.autograd.grad(yr, [xr, rr, gr_] + ([] if rms else [br]), dy.float())
+    assert _rel(y, yr) < 2e-2
+    for a, c in zip(grads, gref):
+        assert _rel(a, c) < 3e-2
+
+
+def test_embedding_and_linear_cross_entropy(ops):
+    torch.manual_seed(3)
+    V, D, pad = 50257, 256, 50256
+    table, w, b = _leaf(V, D, scale=0.1), _leaf(V, D, scale=0.05), _leaf(V, scale=0.1)
+    idx = torch.randint(0, V - 1, (4, 127), device="cuda")
+    tgt = torch.randint(0, V - 1, (4, 127), device="cuda")
+    tgt[:, 100:] = pad
+    h = ops.embedding(idx, table)
+    loss = ops.linear_cross_entropy(h, w, b, tgt, ignore_index=pad, chunk_rows=200)
+    gt, gw, gb = torch.autograd.grad(loss, [table, w, b])
+    tr, wr, br = _ref_copy(table, w, b)
+    lr = F.cross_entropy(F.linear(F.embedding(idx, tr), wr, br).reshape(-1, V), tgt.reshape(-1), ignore_index=pad)
+    rt, rw, rb = torch.autograd.grad(lr, [tr, wr, br])
+    assert abs(loss.item() - lr.item()) < 2e-2
+    assert _rel(gt, rt) < 4e-2 and _rel(gw, rw) < 4e-2 and _rel(gb, rb) < 4e-2
+
+
+def test_lora_linear_op(ops):
+    torch.manual_seed(4)
+    x, w = _leaf(4, 128, 512), _leaf(512, 512, scale=0.05)
+    A, B = _leaf(16, 512, scale=0.05), _leaf(512, 16, scale=0.05)
+    y = ops.lora_linear(x, x, w, None, A, B, 2.0)
+    dy = torch.randn_like(y)
+    gx, gA, gB = torch.autograd.grad(y, [x, A, B], dy)
+    xr, wr, Ar, Br = _ref_copy(x, w, A, B)
+    yr = F.linear(xr, wr) + 2.0 * F.linear(F.linear(xr, Ar), Br)
+    rx, rA, rB = torch.autograd.grad(yr, [xr, Ar, Br], dy.float())
+    assert _rel(y, yr) < 2e-2
+    assert _rel(gx, rx) < 3e-2 and _rel(gA, rA) < 3e-2 and _rel(gB, rB) < 3e-2
+
+
+def test_rope_and_swiglu_ops(ops):
+    torch.manual_seed(5)
+    x = _leaf(2, 64, 8, 128)
+    y = ops.rope(x, 10000.0, layout="bshd")
+    dy = torch.randn_like(y)
+    (gx,) = torch.autograd.grad(y, [x], dy)
+    xc = x.detach().cpu().float().requires_grad_(True)
+    yc = ops.rope(xc, 10000.0, layout="bshd")  # CPU path = plain PyTorch formulation
+    (gc,) = torch.autograd.grad(yc, [xc], dy.cpu().float())
+    assert _rel(y.cpu(), yc) < 2e-2 and _rel(gx.cpu(), gc) < 2e-2
+    g, u = _leaf(512, 1024), _leaf(512, 1024)
+    s = ops.swiglu(g, u)
+    ds = torch.randn_like(s)
+    gg, gu = torch.autograd.grad(s, [g, u], ds)
+    gr_, ur = _ref_copy(g, u)
+    rg, ru = torch.autograd.grad(F.silu(gr_) * ur, [gr_, ur], ds.float())
+    assert _rel(gg, rg) < 3e-2 and _rel(gu, ru) < 3e-2
+
+
+def _model_parity(make, batch_fn, loss_fn, tol_loss=3e-2, tol_grad=8e-2):
+    torch.manual_seed(6)
+    ref = make().float()
+    model = copy.deepcopy(ref).cuda().to(torch.bfloat16)
+    batch = batch_fn()
+    lr = loss_fn(ref, *[t.cpu() if torch.is_tensor(t) else t for t in batch])
+    lr.backward()
+    lg = loss_fn(model, *batch)
+    lg.backward()
+    assert abs(lg.item() - lr.item()) < tol_loss * max(1.0, abs(lr.item())), (lg.item(), lr.item())
+    bad = []
+    for (n, p), (_, q) in zip(model.named_parameters(), ref.named_parameters()):
+        if p.grad is None or q.grad is None or n.endswith("in_proj_bias"):
+            continue
+        if q.grad.norm() < 1e-6:
+            continue
+        e = _rel(p.grad.cpu(), q.grad)
+        if e > tol_grad:
+            bad.append((n, e))
+    assert not bad, bad[:5]
+
+
+def test_simple_lm_matches_cpu_fp32():
+    from hyperion_b200.models import SimpleTransformerLM
+
+    ids = torch.randint(0, 2000, (4, 64))
+    _model_parity(lambda: SimpleTransformerLM(2048, 128, 2, 2, 256, dropout=0.0).eval(),
+                  lambda: (ids[:, :-1].contiguous().cuda(), ids[:, 1:].contiguous().cuda()),
+                  lambda m, x, y: m.loss(x, y))
+
+
+def test_gpt2_matches_cpu_fp32():
+    from hyperion_b200.models import GPT2Config, GPT2LMHeadModel
+
+    cfg = GPT2Config(vocab_size=1024, n_positions=256, n_embd=128, n_layer=2, n_head=2)
+    ids = torch.randint(0, 1024, (2, 256))
+    _model_parity(lambda: GPT2LMHeadModel(cfg), lambda: (ids.cuda(),), lambda m, x: m.loss(x))
+
+
+def test_llama_lora_matches_cpu_fp32():
+    from hyperion_b200.lora import inject_lora
+    from hyperion_b200.models import LlamaConfig, LlamaForCausalLM
+
+    cfg = LlamaConfig(vocab_size=512, hidden_size=256, intermediate_size=688, num_hidden_layers=2, num_attention_heads=2,
+                      num_key_value_heads=2)
+
+    def make():
+        m = inject_lora(LlamaForCausalLM(cfg), dropout=0.0)
+        for mod in m.modules():
+            if hasattr(mod, "lora_B"):
+                torch.nn.init.normal_(mod.lora_B.weight, std=0.05)
+        return m
+
+    ids = torch.randint(3, 512, (2, 128))
+    mask = torch.ones(2, 128, dtype=torch.long)
+    mask[1, 100:] = 0
+    _model_parity(make, lambda: (ids.cuda(), mask.cuda()), lambda m, x, msk: m(x, msk, x).loss)
+
+
+def test_vit_and_resnet_forward_run():
+    from hyperion_b200.models import resnet18, vit_b_16
+
+    x = torch.randn(2, 3, 224, 224, device="cuda", dtype=torch.bfloat16)
+    v = vit_b_16().cuda().to(torch.bfloat16)
+    assert v(x).shape == (2, 1000)
+    r = resnet18(10).cuda().to(torch.bfloat16)
+    out = r(torch.randn(4, 3, 32, 32, device="cuda", dtype=torch.bfloat16))
+    assert out.shape == (4, 10) and torch.isfinite(out.float()).all()
+
+
+@pytest.mark.parametrize("relu,with_res", [(True, False), (True, True), (False, False)])
+def test_bn_act_fused_matches_torch(relu, with_res):
+    import torch.nn as nn
+
+    from hyperion_b200.ops.conv import _BnActFn
+
+    torch.manual_seed(7)
+    N, C, H, W = 8, 64, 14, 14
+    x = torch.randn(N, C, H, W, device="cuda").to(torch.bfloat16).contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    res = (torch.randn(N, C, H, W, device="cuda").to(torch.bfloat16).contiguous(memory_format=torch.channels_last).requires_grad_(True)
+           if with_res else None)
+    g = (1 + 0.1 * torch.randn(C, device="cuda")).to(torch.bfloat16).requires_grad_(True)
+    b = (0.1 * torch.randn(C, device="cuda")).to(torch.bfloat16).requires_grad_(True)
+    rm, rv = torch.zeros(C, device="cuda"), torch.ones(C, device="cuda")
+    y = _BnActFn.apply(x, g, b, res, rm, rv, 1e-5, 0.1, relu)
+    dy = torch.randn_like(y)
+    ins = [x, g, b] + ([res] if with_res else [])
+    grads = torch.autograd.grad(y, ins, dy)
+    xr, gr_, br = (t.detach().float().requires_grad_(True) for t in (x, g, b))
+    rr = res.detach().float().requires_grad_(True) if with_res else None
+    rm2, rv2 = torch.zeros(C, device="cuda"), torch.ones(C, device="cuda")
+    yr = F.batch_norm(xr, rm2, rv2, gr_, br, True, 0.1, 1e-5)
+    if with_res:
+        yr = yr + rr
+    if relu:
+        yr = F.relu(yr)
+    gref = torch.autograd.grad(yr, [xr, gr_, br] + ([rr] if with_res else []), dy.float())
+    assert _rel(y, yr) < 2e-2
+    for a, c in zip(grads, gref):
+        assert _rel(a, c) < 4e-2
+    assert torch.allclose(rm, rm2, atol=1e-3) and torch.allclose(rv, rv2, atol=1e-3)
