@@ -29,12 +29,15 @@ from .runtime import world
 
 class HyperionDDP(nn.Module):
     def __init__(self, module: nn.Module, bucket_cap_mb: float = 25.0, first_bucket_mb: float = 1.0,
-                 broadcast_buffers: bool = True, fused: bool | None = None, process_group=None,
+                 broadcast_buffers: bool = False, fused: bool | None = None, process_group=None,
                  loss_scaler=None, sync_params: bool = True):
         super().__init__()
         self.module = module
         self.rank, self.world_size = world()
         self.group = process_group
+        # torch DDP re-broadcasts rank 0's BatchNorm statistics before every forward (K-C1c).  Here that is opt-in:
+        # by default the buffers are synchronised when a checkpoint is taken (``sync_buffers()``), which keeps NCCL
+        # out of the step (and out of a captured CUDA graph).
         self.broadcast_buffers = broadcast_buffers
         self.loss_scaler = loss_scaler
         p0 = next(p for p in module.parameters() if p.requires_grad)
@@ -126,6 +129,11 @@ class HyperionDDP(nn.Module):
         if self.broadcast_buffers and self.world_size > 1 and self.training:
             self._sync_buffers()
         return self.module(*args, **kwargs)
+
+    def sync_buffers(self) -> None:
+        """Collective: make every rank's buffers equal to rank 0's (call before saving)."""
+        if self.world_size > 1:
+            self._sync_buffers()
 
     def _sync_buffers(self) -> None:
         """K-C1c: rank 0's BatchNorm statistics win, as with torch DDP ``broadcast_buffers=True``."""

@@ -73,7 +73,7 @@ class Engine:
 def build_engine(model: nn.Module, *, strategy: str = "single", precision: str = "bf16", lr: float = 1e-3,
                  betas=(0.9, 0.999), eps: float = 1e-8, weight_decay: float = 0.01, clip: float = 0.0, device=None,
                  fused_comm: bool | None = None, bucket_cap_mb: float = 25.0, fsdp_units=None,
-                 fsdp_min_num_params: int = 100_000, broadcast_buffers: bool = True) -> Engine:
+                 fsdp_min_num_params: int = 100_000, broadcast_buffers: bool = False) -> Engine:
     rank, W = world()
     pol = policy(precision)
     device = torch.device(device) if device is not None else next(model.parameters()).device

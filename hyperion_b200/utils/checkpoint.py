@@ -28,6 +28,8 @@ def unwrap(model):
 
 def full_state_dict(model, to_cpu: bool = True, dtype: torch.dtype | None = torch.float32) -> dict:
     """Unwrapped state_dict (all ranks may call; for HyperionFSDP every rank must call -- it gathers)."""
+    if hasattr(model, "sync_buffers"):
+        model.sync_buffers()
     if hasattr(model, "gather_full_state_dict"):
         sd = model.gather_full_state_dict()
     else:
