@@ -18,6 +18,7 @@
 // the models (02_development/distributed_utils.py:75-88).
 #include "common/ptx.cuh"
 #include "common/util.cuh"
+#include <stdlib.h>
 #include <string.h>
 
 namespace hyp {
@@ -566,6 +567,180 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   if (warp == 1) tmem_dealloc<C::TMEM_COLS>(tmem_base);
 }
 
+// ---------------------------------------------------------------------------------------------------
+// 2-CTA variant (cta_group::2): a CTA pair on one TPC computes a 256 x 256 tile.  Each CTA stages its own
+// 128 rows of A and HALF of the B tile (128 of the 256 columns); the leader's single thread issues
+// tcgen05.mma.cta_group::2 (M = 256), which reads both halves of B from the two CTAs' shared memory, so per-SM
+// operand traffic from L2 drops from 48 KB to 32 KB per k-block and the ring deepens to 6 stages.  Each CTA keeps
+// its 128 accumulator rows in its own TMEM and runs its own epilogue.
+constexpr int G2_STAGES = 6;
+constexpr int G2_BN = 256;
+constexpr int G2_STAGE_BYTES = A_STAGE + (G2_BN / 2) * ROW_BYTES;  // 16 KB A + 16 KB B-half
+constexpr int G2_SMEM = G2_STAGES * G2_STAGE_BYTES + 256 + 1024;
+
+template <int EPI, int ACT>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
+gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+             const __grid_constant__ Params p) {
+  constexpr int BN = G2_BN;
+  constexpr int BH = BN / 2;          // B columns staged by one CTA
+  constexpr int BM2 = 2 * BM;         // tile rows of the pair
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + G2_STAGES * A_STAGE;
+  uint64_t* full = reinterpret_cast<uint64_t*>(sB + G2_STAGES * BH * ROW_BYTES);
+  uint64_t* empty = full + G2_STAGES;
+  uint64_t* tfull = empty + G2_STAGES;
+  uint64_t* tempty = tfull + 2;
+  uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(tempty + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t cta = cluster_ctarank();
+  const bool leader = cta == 0;
+  const int epr = ROW_BYTES / p.esize;
+  const int nkb = (p.K + epr - 1) / epr;
+  const int tiles_m = (p.M + BM2 - 1) / BM2;
+  const int tiles_n = (p.N + BN - 1) / BN;
+  const int total = tiles_m * tiles_n * p.splits;
+  const int cluster_id = blockIdx.x >> 1, num_clusters = gridDim.x >> 1;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      for (int i = 0; i < G2_STAGES; ++i) {
+        mbar_init(&full[i], 1);    // the leader's arrive.expect_tx covers the bytes of BOTH CTAs' TMA loads
+        mbar_init(&empty[i], 1);   // multicast commit from the leader's MMA thread
+      }
+      for (int i = 0; i < 2; ++i) {
+        mbar_init(&tfull[i], 1);
+        mbar_init(&tempty[i], 16); // 8 epilogue warps of each CTA (only the leader's copy is waited on)
+      }
+      mbar_fence_init();
+    }
+    __syncwarp();
+    tmem_alloc_2sm<512>(tmem_holder);
+  }
+  tc_fence_before();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_holder;
+
+  if (warp == 0) {
+    // ------------------------------------------------------- TMA producer (one per CTA)
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = cluster_id; tile < total; tile += num_clusters) {
+        const TileCoord tc = decode_tile(tile, tiles_m, tiles_n, nkb, p.splits);
+        const int m0 = tc.m_blk * BM2 + cta * BM;
+        const int n0 = tc.n_blk * BN + cta * BH;
+        for (int kb = tc.kb0; kb < tc.kb1; ++kb) {
+          mbar_wait(&empty[stage], phase ^ 1);
+          const uint32_t lead_bar = mapa_u32(smem_u32(&full[stage]), 0);
+          // the peer only contributes transaction bytes (no arrival: a remote release-arrive per k-block costs a
+          // cluster-scope fence in the single producer thread and halves the throughput)
+          if (leader) mbar_expect_tx(&full[stage], 2 * G2_STAGE_BYTES);
+          uint8_t* a_dst = sA + stage * A_STAGE;
+          uint8_t* b_dst = sB + stage * BH * ROW_BYTES;
+          if (!p.a_mn) {
+            tma_load_2d_2sm(a_dst, &tmA, lead_bar, kb * epr, m0);
+          } else {
+            for (int j = 0; j < BM / epr; ++j) tma_load_2d_2sm(a_dst + j * epr * ROW_BYTES, &tmA, lead_bar, m0 + j * epr, kb * epr);
+          }
+          if (!p.b_mn) {
+            tma_load_2d_2sm(b_dst, &tmB, lead_bar, kb * epr, n0);
+          } else {
+            for (int j = 0; j < BH / epr; ++j) tma_load_2d_2sm(b_dst + j * epr * ROW_BYTES, &tmB, lead_bar, n0 + j * epr, kb * epr);
+          }
+          if (++stage == G2_STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // --------------------------------------------------------- MMA issuer (leader CTA only)
+    if (lane == 0 && leader) {
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      const uint32_t a_kstep = p.a_mn ? 16u * ROW_BYTES : 32u;
+      const uint32_t b_kstep = p.b_mn ? 16u * ROW_BYTES : 32u;
+      const uint32_t a_lbo = p.a_mn ? epr * ROW_BYTES : 16u;
+      const uint32_t b_lbo = p.b_mn ? epr * ROW_BYTES : 16u;
+      for (int tile = cluster_id; tile < total; tile += num_clusters) {
+        const TileCoord tc = decode_tile(tile, tiles_m, tiles_n, nkb, p.splits);
+        mbar_wait(&tempty[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * BN;
+        for (int kb = tc.kb0; kb < tc.kb1; ++kb) {
+          mbar_wait(&full[stage], phase);
+          tc_fence_after();
+          const uint32_t a_base = smem_u32(sA + stage * A_STAGE);
+          const uint32_t b_base = smem_u32(sB + stage * BH * ROW_BYTES);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const uint64_t ad = make_smem_desc_sw128(a_base + k * a_kstep, a_lbo, 1024);
+            const uint64_t bd = make_smem_desc_sw128(b_base + k * b_kstep, b_lbo, 1024);
+            umma_f16_2sm(d_tmem, ad, bd, p.idesc, (kb > tc.kb0 || k > 0) ? 1u : 0u);
+          }
+          umma_commit_2sm(&empty[stage], 3);
+          if (++stage == G2_STAGES) { stage = 0; phase ^= 1; }
+        }
+        umma_commit_2sm(&tfull[acc], 3);
+        acc ^= 1;
+        if (acc == 0) acc_phase ^= 1;
+      }
+    }
+  } else {
+    // ----------------------------------------------------------- epilogue (both CTAs, own 128 rows)
+    const int quarter = warp & 3;
+    const int chalf = (warp - 2) >> 2;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = cluster_id; tile < total; tile += num_clusters) {
+      const TileCoord tc = decode_tile(tile, tiles_m, tiles_n, nkb, p.splits);
+      mbar_wait(&tfull[acc], acc_phase);
+      tc_fence_after();
+      const int row = tc.m_blk * BM2 + cta * BM + quarter * 32 + lane;
+      const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * BN;
+      const bool has_k = tc.kb1 > tc.kb0;
+#pragma unroll 1
+      for (int c = chalf * (BN / 64); c < (chalf + 1) * (BN / 64); ++c) {
+        const int col0 = tc.n_blk * BN + c * 32;
+        if (col0 >= p.N) break;
+        uint32_t r[32];
+        tmem_ld_32x32(t_row + c * 32, r);
+        tmem_ld_wait();
+        if (row < p.M && has_k) {
+          if (EPI != 3 && col0 + 32 <= p.N) {
+            epilogue32<EPI, ACT>(p, r, row, col0);
+          } else {
+#pragma unroll
+            for (int g = 0; g < 4; ++g)
+              epilogue8(&p, __uint_as_float(r[g * 8]), __uint_as_float(r[g * 8 + 1]), __uint_as_float(r[g * 8 + 2]),
+                        __uint_as_float(r[g * 8 + 3]), __uint_as_float(r[g * 8 + 4]), __uint_as_float(r[g * 8 + 5]),
+                        __uint_as_float(r[g * 8 + 6]), __uint_as_float(r[g * 8 + 7]), row, col0 + g * 8);
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(mapa_u32(smem_u32(&tempty[acc]), 0));  // the leader's MMA thread waits on its copy
+      acc ^= 1;
+      if (acc == 0) acc_phase ^= 1;
+    }
+  }
+
+  tc_fence_before();
+  cluster_sync_all();
+  if (warp == 1) tmem_dealloc_2sm<512>(tmem_base);
+}
+
 // ------------------------------------------------------------------ host side
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
@@ -640,6 +815,48 @@ static int dispatch_ag(const CUtensorMap& ta, const CUtensorMap& tb, const Param
   }
   set_error("hyp_gemm_ag: the all-gather fusion supports the forward epilogues only (plain / bias / activation / residual)");
   return -1;
+}
+
+template <int EPI, int ACT>
+static int launch2(const CUtensorMap& ta, const CUtensorMap& tb, const Params& p, cudaStream_t stream) {
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (!attr_set[dev & 63]) {
+    HYP_CHECK_CUDA(cudaFuncSetAttribute(gemm2_kernel<EPI, ACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, G2_SMEM));
+    attr_set[dev & 63] = true;
+  }
+  const int tiles = ((p.M + 2 * BM - 1) / (2 * BM)) * ((p.N + G2_BN - 1) / G2_BN) * p.splits;
+  int clusters = num_sms() / 2;
+  if (tiles < clusters) clusters = tiles;
+  gemm2_kernel<EPI, ACT><<<2 * clusters, NUM_THREADS, G2_SMEM, stream>>>(ta, tb, p);
+  HYP_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+static int dispatch2(const CUtensorMap& ta, const CUtensorMap& tb, const Params& p, int epi, cudaStream_t st) {
+  if (epi == 0) return launch2<0, 0>(ta, tb, p, st);
+  if (epi == 1) {
+    switch (p.act) {
+      case 0: return launch2<1, 0>(ta, tb, p, st);
+      case 1: return launch2<1, 1>(ta, tb, p, st);
+      case 2: return launch2<1, 2>(ta, tb, p, st);
+      case 3: return launch2<1, 3>(ta, tb, p, st);
+      default: return launch2<1, 4>(ta, tb, p, st);
+    }
+  }
+  if (epi == 2) {
+    switch (p.act) {
+      case 1: return launch2<2, 1>(ta, tb, p, st);
+      case 2: return launch2<2, 2>(ta, tb, p, st);
+      case 3: return launch2<2, 3>(ta, tb, p, st);
+      case 4: return launch2<2, 4>(ta, tb, p, st);
+      default: break;
+    }
+  }
+  if (epi == 4) return launch2<4, 0>(ta, tb, p, st);
+  if (epi == 5) return launch2<5, 0>(ta, tb, p, st);
+  return launch2<3, 0>(ta, tb, p, st);
 }
 
 // epilogue kind -> kernel instantiation
@@ -728,6 +945,22 @@ static int gemm_impl(const void* A, const void* B, void* D, int M, int N, int K,
 
   CUtensorMap ta, tb;
   int rc;
+  // 2-CTA (cta_group::2) path: 256 x 256 tiles on CTA pairs; 16-bit operands, large-enough problems
+  static int use_2cta = -1;
+  if (use_2cta < 0) {
+    const char* e = getenv("HYPERION_GEMM_2CTA");
+    use_2cta = e ? atoi(e) : 1;
+  }
+  if (use_2cta && !ag && es == 2 && BN == 256 && M >= 256) {
+    p.idesc = make_idesc(fmt, 2 * gemm::BM, BN, a_mn_major != 0, b_mn_major != 0);
+    if (!a_mn_major) rc = gemm::make_tmap_2d(&ta, A, in_dtype, K, M, lda, epr, gemm::BM);
+    else             rc = gemm::make_tmap_2d(&ta, A, in_dtype, M, K, lda, epr, epr);
+    if (rc) return rc;
+    if (!b_mn_major) rc = gemm::make_tmap_2d(&tb, B, in_dtype, K, N, ldb, epr, BN / 2);
+    else             rc = gemm::make_tmap_2d(&tb, B, in_dtype, N, K, ldb, epr, epr);
+    if (rc) return rc;
+    return gemm::dispatch2(ta, tb, p, epi, stream);
+  }
   if (!a_mn_major) rc = gemm::make_tmap_2d(&ta, A, in_dtype, K, M, lda, epr, gemm::BM);   // A: [M, K]
   else             rc = gemm::make_tmap_2d(&ta, A, in_dtype, M, K, lda, epr, epr);        // A^T: [K, M]
   if (rc) return rc;
