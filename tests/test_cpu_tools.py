@@ -1,0 +1,92 @@
+"""CPU tests of the benchmark tools and CLIs: output schemas must equal the reference's."""
+import csv
+import json
+import subprocess
+import sys
+from pathlib import Path
+
+import pandas as pd
+import torch
+import torch.nn as nn
+
+ROOT = Path(__file__).resolve().parent.parent
+
+
+def test_probe_csv_schemas(tmp_path):
+    from hyperion_b200.bench import probe
+
+    assert probe.main(["--out", str(tmp_path), "--sizes", "256", "--bw-sizes", "10"]) == 0
+    prec = pd.read_csv(tmp_path / "precision_results.csv")
+    assert list(prec.columns)[:4] == ["Size", "Precision", "Time (s)", "TFLOPS"]
+    assert set(prec["Precision"]) == {"FP32", "FP16", "BF16"}
+    bw = pd.read_csv(tmp_path / "bandwidth_results.csv")
+    assert list(bw.columns)[:2] == ["Size (M elements)", "Bandwidth (GB/s)"]
+
+
+def test_benchmark_utils_return_keys():
+    from hyperion_b200.bench.utils import (benchmark_forward_pass, benchmark_training_step, compare_precision_formats,
+                                           save_benchmark_results)
+
+    keys = {"total_time", "avg_time", "throughput", "memory_usage"}
+    net = lambda: nn.Sequential(nn.Linear(16, 32), nn.ReLU(), nn.Linear(32, 16))
+    assert set(benchmark_forward_pass(net(), (16,), 4, 3, 1)) == keys
+    assert set(benchmark_training_step(net(), (16,), (16,), 4, 3, 1)) == keys
+    df = compare_precision_formats(net, (16,), (16,), batch_sizes=(2, 4), precisions=("fp32",), iterations=2, warmup=1)
+    assert len(df) == 2 and {"batch_size", "precision", "throughput"} <= set(df.columns)
+
+
+def test_baseline_benchmark_columns(tmp_path):
+    from hyperion_b200.bench.baseline import COLUMNS, benchmark_model, test_batch_size_scaling as batch_scaling
+    from hyperion_b200.models import create_custom_transformer
+
+    r = benchmark_model(create_custom_transformer, (2, 16, 512), (2, 16, 512), 2, 1)
+    assert set(COLUMNS) <= set(r)
+    assert COLUMNS == ["Model", "Forward Time (ms)", "Backward Time (ms)", "Optimizer Time (ms)", "Total Time (ms)",
+                       "Memory Usage (MB)", "Throughput (samples/s)"]
+    tiny = lambda: nn.Sequential(nn.Flatten(), nn.Linear(3 * 8 * 8, 10))
+    tiny.__name__ = "tiny"
+    df = batch_scaling(tiny, (3, 8, 8), 10, batch_sizes=(1, 2), out_dir=str(tmp_path), iters=2, warmup=1)
+    assert list(df.columns) == COLUMNS + ["Batch Size"]
+    assert (tmp_path / "scaling" / "tiny_batch_scaling.csv").exists()
+
+
+def test_fusion_bench_outputs(tmp_path):
+    from hyperion_b200.bench import fusion
+
+    df = fusion.run(str(tmp_path), "fp32", 1, variants=("eager", "hyperion"))
+    assert list(df.columns) == ["model", "variant", "time_ms", "mem_gb"]
+    assert set(df["model"]) == {"simple_transformer_lm", "resnet18_cifar10"}
+    out = tmp_path / "results/benchmarks/compilation"
+    assert (out / "compilation_ckpt_benchmark.csv").exists() and (out / "compilation_ckpt_analysis.txt").exists()
+    rows = json.loads((out / "compilation_ckpt_benchmark.json").read_text())
+    assert set(rows[0]) == {"model", "variant", "time_ms", "mem_gb"}
+
+
+def test_bench_reference_arm_reports_unavailable():
+    r = subprocess.run([sys.executable, str(ROOT / "bench.py"), "--impl", "reference"], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0
+    d = json.loads(r.stdout.strip().splitlines()[-1])
+    assert d["impl"] == "reference" and "unavailable" in d
+
+
+def test_cli_help_and_data_synth(tmp_path):
+    r = subprocess.run([sys.executable, "-m", "hyperion_b200"], cwd=ROOT, capture_output=True, text=True, timeout=120)
+    assert r.returncode == 2 and "probe" in r.stdout
+    r = subprocess.run([sys.executable, "-m", "hyperion_b200", "data", "synth", "--small", "--base_dir", str(tmp_path)],
+                       cwd=ROOT, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-500:]
+    assert (tmp_path / "data/processed/cifar10_train.pt").exists()
+    assert (tmp_path / "data/processed/wikitext2_tokenized/dataset_dict.json").exists()
+
+
+def test_header_declares_every_exported_entry_point():
+    """include/hyperion_b200.h is the contract: every `HYP_API` symbol in csrc/ must be declared there."""
+    import re
+
+    hdr = (ROOT / "include/hyperion_b200.h").read_text()
+    missing = []
+    for cu in list((ROOT / "csrc").glob("*.cu")) + list((ROOT / "csrc/common").glob("*.cu")):
+        for m in re.finditer(r"HYP_API\s+[\w\s\*]+?\b(hyp_\w+)\s*\(", cu.read_text()):
+            if not re.search(r"\b" + m.group(1) + r"\s*\(", hdr):
+                missing.append(m.group(1))
+    assert not missing, missing
