@@ -612,28 +612,344 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
   if (warp == 1) tmem_dealloc<512>(tmem_base);
 }
 
-// delta[b,h,q] = sum_d dO[b,h,q,d] * O[b,h,q,d]; one thread per row, 16-byte loads.
+// ---------------------------------------------------------------------------------------------------------
+// D = 64 backward, pipelined.  Same maths and tile shapes as flash_bwd_kernel, but at D = 64 tensor memory has room
+// for a dQ tile of its own ([384,448)) and shared memory for two P/dS buffers, so nothing in an iteration has to wait
+// for the previous one to drain:
+//   MMA thread, iteration i:   wait P_i/dS_i -> issue S_{i+1}, dP_{i+1} -> issue dV += P_i^T dO_i, dK += dS_i^T Q_i
+//                              -> (dQ columns drained?) issue dQ_i = dS_i K
+//   softmax warps, iteration i: S_i, dP_i -> P_i, dS_i (buffer i & 1) -> signal -> drain dQ_{i-1} (finished long ago)
+// so the tensor pipe works on iteration i's three gradient MMAs while the softmax warps are already on S_{i+1}.
+// Eight softmax warps: two per TMEM lane quarter, each taking 64 of the 128 key columns of a query row; the row's
+// lse / delta for the next iteration are fetched one iteration ahead; the mask arithmetic exists only in the
+// instantiation used for blocks that need it (diagonal, ragged tail, key padding).
+constexpr int BWD64_THREADS = 320;
+
+struct Bwd64Smem {
+  static constexpr int TILE = 128 * 64 * 2;
+  static constexpr int K_OFF = 0, V_OFF = TILE;
+  static constexpr int Q_OFF = 2 * TILE;              // 2 stages
+  static constexpr int DO_OFF = 4 * TILE;             // 2 stages
+  static constexpr int P_OFF = 6 * TILE;              // 2 buffers of 32 KiB
+  static constexpr int DS_OFF = P_OFF + 2 * 32768;    // 2 buffers of 32 KiB
+  static constexpr int BAR_OFF = DS_OFF + 2 * 32768;
+  static constexpr int TOTAL = BAR_OFF + 384;         // the dynamic window is declared 1024-aligned
+};
+
+// One 32-column chunk of a query row: P and dS from S and dP.  lse2 is +inf for rows that must produce zeros.
+template <typename T, bool MASK>
+__device__ __forceinline__ void bwd_softmax_chunk(uint32_t tS, uint32_t tDP, uint8_t* prow, uint8_t* drow, int chunk_in_row,
+                                                  int r, float scale_log2, float scale, float lse2, float delta_s,
+                                                  int kcol0, int k_limit, const uint8_t* s_kpm_chunk) {
+  uint32_t vs[32], vd[32];
+  tmem_ld_32x32(tS, vs);
+  tmem_ld_32x32(tDP, vd);
+  tmem_ld_wait();
+#pragma unroll
+  for (int t = 0; t < 4; ++t) {
+    float f[8], g[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int e = t * 8 + i;
+      float x = fmaf(__uint_as_float(vs[e]), scale_log2, -lse2);
+      if constexpr (MASK) {
+        bool ok = (kcol0 + e) < k_limit;
+        if (s_kpm_chunk) ok = ok & (s_kpm_chunk[e] != 0);
+        x = ok ? x : -INFINITY;
+      }
+      const float pv = ex2_fast(x);
+      f[i] = pv;
+      g[i] = pv * fmaf(__uint_as_float(vd[e]), scale, -delta_s);
+    }
+    const int cc = (chunk_in_row * 4 + t) ^ (r & 7);
+    *reinterpret_cast<uint4*>(prow + (cc << 4)) = pack8<T>(f);
+    *reinterpret_cast<uint4*>(drow + (cc << 4)) = pack8<T>(g);
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(BWD64_THREADS, 1)
+flash_bwd64_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                   const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmDO,
+                   const __grid_constant__ BwdParams p) {
+  using L = Bwd64Smem;
+  constexpr int D = 64;
+  extern __shared__ __align__(1024) uint8_t smem_bwd64[];
+  uint8_t* smem = smem_bwd64;
+  uint8_t* sK = smem + L::K_OFF;
+  uint8_t* sV = smem + L::V_OFF;
+  uint8_t* sQ = smem + L::Q_OFF;
+  uint8_t* sDO = smem + L::DO_OFF;
+  uint8_t* sP = smem + L::P_OFF;
+  uint8_t* sDS = smem + L::DS_OFF;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::BAR_OFF);
+  uint64_t* kv_full = bars;            // 1
+  uint64_t* qdo_full = bars + 1;       // 2
+  uint64_t* qdo_empty = bars + 3;      // 2
+  uint64_t* sdp_full = bars + 5;
+  uint64_t* pds_full = bars + 6;       // 256 arrivals
+  uint64_t* dq_full = bars + 7;
+  uint64_t* dq_read = bars + 8;        // 256 arrivals
+  uint64_t* done = bars + 9;
+  uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(bars + 10);
+  uint8_t* s_kpm = reinterpret_cast<uint8_t*>(bars + 12);   // 128 bytes
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int j = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
+  const int k0 = j * BKV;
+  const int shift = p.Sk - p.Sq;
+  const int nq_blk = (p.Sq + BQ - 1) / BQ;
+  int i_start = 0;
+  if (p.causal) i_start = max(0, (k0 - shift) / BQ);
+  const int niter = max(0, nq_blk - i_start);
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmQ); tma_prefetch_desc(&tmK); tma_prefetch_desc(&tmV); tma_prefetch_desc(&tmDO);
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      mbar_init(kv_full, 1);
+      for (int s = 0; s < 2; ++s) { mbar_init(&qdo_full[s], 1); mbar_init(&qdo_empty[s], 1); }
+      mbar_init(sdp_full, 1);
+      mbar_init(pds_full, 256);
+      mbar_init(dq_full, 1);
+      mbar_init(dq_read, 256);
+      mbar_init(done, 1);
+      mbar_fence_init();
+    }
+    __syncwarp();
+    tmem_alloc<512>(tmem_holder);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_holder;
+  const uint32_t tS = tmem_base, tDP = tmem_base + 128, tDV = tmem_base + 256, tDK = tmem_base + 320,
+                 tDQ = tmem_base + 384;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      mbar_expect_tx(kv_full, 2 * L::TILE);
+      tma_load_4d(sK, &tmK, kv_full, 0, k0, h, b);
+      tma_load_4d(sV, &tmV, kv_full, 0, k0, h, b);
+      for (int it = 0; it < niter; ++it) {
+        const int st = it & 1;
+        mbar_wait(&qdo_empty[st], ((it >> 1) & 1) ^ 1);
+        mbar_expect_tx(&qdo_full[st], 2 * L::TILE);
+        const int q0 = (i_start + it) * BQ;
+        tma_load_4d(sQ + st * L::TILE, &tmQ, &qdo_full[st], 0, q0, h, b);
+        tma_load_4d(sDO + st * L::TILE, &tmDO, &qdo_full[st], 0, q0, h, b);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0 && niter > 0) {
+      const uint32_t fmt = (p.dtype == DT_F16) ? 0u : 1u;
+      const uint32_t idesc_s = make_idesc(fmt, 128, 128, false, false);
+      const uint32_t idesc_t = make_idesc(fmt, 128, D, true, true);    // dV, dK: A = P^T / dS^T (MN-major), B MN-major
+      const uint32_t idesc_q = make_idesc(fmt, 128, D, false, true);   // dQ: A = dS (K-major), B = K (MN-major)
+      const uint32_t k_base = smem_u32(sK), v_base = smem_u32(sV);
+      auto issue_sdp = [&](int st) {
+        const uint32_t q_base = smem_u32(sQ + st * L::TILE), do_base = smem_u32(sDO + st * L::TILE);
+#pragma unroll
+        for (int k = 0; k < D / 16; ++k)
+          umma_f16(tS, make_smem_desc_sw128(q_base + k * 32, 16, 1024), make_smem_desc_sw128(k_base + k * 32, 16, 1024),
+                   idesc_s, k > 0 ? 1u : 0u);
+#pragma unroll
+        for (int k = 0; k < D / 16; ++k)
+          umma_f16(tDP, make_smem_desc_sw128(do_base + k * 32, 16, 1024), make_smem_desc_sw128(v_base + k * 32, 16, 1024),
+                   idesc_s, k > 0 ? 1u : 0u);
+        umma_commit(sdp_full);
+      };
+      mbar_wait(kv_full, 0);
+      mbar_wait(&qdo_full[0], 0);
+      tc_fence_after();
+      issue_sdp(0);
+      for (int it = 0; it < niter; ++it) {
+        const int st = it & 1;
+        const uint32_t q_base = smem_u32(sQ + st * L::TILE), do_base = smem_u32(sDO + st * L::TILE);
+        const uint32_t p_base = smem_u32(sP + st * 32768), ds_base = smem_u32(sDS + st * 32768);
+        mbar_wait(pds_full, it & 1);   // P_it / dS_it are in shared memory and S / dP have been read out of TMEM
+        tc_fence_after();
+        if (it + 1 < niter) {
+          mbar_wait(&qdo_full[st ^ 1], ((it + 1) >> 1) & 1);
+          tc_fence_after();
+          issue_sdp(st ^ 1);
+        }
+#pragma unroll
+        for (int k = 0; k < BQ / 16; ++k)  // reduction over the 128 query rows
+          umma_f16(tDV, make_smem_desc_sw128(p_base + k * 2048, 16384, 1024),
+                   make_smem_desc_sw128(do_base + k * 2048, 16384, 1024), idesc_t, (it > 0 || k > 0) ? 1u : 0u);
+#pragma unroll
+        for (int k = 0; k < BQ / 16; ++k)
+          umma_f16(tDK, make_smem_desc_sw128(ds_base + k * 2048, 16384, 1024),
+                   make_smem_desc_sw128(q_base + k * 2048, 16384, 1024), idesc_t, (it > 0 || k > 0) ? 1u : 0u);
+        if (it > 0) {
+          mbar_wait(dq_read, (it - 1) & 1);  // dQ_{it-1} has left its columns
+          tc_fence_after();
+        }
+#pragma unroll
+        for (int k = 0; k < BKV / 16; ++k)  // reduction over the 128 keys
+          umma_f16(tDQ, make_smem_desc_sw128(ds_base + (k >> 2) * 16384 + (k & 3) * 32, 16, 1024),
+                   make_smem_desc_sw128(k_base + k * 2048, 16384, 1024), idesc_q, k > 0 ? 1u : 0u);
+        umma_commit(dq_full);
+        umma_commit(&qdo_empty[st]);
+      }
+      umma_commit(done);
+    }
+  } else {
+    const int quarter = warp & 3;
+    const int half = (warp - 2) >> 2;          // which 64 key columns of the row (and which 32 dQ/dK/dV columns)
+    const int r = quarter * 32 + lane;
+    const int tid256 = (warp - 2) * 32 + lane;
+    const uint32_t lane_off = static_cast<uint32_t>(quarter * 32) << 16;
+    if (p.kpm) {
+      if (tid256 < 128) {
+        const int kk = k0 + tid256;
+        s_kpm[tid256] = (kk < p.Sk) ? p.kpm[static_cast<long long>(b) * p.Sk + kk] : 0;
+      }
+      named_bar_sync(1, 256);
+    }
+    const long long bh = static_cast<long long>(b) * p.H + h;
+    auto drain_dq = [&](int it_prev) {
+      const int qi = (i_start + it_prev) * BQ + r;
+      mbar_wait(dq_full, it_prev & 1);
+      tc_fence_after();
+      uint32_t v[32];
+      tmem_ld_32x32(tDQ + lane_off + half * 32, v);
+      tmem_ld_wait();
+      tc_fence_before();
+      mbar_arrive(dq_read);
+      if (qi < p.Sq) {
+        float* dq_row = p.dq_acc + (bh * p.Sq + qi) * D + half * 32;
+#pragma unroll
+        for (int g = 0; g < 8; ++g)
+          atomicAdd(reinterpret_cast<float4*>(dq_row) + g,
+                    make_float4(__uint_as_float(v[4 * g]), __uint_as_float(v[4 * g + 1]), __uint_as_float(v[4 * g + 2]),
+                                __uint_as_float(v[4 * g + 3])));
+      }
+    };
+    float lse_n = INFINITY, delta_n = 0.f;
+    if (niter > 0) {
+      const int qi = i_start * BQ + r;
+      if (qi < p.Sq) { lse_n = p.lse[bh * p.Sq + qi]; delta_n = p.delta[bh * p.Sq + qi]; }
+    }
+    for (int it = 0; it < niter; ++it) {
+      const int q0 = (i_start + it) * BQ;
+      const int qi = q0 + r;
+      // a row with no visible key has lse = -inf: make the exponent -inf instead of nan
+      const float lse2 = (lse_n == -INFINITY || qi >= p.Sq) ? INFINITY : lse_n * LOG2E;
+      const float delta_s = delta_n * p.scale;
+      if (it + 1 < niter) {
+        const int qn = qi + BQ;
+        lse_n = INFINITY; delta_n = 0.f;
+        if (qn < p.Sq) { lse_n = p.lse[bh * p.Sq + qn]; delta_n = p.delta[bh * p.Sq + qn]; }
+      }
+      const bool need_mask = (k0 + BKV > p.Sk) || (p.causal && (k0 + BKV - 1 > q0 + shift)) || (p.kpm != nullptr);
+      uint8_t* prow = sP + (it & 1) * 32768 + half * 16384 + r * 128;
+      uint8_t* drow = sDS + (it & 1) * 32768 + half * 16384 + r * 128;
+      mbar_wait(sdp_full, it & 1);
+      tc_fence_after();
+      if (need_mask) {
+        int k_limit = p.Sk;
+        if (p.causal) k_limit = min(k_limit, qi + shift + 1);
+#pragma unroll 1
+        for (int c = 0; c < 2; ++c) {
+          const int col = half * 64 + c * 32;
+          bwd_softmax_chunk<T, true>(tS + lane_off + col, tDP + lane_off + col, prow, drow, c, r, p.scale_log2, p.scale,
+                                     lse2, delta_s, k0 + col, k_limit, p.kpm ? s_kpm + col : nullptr);
+        }
+      } else {
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          const int col = half * 64 + c * 32;
+          bwd_softmax_chunk<T, false>(tS + lane_off + col, tDP + lane_off + col, prow, drow, c, r, p.scale_log2, p.scale,
+                                      lse2, delta_s, 0, 0, nullptr);
+        }
+      }
+      tc_fence_before();
+      fence_proxy_async_smem();
+      mbar_arrive(pds_full);
+      if (it > 0) drain_dq(it - 1);
+    }
+    if (niter > 0) {
+      drain_dq(niter - 1);
+      mbar_wait(done, 0);
+    }
+    tc_fence_after();
+    // dV_j, dK_j: thread r owns key row k0 + r, columns [half*32, half*32+32)
+    const int kj = k0 + r;
+    T* dv_row = reinterpret_cast<T*>(p.dv) + b * p.dv_sb + h * p.dv_sh + static_cast<long long>(kj) * p.dv_ss + half * 32;
+    T* dk_row = reinterpret_cast<T*>(p.dk) + b * p.dk_sb + h * p.dk_sh + static_cast<long long>(kj) * p.dk_ss + half * 32;
+    uint32_t v[32], w[32];
+    if (niter > 0) {
+      tmem_ld_32x32(tDV + lane_off + half * 32, v);
+      tmem_ld_32x32(tDK + lane_off + half * 32, w);
+      tmem_ld_wait();
+    } else {
+#pragma unroll
+      for (int i = 0; i < 32; ++i) { v[i] = 0u; w[i] = 0u; }
+    }
+    if (kj < p.Sk) {
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {
+        float f[8], e[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { f[i] = __uint_as_float(v[g * 8 + i]); e[i] = __uint_as_float(w[g * 8 + i]); }
+        *reinterpret_cast<uint4*>(dv_row + g * 8) = pack8<T>(f);
+        *reinterpret_cast<uint4*>(dk_row + g * 8) = pack8<T>(e);
+      }
+    }
+    tc_fence_before();
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc<512>(tmem_base);
+}
+
+template <typename T>
+static int launch_bwd64(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const CUtensorMap& tdo,
+                        const BwdParams& p, cudaStream_t st) {
+  using L = Bwd64Smem;
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (!attr_set[dev & 63]) {
+    HYP_CHECK_CUDA(cudaFuncSetAttribute(flash_bwd64_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
+    attr_set[dev & 63] = true;
+  }
+  dim3 grid((p.Sk + BKV - 1) / BKV, p.H, p.B);
+  flash_bwd64_kernel<T><<<grid, BWD64_THREADS, L::TOTAL, st>>>(tq, tk, tv, tdo, p);
+  HYP_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// delta[b,h,q] = sum_d dO[b,h,q,d] * O[b,h,q,d]; D/8 adjacent lanes share a row (one 16-byte load of each operand per
+// lane, so a row is read as one contiguous 128/256-byte segment) and combine with shuffles.
 template <typename T>
 __global__ void __launch_bounds__(256)
 attn_delta_kernel(const T* __restrict__ o, const T* __restrict__ d_o, float* __restrict__ delta, int B, int H, int S, int D,
                   long long o_sb, long long o_sh, long long o_ss, long long g_sb, long long g_sh, long long g_ss) {
-  const long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const int lpr = D >> 3;  // lanes per row: 8 or 16
+  const long long gid = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const long long idx = gid / lpr;
+  const int c = static_cast<int>(gid % lpr) * 8;
   const long long total = static_cast<long long>(B) * H * S;
-  if (idx >= total) return;
-  const int s = static_cast<int>(idx % S);
-  const int h = static_cast<int>((idx / S) % H);
-  const int b = static_cast<int>(idx / (static_cast<long long>(S) * H));
-  const T* po = o + b * o_sb + h * o_sh + static_cast<long long>(s) * o_ss;
-  const T* pg = d_o + b * g_sb + h * g_sh + static_cast<long long>(s) * g_ss;
+  const bool valid = idx < total;
   float acc = 0.f;
-  for (int c = 0; c < D; c += 8) {
+  if (valid) {
+    const int s = static_cast<int>(idx % S);
+    const int h = static_cast<int>((idx / S) % H);
+    const int b = static_cast<int>(idx / (static_cast<long long>(S) * H));
+    const T* po = o + b * o_sb + h * o_sh + static_cast<long long>(s) * o_ss + c;
+    const T* pg = d_o + b * g_sb + h * g_sh + static_cast<long long>(s) * g_ss + c;
     float a[8], g[8];
-    unpack8<T>(*reinterpret_cast<const uint4*>(po + c), a);
-    unpack8<T>(*reinterpret_cast<const uint4*>(pg + c), g);
+    unpack8<T>(ld_nc_v4(po), a);
+    unpack8<T>(ld_nc_v4(pg), g);
 #pragma unroll
     for (int i = 0; i < 8; ++i) acc += a[i] * g[i];
   }
-  delta[idx] = acc;
+  for (int off = lpr >> 1; off > 0; off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
+  if (valid && c == 0) delta[idx] = acc;
 }
 
 template <typename T, int D>
@@ -669,7 +985,7 @@ HYP_API int hyp_flash_attn_bwd(const void* q, const void* k, const void* v, cons
   HYP_REQUIRE(dtype == DT_F16 || dtype == DT_BF16, "hyp_flash_attn_bwd: 16-bit dtypes only");
   HYP_REQUIRE(D == 64 || D == 128, "hyp_flash_attn_bwd: head dim must be 64 or 128 (got %d)", D);
   const long long rows = static_cast<long long>(B) * H * Sq;
-  const int dgrid = static_cast<int>((rows + 255) / 256);
+  const int dgrid = static_cast<int>((rows * (D / 8) + 255) / 256);
   if (dtype == DT_BF16)
     attn::attn_delta_kernel<__nv_bfloat16><<<dgrid, 256, 0, st>>>((const __nv_bfloat16*)o, (const __nv_bfloat16*)d_o, delta, B, H, Sq, D, o_sb, o_sh, o_ss, g_sb, g_sh, g_ss);
   else
@@ -687,6 +1003,11 @@ HYP_API int hyp_flash_attn_bwd(const void* q, const void* k, const void* v, cons
   p.kpm = key_padding_mask; p.lse = lse; p.delta = delta; p.dq_acc = dq_acc; p.dk = dk; p.dv = dv;
   p.dk_sb = dkv_sb; p.dk_sh = dkv_sh; p.dk_ss = dkv_ss; p.dv_sb = dkv_sb; p.dv_sh = dkv_sh; p.dv_ss = dkv_ss;
   p.dtype = dtype;
+  // HYPERION_FLASH_BWD=v1 keeps D = 64 on the non-pipelined kernel (A/B timing only)
+  static const bool v1 = [] { const char* e = getenv("HYPERION_FLASH_BWD"); return e && e[0] == 'v' && e[1] == '1'; }();
+  if (D == 64 && !v1)
+    return dtype == DT_BF16 ? attn::launch_bwd64<__nv_bfloat16>(tq, tk, tv, tdo, p, st)
+                            : attn::launch_bwd64<__half>(tq, tk, tv, tdo, p, st);
   if (dtype == DT_BF16) return D == 64 ? attn::launch_bwd<__nv_bfloat16, 64>(tq, tk, tv, tdo, p, st) : attn::launch_bwd<__nv_bfloat16, 128>(tq, tk, tv, tdo, p, st);
   return D == 64 ? attn::launch_bwd<__half, 64>(tq, tk, tv, tdo, p, st) : attn::launch_bwd<__half, 128>(tq, tk, tv, tdo, p, st);
 }

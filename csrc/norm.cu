@@ -110,48 +110,83 @@ norm_fwd_kernel(const T* __restrict__ x, const T* __restrict__ residual, const T
   }
 }
 
-// dz and per-(block,warp-row) partial dgamma / dbeta.
-// partial layout: [P][2][d] fp32 with P = gridDim.x * RPB.
+// Raw (still packed) 8-element chunk: kept in registers between the two passes over a row so that the 16-bit
+// types cost 4 registers per chunk instead of 8.
+template <typename T> struct Raw8 { uint4 v; };
+template <> struct Raw8<float> { float4 lo, hi; };
+template <typename T>
+__device__ __forceinline__ Raw8<T> load_raw(const T* p) {
+  Raw8<T> r;
+  if constexpr (sizeof(T) == 4) {
+    r.lo = *reinterpret_cast<const float4*>(p);
+    r.hi = *reinterpret_cast<const float4*>(p + 4);
+  } else {
+    r.v = ld_nc_v4(p);
+  }
+  return r;
+}
+template <typename T>
+__device__ __forceinline__ void unpack_raw(const Raw8<T>& r, float (&f)[8]) {
+  if constexpr (sizeof(T) == 4) {
+    f[0] = r.lo.x; f[1] = r.lo.y; f[2] = r.lo.z; f[3] = r.lo.w; f[4] = r.hi.x; f[5] = r.hi.y; f[6] = r.hi.z; f[7] = r.hi.w;
+  } else {
+    unpack8<T>(r.v, f);
+  }
+}
+
+__host__ __device__ constexpr int bwd_block(int tpr) { return tpr == 32 ? 256 : tpr; }
+
+// dz and per-block partial dgamma / dbeta.  partial layout: [gridDim.x][2][d] fp32.
+// TPR == 32 (d <= 1024): eight warps per block, one row per warp per trip; the warps' running sums are folded
+// through shared memory at the end so a block writes one partial row.
 template <typename T, int TPR>
-__global__ void __launch_bounds__(TPR < 128 ? 128 : TPR)
+__global__ void __launch_bounds__(bwd_block(TPR), TPR == 32 ? 2 : 1)
 norm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ z, const T* __restrict__ gamma,
                 const float* __restrict__ mean_in, const float* __restrict__ rstd_in, T* __restrict__ dz,
                 float* __restrict__ partial, int rows, int d, int rms) {
   __shared__ float red[32];
-  constexpr int BLOCK = TPR < 128 ? 128 : TPR;
+  constexpr int BLOCK = bwd_block(TPR);
   constexpr int RPB = BLOCK / TPR;
+  __shared__ __align__(16) float fold[RPB > 1 ? 2 * TPR * 8 * MAXC : 4];
   const int sub = threadIdx.x / TPR;
   const int t = threadIdx.x % TPR;
-  float dg[MAXC][8], db[MAXC][8], g[MAXC][8];
+  float dg[MAXC][8], db[MAXC][8];
 #pragma unroll
   for (int k = 0; k < MAXC; ++k) {
-    const int c = (t + k * TPR) * 8;
 #pragma unroll
-    for (int i = 0; i < 8; ++i) { dg[k][i] = 0.f; db[k][i] = 0.f; g[k][i] = 0.f; }
-    if (c < d) load8<T>(gamma + c, g[k]);
+    for (int i = 0; i < 8; ++i) { dg[k][i] = 0.f; db[k][i] = 0.f; }
   }
   const float inv_d = 1.f / d;
   for (int row = blockIdx.x * RPB + sub; row < rows; row += gridDim.x * RPB) {
     const long long base = static_cast<long long>(row) * d;
     const float mean = rms ? 0.f : mean_in[row];
     const float rstd = rstd_in[row];
-    float xh[MAXC][8], wdy[MAXC][8];
+    Raw8<T> ra[MAXC], rb[MAXC];
+#pragma unroll
+    for (int k = 0; k < MAXC; ++k) {
+      const int c = (t + k * TPR) * 8;
+      if (c < d) {
+        ra[k] = load_raw<T>(dy + base + c);
+        rb[k] = load_raw<T>(z + base + c);
+      }
+    }
     float s1 = 0.f, s2 = 0.f;
 #pragma unroll
     for (int k = 0; k < MAXC; ++k) {
       const int c = (t + k * TPR) * 8;
       if (c < d) {
-        float a[8], b[8];
-        load8<T>(dy + base + c, a);
-        load8<T>(z + base + c, b);
+        float a[8], b[8], g[8];
+        unpack_raw<T>(ra[k], a);
+        unpack_raw<T>(rb[k], b);
+        load8<T>(gamma + c, g);
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-          xh[k][i] = (b[i] - mean) * rstd;
-          wdy[k][i] = a[i] * g[k][i];
-          dg[k][i] += a[i] * xh[k][i];
+          const float xh = (b[i] - mean) * rstd;
+          const float wdy = a[i] * g[i];
+          dg[k][i] += a[i] * xh;
           db[k][i] += a[i];
-          s1 += wdy[k][i];
-          s2 += wdy[k][i] * xh[k][i];
+          s1 += wdy;
+          s2 += wdy * xh;
         }
       }
     }
@@ -161,20 +196,51 @@ norm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ z, const T* __re
     for (int k = 0; k < MAXC; ++k) {
       const int c = (t + k * TPR) * 8;
       if (c < d) {
-        float o[8];
+        float a[8], b[8], g[8], o[8];
+        unpack_raw<T>(ra[k], a);
+        unpack_raw<T>(rb[k], b);
+        load8<T>(gamma + c, g);
 #pragma unroll
-        for (int i = 0; i < 8; ++i) o[i] = rstd * (wdy[k][i] - s1 - xh[k][i] * s2);
+        for (int i = 0; i < 8; ++i) {
+          const float xh = (b[i] - mean) * rstd;
+          o[i] = rstd * (a[i] * g[i] - s1 - xh * s2);
+        }
         store8<T>(dz + base + c, o);
       }
     }
   }
-  float* pg = partial + static_cast<long long>(blockIdx.x * RPB + sub) * 2 * d;
+  float* pg = partial + static_cast<long long>(blockIdx.x) * 2 * d;
+  if constexpr (RPB > 1) {
+    for (int w = 0; w < RPB; ++w) {
+      if (sub == w) {
 #pragma unroll
-  for (int k = 0; k < MAXC; ++k) {
-    const int c = (t + k * TPR) * 8;
-    if (c < d) {
-      store8<float>(pg + c, dg[k]);
-      store8<float>(pg + d + c, db[k]);
+        for (int k = 0; k < MAXC; ++k) {
+          const int c = (t + k * TPR) * 8;
+          if (c < d) {
+            if (w > 0) {
+#pragma unroll
+              for (int i = 0; i < 8; ++i) { dg[k][i] += fold[c + i]; db[k][i] += fold[d + c + i]; }
+            }
+            if (w == RPB - 1) {
+              store8<float>(pg + c, dg[k]);
+              store8<float>(pg + d + c, db[k]);
+            } else {
+              store8<float>(fold + c, dg[k]);
+              store8<float>(fold + d + c, db[k]);
+            }
+          }
+        }
+      }
+      __syncthreads();
+    }
+  } else {
+#pragma unroll
+    for (int k = 0; k < MAXC; ++k) {
+      const int c = (t + k * TPR) * 8;
+      if (c < d) {
+        store8<float>(pg + c, dg[k]);
+        store8<float>(pg + d + c, db[k]);
+      }
     }
   }
 }
@@ -188,6 +254,7 @@ __global__ void __launch_bounds__(256) norm_bwd_reduce_kernel(const float* __res
   const int col = blockIdx.x * 32 + cx;
   float a = 0.f, b = 0.f;
   if (col < d) {
+#pragma unroll 4
     for (int p = py; p < P; p += 8) {
       const float* row = partial + static_cast<long long>(p) * 2 * d;
       a += row[col];
@@ -211,8 +278,7 @@ __global__ void __launch_bounds__(256) norm_bwd_reduce_kernel(const float* __res
 
 inline int pick_tpr(int d) { return d <= 1024 ? 32 : (d <= 4096 ? 128 : 256); }
 inline int bwd_grid(int rows, int tpr) {
-  const int block = tpr < 128 ? 128 : tpr;
-  const int rpb = block / tpr;
+  const int rpb = bwd_block(tpr) / tpr;
   int g = (rows + rpb - 1) / rpb;
   const int cap = num_sms() * 2;
   return g > cap ? cap : g;
@@ -249,9 +315,7 @@ HYP_API int hyp_norm_fwd(const void* x, const void* residual, const void* gamma,
 
 // Bytes of fp32 scratch hyp_norm_bwd needs for (rows, d).
 HYP_API long long hyp_norm_bwd_scratch_bytes(int rows, int d) {
-  const int tpr = norm::pick_tpr(d);
-  const int block = tpr < 128 ? 128 : tpr;
-  const long long P = static_cast<long long>(norm::bwd_grid(rows, tpr)) * (block / tpr);
+  const long long P = norm::bwd_grid(rows, norm::pick_tpr(d));  // one partial row per block
   return P * 2 * d * static_cast<long long>(sizeof(float));
 }
 
@@ -261,8 +325,8 @@ int launch_bwd(const void* dy, const void* z, const void* gamma, const float* me
                cudaStream_t st) {
   const int tpr = pick_tpr(d);
   const int grid = bwd_grid(rows, tpr);
-  const int block = tpr < 128 ? 128 : tpr;
-  const int P = grid * (block / tpr);
+  const int block = bwd_block(tpr);
+  const int P = grid;
 #define HYP_NORM_BWD(T, TPR)                                                                                  \
   norm_bwd_kernel<T, TPR><<<grid, block, 0, st>>>((const T*)dy, (const T*)z, (const T*)gamma, mean, rstd,     \
                                                   (T*)dz, scratch, rows, d, rms)
