@@ -17,6 +17,7 @@
 // (Phase 1/01_hardware_exploration.ipynb c1 L92) and every nn.Linear inside
 // the models (02_development/distributed_utils.py:75-88).
 #include "common/ptx.cuh"
+#include "common/tmap.cuh"
 #include "common/util.cuh"
 #include <stdlib.h>
 #include <string.h>
@@ -54,6 +55,8 @@ struct Params {
   int M, N, K;
   int esize;       // 2 (f16/bf16) or 4 (tf32)
   int a_mn, b_mn;  // operand majors
+  int a_mn_mma, b_mn_mma;  // what the MMA descriptors assume (differs from a_mn/b_mn only under HYPERION_GEMM_DBG)
+  int a_mn3, b_mn3;        // MN-major operand addressed through a rank-3 map: one TMA instruction per stage
   uint32_t idesc;
   int splits;      // split-K factor (fp32 atomic epilogue when > 1)
   // epilogue
@@ -429,12 +432,16 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           uint8_t* b_dst = sB + stage * C::B_STAGE;
           if (!p.a_mn) {
             tma_load_2d(a_dst, &tmA, &full[stage], kb * epr, tc.m_blk * BM);
+          } else if (p.a_mn3) {
+            tma_load_3d(a_dst, &tmA, &full[stage], 0, kb * epr, tc.m_blk * (BM / 64));
           } else {
             for (int j = 0; j < BM / epr; ++j)
               tma_load_2d(a_dst + j * epr * ROW_BYTES, &tmA, &full[stage], tc.m_blk * BM + j * epr, kb * epr);
           }
           if (!p.b_mn) {
             tma_load_2d(b_dst, &tmB, &full[stage], kb * epr, tc.n_blk * BN);
+          } else if (p.b_mn3) {
+            tma_load_3d(b_dst, &tmB, &full[stage], 0, kb * epr, tc.n_blk * (BN / 64));
           } else {
             for (int j = 0; j < BN / epr; ++j)
               tma_load_2d(b_dst + j * epr * ROW_BYTES, &tmB, &full[stage], tc.n_blk * BN + j * epr, kb * epr);
@@ -649,11 +656,15 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
           uint8_t* b_dst = sB + stage * BH * ROW_BYTES;
           if (!p.a_mn) {
             tma_load_2d_2sm(a_dst, &tmA, lead_bar, kb * epr, m0);
+          } else if (p.a_mn3) {
+            tma_load_3d_2sm(a_dst, &tmA, lead_bar, 0, kb * epr, m0 >> 6);
           } else {
             for (int j = 0; j < BM / epr; ++j) tma_load_2d_2sm(a_dst + j * epr * ROW_BYTES, &tmA, lead_bar, m0 + j * epr, kb * epr);
           }
           if (!p.b_mn) {
             tma_load_2d_2sm(b_dst, &tmB, lead_bar, kb * epr, n0);
+          } else if (p.b_mn3) {
+            tma_load_3d_2sm(b_dst, &tmB, lead_bar, 0, kb * epr, n0 >> 6);
           } else {
             for (int j = 0; j < BH / epr; ++j) tma_load_2d_2sm(b_dst + j * epr * ROW_BYTES, &tmB, lead_bar, n0 + j * epr, kb * epr);
           }
@@ -668,10 +679,10 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      const uint32_t a_kstep = p.a_mn ? 16u * ROW_BYTES : 32u;
-      const uint32_t b_kstep = p.b_mn ? 16u * ROW_BYTES : 32u;
-      const uint32_t a_lbo = p.a_mn ? epr * ROW_BYTES : 16u;
-      const uint32_t b_lbo = p.b_mn ? epr * ROW_BYTES : 16u;
+      const uint32_t a_kstep = p.a_mn_mma ? 16u * ROW_BYTES : 32u;
+      const uint32_t b_kstep = p.b_mn_mma ? 16u * ROW_BYTES : 32u;
+      const uint32_t a_lbo = p.a_mn_mma ? epr * ROW_BYTES : 16u;
+      const uint32_t b_lbo = p.b_mn_mma ? epr * ROW_BYTES : 16u;
       for (int tile = cluster_id; tile < total; tile += num_clusters) {
         const TileCoord tc = decode_tile(tile, tiles_m, tiles_n, nkb, p.splits);
         mbar_wait(&tempty[acc], acc_phase ^ 1);
@@ -742,21 +753,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
 }
 
 // ------------------------------------------------------------------ host side
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
-                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
-                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-static EncodeTiledFn get_encode() {
-  static EncodeTiledFn fn = nullptr;
-  if (!fn) {
-    void* f = nullptr;
-    cudaDriverEntryPointQueryResult q;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) == cudaSuccess &&
-        q == cudaDriverEntryPointSuccess)
-      fn = reinterpret_cast<EncodeTiledFn>(f);
-  }
-  return fn;
-}
+static EncodeTiledFn get_encode() { return tmap_encode_fn(); }
 
 // 2D map over a row-major [outer, inner] matrix with leading dimension ld (elements).
 int make_tmap_2d(CUtensorMap* tm, const void* ptr, int dtype, long long inner, long long outer, long long ld,
@@ -781,6 +778,18 @@ int make_tmap_2d(CUtensorMap* tm, const void* ptr, int dtype, long long inner, l
                    CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   HYP_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with CUresult %d", static_cast<int>(r));
   return 0;
+}
+
+// Rank-3 map over an MN-major 16-bit operand stored [K, MN] (leading dimension ld): (64 MN elements, K, MN / 64) with
+// strides (1, ld, 64), so a box (64, 64, chunks) lands in shared memory as `chunks` consecutive [64 k][64 mn] swizzled
+// blocks -- the layout the MN-major UMMA descriptor walks -- with ONE TMA instruction.  Issuing one 64 x 64 box per
+// chunk instead costs 15-40% of the GEMM's throughput (the producer thread becomes the bottleneck).  With a ragged MN the
+// last chunk runs past the row end, so the caller must guarantee ld >= roundup(MN, 64).
+int make_tmap_mn3(CUtensorMap* tm, const void* ptr, int dtype, long long mn, long long k, long long ld, int chunks) {
+  const unsigned long long dims[3] = {64ull, static_cast<unsigned long long>(k), static_cast<unsigned long long>((mn + 63) / 64)};
+  const unsigned long long strides[2] = {static_cast<unsigned long long>(ld) * 2ull, 128ull};
+  const unsigned box[3] = {64u, 64u, static_cast<unsigned>(chunks)};
+  return make_tmap_nd(tm, ptr, dtype, 3, dims, strides, box);
 }
 
 template <int BN, int EPI, int ACT, bool AG = false>
@@ -951,21 +960,35 @@ static int gemm_impl(const void* A, const void* B, void* D, int M, int N, int K,
     const char* e = getenv("HYPERION_GEMM_2CTA");
     use_2cta = e ? atoi(e) : 1;
   }
+  p.a_mn_mma = p.a_mn; p.b_mn_mma = p.b_mn;
+  static const bool mn3_off = [] { const char* e = getenv("HYPERION_GEMM_MN3"); return e && e[0] == '0'; }();
+  // ragged MN is fine when the row padding covers the last chunk's over-read (what it reads there only reaches output
+  // rows / columns that are never stored)
+  p.a_mn3 = (a_mn_major && es == 2 && (M % 64 == 0 || lda >= (M + 63) / 64 * 64) && !mn3_off) ? 1 : 0;
+  p.b_mn3 = (b_mn_major && es == 2 && (N % 64 == 0 || ldb >= (N + 63) / 64 * 64) && !mn3_off) ? 1 : 0;
   if (use_2cta && !ag && es == 2 && BN == 256 && M >= 256) {
-    p.idesc = make_idesc(fmt, 2 * gemm::BM, BN, a_mn_major != 0, b_mn_major != 0);
-    if (!a_mn_major) rc = gemm::make_tmap_2d(&ta, A, in_dtype, K, M, lda, epr, gemm::BM);
-    else             rc = gemm::make_tmap_2d(&ta, A, in_dtype, M, K, lda, epr, epr);
+    static int dbg = -1;  // timing experiments only (results are wrong): 1 = TMA loads K-major boxes, 2 = MMA assumes K-major
+    if (dbg < 0) { const char* e = getenv("HYPERION_GEMM_DBG"); dbg = e ? atoi(e) : 0; }
+    if (dbg & 1) { a_mn_major = 0; b_mn_major = 0; p.a_mn = 0; p.b_mn = 0; }
+    if (dbg & 2) { p.a_mn_mma = 0; p.b_mn_mma = 0; }
+    p.idesc = make_idesc(fmt, 2 * gemm::BM, BN, p.a_mn_mma != 0, p.b_mn_mma != 0);
+    if (!a_mn_major)   rc = gemm::make_tmap_2d(&ta, A, in_dtype, K, M, lda, epr, gemm::BM);
+    else if (p.a_mn3)  rc = gemm::make_tmap_mn3(&ta, A, in_dtype, M, K, lda, gemm::BM / 64);
+    else               rc = gemm::make_tmap_2d(&ta, A, in_dtype, M, K, lda, epr, epr);
     if (rc) return rc;
-    if (!b_mn_major) rc = gemm::make_tmap_2d(&tb, B, in_dtype, K, N, ldb, epr, BN / 2);
-    else             rc = gemm::make_tmap_2d(&tb, B, in_dtype, N, K, ldb, epr, epr);
+    if (!b_mn_major)   rc = gemm::make_tmap_2d(&tb, B, in_dtype, K, N, ldb, epr, BN / 2);
+    else if (p.b_mn3)  rc = gemm::make_tmap_mn3(&tb, B, in_dtype, N, K, ldb, BN / 128);
+    else               rc = gemm::make_tmap_2d(&tb, B, in_dtype, N, K, ldb, epr, epr);
     if (rc) return rc;
     return gemm::dispatch2(ta, tb, p, epi, stream);
   }
-  if (!a_mn_major) rc = gemm::make_tmap_2d(&ta, A, in_dtype, K, M, lda, epr, gemm::BM);   // A: [M, K]
-  else             rc = gemm::make_tmap_2d(&ta, A, in_dtype, M, K, lda, epr, epr);        // A^T: [K, M]
+  if (!a_mn_major)   rc = gemm::make_tmap_2d(&ta, A, in_dtype, K, M, lda, epr, gemm::BM);   // A: [M, K]
+  else if (p.a_mn3)  rc = gemm::make_tmap_mn3(&ta, A, in_dtype, M, K, lda, gemm::BM / 64);
+  else               rc = gemm::make_tmap_2d(&ta, A, in_dtype, M, K, lda, epr, epr);        // A^T: [K, M]
   if (rc) return rc;
-  if (!b_mn_major) rc = gemm::make_tmap_2d(&tb, B, in_dtype, K, N, ldb, epr, BN);         // B: [N, K]
-  else             rc = gemm::make_tmap_2d(&tb, B, in_dtype, N, K, ldb, epr, epr);        // B^T: [K, N]
+  if (!b_mn_major)   rc = gemm::make_tmap_2d(&tb, B, in_dtype, K, N, ldb, epr, BN);         // B: [N, K]
+  else if (p.b_mn3)  rc = gemm::make_tmap_mn3(&tb, B, in_dtype, N, K, ldb, BN / 64);
+  else               rc = gemm::make_tmap_2d(&tb, B, in_dtype, N, K, ldb, epr, epr);        // B^T: [K, N]
   if (rc) return rc;
   if (ag) {
     HYP_REQUIRE(!b_mn_major && splits <= 1, "hyp_gemm_ag: B must be the [N, K] weight layout and split-K is not supported");
