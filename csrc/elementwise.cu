@@ -200,6 +200,28 @@ __global__ void cast_kernel(const TI* __restrict__ x, TO* __restrict__ y, long l
     y[i] = from_f32<TO>(to_f32<TI>(x[i]) * scale);
 }
 
+// fp32 -> 16-bit, 8 elements per thread (two 16-byte loads, one 16-byte store); scale = host value * optional device value
+template <typename TO>
+__global__ void __launch_bounds__(256) cast_f32_vec_kernel(const float* __restrict__ x, TO* __restrict__ y, long long n8,
+                                                           float scale, const float* __restrict__ scale_ptr) {
+  const float sc = scale_ptr ? scale * *scale_ptr : scale;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n8; i += stride) {
+    const float4 a = *reinterpret_cast<const float4*>(x + i * 8);
+    const float4 b = *reinterpret_cast<const float4*>(x + i * 8 + 4);
+    float f[8] = {a.x * sc, a.y * sc, a.z * sc, a.w * sc, b.x * sc, b.y * sc, b.z * sc, b.w * sc};
+    *reinterpret_cast<uint4*>(y + i * 8) = pack8<TO>(f);
+  }
+}
+template <typename TI, typename TO>
+__global__ void cast_dscale_kernel(const TI* __restrict__ x, TO* __restrict__ y, long long n, float scale,
+                                   const float* __restrict__ scale_ptr) {
+  const float sc = scale_ptr ? scale * *scale_ptr : scale;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride)
+    y[i] = from_f32<TO>(to_f32<TI>(x[i]) * sc);
+}
+
 static inline int stream_grid(long long work_items, int threads) {
   long long b = (work_items + threads - 1) / threads;
   const long long cap = static_cast<long long>(num_sms()) * 8;
@@ -286,11 +308,20 @@ HYP_API int hyp_swiglu_bwd(const void* gate, const void* up, const void* dout, v
   return 0;
 }
 
-HYP_API int hyp_cast(const void* x, void* y, long long n, int in_dtype, int out_dtype, float scale, void* stream_) {
-  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+static int cast_impl(const void* x, void* y, long long n, int in_dtype, int out_dtype, float scale, const float* scale_ptr,
+                     cudaStream_t st) {
   if (n == 0) return 0;
+  const bool vec = in_dtype == DT_F32 && out_dtype != DT_F32 && n % 8 == 0 &&
+                   reinterpret_cast<uintptr_t>(x) % 16 == 0 && reinterpret_cast<uintptr_t>(y) % 16 == 0;
+  if (vec) {
+    const int gv = stream_grid(n / 8, 256);
+    if (out_dtype == DT_BF16) cast_f32_vec_kernel<__nv_bfloat16><<<gv, 256, 0, st>>>((const float*)x, (__nv_bfloat16*)y, n / 8, scale, scale_ptr);
+    else cast_f32_vec_kernel<__half><<<gv, 256, 0, st>>>((const float*)x, (__half*)y, n / 8, scale, scale_ptr);
+    HYP_CHECK_CUDA(cudaGetLastError());
+    return 0;
+  }
   const int g = stream_grid(n, 256);
-#define HYP_CAST_CASE(TI, TO) cast_kernel<TI, TO><<<g, 256, 0, st>>>((const TI*)x, (TO*)y, n, scale)
+#define HYP_CAST_CASE(TI, TO) cast_dscale_kernel<TI, TO><<<g, 256, 0, st>>>((const TI*)x, (TO*)y, n, scale, scale_ptr)
   if (in_dtype == DT_F32 && out_dtype == DT_BF16) HYP_CAST_CASE(float, __nv_bfloat16);
   else if (in_dtype == DT_F32 && out_dtype == DT_F16) HYP_CAST_CASE(float, __half);
   else if (in_dtype == DT_BF16 && out_dtype == DT_F32) HYP_CAST_CASE(__nv_bfloat16, float);
@@ -302,4 +333,15 @@ HYP_API int hyp_cast(const void* x, void* y, long long n, int in_dtype, int out_
 #undef HYP_CAST_CASE
   HYP_CHECK_CUDA(cudaGetLastError());
   return 0;
+}
+
+HYP_API int hyp_cast(const void* x, void* y, long long n, int in_dtype, int out_dtype, float scale, void* stream_) {
+  return cast_impl(x, y, n, in_dtype, out_dtype, scale, nullptr, reinterpret_cast<cudaStream_t>(stream_));
+}
+
+// y = cast(x * scale * *scale_ptr): the extra factor is read on the device (e.g. the incoming gradient of a scalar loss),
+// so the caller never has to bring it to the host.
+HYP_API int hyp_cast_dscale(const void* x, void* y, long long n, int in_dtype, int out_dtype, float scale,
+                            const float* scale_ptr, void* stream_) {
+  return cast_impl(x, y, n, in_dtype, out_dtype, scale, scale_ptr, reinterpret_cast<cudaStream_t>(stream_));
 }

@@ -142,8 +142,8 @@ __host__ __device__ constexpr int bwd_block(int tpr) { return tpr == 32 ? 256 : 
 template <typename T, int TPR>
 __global__ void __launch_bounds__(bwd_block(TPR), TPR == 32 ? 2 : 1)
 norm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ z, const T* __restrict__ gamma,
-                const float* __restrict__ mean_in, const float* __restrict__ rstd_in, T* __restrict__ dz,
-                float* __restrict__ partial, int rows, int d, int rms) {
+                const float* __restrict__ mean_in, const float* __restrict__ rstd_in, const T* __restrict__ dres,
+                T* __restrict__ dz, float* __restrict__ partial, int rows, int d, int rms) {
   __shared__ float red[32];
   constexpr int BLOCK = bwd_block(TPR);
   constexpr int RPB = BLOCK / TPR;
@@ -205,6 +205,12 @@ norm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ z, const T* __re
           const float xh = (b[i] - mean) * rstd;
           o[i] = rstd * (a[i] * g[i] - s1 - xh * s2);
         }
+        if (dres) {  // gradient arriving through the skip connection that forked off the norm's input
+          float e[8];
+          load8<T>(dres + base + c, e);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) o[i] += e[i];
+        }
         store8<T>(dz + base + c, o);
       }
     }
@@ -246,9 +252,10 @@ norm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ z, const T* __re
 }
 
 // Column reduce of the partials: out[0][c] = sum_p partial[p][0][c] etc.
+// out_dtype: DT_F32 (dgamma / dbeta are float*, optional accumulate) or a 16-bit code (they point at T storage).
 __global__ void __launch_bounds__(256) norm_bwd_reduce_kernel(const float* __restrict__ partial, int P, int d,
-                                                              float* __restrict__ dgamma, float* __restrict__ dbeta,
-                                                              int accumulate) {
+                                                              void* __restrict__ dgamma, void* __restrict__ dbeta,
+                                                              int accumulate, int out_dtype) {
   __shared__ float red[2][8][32];
   const int cx = threadIdx.x & 31, py = threadIdx.x >> 5;
   const int col = blockIdx.x * 32 + cx;
@@ -270,8 +277,17 @@ __global__ void __launch_bounds__(256) norm_bwd_reduce_kernel(const float* __res
 #pragma unroll
     for (int k = 0; k < 8; ++k) s += red[which][k][cx];
     if (col < d) {
-      float* out = which ? dbeta : dgamma;
-      if (out) out[col] = accumulate ? out[col] + s : s;
+      void* out = which ? dbeta : dgamma;
+      if (out) {
+        if (out_dtype == DT_F32) {
+          float* o = reinterpret_cast<float*>(out);
+          o[col] = accumulate ? o[col] + s : s;
+        } else if (out_dtype == DT_BF16) {
+          reinterpret_cast<__nv_bfloat16*>(out)[col] = __float2bfloat16(s);
+        } else {
+          reinterpret_cast<__half*>(out)[col] = __float2half(s);
+        }
+      }
     }
   }
 }
@@ -321,15 +337,15 @@ HYP_API long long hyp_norm_bwd_scratch_bytes(int rows, int d) {
 
 namespace hyp { namespace norm {
 int launch_bwd(const void* dy, const void* z, const void* gamma, const float* mean, const float* rstd, void* dz,
-               float* dgamma, float* dbeta, float* scratch, int rows, int d, int rms, int dtype, int accumulate,
-               cudaStream_t st) {
+               void* dgamma, void* dbeta, float* scratch, int rows, int d, int rms, int dtype, int accumulate,
+               cudaStream_t st, const void* dres = nullptr, int param_dtype = DT_F32) {
   const int tpr = pick_tpr(d);
   const int grid = bwd_grid(rows, tpr);
   const int block = bwd_block(tpr);
   const int P = grid;
 #define HYP_NORM_BWD(T, TPR)                                                                                  \
   norm_bwd_kernel<T, TPR><<<grid, block, 0, st>>>((const T*)dy, (const T*)z, (const T*)gamma, mean, rstd,     \
-                                                  (T*)dz, scratch, rows, d, rms)
+                                                  (const T*)dres, (T*)dz, scratch, rows, d, rms)
 #define HYP_NORM_BWD_T(T)             \
   if (tpr == 32) HYP_NORM_BWD(T, 32); \
   else if (tpr == 128) HYP_NORM_BWD(T, 128); \
@@ -340,7 +356,7 @@ int launch_bwd(const void* dy, const void* z, const void* gamma, const float* me
 #undef HYP_NORM_BWD_T
 #undef HYP_NORM_BWD
   HYP_CHECK_CUDA(cudaGetLastError());
-  norm_bwd_reduce_kernel<<<(d + 31) / 32, 256, 0, st>>>(scratch, P, d, dgamma, dbeta, accumulate);
+  norm_bwd_reduce_kernel<<<(d + 31) / 32, 256, 0, st>>>(scratch, P, d, dgamma, dbeta, accumulate, param_dtype);
   HYP_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -355,6 +371,22 @@ HYP_API int hyp_norm_bwd(const void* dy, const void* z, const void* gamma, const
               "hyp_norm_bwd: scratch too small (%lld < %lld bytes)", scratch_bytes, hyp_norm_bwd_scratch_bytes(rows, d));
   return norm::launch_bwd(dy, z, gamma, mean, rstd, dz, dgamma, dbeta, reinterpret_cast<float*>(scratch), rows, d, rms,
                           dtype, accumulate, st);
+}
+
+// hyp_norm_bwd with two fusions for pre-norm residual blocks: `dres` (same shape/dtype as dz, may be null) is added to
+// dz -- the gradient that reaches the norm's input through the skip connection, which autograd would otherwise add
+// with a separate elementwise pass -- and dgamma / dbeta are written in `param_dtype` (DT_F32, or the 16-bit dtype of
+// the parameters so they can land directly in the flat gradient buffer).
+HYP_API int hyp_norm_bwd_fused(const void* dy, const void* z, const void* gamma, const float* mean, const float* rstd,
+                               const void* dres, void* dz, void* dgamma, void* dbeta, int param_dtype, void* scratch,
+                               long long scratch_bytes, int rows, int d, int rms, int dtype, void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  HYP_REQUIRE(rows > 0 && d > 0 && d % 8 == 0 && d <= 8192, "hyp_norm_bwd_fused: need d %% 8 == 0 and d <= 8192 (d=%d)", d);
+  HYP_REQUIRE(param_dtype == DT_F32 || param_dtype == DT_F16 || param_dtype == DT_BF16, "hyp_norm_bwd_fused: bad param dtype");
+  HYP_REQUIRE(scratch != nullptr && scratch_bytes >= hyp_norm_bwd_scratch_bytes(rows, d),
+              "hyp_norm_bwd_fused: scratch too small (%lld < %lld bytes)", scratch_bytes, hyp_norm_bwd_scratch_bytes(rows, d));
+  return norm::launch_bwd(dy, z, gamma, mean, rstd, dz, dgamma, dbeta, reinterpret_cast<float*>(scratch), rows, d, rms,
+                          dtype, 0, st, dres, param_dtype);
 }
 
 // ---------------------------------------------------------------------------------------------------------

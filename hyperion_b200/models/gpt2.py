@@ -76,8 +76,11 @@ class Block(nn.Module):
         self.mlp = _MLP(c)
 
     def forward(self, x):
-        x = self.attn(ops.layer_norm(x, self.ln_1.weight, self.ln_1.bias, self.ln_1.eps), residual=x)
-        return self.mlp(ops.layer_norm(x, self.ln_2.weight, self.ln_2.bias, self.ln_2.eps), residual=x)
+        # layer_norm_fork hands back x for the skip connection, so the backward sums both branches in the norm kernel
+        h, skip = ops.layer_norm_fork(x, self.ln_1.weight, self.ln_1.bias, self.ln_1.eps)
+        x = self.attn(h, residual=skip)
+        h, skip = ops.layer_norm_fork(x, self.ln_2.weight, self.ln_2.bias, self.ln_2.eps)
+        return self.mlp(h, residual=skip)
 
 
 class GPT2LMHeadModel(nn.Module):

@@ -51,6 +51,10 @@ class LlamaRMSNorm(nn.Module):
     def forward(self, x):
         return ops.rms_norm(x, self.weight, self.eps)
 
+    def fork(self, x):
+        """(norm(x), x) with the skip-connection gradient summed inside the norm backward (ops.rms_norm_fork)."""
+        return ops.rms_norm_fork(x, self.weight, self.eps)
+
 
 def _proj(module, x, residual=None):
     """Apply a (possibly LoRA-wrapped) bias-free projection."""
@@ -109,8 +113,10 @@ class LlamaDecoderLayer(nn.Module):
         self.post_attention_layernorm = LlamaRMSNorm(c.hidden_size, c.rms_norm_eps)
 
     def forward(self, x, attention_mask=None):
-        x = self.self_attn(self.input_layernorm(x), attention_mask, residual=x)
-        return self.mlp(self.post_attention_layernorm(x), residual=x)
+        h, skip = self.input_layernorm.fork(x)
+        x = self.self_attn(h, attention_mask, residual=skip)
+        h, skip = self.post_attention_layernorm.fork(x)
+        return self.mlp(h, residual=skip)
 
 
 class LlamaModel(nn.Module):

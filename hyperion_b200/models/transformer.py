@@ -69,13 +69,13 @@ class TransformerEncoderLayer(nn.Module):
     def forward(self, x, causal: bool = False, key_padding_mask=None):
         drop = self.training and self.p > 0.0
         if self.norm_first:
-            h = ops.layer_norm(x, self.norm1.weight, self.norm1.bias, self.norm1.eps)
+            h, skip = ops.layer_norm_fork(x, self.norm1.weight, self.norm1.bias, self.norm1.eps)
             if drop:
-                x = x + F.dropout(self.self_attn(h, causal, key_padding_mask), self.p, True)
+                x = skip + F.dropout(self.self_attn(h, causal, key_padding_mask), self.p, True)
             else:
-                x = self.self_attn(h, causal, key_padding_mask, residual=x)
-            h = ops.layer_norm(x, self.norm2.weight, self.norm2.bias, self.norm2.eps)
-            return self._ffn(h, residual=x)
+                x = self.self_attn(h, causal, key_padding_mask, residual=skip)
+            h, skip = ops.layer_norm_fork(x, self.norm2.weight, self.norm2.bias, self.norm2.eps)
+            return self._ffn(h, residual=skip)
         # post-norm: x = LN(x + sublayer(x)); the residual add is fused into the norm kernel
         a = self.self_attn(x, causal, key_padding_mask)
         if drop:

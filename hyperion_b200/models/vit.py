@@ -35,10 +35,10 @@ class EncoderBlock(nn.Module):
         self.mlp = _MLP(dim, hidden, dropout)
 
     def forward(self, x):
-        h = ops.layer_norm(x, self.ln_1.weight, self.ln_1.bias, 1e-6)
-        x = self.self_attention(h, residual=x)
-        h = ops.layer_norm(x, self.ln_2.weight, self.ln_2.bias, 1e-6)
-        return ops.mlp(h, self.mlp[0].weight, self.mlp[0].bias, self.mlp[3].weight, self.mlp[3].bias, act="gelu", residual=x)
+        h, skip = ops.layer_norm_fork(x, self.ln_1.weight, self.ln_1.bias, 1e-6)
+        x = self.self_attention(h, residual=skip)
+        h, skip = ops.layer_norm_fork(x, self.ln_2.weight, self.ln_2.bias, 1e-6)
+        return ops.mlp(h, self.mlp[0].weight, self.mlp[0].bias, self.mlp[3].weight, self.mlp[3].bias, act="gelu", residual=skip)
 
 
 class Encoder(nn.Module):

@@ -30,8 +30,10 @@ _SIGS = {
     "hyp_swiglu_fwd": "ppplip",
     "hyp_swiglu_bwd": "ppppplip",
     "hyp_cast": "ppliifp",
+    "hyp_cast_dscale": "ppliifpp",
     "hyp_norm_fwd": "ppppppppiifiip",
     "hyp_norm_bwd": "pppppppppliiiiip",
+    "hyp_norm_bwd_fused": "pppppppppipliiiip",
     "hyp_adamw": "ppppplii" + "fffff" + "i" + "f" + "ppppp",
     "hyp_sumsq": "plipp",
     "hyp_ce_fwd_bwd": "plpiilpppfiip",
@@ -115,7 +117,7 @@ def stream_ptr(device=None) -> int:
 
 _launches = 0
 # kernels launched per entry-point call (everything not listed launches exactly one)
-_KERNELS_PER_CALL = {"hyp_norm_bwd": 2, "hyp_ipc_alloc": 0, "hyp_ipc_open": 0, "hyp_ipc_close": 0, "hyp_ipc_free": 0}
+_KERNELS_PER_CALL = {"hyp_norm_bwd": 2, "hyp_norm_bwd_fused": 2, "hyp_ipc_alloc": 0, "hyp_ipc_open": 0, "hyp_ipc_close": 0, "hyp_ipc_free": 0}
 
 
 def launch_count() -> int:

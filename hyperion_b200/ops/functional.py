@@ -13,7 +13,7 @@ import math
 import torch
 import torch.nn.functional as F
 
-from . import _lib, native
+from . import _lib, gradslot, native
 
 _SUPPORTED = (torch.float32, torch.float16, torch.bfloat16)
 
@@ -61,10 +61,11 @@ def _padded_copy(t2: torch.Tensor) -> torch.Tensor:
 _SM_COUNT = 148
 
 
-def _wgrad(dy2: torch.Tensor, x2: torch.Tensor, out_dtype) -> torch.Tensor:
-    """dW[N, K] = dy2[M, N]^T @ x2[M, K] (both operands MN-major).  The output has few tiles (N*K is small next to
-    the token count M), so the reduction is split across SMs: split-K partial tiles are reduced with vector fp32
-    atomics, then rounded to the parameter dtype."""
+def _wgrad(dy2: torch.Tensor, x2: torch.Tensor, out_dtype, slot=None) -> torch.Tensor:
+    """dW[N, K] = dy2[M, N]^T @ x2[M, K] (both operands MN-major).  When the output has few tiles (N*K is small next
+    to the token count M) the reduction is split across SMs: split-K partial tiles are reduced with vector fp32
+    atomics, then rounded to the parameter dtype.  ``slot``: the weight's gradient slot (ops/gradslot.py) -- when it
+    can be claimed the result is stored straight into the flat gradient buffer."""
     N, K = dy2.shape[1], x2.shape[1]
     splits = 1
     if min(N, K) >= 256:
@@ -77,13 +78,28 @@ def _wgrad(dy2: torch.Tensor, x2: torch.Tensor, out_dtype) -> torch.Tensor:
         tiles = ((N + 127) // 128) * ((K + 255) // 256 if K > 128 else 1)
         if tiles < 120 and dy2.shape[0] >= 2048:
             splits = min(8, max(1, (2 * _SM_COUNT) // tiles), dy2.shape[0] // 512)
+    es = torch.empty((), dtype=out_dtype).element_size()
+    dst = gradslot.claim(slot, out_dtype) if (K * es) % 16 == 0 else None
+    if dst is not None:
+        dst = dst.view(N, K)
     if splits > 1 and (K * 4) % 16 == 0:
         acc = torch.zeros((N, K), device=dy2.device, dtype=torch.float32)
         native.gemm(dy2, x2, a_mn_major=True, b_mn_major=True, out=acc, splits=splits)
-        return acc if out_dtype == torch.float32 else native.cast(acc, out_dtype)
-    out = _padded_empty(N, K, out_dtype, dy2.device)
+        if out_dtype == torch.float32:
+            return acc if dst is None else dst.copy_(acc)
+        return native.cast(acc, out_dtype, out=dst)
+    out = dst if dst is not None else _padded_empty(N, K, out_dtype, dy2.device)
     native.gemm(dy2, x2, a_mn_major=True, b_mn_major=True, out=out)
     return out if out.is_contiguous() else out.contiguous()
+
+
+def _bias_grad(dy2: torch.Tensor, dtype, slot=None) -> torch.Tensor:
+    """db[N] = column sums of dy2 (fp32 accumulation), rounded into the bias's gradient slot when it can be claimed."""
+    acc = native.colsum(dy2)
+    if dtype == torch.float32:
+        dst = gradslot.claim(slot, dtype)
+        return acc if dst is None else dst.copy_(acc)
+    return native.cast(acc, dtype, out=gradslot.claim(slot, dtype))
 
 
 def _act_ref(x, act):
@@ -120,6 +136,7 @@ class _LinearFn(torch.autograd.Function):
         ctx.has_bias = b is not None
         ctx.has_res = residual is not None
         ctx.x_shape = x.shape
+        ctx.slots = (gradslot.slot_of(w), gradslot.slot_of(b) if b is not None else None)
         # relu'(h) is recoverable from the output only when no residual was added
         if act == "relu":
             if residual is not None:
@@ -144,9 +161,9 @@ class _LinearFn(torch.autograd.Function):
             dx = native.gemm(dh, w2, b_mn_major=True, out=_padded_empty(dh.shape[0], w2.shape[1], dh.dtype, dh.device))
             dx = dx.reshape(ctx.x_shape)
         if ctx.needs_input_grad[1]:
-            dw = _wgrad(dh, x2, w2.dtype)
+            dw = _wgrad(dh, x2, w2.dtype, ctx.slots[0])
         if ctx.has_bias and ctx.needs_input_grad[2]:
-            db = native.colsum(dh).to(dy.dtype)
+            db = _bias_grad(dh, dy.dtype, ctx.slots[1])
         if ctx.has_res and ctx.needs_input_grad[3]:
             dres = dy
         return dx, dw, db, dres, None, None
@@ -202,6 +219,7 @@ class _MlpFn(torch.autograd.Function):
         ctx.save_for_backward(x2, w1, w2, h, a)
         ctx.act = act
         ctx.flags = (b1 is not None, b2 is not None, residual is not None)
+        ctx.slots = tuple(gradslot.slot_of(t) if t is not None else None for t in (w1, b1, w2, b2))
         ctx.x_shape = x.shape
         return y.reshape(*x.shape[:-1], w2.shape[0])
 
@@ -212,11 +230,12 @@ class _MlpFn(torch.autograd.Function):
         has_b1, has_b2, has_res = ctx.flags
         # dh = (dy @ W2) * act'(h): activation derivative applied in the GEMM epilogue
         dh = native.gemm(dy2, w2, b_mn_major=True, aux=h, act=ctx.act, mode=1)
-        dw2 = _wgrad(dy2, a, w2.dtype)
-        dw1 = _wgrad(dh, x2, w1.dtype)
+        s_w1, s_b1, s_w2, s_b2 = ctx.slots
+        dw2 = _wgrad(dy2, a, w2.dtype, s_w2)
+        dw1 = _wgrad(dh, x2, w1.dtype, s_w1)
         dx = native.gemm(dh, w1, b_mn_major=True).reshape(ctx.x_shape) if ctx.needs_input_grad[0] else None
-        db1 = native.colsum(dh).to(dy.dtype) if has_b1 else None
-        db2 = native.colsum(dy2).to(dy.dtype) if has_b2 else None
+        db1 = _bias_grad(dh, dy.dtype, s_b1) if has_b1 else None
+        db2 = _bias_grad(dy2, dy.dtype, s_b2) if has_b2 else None
         return dx, dw1, db1, dw2, db2, (dy if has_res else None), None, None, None
 
 
@@ -230,6 +249,21 @@ def mlp(x, w1, b1, w2, b2, act: str = "relu", residual=None):
 
 
 # --------------------------------------------------------------------------- norms
+def _norm_param_grads(ctx, dy, dres):
+    """Shared backward of the norm ops: dz (+ dres), dgamma / dbeta stored into their gradient slots when claimable."""
+    z, gamma, mean, rstd = ctx.saved_tensors
+    s_g, s_b = ctx.slots
+    g_out = gradslot.claim(s_g, gamma.dtype)
+    b_out = gradslot.claim(s_b, gamma.dtype) if ctx.has_beta else None
+    dz, dgamma, dbeta = native.norm_bwd(dy.contiguous(), z, gamma, mean, rstd, rms=ctx.rms, need_beta=ctx.has_beta,
+                                        dres=dres.contiguous() if dres is not None else None,
+                                        dgamma_out=g_out, dbeta_out=b_out)
+    dgamma = dgamma if dgamma.dtype == gamma.dtype else dgamma.to(gamma.dtype)
+    if dbeta is not None and dbeta.dtype != gamma.dtype:
+        dbeta = dbeta.to(gamma.dtype)
+    return dz, dgamma, dbeta
+
+
 class _NormFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, gamma, beta, residual, eps, rms):
@@ -240,14 +274,36 @@ class _NormFn(torch.autograd.Function):
         ctx.rms = rms
         ctx.has_beta = beta is not None
         ctx.has_res = residual is not None
+        ctx.slots = (gradslot.slot_of(gamma), gradslot.slot_of(beta) if beta is not None else None)
         return y
 
     @staticmethod
     def backward(ctx, dy):
-        z, gamma, mean, rstd = ctx.saved_tensors
-        dz, dgamma, dbeta = native.norm_bwd(dy.contiguous(), z, gamma, mean, rstd, rms=ctx.rms, need_beta=ctx.has_beta)
-        return (dz, dgamma.to(gamma.dtype), dbeta.to(gamma.dtype) if dbeta is not None else None,
-                dz if ctx.has_res else None, None, None)
+        dz, dgamma, dbeta = _norm_param_grads(ctx, dy, None)
+        return dz, dgamma, dbeta, dz if ctx.has_res else None, None, None
+
+
+class _NormForkFn(torch.autograd.Function):
+    """(norm(x), x): the second output is x itself, handed on to the skip connection of a pre-norm block.  Owning the
+    fork lets the backward add the skip-connection gradient to dz inside the norm-backward kernel instead of leaving
+    the sum of the two branches to a separate autograd elementwise pass."""
+
+    @staticmethod
+    def forward(ctx, x, gamma, beta, eps, rms):
+        xc = x.contiguous()
+        y, _, mean, rstd = native.norm_fwd(xc, gamma, beta, residual=None, eps=eps, rms=rms)
+        ctx.save_for_backward(xc, gamma, mean, rstd)
+        ctx.rms = rms
+        ctx.has_beta = beta is not None
+        ctx.slots = (gradslot.slot_of(gamma), gradslot.slot_of(beta) if beta is not None else None)
+        return y, x.view_as(x)
+
+    @staticmethod
+    def backward(ctx, dy, dskip):
+        if dy is None:  # only the skip branch was used
+            return dskip, None, None, None, None
+        dz, dgamma, dbeta = _norm_param_grads(ctx, dy, dskip)
+        return dz, dgamma, dbeta, None, None
 
 
 def layer_norm(x, gamma, beta, eps: float = 1e-5, residual=None):
@@ -257,6 +313,23 @@ def layer_norm(x, gamma, beta, eps: float = 1e-5, residual=None):
         return _NormFn.apply(x, gamma, beta, residual, eps, False)
     z = x if residual is None else x + residual
     return F.layer_norm(z, (d,), gamma, beta, eps)
+
+
+def layer_norm_fork(x, gamma, beta, eps: float = 1e-5):
+    """``(LayerNorm(x), x)`` for a pre-norm residual block: feed the second value to the skip connection
+    (``residual=`` of the block's last linear) so the backward sums both branches inside the norm kernel."""
+    d = x.shape[-1]
+    if _native(x, gamma) and d % 8 == 0 and d <= 8192:
+        return _NormForkFn.apply(x, gamma, beta, eps, False)
+    return F.layer_norm(x, (d,), gamma, beta, eps), x
+
+
+def rms_norm_fork(x, gamma, eps: float = 1e-6):
+    """RMSNorm flavour of :func:`layer_norm_fork`."""
+    d = x.shape[-1]
+    if _native(x, gamma) and d % 8 == 0 and d <= 8192:
+        return _NormForkFn.apply(x, gamma, None, eps, True)
+    return rms_norm(x, gamma, eps), x
 
 
 def rms_norm(x, gamma, eps: float = 1e-6, residual=None):
@@ -276,6 +349,7 @@ class _EmbeddingFn(torch.autograd.Function):
         ctx.shape = table.shape
         ctx.dtype = table.dtype
         ctx.padding_idx = -1 if padding_idx is None else padding_idx
+        ctx.slot = gradslot.slot_of(table)
         return native.embedding_fwd(table, idx.contiguous())
 
     @staticmethod
@@ -283,7 +357,9 @@ class _EmbeddingFn(torch.autograd.Function):
         (idx,) = ctx.saved_tensors
         dt = torch.zeros(ctx.shape, device=dout.device, dtype=torch.float32)
         native.embedding_bwd(dout.contiguous(), idx.contiguous(), dt, ctx.padding_idx)
-        return None, dt.to(ctx.dtype), None
+        if ctx.dtype == torch.float32:
+            return None, dt, None
+        return None, native.cast(dt, ctx.dtype, out=gradslot.claim(ctx.slot, ctx.dtype)), None
 
 
 def embedding(idx, table, padding_idx=None):
@@ -331,15 +407,17 @@ class _LinearCEFn(torch.autograd.Function):
         native.ce_finalize(sum_count, loss)
         ctx.save_for_backward(dx, dw, db)
         ctx.x_shape, ctx.w_dtype = x.shape, w.dtype
+        ctx.slots = (gradslot.slot_of(w), gradslot.slot_of(b) if b is not None else None)
         return loss
 
     @staticmethod
     def backward(ctx, dloss):
         dx, dw, db = ctx.saved_tensors
-        s = dloss.to(torch.float32)
+        s = dloss.to(torch.float32).reshape(1)
         gx = (dx * s.to(dx.dtype)).reshape(ctx.x_shape)
-        gw = (dw * s).to(ctx.w_dtype)
-        gb = (db * s).to(ctx.w_dtype) if db is not None else None
+        # scale by the incoming gradient and round in one pass, into the head's gradient slot when it is free
+        gw = native.cast(dw, ctx.w_dtype, scale_t=s, out=gradslot.claim(ctx.slots[0], ctx.w_dtype))
+        gb = native.cast(db, ctx.w_dtype, scale_t=s, out=gradslot.claim(ctx.slots[1], ctx.w_dtype)) if db is not None else None
         return gx, gw, gb, None, None, None
 
 
@@ -463,6 +541,7 @@ class _LoraLinearFn(torch.autograd.Function):
         ctx.save_for_backward(x2, xd2, w, A, B, t)
         ctx.scaling, ctx.same = scaling, same
         ctx.has_bias, ctx.has_res = b is not None, residual is not None
+        ctx.slots = (gradslot.slot_of(A), gradslot.slot_of(B))
         ctx.x_shape = x.shape
         return y.reshape(*x.shape[:-1], w.shape[0])
 
@@ -472,8 +551,9 @@ class _LoraLinearFn(torch.autograd.Function):
         dy2 = _as2d(dy)
         need_x, need_xd, need_w = ctx.needs_input_grad[0], ctx.needs_input_grad[1], ctx.needs_input_grad[2]
         dt = native.gemm(dy2, B, b_mn_major=True, alpha=ctx.scaling)        # [M, r]
-        dB = native.gemm(dy2, t, a_mn_major=True, b_mn_major=True)          # [out, r]
-        dA = native.gemm(dt, xd2, a_mn_major=True, b_mn_major=True)         # [r, in]
+        s_A, s_B = ctx.slots
+        dB = native.gemm(dy2, t, a_mn_major=True, b_mn_major=True, out=gradslot.claim(s_B, B.dtype))    # [out, r]
+        dA = native.gemm(dt, xd2, a_mn_major=True, b_mn_major=True, out=gradslot.claim(s_A, A.dtype))   # [r, in]
         dx = dxd = None
         if need_x or (ctx.same and need_xd):
             dx = native.gemm(dy2, w, b_mn_major=True)

@@ -94,10 +94,17 @@ def swiglu_bwd(gate, up, dout):
     return dgate, dup
 
 
-def cast(x: torch.Tensor, dtype: torch.dtype, scale: float = 1.0, out: torch.Tensor | None = None) -> torch.Tensor:
+def cast(x: torch.Tensor, dtype: torch.dtype, scale: float = 1.0, out: torch.Tensor | None = None,
+         scale_t: torch.Tensor | None = None) -> torch.Tensor:
+    """``out = (x * scale * scale_t).to(dtype)``; ``scale_t`` is an fp32 device scalar read by the kernel."""
     if out is None:
         out = torch.empty(x.shape, device=x.device, dtype=dtype)
-    call("hyp_cast", ptr(x), ptr(out), x.numel(), DT[x.dtype], DT[dtype], float(scale), stream_ptr())
+    assert out.numel() == x.numel() and out.dtype == dtype and out.is_contiguous() and x.is_contiguous()
+    if scale_t is not None:
+        assert scale_t.dtype == torch.float32 and scale_t.numel() == 1
+        call("hyp_cast_dscale", ptr(x), ptr(out), x.numel(), DT[x.dtype], DT[dtype], float(scale), ptr(scale_t), stream_ptr())
+    else:
+        call("hyp_cast", ptr(x), ptr(out), x.numel(), DT[x.dtype], DT[dtype], float(scale), stream_ptr())
     return out
 
 
@@ -125,16 +132,32 @@ def _get_scratch(device, nbytes: int) -> torch.Tensor:
     return buf
 
 
-def norm_bwd(dy, z, gamma, mean, rstd, rms: bool = False, need_beta: bool = True):
+def norm_bwd(dy, z, gamma, mean, rstd, rms: bool = False, need_beta: bool = True, dres=None, dgamma_out=None,
+             dbeta_out=None):
+    """dz (+ ``dres``: the skip-connection gradient, added in the same pass), dgamma, dbeta.  ``dgamma_out`` /
+    ``dbeta_out``: contiguous tensors of gamma's dtype (e.g. flat-gradient slots) that receive the parameter
+    gradients directly; otherwise they come back as fresh fp32 tensors."""
     d = z.shape[-1]
     rows = z.numel() // d
     dz = torch.empty_like(z)
-    dgamma = torch.empty(d, device=z.device, dtype=torch.float32)
-    dbeta = torch.empty(d, device=z.device, dtype=torch.float32) if (need_beta and not rms) else None
     nbytes = _lib.require().hyp_norm_bwd_scratch_bytes(rows, d)
     scratch = _get_scratch(z.device, nbytes)
-    call("hyp_norm_bwd", ptr(dy), ptr(z), ptr(gamma), ptr(mean), ptr(rstd), ptr(dz), ptr(dgamma), ptr(dbeta),
-         ptr(scratch), scratch.numel(), rows, d, int(rms), DT[z.dtype], 0, stream_ptr())
+    want_beta = need_beta and not rms
+    if dres is None and dgamma_out is None and dbeta_out is None:
+        dgamma = torch.empty(d, device=z.device, dtype=torch.float32)
+        dbeta = torch.empty(d, device=z.device, dtype=torch.float32) if want_beta else None
+        call("hyp_norm_bwd", ptr(dy), ptr(z), ptr(gamma), ptr(mean), ptr(rstd), ptr(dz), ptr(dgamma), ptr(dbeta),
+             ptr(scratch), scratch.numel(), rows, d, int(rms), DT[z.dtype], 0, stream_ptr())
+        return dz, dgamma, dbeta
+    # fused variant: parameter gradients are written in ONE dtype -- the slots' when given, else fp32
+    pdt = dgamma_out.dtype if dgamma_out is not None else (dbeta_out.dtype if dbeta_out is not None else torch.float32)
+    dgamma = dgamma_out if dgamma_out is not None else torch.empty(d, device=z.device, dtype=pdt)
+    dbeta = (dbeta_out if dbeta_out is not None else torch.empty(d, device=z.device, dtype=pdt)) if want_beta else None
+    assert dgamma.dtype == pdt and (dbeta is None or dbeta.dtype == pdt)
+    if dres is not None:
+        assert dres.shape == z.shape and dres.dtype == z.dtype and dres.is_contiguous()
+    call("hyp_norm_bwd_fused", ptr(dy), ptr(z), ptr(gamma), ptr(mean), ptr(rstd), ptr(dres), ptr(dz), ptr(dgamma),
+         ptr(dbeta), DT[pdt], ptr(scratch), scratch.numel(), rows, d, int(rms), DT[z.dtype], stream_ptr())
     return dz, dgamma, dbeta
 
 

@@ -18,6 +18,8 @@ from dataclasses import dataclass
 import torch
 import torch.nn as nn
 
+from ..ops.gradslot import GradSlot
+
 ALIGN_BYTES = 256
 
 
@@ -74,18 +76,47 @@ class FlatParams:
         self.grad = galloc(self.numel, self.dtype, self.device)
         self.data.zero_()
         self.grad.zero_()
+        self.stray_copies = 0  # gradients that arrived outside their slot and had to be copied in (see ops/gradslot.py)
+        self.slots: list[GradSlot] = []
         with torch.no_grad():
             for s in self.specs:
                 view = self.data[s.offset:s.offset + s.numel].view(s.param.shape)
                 view.copy_(s.param.data.to(self.dtype))
                 s.param.data = view
-                s.param.grad = self.grad[s.offset:s.offset + s.numel].view(s.param.shape)
+                s.param.grad = None
+                slot = GradSlot(self, s)
+                s.param._hyp_slot = slot
+                self.slots.append(slot)
+                # registered before any DDP / FSDP hook, so those see the gradient in the flat buffer
+                s.param.register_post_accumulate_grad_hook(self._make_settle_hook(slot))
+
+    def _make_settle_hook(self, slot: GradSlot):
+        es = torch.empty((), dtype=self.dtype).element_size()
+
+        def settle(param):
+            g = param.grad
+            if g is None:
+                return
+            if g.data_ptr() != self.grad.data_ptr() + slot.spec.offset * es or g.dtype != self.grad.dtype:
+                view = slot.view()
+                with torch.no_grad():
+                    view.copy_(g)
+                param.grad = view
+                self.stray_copies += 1
+
+        return settle
+
+    def grad_view(self, i: int) -> torch.Tensor:
+        """View of parameter ``i``'s range of the flat gradient (what ``param.grad`` is after a backward)."""
+        return self.slots[i].view()
 
     def zero_grad(self) -> None:
+        """Zero the flat gradient and leave every ``param.grad`` undefined, so the next backward's kernels can store
+        straight into the slots (ops/gradslot.py); after a backward ``param.grad`` is the slot view again."""
         self.grad.zero_()
-        for s in self.specs:  # re-attach in case something set .grad to None
-            if s.param.grad is None or s.param.grad.data_ptr() != self.grad.data_ptr() + s.offset * self.grad.element_size():
-                s.param.grad = self.grad[s.offset:s.offset + s.numel].view(s.param.shape)
+        for slot in self.slots:
+            slot.claimed = False
+            slot.spec.param.grad = None
 
     def rebind(self, data: torch.Tensor | None = None, grad: torch.Tensor | None = None) -> None:
         """Point parameters / grads at new flat buffers of the same size (contents are copied)."""
@@ -99,7 +130,8 @@ class FlatParams:
                 grad.copy_(self.grad)
                 self.grad = grad
                 for s in self.specs:
-                    s.param.grad = grad[s.offset:s.offset + s.numel].view(s.param.shape)
+                    if s.param.grad is not None:
+                        s.param.grad = grad[s.offset:s.offset + s.numel].view(s.param.shape)
 
     def buckets(self, cap_bytes: int, first_cap_bytes: int | None = None) -> list[tuple[int, int, list[int]]]:
         """Contiguous (start, end, [spec indices]) element ranges of at most ``cap_bytes`` (whole parameters)."""

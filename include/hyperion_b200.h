@@ -53,6 +53,9 @@ int hyp_swiglu_fwd(const void* gate, const void* up, void* out, long long n, int
 int hyp_swiglu_bwd(const void* gate, const void* up, const void* dout, void* dgate, void* dup, long long n, int dtype,
                    void* stream);
 int hyp_cast(const void* x, void* y, long long n, int in_dtype, int out_dtype, float scale, void* stream);
+/* hyp_cast with one more factor read from device memory (fp32 scalar, may be NULL). */
+int hyp_cast_dscale(const void* x, void* y, long long n, int in_dtype, int out_dtype, float scale, const float* scale_ptr,
+                    void* stream);
 
 /* ---- fused_norm (csrc/norm.cu) ----------------------------------------------
  * z = x (+ residual); y = LayerNorm(z) or RMSNorm(z) (rms != 0). sum_out (optional)
@@ -67,6 +70,14 @@ long long hyp_norm_bwd_scratch_bytes(int rows, int d);
 int hyp_norm_bwd(const void* dy, const void* z, const void* gamma, const float* mean, const float* rstd, void* dz,
                  float* dgamma, float* dbeta, void* scratch, long long scratch_bytes, int rows, int d, int rms,
                  int dtype, int accumulate, void* stream);
+
+/* hyp_norm_bwd for pre-norm residual blocks: `dres` (may be NULL) is the gradient reaching the norm's input through
+ * the skip connection and is added to dz in the same pass; dgamma / dbeta are written as `param_dtype` (0 fp32,
+ * 1 fp16, 2 bf16) so they can be stored straight into a 16-bit flat gradient buffer.  No reference counterpart
+ * (autograd adds the two branches with a separate elementwise kernel there). */
+int hyp_norm_bwd_fused(const void* dy, const void* z, const void* gamma, const float* mean, const float* rstd,
+                       const void* dres, void* dz, void* dgamma, void* dbeta, int param_dtype, void* scratch,
+                       long long scratch_bytes, int rows, int d, int rms, int dtype, void* stream);
 
 /* hyp_norm_bwd without caller scratch.  It has no counterpart in the reference: it exists for callers that
  * cannot allocate device memory at the point where they call us -- a plugin inside another runtime's callback,

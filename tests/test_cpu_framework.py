@@ -286,3 +286,41 @@ def test_fsdp_unit_policy_matches_reference_wrap():
     assert len(units) == 8
     sizes = sorted(sum(p.numel() for p in u.parameters()) for u in units)
     assert sizes[-1] == 12_916_049 and sizes[-2] == 12_865_792
+
+
+def test_flat_params_gradient_slots_cpu():
+    """param.grad is undefined after zero_grad, is the flat-buffer view after a backward (whatever autograd did to get
+    there), accumulates across backwards, and tied parameters sum."""
+    from hyperion_b200.parallel.flat import FlatParams
+
+    torch.manual_seed(0)
+
+    class Tied(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.emb = nn.Embedding(11, 8)
+            self.lin = nn.Linear(8, 8)
+
+        def forward(self, idx):
+            return torch.nn.functional.linear(self.lin(self.emb(idx)), self.emb.weight)  # emb.weight used twice
+
+    m = Tied()
+    ref = copy.deepcopy(m)
+    flat = FlatParams(m.named_parameters())
+    assert all(p.grad is None for p in m.parameters())
+    idx = torch.randint(0, 11, (5, 3))
+    m(idx).square().mean().backward()
+    ref(idx).square().mean().backward()
+    es = flat.grad.element_size()
+    for s, (n, q) in zip(flat.specs[::-1], ref.named_parameters()):
+        assert s.name == n
+        assert s.param.grad.data_ptr() == flat.grad.data_ptr() + s.offset * es   # settled into its slot
+        assert torch.allclose(s.param.grad, q.grad, atol=1e-6)
+    assert flat.stray_copies > 0   # plain torch ops know nothing about slots: their gradients are copied in
+    # second backward without zero_grad accumulates in place
+    m(idx).square().mean().backward()
+    for s, (n, q) in zip(flat.specs[::-1], ref.named_parameters()):
+        assert torch.allclose(s.param.grad, 2 * q.grad, atol=1e-6)
+    flat.zero_grad()
+    assert all(p.grad is None for p in m.parameters()) and float(flat.grad.abs().sum()) == 0.0
+    assert all(not sl.claimed for sl in flat.slots)

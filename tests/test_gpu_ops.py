@@ -235,3 +235,66 @@ def test_bn_act_fused_matches_torch(relu, with_res):
     for a, c in zip(grads, gref):
         assert _rel(a, c) < 4e-2
     assert torch.allclose(rm, rm2, atol=1e-3) and torch.allclose(rv, rv2, atol=1e-3)
+
+
+@pytest.mark.parametrize("rms", [False, True])
+def test_norm_fork_op_sums_skip_gradient_in_kernel(ops, rms):
+    """(norm(x), x): the backward's dz must equal norm-backward + the gradient of the skip branch."""
+    torch.manual_seed(11)
+    x, g, b = _leaf(4, 96, 1024), _leaf(1024), _leaf(1024)
+    y, skip = ops.rms_norm_fork(x, g, 1e-5) if rms else ops.layer_norm_fork(x, g, b, 1e-5)
+    assert skip.data_ptr() == x.data_ptr()
+    dy, ds = torch.randn_like(y), torch.randn_like(y)
+    ins = [x, g] + ([] if rms else [b])
+    grads = torch.autograd.grad([y, skip], ins, [dy, ds])
+    xr, gr_, br = _ref_copy(x, g, b)
+    yr = xr * torch.rsqrt(xr.pow(2).mean(-1, keepdim=True) + 1e-5) * gr_ if rms else F.layer_norm(xr, (1024,), gr_, br, 1e-5)
+    gref = torch.autograd.grad([yr, xr * 1.0], [xr, gr_] + ([] if rms else [br]), [dy.float(), ds.float()])
+    assert _rel(y, yr) < 2e-2
+    for a, c in zip(grads, gref):
+        assert _rel(a, c) < 3e-2
+    # only the skip branch used
+    y2, skip2 = ops.layer_norm_fork(x, g, b, 1e-5)
+    (gx,) = torch.autograd.grad(skip2, [x], ds)
+    assert torch.equal(gx, ds)
+
+
+def test_gradient_slots_receive_kernel_output_directly():
+    """With FlatParams, the wgrad / bias / norm / head kernels store into the flat gradient buffer and autograd adopts
+    those views (no stray copies); the values equal the slot-less run."""
+    from hyperion_b200.models import GPT2Config, GPT2LMHeadModel
+    from hyperion_b200.ops import gradslot
+    from hyperion_b200.parallel.flat import FlatParams
+
+    torch.manual_seed(12)
+    cfg = GPT2Config(vocab_size=1024, n_positions=128, n_embd=128, n_layer=2, n_head=2)
+    model = GPT2LMHeadModel(cfg).cuda().to(torch.bfloat16)
+    ref = copy.deepcopy(model)
+    ids = torch.randint(0, 1024, (2, 128), device="cuda")
+    flat = FlatParams(model.named_parameters())
+    model.loss(ids).backward()
+    ref.loss(ids).backward()
+    es = flat.grad.element_size()
+    # wpe is the only parameter whose gradient is produced twice... no: wte is (head + embedding); everything else lands directly
+    assert flat.stray_copies <= 1, flat.stray_copies
+    for (n, p), (_, q) in zip(model.named_parameters(), ref.named_parameters()):
+        s = p._hyp_slot.spec
+        assert p.grad.data_ptr() == flat.grad.data_ptr() + s.offset * es, n
+        assert _rel(p.grad, q.grad) < 2e-2, (n, _rel(p.grad, q.grad))
+    # accumulation: a second backward adds in place
+    g1 = flat.grad.clone()
+    model.loss(ids).backward()
+    assert _rel(flat.grad, 2 * g1.float()) < 2e-2
+    # next step after zero_grad claims again
+    flat.zero_grad()
+    n0 = flat.stray_copies
+    model.loss(ids).backward()
+    assert flat.stray_copies - n0 <= 1 and _rel(flat.grad, g1) < 1e-2
+    # switch off: same numbers through ordinary autograd accumulation
+    flat.zero_grad()
+    gradslot.ENABLED = False
+    try:
+        model.loss(ids).backward()
+    finally:
+        gradslot.ENABLED = True
+    assert _rel(flat.grad, g1) < 1e-2
