@@ -952,6 +952,26 @@ attn_delta_kernel(const T* __restrict__ o, const T* __restrict__ d_o, float* __r
   if (valid && c == 0) delta[idx] = acc;
 }
 
+// dq[b,h,s,:] (16-bit, arbitrary b/h/s strides) = round(dq_acc[b,h,s,:]) -- the fp32 accumulator the backward reduces
+// into, converted into its slot of the packed gradient buffer; 8 elements per thread.
+template <typename T>
+__global__ void __launch_bounds__(256)
+dq_convert_kernel(const float* __restrict__ acc, T* __restrict__ dq, int B, int H, int S, int D, long long sb, long long sh,
+                  long long ss) {
+  const int lpr = D >> 3;
+  const long long gid = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const long long row = gid / lpr;
+  const int c = static_cast<int>(gid % lpr) * 8;
+  if (row >= static_cast<long long>(B) * H * S) return;
+  const int s = static_cast<int>(row % S);
+  const int h = static_cast<int>((row / S) % H);
+  const int b = static_cast<int>(row / (static_cast<long long>(S) * H));
+  const float4 a0 = *reinterpret_cast<const float4*>(acc + row * D + c);
+  const float4 a1 = *reinterpret_cast<const float4*>(acc + row * D + c + 4);
+  const float f[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+  *reinterpret_cast<uint4*>(dq + b * sb + h * sh + static_cast<long long>(s) * ss + c) = pack8<T>(f);
+}
+
 template <typename T, int D>
 static int launch_bwd(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const CUtensorMap& tdo,
                       const BwdParams& p, cudaStream_t st) {
@@ -1010,4 +1030,21 @@ HYP_API int hyp_flash_attn_bwd(const void* q, const void* k, const void* v, cons
                             : attn::launch_bwd64<__half>(tq, tk, tv, tdo, p, st);
   if (dtype == DT_BF16) return D == 64 ? attn::launch_bwd<__nv_bfloat16, 64>(tq, tk, tv, tdo, p, st) : attn::launch_bwd<__nv_bfloat16, 128>(tq, tk, tv, tdo, p, st);
   return D == 64 ? attn::launch_bwd<__half, 64>(tq, tk, tv, tdo, p, st) : attn::launch_bwd<__half, 128>(tq, tk, tv, tdo, p, st);
+}
+
+// dq (16-bit, [b,h,s,d] through element strides, unit stride in d) = dq_acc (fp32 contiguous [B,H,S,D]).
+HYP_API int hyp_flash_dq_convert(const float* dq_acc, void* dq, int B, int H, int S, int D, long long sb, long long sh,
+                                 long long ss, int dtype, void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  HYP_REQUIRE(dtype == DT_F16 || dtype == DT_BF16, "hyp_flash_dq_convert: 16-bit outputs only");
+  HYP_REQUIRE(D % 8 == 0 && (sb % 8 == 0) && (sh % 8 == 0) && (ss % 8 == 0) && reinterpret_cast<uintptr_t>(dq) % 16 == 0,
+              "hyp_flash_dq_convert: rows must be 16-byte aligned");
+  const long long threads = static_cast<long long>(B) * H * S * (D / 8);
+  const int grid = static_cast<int>((threads + 255) / 256);
+  if (dtype == DT_BF16)
+    attn::dq_convert_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(dq_acc, (__nv_bfloat16*)dq, B, H, S, D, sb, sh, ss);
+  else
+    attn::dq_convert_kernel<__half><<<grid, 256, 0, st>>>(dq_acc, (__half*)dq, B, H, S, D, sb, sh, ss);
+  HYP_CHECK_CUDA(cudaGetLastError());
+  return 0;
 }

@@ -160,6 +160,66 @@ __global__ void __launch_bounds__(256) colsum8_kernel(const T* __restrict__ x, f
   if (c < N) atomicAdd(out + c, t);
 }
 
+// Column sums rounded to 16 bits in ONE launch (bias gradients): blocks add their partial sums into `acc` (fp32, all
+// zero on entry), count themselves in `counter`, and the last block to finish rounds acc into out16 and puts acc and
+// counter back to zero -- so the caller keeps one persistent workspace and never has to clear or convert anything.
+template <typename T>
+__global__ void __launch_bounds__(256) colsum8_cast_kernel(const T* __restrict__ x, T* __restrict__ out16,
+                                                           float* __restrict__ acc, unsigned* __restrict__ counter, int M,
+                                                           int N, long long ld, int rows_per_block) {
+  __shared__ float red[8][256 + 8];
+  __shared__ bool is_last;
+  const int cx = threadIdx.x & 31, ry = threadIdx.x >> 5;
+  const int col = blockIdx.x * 256 + cx * 8;
+  const int r0 = blockIdx.y * rows_per_block;
+  const int r1 = min(M, r0 + rows_per_block);
+  float s[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) s[i] = 0.f;
+  if (col < N) {
+    const T* base = x + col;
+    int r = r0 + ry;
+    for (; r + 24 < r1; r += 32) {
+      uint4 v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) v[u] = ld_nc_v4(reinterpret_cast<const uint4*>(base + static_cast<long long>(r + 8 * u) * ld));
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        float f[8];
+        unpack8<T>(v[u], f);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) s[i] += f[i];
+      }
+    }
+    for (; r < r1; r += 8) {
+      float f[8];
+      unpack8<T>(ld_nc_v4(reinterpret_cast<const uint4*>(base + static_cast<long long>(r) * ld)), f);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) s[i] += f[i];
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) red[ry][cx * 8 + i] = s[i];
+  __syncthreads();
+  float t = 0.f;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) t += red[k][threadIdx.x];
+  const int c = blockIdx.x * 256 + threadIdx.x;
+  if (c < N) atomicAdd(acc + c, t);
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) is_last = atomicAdd(counter, 1u) == gridDim.x * gridDim.y - 1;
+  __syncthreads();
+  if (is_last) {
+    __threadfence();
+    for (int i = threadIdx.x; i < N; i += 256) {
+      out16[i] = from_f32<T>(__ldcg(acc + i));
+      acc[i] = 0.f;
+    }
+    if (threadIdx.x == 0) *counter = 0u;
+  }
+}
+
 // SwiGLU: out = silu(gate) * up, and its backward.
 template <typename T>
 __global__ void swiglu_fwd_kernel(const T* __restrict__ gate, const T* __restrict__ up, T* __restrict__ out,
@@ -280,6 +340,30 @@ HYP_API int hyp_colsum(const void* x, float* out, int M, int N, long long ld, in
     if (vec) colsum8_kernel<__half><<<grid, 256, 0, st>>>((const __half*)x, out, M, N, ld, rpb);
     else colsum_kernel<__half><<<grid, 256, 0, st>>>((const __half*)x, out, M, N, ld, rpb);
   }
+  HYP_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// out16[c] = round(sum_r x[r, c]) for 16-bit x; acc_ws: >= N fp32 zeros, counter: one zero word -- both are returned
+// zeroed, so the same workspace serves every call on a stream.  Needs N % 8 == 0 and 16-byte aligned rows.
+HYP_API int hyp_colsum_cast(const void* x, void* out16, int M, int N, long long ld, int dtype, float* acc_ws,
+                            unsigned* counter, void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  HYP_REQUIRE(M > 0 && N > 0, "hyp_colsum_cast: empty input");
+  HYP_REQUIRE(dtype == DT_F16 || dtype == DT_BF16, "hyp_colsum_cast: 16-bit inputs only");
+  HYP_REQUIRE(N % 8 == 0 && ld % 8 == 0 && reinterpret_cast<uintptr_t>(x) % 16 == 0,
+              "hyp_colsum_cast: needs N %% 8 == 0 and 16-byte aligned rows (N=%d ld=%lld)", N, ld);
+  const int gx = (N + 255) / 256;
+  int gy = (num_sms() * 4 + gx - 1) / gx;
+  if (gy > (M + 31) / 32) gy = (M + 31) / 32;
+  if (gy < 1) gy = 1;
+  const int rpb = (M + gy - 1) / gy;
+  gy = (M + rpb - 1) / rpb;
+  dim3 grid(gx, gy);
+  if (dtype == DT_BF16)
+    colsum8_cast_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)out16, acc_ws, counter, M, N, ld, rpb);
+  else
+    colsum8_cast_kernel<__half><<<grid, 256, 0, st>>>((const __half*)x, (__half*)out16, acc_ws, counter, M, N, ld, rpb);
   HYP_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

@@ -28,6 +28,10 @@ namespace gemm {
 constexpr int BM = 128;
 constexpr int ROW_BYTES = 128;  // one swizzle row: 64 x 16-bit or 32 x fp32
 constexpr int A_STAGE = BM * ROW_BYTES;
+// per-warp shared-memory stage of the coalesced epilogue (see epilogue32s)
+constexpr int STG_ROW = 80;
+constexpr int STG_WARP_BYTES = 32 * STG_ROW;
+constexpr int STG_BYTES = 8 * STG_WARP_BYTES;   // eight epilogue warps
 constexpr int NUM_THREADS = 320;  // warp0 TMA, warp1 MMA, warps2-9 epilogue (two warps per TMEM lane quarter)
 constexpr int GROUP_M = 8;
 
@@ -82,7 +86,7 @@ struct Cfg {
   static constexpr int STAGES = (BN == 256) ? 4 : 6;
   static constexpr int B_STAGE = BN * ROW_BYTES;
   static constexpr int TMEM_COLS = 2 * BN;
-  static constexpr int SMEM_BYTES = STAGES * (A_STAGE + B_STAGE) + 256 + 1024;
+  static constexpr int SMEM_BYTES = STAGES * (A_STAGE + B_STAGE) + 256 + STG_BYTES + 1024;
 };
 
 __device__ __forceinline__ float load_as_f32(const void* p, long long idx, int dt) {
@@ -229,6 +233,112 @@ __device__ __forceinline__ TileCoord decode_tile(int tile, int tiles_m, int tile
 //   EPI 4: D += alpha*acc with red.global.add.v4.f32           (split-K partial tiles, fp32 output)
 //   EPI 5: D = alpha*acc + beta*D                              (gradient accumulation)
 // Requires 16-byte aligned rows (vec_ok), a full 32-column chunk, 16-bit aux / preact.
+// ---- staged (coalesced) epilogue for 16-bit tensors -------------------------------------------------------------
+// A thread owns one accumulator row (TMEM lane), so storing its 32 columns directly makes every warp-level store
+// touch 32 different rows: 32 L1 transactions for 512 bytes, and an epilogue with two outputs and one input
+// (bias + GELU + pre-activation, or act' * aux) runs longer than the 256x256x1024 main loop it should hide behind.
+// Instead each warp bounces its 32 x 32 tile through a private 2.5 KB shared-memory stage: the row owner writes /
+// reads 64 B rows there, and global memory is accessed with 4 lanes per row (64 B contiguous, 8 rows per
+// instruction).  Stage rows are padded to 80 B so 16-byte accesses by 8 consecutive rows hit 32 distinct banks.
+
+// the 16-bit tile this epilogue kind reads back (residual / activation input / beta*D), or null
+template <int EPI>
+__device__ __forceinline__ const uint16_t* epi_input(const Params& p, long long* ld) {
+  if ((EPI == 1 || EPI == 2) && p.aux) { *ld = p.ld_aux; return reinterpret_cast<const uint16_t*>(p.aux); }
+  if (EPI == 5 && p.out_dtype != DT_F32) { *ld = p.ldd; return reinterpret_cast<const uint16_t*>(p.D); }
+  *ld = 0;
+  return nullptr;
+}
+// issue the coalesced loads of that tile (lane -> row 8i + lane/4, 16-byte segment lane%4)
+template <int EPI>
+__device__ __forceinline__ void epi_prefetch(const Params& p, uint4 (&pre)[4], int row0, int lane, int col0) {
+  long long ld;
+  const uint16_t* base = epi_input<EPI>(p, &ld);
+  if (base == nullptr) return;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int gr = row0 + i * 8 + (lane >> 2);
+    pre[i] = make_uint4(0u, 0u, 0u, 0u);
+    if (gr < p.M) pre[i] = *reinterpret_cast<const uint4*>(base + static_cast<long long>(gr) * ld + col0 + (lane & 3) * 8);
+  }
+}
+__device__ __forceinline__ void stage_store_tile(uint8_t* stg, const float (&v)[32], int out_dtype, void* dst, long long ld,
+                                                 int row0, int lane, int col0, int M) {
+#pragma unroll
+  for (int g = 0; g < 4; ++g) {
+    float t[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) t[i] = v[g * 8 + i];
+    *reinterpret_cast<uint4*>(stg + lane * STG_ROW + g * 16) = (out_dtype == DT_BF16) ? pack8<__nv_bfloat16>(t) : pack8<__half>(t);
+  }
+  __syncwarp();
+  uint16_t* d = reinterpret_cast<uint16_t*>(dst);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int rr = i * 8 + (lane >> 2);
+    const uint4 u = *reinterpret_cast<const uint4*>(stg + rr * STG_ROW + (lane & 3) * 16);
+    if (row0 + rr < M) *reinterpret_cast<uint4*>(d + static_cast<long long>(row0 + rr) * ld + col0 + (lane & 3) * 8) = u;
+  }
+  __syncwarp();
+}
+
+template <int EPI, int ACT>
+__device__ __forceinline__ void epilogue32s(const Params& p, const uint32_t (&r)[32], const uint4 (&pre)[4], int row0,
+                                            int lane, int col0, uint8_t* stg) {
+  float v[32];
+#pragma unroll
+  for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]) * p.alpha;
+  if (EPI != 2 && EPI != 5 && p.bias) {
+    if (p.bias_dtype == DT_F32) {
+      const float4* b4 = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.bias) + col0);
+#pragma unroll
+      for (int g = 0; g < 8; ++g) {
+        const float4 t = b4[g];
+        v[4 * g] += t.x; v[4 * g + 1] += t.y; v[4 * g + 2] += t.z; v[4 * g + 3] += t.w;
+      }
+    } else {
+      const uint4* b4 = reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(p.bias) + col0);
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {
+        float t[8];
+        const uint4 u = b4[g];
+        if (p.bias_dtype == DT_BF16) unpack8<__nv_bfloat16>(u, t); else unpack8<__half>(u, t);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) v[g * 8 + i] += t[i];
+      }
+    }
+  }
+  if (EPI == 1 && p.preact_out) stage_store_tile(stg, v, p.out_dtype, p.preact_out, p.ldd, row0, lane, col0, p.M);
+  if (EPI == 1) {
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = act_fast<ACT>(v[i]);
+  }
+  long long in_ld;
+  const uint16_t* in_base = epi_input<EPI>(p, &in_ld);
+  if (in_base != nullptr) {
+    // prefetched tile -> stage -> my row
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+      *reinterpret_cast<uint4*>(stg + (i * 8 + (lane >> 2)) * STG_ROW + (lane & 3) * 16) = pre[i];
+    __syncwarp();
+    const int in_dt = (EPI == 5) ? p.out_dtype : p.aux_dtype;
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+      float t[8];
+      const uint4 u = *reinterpret_cast<const uint4*>(stg + lane * STG_ROW + g * 16);
+      if (in_dt == DT_BF16) unpack8<__nv_bfloat16>(u, t); else unpack8<__half>(u, t);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        if (EPI == 1) v[g * 8 + i] += t[i];
+        else if (EPI == 2) v[g * 8 + i] *= dact_fast<ACT>(t[i]);
+        else v[g * 8 + i] += p.beta * t[i];
+      }
+    }
+    __syncwarp();
+  }
+  stage_store_tile(stg, v, p.out_dtype, p.D, p.ldd, row0, lane, col0, p.M);
+}
+
 template <int EPI, int ACT>
 __device__ __forceinline__ void epilogue32(const Params& p, const uint32_t (&r)[32], int row, int col0) {
   const long long doff = static_cast<long long>(row) * p.ldd + col0;
@@ -369,6 +479,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   uint64_t* tfull = empty + C::STAGES;
   uint64_t* tempty = tfull + 2;
   uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(tempty + 2);
+  uint8_t* stg_base = reinterpret_cast<uint8_t*>(full) + 256;  // 8 x STG_WARP_BYTES, one stage per epilogue warp
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -526,6 +637,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     // ----------------------------------------------------------- epilogue
     const int quarter = warp & 3;  // TMEM lanes [32q, 32q+32) are visible to this warp
     const int chalf = (warp - 2) >> 2;  // which half of the tile's column chunks this warp drains
+    uint8_t* stg = stg_base + (warp - 2) * STG_WARP_BYTES;
     int acc = 0;
     uint32_t acc_phase = 0;
     if (AG && p.ag.enabled && p.bias && p.ag.bias_off_bytes >= 0) {
@@ -547,6 +659,16 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         const int col0 = tc.n_blk * BN + c * 32;
         if (col0 >= p.N) break;  // warp-uniform
         uint32_t r[32];
+        constexpr bool kStageable = (EPI == 0 || EPI == 1 || EPI == 2 || EPI == 5);
+        const bool staged = kStageable && p.out_dtype != DT_F32 && has_k && col0 + 32 <= p.N;  // warp-uniform
+        if (kStageable && staged) {
+          uint4 pre[4];
+          epi_prefetch<EPI>(p, pre, row - lane, lane, col0);  // global loads in flight while TMEM is read
+          tmem_ld_32x32(t_row + c * 32, r);
+          tmem_ld_wait();
+          epilogue32s<EPI, ACT>(p, r, pre, row - lane, lane, col0, stg);
+          continue;
+        }
         tmem_ld_32x32(t_row + c * 32, r);
         tmem_ld_wait();
         if (row < p.M && has_k) {
@@ -583,7 +705,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 constexpr int G2_STAGES = 6;
 constexpr int G2_BN = 256;
 constexpr int G2_STAGE_BYTES = A_STAGE + (G2_BN / 2) * ROW_BYTES;  // 16 KB A + 16 KB B-half
-constexpr int G2_SMEM = G2_STAGES * G2_STAGE_BYTES + 256 + 1024;
+constexpr int G2_SMEM = G2_STAGES * G2_STAGE_BYTES + 256 + STG_BYTES + 1024;
 
 template <int EPI, int ACT>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
@@ -601,6 +723,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
   uint64_t* tfull = empty + G2_STAGES;
   uint64_t* tempty = tfull + 2;
   uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(tempty + 2);
+  uint8_t* stg_base = reinterpret_cast<uint8_t*>(full) + 256;  // 8 x STG_WARP_BYTES, one stage per epilogue warp
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -711,6 +834,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     // ----------------------------------------------------------- epilogue (both CTAs, own 128 rows)
     const int quarter = warp & 3;
     const int chalf = (warp - 2) >> 2;
+    uint8_t* stg = stg_base + (warp - 2) * STG_WARP_BYTES;
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int tile = cluster_id; tile < total; tile += num_clusters) {
@@ -725,6 +849,16 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         const int col0 = tc.n_blk * BN + c * 32;
         if (col0 >= p.N) break;
         uint32_t r[32];
+        constexpr bool kStageable = (EPI == 0 || EPI == 1 || EPI == 2 || EPI == 5);
+        const bool staged = kStageable && p.out_dtype != DT_F32 && has_k && col0 + 32 <= p.N;  // warp-uniform
+        if (kStageable && staged) {
+          uint4 pre[4];
+          epi_prefetch<EPI>(p, pre, row - lane, lane, col0);  // global loads in flight while TMEM is read
+          tmem_ld_32x32(t_row + c * 32, r);
+          tmem_ld_wait();
+          epilogue32s<EPI, ACT>(p, r, pre, row - lane, lane, col0, stg);
+          continue;
+        }
         tmem_ld_32x32(t_row + c * 32, r);
         tmem_ld_wait();
         if (row < p.M && has_k) {

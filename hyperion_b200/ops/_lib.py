@@ -27,6 +27,7 @@ _SIGS = {
     "hyp_stream_add": "ppplip",
     "hyp_stream_copy": "pplp",
     "hyp_colsum": "ppiilip",
+    "hyp_colsum_cast": "ppiilippp",
     "hyp_swiglu_fwd": "ppplip",
     "hyp_swiglu_bwd": "ppppplip",
     "hyp_cast": "ppliifp",

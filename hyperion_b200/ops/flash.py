@@ -24,6 +24,7 @@ def _declare():
     lib = _lib.require()
     if hasattr(lib, "hyp_flash_attn_bwd"):
         _lib.declare("hyp_flash_attn_bwd", "pppppp" + "ppp" + "pp" + "iiiii" + "l" * 18 + "ifip")
+        _lib.declare("hyp_flash_dq_convert", "pp" + "iiii" + "lll" + "ip")
     _declared = True
 
 
@@ -115,7 +116,8 @@ class _FlashPackedFn(torch.autograd.Function):
         call("hyp_flash_attn_bwd", ptr(q), ptr(k), ptr(v), ptr(o), ptr(do), ptr(lse), ptr(dq_acc), ptr(dk), ptr(dv),
              ptr(delta), ptr(kpm), B, H, S, S, D, *_strides_bhs(q), *_strides_bhs(k), *_strides_bhs(v), *_strides_bhs(o),
              *_strides_bhs(do), *_strides_bhs(dk), int(ctx.causal), float(ctx.scale), DT[qkv.dtype], stream_ptr())
-        dqkv[:, :, 0].copy_(dq_acc.permute(0, 2, 1, 3))
+        dq = dqkv[:, :, 0].permute(0, 2, 1, 3)
+        call("hyp_flash_dq_convert", ptr(dq_acc), ptr(dq), B, H, S, D, *_strides_bhs(dq), DT[qkv.dtype], stream_ptr())
         return dqkv, None, None, None
 
 

@@ -95,6 +95,9 @@ def _wgrad(dy2: torch.Tensor, x2: torch.Tensor, out_dtype, slot=None) -> torch.T
 
 def _bias_grad(dy2: torch.Tensor, dtype, slot=None) -> torch.Tensor:
     """db[N] = column sums of dy2 (fp32 accumulation), rounded into the bias's gradient slot when it can be claimed."""
+    N = dy2.shape[1]
+    if dtype == dy2.dtype and dtype != torch.float32 and N % 8 == 0 and dy2.stride(0) % 8 == 0 and dy2.data_ptr() % 16 == 0:
+        return native.colsum_cast(dy2, out=gradslot.claim(slot, dtype))  # one launch: sum, round, store
     acc = native.colsum(dy2)
     if dtype == torch.float32:
         dst = gradslot.claim(slot, dtype)

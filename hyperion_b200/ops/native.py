@@ -81,6 +81,25 @@ def colsum(x: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
     return out
 
 
+_colsum_ws: dict = {}
+
+
+def colsum_cast(x: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
+    """Column sums of a 16-bit 2-D tensor, accumulated in fp32 and rounded to x's dtype, in one launch (bias
+    gradients).  The fp32 accumulator is a per-device workspace the kernel leaves zeroed."""
+    M, N = x.shape
+    ws = _colsum_ws.get(x.device)
+    if ws is None or ws[0].numel() < N:
+        ws = (torch.zeros(max(N, 65536), device=x.device, dtype=torch.float32),
+              torch.zeros(1, device=x.device, dtype=torch.int32))
+        _colsum_ws[x.device] = ws
+    if out is None:
+        out = torch.empty(N, device=x.device, dtype=x.dtype)
+    assert out.dtype == x.dtype and out.numel() == N and out.is_contiguous()
+    call("hyp_colsum_cast", ptr(x), ptr(out), M, N, _ld(x), DT[x.dtype], ptr(ws[0]), ptr(ws[1]), stream_ptr())
+    return out
+
+
 def swiglu_fwd(gate: torch.Tensor, up: torch.Tensor) -> torch.Tensor:
     out = torch.empty_like(gate)
     call("hyp_swiglu_fwd", ptr(gate), ptr(up), ptr(out), gate.numel(), DT[gate.dtype], stream_ptr())

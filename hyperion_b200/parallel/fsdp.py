@@ -333,7 +333,7 @@ class HyperionFSDP(nn.Module):
         self.step_t += 1
         if self.loss_scaler is not None:
             self.loss_scaler.update()
-        self.flat.grad.zero_()
+        self.flat.zero_grad()  # also leaves param.grad undefined so the next backward's kernels write into the slots
         if W > 1:
             self._queue_gathers()
         if self.arena is not None:

@@ -49,6 +49,10 @@ int hyp_stream_add(const void* x, const void* y, void* z, long long n, int dtype
 int hyp_stream_copy(const void* x, void* z, long long nbytes, void* stream);
 /* out[c] += sum_r x[r,c]; out is fp32 and must be initialised by the caller. */
 int hyp_colsum(const void* x, float* out, int M, int N, long long ld, int dtype, void* stream);
+/* Column sums of a 16-bit matrix rounded to the same dtype in one launch.  acc_ws (>= N fp32) and counter (one
+ * word) must be zero on entry and are zero again on return (the last block converts and clears). */
+int hyp_colsum_cast(const void* x, void* out16, int M, int N, long long ld, int dtype, float* acc_ws, unsigned* counter,
+                    void* stream);
 int hyp_swiglu_fwd(const void* gate, const void* up, void* out, long long n, int dtype, void* stream);
 int hyp_swiglu_bwd(const void* gate, const void* up, const void* dout, void* dgate, void* dup, long long n, int dtype,
                    void* stream);
@@ -144,6 +148,10 @@ int hyp_flash_attn_bwd(const void* q, const void* k, const void* v, const void* 
                        long long k_ss, long long v_sb, long long v_sh, long long v_ss, long long o_sb, long long o_sh,
                        long long o_ss, long long g_sb, long long g_sh, long long g_ss, long long dkv_sb, long long dkv_sh,
                        long long dkv_ss, int causal, float scale, int dtype, void* stream);
+/* Rounds the fp32 dQ accumulator ([B,H,S,D] contiguous) into a 16-bit tensor addressed [b,h,s,d] through element
+ * strides (e.g. the q slice of the packed [B,S,3,H,D] gradient buffer). */
+int hyp_flash_dq_convert(const float* dq_acc, void* dq, int B, int H, int S, int D, long long sb, long long sh,
+                         long long ss, int dtype, void* stream);
 
 /* ---- NVLink communication kernels (csrc/comm.cu) ------------------------------------
  * peer_bufs / peer_flags are HOST arrays of W device addresses: this rank's mapping of every rank's symmetric data

@@ -111,6 +111,31 @@ def test_stream_add_copy(nat, dtype):
     assert torch.equal(nat.stream_copy(xc), xc)
 
 
+@pytest.mark.parametrize("M,N", [(8192, 4096), (4064, 1024), (333, 72), (5, 8)])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_colsum_and_colsum_cast(nat, M, N, dtype):
+    """Column sums (fp32 atomics) and the one-launch sum+round variant; the latter twice in a row, because it has to
+    leave its accumulator workspace zeroed for the next call."""
+    torch.manual_seed(1)
+    x = torch.randn(M, N, device="cuda", dtype=dtype)
+    ref = x.float().sum(0)
+    assert _rel_err(nat.colsum(x), ref) < 1e-3
+    for _ in range(2):
+        out = nat.colsum_cast(x)
+        assert out.dtype == dtype and _rel_err(out, ref) < 1e-2
+    xs = x[:, : N // 16 * 8] if N >= 16 else x   # strided rows, still a multiple of 8 columns
+    assert _rel_err(nat.colsum_cast(xs), xs.float().sum(0)) < 1e-2
+
+
+def test_cast_with_device_scale(nat):
+    x = torch.randn(1000, 264, device="cuda")
+    s = torch.tensor([0.37], device="cuda")
+    for dt in (torch.bfloat16, torch.float16):
+        assert _rel_err(nat.cast(x, dt, scale=2.0, scale_t=s), x * 0.74) < 1e-2
+        assert _rel_err(nat.cast(x[:, :7].contiguous(), dt, scale_t=s), x[:, :7] * 0.37) < 1e-2   # scalar tail path
+    assert _rel_err(nat.cast(x.to(torch.bfloat16), torch.float32, scale_t=s), x.to(torch.bfloat16).float() * 0.37) < 1e-6
+
+
 @pytest.mark.parametrize("rows,d", [(4064, 256), (512, 512), (1024, 768), (6304, 768), (333, 1024), (256, 4096), (64, 8192)])
 @pytest.mark.parametrize("rms", [False, True])
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
