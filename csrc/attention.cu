@@ -52,6 +52,41 @@ struct Smem {
   static constexpr int TOTAL = BAR_OFF + 256;  // no alignment slack: the dynamic window is declared 1024-aligned
 };
 
+// Softmax passes over one 32-column chunk of a score row.  Masking is a compare + select against the row's key limit
+// (and the key-padding bytes) -- no per-element branches; the unmasked instantiation has no mask arithmetic at all.
+template <bool MASK, bool KPM>
+__device__ __forceinline__ float fwd_chunk_max(const uint32_t (&v)[32], int kcol0, int k_limit, const uint8_t* kpm_chunk) {
+  float mx = -INFINITY;
+#pragma unroll
+  for (int i = 0; i < 32; ++i) {
+    float x = __uint_as_float(v[i]);
+    if constexpr (MASK) {
+      bool ok = (kcol0 + i) < k_limit;
+      if constexpr (KPM) ok = ok & (kpm_chunk[i] != 0);
+      x = ok ? x : -INFINITY;
+    }
+    mx = fmaxf(mx, x);
+  }
+  return mx;
+}
+template <bool MASK, bool KPM>
+__device__ __forceinline__ float fwd_chunk_exp(const uint32_t (&v)[32], float (&pr)[32], float scale_log2, float neg_m,
+                                               int kcol0, int k_limit, const uint8_t* kpm_chunk) {
+  float l = 0.f;
+#pragma unroll
+  for (int i = 0; i < 32; ++i) {
+    float x = fmaf(__uint_as_float(v[i]), scale_log2, neg_m);
+    if constexpr (MASK) {
+      bool ok = (kcol0 + i) < k_limit;
+      if constexpr (KPM) ok = ok & (kpm_chunk[i] != 0);
+      x = ok ? x : -INFINITY;
+    }
+    pr[i] = ex2_fast(x);
+    l += pr[i];
+  }
+  return l;
+}
+
 template <typename T, int D>
 __global__ void __launch_bounds__(THREADS, (D == 64) ? 2 : 1)
 flash_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
@@ -76,8 +111,12 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nq_blk = (p.Sq + BQ - 1) / BQ;
-  const int q_blk = nq_blk - 1 - blockIdx.x;  // heavy (late) causal blocks first
-  const int h = blockIdx.y, b = blockIdx.z;
+  // 1-D grid, heaviest first: all (batch, head) pairs of the last query block (the most key blocks under a causal
+  // mask), then the next one, ... so the final wave is made of the shortest CTAs
+  const int bh_count = p.H * p.B;
+  const int q_blk = nq_blk - 1 - static_cast<int>(blockIdx.x / bh_count);
+  const int bh_idx = static_cast<int>(blockIdx.x % bh_count);
+  const int h = bh_idx % p.H, b = bh_idx / p.H;
   const int q0 = q_blk * BQ;
   const int shift = p.Sk - p.Sq;  // causal alignment: query i sees keys <= i + shift
   int kv_end = p.Sk;
@@ -162,6 +201,7 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
     const int r = quarter * 32 + lane;         // row inside the query block == TMEM lane
     const int tid128 = (warp - 2) * 32 + lane; // 0..127 among the softmax threads
     const int qi = q0 + r;
+    const int k_limit = p.causal ? min(p.Sk, qi + shift + 1) : p.Sk;  // first key this row may NOT see
     const uint32_t lane_off = static_cast<uint32_t>(quarter * 32) << 16;
     float o_acc[D];
 #pragma unroll
@@ -185,18 +225,9 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
         uint32_t v[32];
         tmem_ld_32x32(tS + lane_off + c * 32, v);
         tmem_ld_wait();
-        if (need_mask) {
-#pragma unroll
-          for (int i = 0; i < 32; ++i) {
-            const int kj = k0 + c * 32 + i;
-            bool ok = (kj < p.Sk) & (!p.causal | (kj <= qi + shift));
-            if (p.kpm) ok = ok & (s_kpm[c * 32 + i] != 0);
-            mx = fmaxf(mx, ok ? __uint_as_float(v[i]) : -INFINITY);
-          }
-        } else {
-#pragma unroll
-          for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(v[i]));
-        }
+        if (!need_mask) mx = fmaxf(mx, fwd_chunk_max<false, false>(v, 0, 0, nullptr));
+        else if (p.kpm) mx = fmaxf(mx, fwd_chunk_max<true, true>(v, k0 + c * 32, k_limit, s_kpm + c * 32));
+        else mx = fmaxf(mx, fwd_chunk_max<true, false>(v, k0 + c * 32, k_limit, nullptr));
       }
       const float m_new = fmaxf(m_run, mx * p.scale_log2);
       const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
@@ -210,22 +241,9 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
         tmem_ld_32x32(tS + lane_off + c * 32, v);
         tmem_ld_wait();
         float pr[32];
-        if (need_mask) {
-#pragma unroll
-          for (int i = 0; i < 32; ++i) {
-            const int kj = k0 + c * 32 + i;
-            bool ok = (kj < p.Sk) & (!p.causal | (kj <= qi + shift));
-            if (p.kpm) ok = ok & (s_kpm[c * 32 + i] != 0);
-            pr[i] = ok ? ex2_fast(fmaf(__uint_as_float(v[i]), p.scale_log2, neg_m)) : 0.f;
-            l_blk += pr[i];
-          }
-        } else {
-#pragma unroll
-          for (int i = 0; i < 32; ++i) {
-            pr[i] = ex2_fast(fmaf(__uint_as_float(v[i]), p.scale_log2, neg_m));
-            l_blk += pr[i];
-          }
-        }
+        if (!need_mask) l_blk += fwd_chunk_exp<false, false>(v, pr, p.scale_log2, neg_m, 0, 0, nullptr);
+        else if (p.kpm) l_blk += fwd_chunk_exp<true, true>(v, pr, p.scale_log2, neg_m, k0 + c * 32, k_limit, s_kpm + c * 32);
+        else l_blk += fwd_chunk_exp<true, false>(v, pr, p.scale_log2, neg_m, k0 + c * 32, k_limit, nullptr);
         uint8_t* prow = sP + (c >> 1) * 16384 + r * 128;
 #pragma unroll
         for (int t = 0; t < 4; ++t) {
@@ -294,7 +312,7 @@ static int launch_fwd(const CUtensorMap& tq, const CUtensorMap& tk, const CUtens
     HYP_CHECK_CUDA(cudaFuncSetAttribute(flash_fwd_kernel<T, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
     attr_set[dev & 63] = true;
   }
-  dim3 grid((p.Sq + BQ - 1) / BQ, p.H, p.B);
+  dim3 grid(static_cast<unsigned>((p.Sq + BQ - 1) / BQ) * p.H * p.B);
   flash_fwd_kernel<T, D><<<grid, THREADS, L::TOTAL, st>>>(tq, tk, tv, p);
   HYP_CHECK_CUDA(cudaGetLastError());
   return 0;
@@ -397,7 +415,10 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
   uint8_t* s_kpm = reinterpret_cast<uint8_t*>(bars + 12);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int j = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
+  // 1-D grid: key block 0 (the most query blocks under a causal mask) of every (batch, head) first
+  const int bh_count = p.H * p.B;
+  const int j = static_cast<int>(blockIdx.x / bh_count);
+  const int h = static_cast<int>(blockIdx.x % bh_count) % p.H, b = static_cast<int>(blockIdx.x % bh_count) / p.H;
   const int k0 = j * BKV;
   const int shift = p.Sk - p.Sq;
   const int nq_blk = (p.Sq + BQ - 1) / BQ;
@@ -695,7 +716,10 @@ flash_bwd64_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
   uint8_t* s_kpm = reinterpret_cast<uint8_t*>(bars + 12);   // 128 bytes
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int j = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
+  // 1-D grid: key block 0 (the most query blocks under a causal mask) of every (batch, head) first
+  const int bh_count = p.H * p.B;
+  const int j = static_cast<int>(blockIdx.x / bh_count);
+  const int h = static_cast<int>(blockIdx.x % bh_count) % p.H, b = static_cast<int>(blockIdx.x % bh_count) / p.H;
   const int k0 = j * BKV;
   const int shift = p.Sk - p.Sq;
   const int nq_blk = (p.Sq + BQ - 1) / BQ;
@@ -917,7 +941,7 @@ static int launch_bwd64(const CUtensorMap& tq, const CUtensorMap& tk, const CUte
     HYP_CHECK_CUDA(cudaFuncSetAttribute(flash_bwd64_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
     attr_set[dev & 63] = true;
   }
-  dim3 grid((p.Sk + BKV - 1) / BKV, p.H, p.B);
+  dim3 grid(static_cast<unsigned>((p.Sk + BKV - 1) / BKV) * p.H * p.B);
   flash_bwd64_kernel<T><<<grid, BWD64_THREADS, L::TOTAL, st>>>(tq, tk, tv, tdo, p);
   HYP_CHECK_CUDA(cudaGetLastError());
   return 0;
@@ -983,7 +1007,7 @@ static int launch_bwd(const CUtensorMap& tq, const CUtensorMap& tk, const CUtens
     HYP_CHECK_CUDA(cudaFuncSetAttribute(flash_bwd_kernel<T, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
     attr_set[dev & 63] = true;
   }
-  dim3 grid((p.Sk + BKV - 1) / BKV, p.H, p.B);
+  dim3 grid(static_cast<unsigned>((p.Sk + BKV - 1) / BKV) * p.H * p.B);
   flash_bwd_kernel<T, D><<<grid, THREADS, L::TOTAL, st>>>(tq, tk, tv, tdo, p);
   HYP_CHECK_CUDA(cudaGetLastError());
   return 0;

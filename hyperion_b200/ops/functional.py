@@ -59,6 +59,7 @@ def _padded_copy(t2: torch.Tensor) -> torch.Tensor:
 
 
 _SM_COUNT = 148
+_CE_LOGITS_BUDGET = 2 << 30  # bytes of logits linear_cross_entropy may hold at once
 
 
 def _wgrad(dy2: torch.Tensor, x2: torch.Tensor, out_dtype, slot=None) -> torch.Tensor:
@@ -391,7 +392,12 @@ class _LinearCEFn(torch.autograd.Function):
         sum_count = torch.zeros(2, device=dev, dtype=torch.float32)
         inv_cnt = (tgt != ignore_index).sum().clamp(min=1).to(torch.float32).reciprocal().reshape(1)
         dx = torch.empty_like(x2)
-        dw = torch.zeros((V, K), device=dev, dtype=torch.float32)
+        # one chunk when the whole logits matrix is affordable (<= 2 GiB): the head's wgrad is then a single GEMM with a
+        # 16-bit output instead of fp32 accumulation across chunks (which reads and writes V x K fp32 per chunk)
+        if M * V * x.element_size() <= _CE_LOGITS_BUDGET:
+            chunk_rows = M
+        single = chunk_rows >= M
+        dw = None if single else torch.zeros((V, K), device=dev, dtype=torch.float32)
         db = torch.zeros(V, device=dev, dtype=torch.float32) if b is not None else None
         ag = getattr(w, "_hyp_ag", None)
         for r0 in range(0, M, chunk_rows):
@@ -403,7 +409,10 @@ class _LinearCEFn(torch.autograd.Function):
                 native.gemm(x2[r0:r1], w2, out=logits, bias=b)
             native.ce_fwd_bwd(logits, tgt[r0:r1], ignore_index, sum_count, gscale_ptr=inv_cnt, n_classes=V)
             native.gemm(logits, w2, b_mn_major=True, out=dx[r0:r1])
-            native.gemm(logits, x2[r0:r1], a_mn_major=True, b_mn_major=True, out=dw, beta=1.0)
+            if single:
+                dw = _wgrad(logits, x2, w.dtype)
+            else:
+                native.gemm(logits, x2[r0:r1], a_mn_major=True, b_mn_major=True, out=dw, beta=1.0)
             if db is not None:
                 native.colsum(logits, out=db)
         loss = torch.empty((), device=dev, dtype=torch.float32)

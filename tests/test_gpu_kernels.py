@@ -134,6 +134,8 @@ def test_cast_with_device_scale(nat):
         assert _rel_err(nat.cast(x, dt, scale=2.0, scale_t=s), x * 0.74) < 1e-2
         assert _rel_err(nat.cast(x[:, :7].contiguous(), dt, scale_t=s), x[:, :7] * 0.37) < 1e-2   # scalar tail path
     assert _rel_err(nat.cast(x.to(torch.bfloat16), torch.float32, scale_t=s), x.to(torch.bfloat16).float() * 0.37) < 1e-6
+    xb = x.to(torch.bfloat16)
+    assert _rel_err(nat.cast(xb, torch.bfloat16, scale_t=s), xb.float() * 0.37) < 1e-2   # 16-bit -> same type, vector path
 
 
 @pytest.mark.parametrize("rows,d", [(4064, 256), (512, 512), (1024, 768), (6304, 768), (333, 1024), (256, 4096), (64, 8192)])
