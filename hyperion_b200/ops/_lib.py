@@ -66,6 +66,8 @@ def _load():
     lib.hyp_last_error.restype = ctypes.c_char_p
     lib.hyp_norm_bwd_scratch_bytes.restype = _L
     lib.hyp_norm_bwd_scratch_bytes.argtypes = [_I, _I]
+    lib.hyp_norm_bwd_fused_ws_bytes.restype = _L
+    lib.hyp_norm_bwd_fused_ws_bytes.argtypes = [_I]
     for name, sig in _SIGS.items():
         fn = getattr(lib, name, None)
         if fn is None:
@@ -118,7 +120,7 @@ def stream_ptr(device=None) -> int:
 
 _launches = 0
 # kernels launched per entry-point call (everything not listed launches exactly one)
-_KERNELS_PER_CALL = {"hyp_norm_bwd": 2, "hyp_norm_bwd_fused": 2, "hyp_ipc_alloc": 0, "hyp_ipc_open": 0, "hyp_ipc_close": 0, "hyp_ipc_free": 0}
+_KERNELS_PER_CALL = {"hyp_norm_bwd": 2, "hyp_ipc_alloc": 0, "hyp_ipc_open": 0, "hyp_ipc_close": 0, "hyp_ipc_free": 0}
 
 
 def launch_count() -> int:

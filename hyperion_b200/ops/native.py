@@ -151,32 +151,46 @@ def _get_scratch(device, nbytes: int) -> torch.Tensor:
     return buf
 
 
+_norm_ws: dict = {}
+
+
 def norm_bwd(dy, z, gamma, mean, rstd, rms: bool = False, need_beta: bool = True, dres=None, dgamma_out=None,
              dbeta_out=None):
-    """dz (+ ``dres``: the skip-connection gradient, added in the same pass), dgamma, dbeta.  ``dgamma_out`` /
-    ``dbeta_out``: contiguous tensors of gamma's dtype (e.g. flat-gradient slots) that receive the parameter
-    gradients directly; otherwise they come back as fresh fp32 tensors."""
+    """dz (+ ``dres``: the skip-connection gradient, added in the same pass), dgamma, dbeta -- one kernel.
+    ``dgamma_out`` / ``dbeta_out``: contiguous tensors of gamma's dtype (e.g. flat-gradient slots) that receive the
+    parameter gradients directly; otherwise they come back as fresh fp32 tensors."""
     d = z.shape[-1]
     rows = z.numel() // d
     dz = torch.empty_like(z)
-    nbytes = _lib.require().hyp_norm_bwd_scratch_bytes(rows, d)
-    scratch = _get_scratch(z.device, nbytes)
     want_beta = need_beta and not rms
-    if dres is None and dgamma_out is None and dbeta_out is None:
-        dgamma = torch.empty(d, device=z.device, dtype=torch.float32)
-        dbeta = torch.empty(d, device=z.device, dtype=torch.float32) if want_beta else None
-        call("hyp_norm_bwd", ptr(dy), ptr(z), ptr(gamma), ptr(mean), ptr(rstd), ptr(dz), ptr(dgamma), ptr(dbeta),
-             ptr(scratch), scratch.numel(), rows, d, int(rms), DT[z.dtype], 0, stream_ptr())
-        return dz, dgamma, dbeta
-    # fused variant: parameter gradients are written in ONE dtype -- the slots' when given, else fp32
+    # parameter gradients are written in ONE dtype -- the slots' when given, else fp32
     pdt = dgamma_out.dtype if dgamma_out is not None else (dbeta_out.dtype if dbeta_out is not None else torch.float32)
     dgamma = dgamma_out if dgamma_out is not None else torch.empty(d, device=z.device, dtype=pdt)
     dbeta = (dbeta_out if dbeta_out is not None else torch.empty(d, device=z.device, dtype=pdt)) if want_beta else None
     assert dgamma.dtype == pdt and (dbeta is None or dbeta.dtype == pdt)
     if dres is not None:
         assert dres.shape == z.shape and dres.dtype == z.dtype and dres.is_contiguous()
+    ws = _norm_ws.get(z.device)   # persistent accumulator the kernel leaves zeroed
+    if ws is None:
+        ws = torch.zeros(2 * 8192 + 8, device=z.device, dtype=torch.float32)
+        _norm_ws[z.device] = ws
     call("hyp_norm_bwd_fused", ptr(dy), ptr(z), ptr(gamma), ptr(mean), ptr(rstd), ptr(dres), ptr(dz), ptr(dgamma),
-         ptr(dbeta), DT[pdt], ptr(scratch), scratch.numel(), rows, d, int(rms), DT[z.dtype], stream_ptr())
+         ptr(dbeta), DT[pdt], ptr(ws), ws.numel() * 4, rows, d, int(rms), DT[z.dtype], stream_ptr())
+    return dz, dgamma, dbeta
+
+
+def norm_bwd_two_pass(dy, z, gamma, mean, rstd, rms: bool = False, need_beta: bool = True):
+    """The deterministic two-kernel backward (``hyp_norm_bwd``: per-block partial sums in caller scratch, then a
+    column reduce); fp32 dgamma / dbeta."""
+    d = z.shape[-1]
+    rows = z.numel() // d
+    dz = torch.empty_like(z)
+    dgamma = torch.empty(d, device=z.device, dtype=torch.float32)
+    dbeta = torch.empty(d, device=z.device, dtype=torch.float32) if (need_beta and not rms) else None
+    nbytes = _lib.require().hyp_norm_bwd_scratch_bytes(rows, d)
+    scratch = _get_scratch(z.device, nbytes)
+    call("hyp_norm_bwd", ptr(dy), ptr(z), ptr(gamma), ptr(mean), ptr(rstd), ptr(dz), ptr(dgamma), ptr(dbeta),
+         ptr(scratch), scratch.numel(), rows, d, int(rms), DT[z.dtype], 0, stream_ptr())
     return dz, dgamma, dbeta
 
 

@@ -170,6 +170,22 @@ def test_norm_fwd_bwd(nat, rows, d, rms, dtype):
     assert _rel_err(dgamma, gf.grad) < tol
     if not rms:
         assert _rel_err(dbeta, bf.grad) < tol
+    # again (the one-kernel backward must have left its accumulator workspace zeroed), with the skip-connection
+    # gradient added in-kernel and the parameter gradients written in the parameter dtype
+    dres = torch.randn(rows, d, device="cuda").to(dtype)
+    g_out = torch.empty(d, device="cuda", dtype=dtype)
+    b_out = torch.empty(d, device="cuda", dtype=dtype)
+    dz2, dgamma2, dbeta2 = nat.norm_bwd(dy, z, g, mean, rstd, rms=rms, dres=dres, dgamma_out=g_out, dbeta_out=b_out)
+    assert dgamma2.data_ptr() == g_out.data_ptr()
+    assert _rel_err(dz2, zq.grad + dres.float()) < tol
+    assert _rel_err(dgamma2, gf.grad) < tol
+    if not rms:
+        assert _rel_err(dbeta2, bf.grad) < tol
+    # the deterministic two-kernel entry point
+    dz3, dgamma3, dbeta3 = nat.norm_bwd_two_pass(dy, z, g, mean, rstd, rms=rms)
+    assert _rel_err(dz3, zq.grad) < tol and _rel_err(dgamma3, gf.grad) < tol
+    if not rms:
+        assert _rel_err(dbeta3, bf.grad) < tol
 
 
 def test_adamw_matches_torch(nat):
