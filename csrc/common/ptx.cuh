@@ -224,6 +224,12 @@ __device__ __forceinline__ uint32_t mapa_u32(uint32_t local_smem_addr, uint32_t 
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
   asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
+// Same without release semantics: for arrivals that only hand back a TMEM buffer whose reads were already ordered by
+// tcgen05.wait::ld + tcgen05.fence::before_thread_sync -- a release at cluster scope would first flush the thread's
+// outstanding global stores (ncu: MEMBAR stalls on the epilogue's tempty arrive).
+__device__ __forceinline__ void mbar_arrive_cluster_relaxed(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
 // TMA load whose completion is signalled on an mbarrier that may live in the peer CTA of the pair.
 __device__ __forceinline__ void tma_load_2d_2sm(void* smem_dst, const CUtensorMap* m, uint32_t bar_cluster_addr,
                                                 int32_t c0, int32_t c1) {

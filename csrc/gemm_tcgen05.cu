@@ -285,16 +285,24 @@ __device__ __forceinline__ void stage_store_tile(uint8_t* stg, const float (&v)[
 template <int EPI, int ACT>
 __device__ __forceinline__ void epilogue32s(const Params& p, const uint32_t (&r)[32], const uint4 (&pre)[4], int row0,
                                             int lane, int col0, uint8_t* stg) {
-  float v[32];
+  // fp32 math on packed pairs (util.cuh: ffma2 / fmul2 / fadd2)
+  float2 vv[16];
+  float (&v)[32] = reinterpret_cast<float (&)[32]>(vv);
 #pragma unroll
-  for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]) * p.alpha;
+  for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+  if (p.alpha != 1.f) {
+    const float2 al = splat2(p.alpha);
+#pragma unroll
+    for (int i = 0; i < 16; ++i) vv[i] = fmul2(vv[i], al);
+  }
   if (EPI != 2 && EPI != 5 && p.bias) {
     if (p.bias_dtype == DT_F32) {
       const float4* b4 = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.bias) + col0);
 #pragma unroll
       for (int g = 0; g < 8; ++g) {
         const float4 t = b4[g];
-        v[4 * g] += t.x; v[4 * g + 1] += t.y; v[4 * g + 2] += t.z; v[4 * g + 3] += t.w;
+        vv[2 * g] = fadd2(vv[2 * g], make_float2(t.x, t.y));
+        vv[2 * g + 1] = fadd2(vv[2 * g + 1], make_float2(t.z, t.w));
       }
     } else {
       const uint4* b4 = reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(p.bias) + col0);
@@ -304,14 +312,14 @@ __device__ __forceinline__ void epilogue32s(const Params& p, const uint32_t (&r)
         const uint4 u = b4[g];
         if (p.bias_dtype == DT_BF16) unpack8<__nv_bfloat16>(u, t); else unpack8<__half>(u, t);
 #pragma unroll
-        for (int i = 0; i < 8; ++i) v[g * 8 + i] += t[i];
+        for (int i = 0; i < 4; ++i) vv[g * 4 + i] = fadd2(vv[g * 4 + i], make_float2(t[2 * i], t[2 * i + 1]));
       }
     }
   }
   if (EPI == 1 && p.preact_out) stage_store_tile(stg, v, p.out_dtype, p.preact_out, p.ldd, row0, lane, col0, p.M);
   if (EPI == 1) {
 #pragma unroll
-    for (int i = 0; i < 32; ++i) v[i] = act_fast<ACT>(v[i]);
+    for (int i = 0; i < 16; ++i) vv[i] = act_fast2<ACT>(vv[i]);
   }
   long long in_ld;
   const uint16_t* in_base = epi_input<EPI>(p, &in_ld);
@@ -322,16 +330,18 @@ __device__ __forceinline__ void epilogue32s(const Params& p, const uint32_t (&r)
       *reinterpret_cast<uint4*>(stg + (i * 8 + (lane >> 2)) * STG_ROW + (lane & 3) * 16) = pre[i];
     __syncwarp();
     const int in_dt = (EPI == 5) ? p.out_dtype : p.aux_dtype;
+    const float2 be = splat2(p.beta);
 #pragma unroll
     for (int g = 0; g < 4; ++g) {
       float t[8];
       const uint4 u = *reinterpret_cast<const uint4*>(stg + lane * STG_ROW + g * 16);
       if (in_dt == DT_BF16) unpack8<__nv_bfloat16>(u, t); else unpack8<__half>(u, t);
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        if (EPI == 1) v[g * 8 + i] += t[i];
-        else if (EPI == 2) v[g * 8 + i] *= dact_fast<ACT>(t[i]);
-        else v[g * 8 + i] += p.beta * t[i];
+      for (int i = 0; i < 4; ++i) {
+        const float2 tt = make_float2(t[2 * i], t[2 * i + 1]);
+        if (EPI == 1) vv[g * 4 + i] = fadd2(vv[g * 4 + i], tt);
+        else if (EPI == 2) vv[g * 4 + i] = fmul2(vv[g * 4 + i], dact_fast2<ACT>(tt));
+        else vv[g * 4 + i] = ffma2(be, tt, vv[g * 4 + i]);
       }
     }
     __syncwarp();
@@ -839,43 +849,62 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     uint32_t acc_phase = 0;
     for (int tile = cluster_id; tile < total; tile += num_clusters) {
       const TileCoord tc = decode_tile(tile, tiles_m, tiles_n, nkb, p.splits);
+      const int row = tc.m_blk * BM2 + cta * BM + quarter * 32 + lane;
+      const bool has_k = tc.kb1 > tc.kb0;
+      constexpr bool kStageable = (EPI == 0 || EPI == 1 || EPI == 2 || EPI == 5);
+      constexpr int NCH = BN / 64;   // 32-column chunks per warp
+      const int c_begin = chalf * NCH;
+      // whole-tile fast path: every chunk of this warp is inside N and goes through the staged epilogue
+      const bool staged_tile = kStageable && p.out_dtype != DT_F32 && has_k && tc.n_blk * BN + (c_begin + NCH) * 32 <= p.N;
+      uint4 pre[NCH][4];
+      if (kStageable && staged_tile) {
+        // the tile this epilogue reads back (residual / act' input / beta*D) is requested for ALL chunks before
+        // waiting for the accumulator, so the loads fly while the tile's MMAs finish (ncu: with a per-chunk prefetch the
+        // epilogue sat in long-scoreboard stalls on these loads and throttled the main loop)
+#pragma unroll
+        for (int k = 0; k < NCH; ++k) epi_prefetch<EPI>(p, pre[k], row - lane, lane, tc.n_blk * BN + (c_begin + k) * 32);
+      }
       mbar_wait(&tfull[acc], acc_phase);
       tc_fence_after();
-      const int row = tc.m_blk * BM2 + cta * BM + quarter * 32 + lane;
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * BN;
-      const bool has_k = tc.kb1 > tc.kb0;
+      if (kStageable && staged_tile) {
+#pragma unroll
+        for (int k = 0; k < NCH; ++k) {
+          uint32_t r[32];
+          tmem_ld_32x32(t_row + (c_begin + k) * 32, r);
+          tmem_ld_wait();
+          if (k == NCH - 1) {
+            // accumulator fully read: hand the TMEM buffer back before this chunk's math and stores
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cluster_relaxed(mapa_u32(smem_u32(&tempty[acc]), 0));
+          }
+          epilogue32s<EPI, ACT>(p, r, pre[k], row - lane, lane, tc.n_blk * BN + (c_begin + k) * 32, stg);
+        }
+      } else {
 #pragma unroll 1
-      for (int c = chalf * (BN / 64); c < (chalf + 1) * (BN / 64); ++c) {
-        const int col0 = tc.n_blk * BN + c * 32;
-        if (col0 >= p.N) break;
-        uint32_t r[32];
-        constexpr bool kStageable = (EPI == 0 || EPI == 1 || EPI == 2 || EPI == 5);
-        const bool staged = kStageable && p.out_dtype != DT_F32 && has_k && col0 + 32 <= p.N;  // warp-uniform
-        if (kStageable && staged) {
-          uint4 pre[4];
-          epi_prefetch<EPI>(p, pre, row - lane, lane, col0);  // global loads in flight while TMEM is read
+        for (int c = c_begin; c < c_begin + NCH; ++c) {
+          const int col0 = tc.n_blk * BN + c * 32;
+          if (col0 >= p.N) break;
+          uint32_t r[32];
           tmem_ld_32x32(t_row + c * 32, r);
           tmem_ld_wait();
-          epilogue32s<EPI, ACT>(p, r, pre, row - lane, lane, col0, stg);
-          continue;
-        }
-        tmem_ld_32x32(t_row + c * 32, r);
-        tmem_ld_wait();
-        if (row < p.M && has_k) {
-          if (EPI != 3 && col0 + 32 <= p.N) {
-            epilogue32<EPI, ACT>(p, r, row, col0);
-          } else {
+          if (row < p.M && has_k) {
+            if (EPI != 3 && col0 + 32 <= p.N) {
+              epilogue32<EPI, ACT>(p, r, row, col0);
+            } else {
 #pragma unroll
-            for (int g = 0; g < 4; ++g)
-              epilogue8(&p, __uint_as_float(r[g * 8]), __uint_as_float(r[g * 8 + 1]), __uint_as_float(r[g * 8 + 2]),
-                        __uint_as_float(r[g * 8 + 3]), __uint_as_float(r[g * 8 + 4]), __uint_as_float(r[g * 8 + 5]),
-                        __uint_as_float(r[g * 8 + 6]), __uint_as_float(r[g * 8 + 7]), row, col0 + g * 8);
+              for (int g = 0; g < 4; ++g)
+                epilogue8(&p, __uint_as_float(r[g * 8]), __uint_as_float(r[g * 8 + 1]), __uint_as_float(r[g * 8 + 2]),
+                          __uint_as_float(r[g * 8 + 3]), __uint_as_float(r[g * 8 + 4]), __uint_as_float(r[g * 8 + 5]),
+                          __uint_as_float(r[g * 8 + 6]), __uint_as_float(r[g * 8 + 7]), row, col0 + g * 8);
+            }
           }
         }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster_relaxed(mapa_u32(smem_u32(&tempty[acc]), 0));  // the leader's MMA thread waits on its copy
       }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive_cluster(mapa_u32(smem_u32(&tempty[acc]), 0));  // the leader's MMA thread waits on its copy
       acc ^= 1;
       if (acc == 0) acc_phase ^= 1;
     }

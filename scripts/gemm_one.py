@@ -10,6 +10,7 @@ from hyperion_b200.ops import native as nat
 M, N, K = (int(x) for x in sys.argv[1:4])
 layout = sys.argv[4] if len(sys.argv) > 4 else "tn"   # tn: fwd, nn: dgrad (B mn-major), wg: wgrad (both mn-major)
 iters = int(sys.argv[5]) if len(sys.argv) > 5 else 5
+epi = sys.argv[6] if len(sys.argv) > 6 else "plain"   # plain | dact (gelu' * aux) | act (bias + gelu + preact)
 dt = torch.bfloat16
 a = torch.randn(M, K, device="cuda", dtype=dt)
 b = torch.randn(N, K, device="cuda", dtype=dt)
@@ -22,6 +23,10 @@ elif layout == "wg":
 else:
     kw = {}
 d = torch.empty(M, N, device="cuda", dtype=dt)
+if epi == "dact":
+    kw.update(aux=torch.randn(M, N, device="cuda", dtype=dt), act="gelu_tanh", mode=1)
+elif epi == "act":
+    kw.update(bias=torch.randn(N, device="cuda", dtype=dt), act="gelu_tanh", preact_out=torch.empty(M, N, device="cuda", dtype=dt))
 for _ in range(iters):
     nat.gemm(a, b, out=d, **kw)
 torch.cuda.synchronize()
