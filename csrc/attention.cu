@@ -72,19 +72,24 @@ __device__ __forceinline__ float fwd_chunk_max(const uint32_t (&v)[32], int kcol
 template <bool MASK, bool KPM>
 __device__ __forceinline__ float fwd_chunk_exp(const uint32_t (&v)[32], float (&pr)[32], float scale_log2, float neg_m,
                                                int kcol0, int k_limit, const uint8_t* kpm_chunk) {
-  float l = 0.f;
+  // scale and shift on packed fp32 pairs (one FFMA2 per two scores), exponentials on the MUFU, pairwise partial sums
+  const float2 sc = splat2(scale_log2), nm = splat2(neg_m);
+  float2 l2 = make_float2(0.f, 0.f);
 #pragma unroll
-  for (int i = 0; i < 32; ++i) {
-    float x = fmaf(__uint_as_float(v[i]), scale_log2, neg_m);
+  for (int i = 0; i < 32; i += 2) {
+    float2 x = ffma2(make_float2(__uint_as_float(v[i]), __uint_as_float(v[i + 1])), sc, nm);
     if constexpr (MASK) {
-      bool ok = (kcol0 + i) < k_limit;
-      if constexpr (KPM) ok = ok & (kpm_chunk[i] != 0);
-      x = ok ? x : -INFINITY;
+      bool ok0 = (kcol0 + i) < k_limit, ok1 = (kcol0 + i + 1) < k_limit;
+      if constexpr (KPM) { ok0 = ok0 & (kpm_chunk[i] != 0); ok1 = ok1 & (kpm_chunk[i + 1] != 0); }
+      x.x = ok0 ? x.x : -INFINITY;
+      x.y = ok1 ? x.y : -INFINITY;
     }
-    pr[i] = ex2_fast(x);
-    l += pr[i];
+    const float2 e = make_float2(ex2_fast(x.x), ex2_fast(x.y));
+    pr[i] = e.x;
+    pr[i + 1] = e.y;
+    l2 = fadd2(l2, e);
   }
-  return l;
+  return l2.x + l2.y;
 }
 
 template <typename T, int D>
@@ -267,8 +272,14 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
         uint32_t v[32];
         tmem_ld_32x32(tO + lane_off + c * 32, v);
         tmem_ld_wait();
+        const float2 al2 = splat2(alpha);
 #pragma unroll
-        for (int i = 0; i < 32; ++i) o_acc[c * 32 + i] = o_acc[c * 32 + i] * alpha + __uint_as_float(v[i]);
+        for (int i = 0; i < 32; i += 2) {
+          const float2 o2 = ffma2(make_float2(o_acc[c * 32 + i], o_acc[c * 32 + i + 1]), al2,
+                                  make_float2(__uint_as_float(v[i]), __uint_as_float(v[i + 1])));
+          o_acc[c * 32 + i] = o2.x;
+          o_acc[c * 32 + i + 1] = o2.y;
+        }
       }
       tc_fence_before();
     }
@@ -666,21 +677,24 @@ __device__ __forceinline__ void bwd_softmax_chunk(uint32_t tS, uint32_t tDP, uin
   tmem_ld_32x32(tS, vs);
   tmem_ld_32x32(tDP, vd);
   tmem_ld_wait();
+  const float2 sc2 = splat2(scale_log2), nl2 = splat2(-lse2), s2 = splat2(scale), nd2 = splat2(-delta_s);
 #pragma unroll
   for (int t = 0; t < 4; ++t) {
     float f[8], g[8];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
+    for (int i = 0; i < 8; i += 2) {   // packed fp32 pairs: two scores per FFMA2 / FMUL2
       const int e = t * 8 + i;
-      float x = fmaf(__uint_as_float(vs[e]), scale_log2, -lse2);
+      float2 x = ffma2(make_float2(__uint_as_float(vs[e]), __uint_as_float(vs[e + 1])), sc2, nl2);
       if constexpr (MASK) {
-        bool ok = (kcol0 + e) < k_limit;
-        if (s_kpm_chunk) ok = ok & (s_kpm_chunk[e] != 0);
-        x = ok ? x : -INFINITY;
+        bool ok0 = (kcol0 + e) < k_limit, ok1 = (kcol0 + e + 1) < k_limit;
+        if (s_kpm_chunk) { ok0 = ok0 & (s_kpm_chunk[e] != 0); ok1 = ok1 & (s_kpm_chunk[e + 1] != 0); }
+        x.x = ok0 ? x.x : -INFINITY;
+        x.y = ok1 ? x.y : -INFINITY;
       }
-      const float pv = ex2_fast(x);
-      f[i] = pv;
-      g[i] = pv * fmaf(__uint_as_float(vd[e]), scale, -delta_s);
+      const float2 pv = make_float2(ex2_fast(x.x), ex2_fast(x.y));
+      const float2 ds = fmul2(pv, ffma2(make_float2(__uint_as_float(vd[e]), __uint_as_float(vd[e + 1])), s2, nd2));
+      f[i] = pv.x; f[i + 1] = pv.y;
+      g[i] = ds.x; g[i + 1] = ds.y;
     }
     const int cc = (chunk_in_row * 4 + t) ^ (r & 7);
     *reinterpret_cast<uint4*>(prow + (cc << 4)) = pack8<T>(f);
