@@ -78,6 +78,8 @@ struct FinishArgs {
   unsigned* counter;
   void* dgamma;
   void* dbeta;
+  void* dzsum;   // optional third output (one-kernel mode, one chunk per thread): column sums of dz, i.e. the bias
+                 // gradient of the linear layer whose output fed this norm's input -- saves that layer a column-sum pass
   int param_dtype;
 };
 template <int TPR>
@@ -189,12 +191,16 @@ norm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ z, const T* __re
   __shared__ float2 red[2 * MAX_RPB * 8];
   constexpr int RPB = BLOCK / TPR;
   static_assert(RPB <= MAX_RPB && TPR / 32 <= 8, "bad norm config");
-  __shared__ __align__(16) float fold[RPB > 1 ? 2 * TPR * 8 * CH : 4];
+  constexpr bool DZS = (CH == 1);   // dz column sums are only carried by the narrow configurations (d <= 2048)
+  constexpr int NACC = DZS ? 3 : 2;
+  __shared__ __align__(16) float fold[RPB > 1 ? NACC * TPR * 8 * CH : 4];
   __shared__ bool is_last;
   const int sub = threadIdx.x / TPR;
   const int t = threadIdx.x % TPR;
   unsigned parity = 0;
-  float dg[CH][8], db[CH][8], g[CH][8];
+  float dg[CH][8], db[CH][8], g[CH][8], dzs[DZS ? 8 : 1];
+#pragma unroll
+  for (int i = 0; i < (DZS ? 8 : 1); ++i) dzs[i] = 0.f;
 #pragma unroll
   for (int k = 0; k < CH; ++k) {
     const int c = (t + k * TPR) * 8;
@@ -259,6 +265,10 @@ norm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ z, const T* __re
 #pragma unroll
           for (int i = 0; i < 8; ++i) o[i] += e[i];
         }
+        if constexpr (DZS) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) dzs[i] += o[i];
+        }
         store8<T>(dz + base + c, o);
       }
     }
@@ -266,6 +276,7 @@ norm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ z, const T* __re
   // Block totals: folded through shared memory group by group; the last group then either stores the block's
   // partial row (two-kernel mode, `partial`) or adds it to the fp32 accumulator `fin.acc` (one-kernel mode).
   float* pg = fin.acc ? fin.acc : partial + static_cast<long long>(blockIdx.x) * 2 * d;
+  const bool want_dzs = DZS && fin.acc != nullptr && fin.dzsum != nullptr;
   for (int w = 0; w < RPB; ++w) {
     if (sub == w) {
 #pragma unroll
@@ -275,6 +286,10 @@ norm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ z, const T* __re
           if (w > 0) {
 #pragma unroll
             for (int i = 0; i < 8; ++i) { dg[k][i] += fold[c + i]; db[k][i] += fold[d + c + i]; }
+            if constexpr (DZS) {
+#pragma unroll
+              for (int i = 0; i < 8; ++i) dzs[i] += fold[2 * d + c + i];
+            }
           }
           if (w == RPB - 1) {
             if (fin.acc) {
@@ -282,6 +297,10 @@ norm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ z, const T* __re
               for (int h = 0; h < 2; ++h) {
                 atomicAdd(reinterpret_cast<float4*>(pg + c) + h, make_float4(dg[k][4 * h], dg[k][4 * h + 1], dg[k][4 * h + 2], dg[k][4 * h + 3]));
                 atomicAdd(reinterpret_cast<float4*>(pg + d + c) + h, make_float4(db[k][4 * h], db[k][4 * h + 1], db[k][4 * h + 2], db[k][4 * h + 3]));
+                if constexpr (DZS) {
+                  if (want_dzs)
+                    atomicAdd(reinterpret_cast<float4*>(pg + 2 * d + c) + h, make_float4(dzs[4 * h], dzs[4 * h + 1], dzs[4 * h + 2], dzs[4 * h + 3]));
+                }
               }
             } else {
               store8<float>(pg + c, dg[k]);
@@ -290,6 +309,7 @@ norm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ z, const T* __re
           } else {
             store8<float>(fold + c, dg[k]);
             store8<float>(fold + d + c, db[k]);
+            if constexpr (DZS) store8<float>(fold + 2 * d + c, dzs);
           }
         }
       }
@@ -297,18 +317,19 @@ norm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ z, const T* __re
     if (RPB > 1) __syncthreads();
   }
   if (fin.acc == nullptr) return;
-  // one-kernel mode: the last block to arrive rounds the accumulator into dgamma / dbeta and clears it
+  // one-kernel mode: the last block to arrive rounds the accumulator into dgamma / dbeta (/ dz sums) and clears it
   __threadfence();
   __syncthreads();
   if (threadIdx.x == 0) is_last = atomicAdd(fin.counter, 1u) == gridDim.x - 1;
   __syncthreads();
   if (!is_last) return;
   __threadfence();
-  for (int i = threadIdx.x; i < 2 * d; i += BLOCK) {
+  const int n_out = (want_dzs ? 3 : 2) * d;
+  for (int i = threadIdx.x; i < n_out; i += BLOCK) {
     const float v = __ldcg(fin.acc + i);
     fin.acc[i] = 0.f;
-    void* out = i < d ? fin.dgamma : fin.dbeta;
-    const int col = i < d ? i : i - d;
+    void* out = i < d ? fin.dgamma : (i < 2 * d ? fin.dbeta : fin.dzsum);
+    const int col = i < d ? i : (i < 2 * d ? i - d : i - 2 * d);
     if (out == nullptr) continue;
     if (fin.param_dtype == DT_F32) reinterpret_cast<float*>(out)[col] = v;
     else if (fin.param_dtype == DT_BF16) reinterpret_cast<__nv_bfloat16*>(out)[col] = __float2bfloat16(v);
@@ -433,13 +454,14 @@ HYP_API long long hyp_norm_bwd_scratch_bytes(int rows, int d) {
 namespace hyp { namespace norm {
 int launch_bwd(const void* dy, const void* z, const void* gamma, const float* mean, const float* rstd, void* dz,
                void* dgamma, void* dbeta, float* scratch, int rows, int d, int rms, int dtype, int accumulate,
-               cudaStream_t st, const void* dres = nullptr, int param_dtype = DT_F32, bool one_kernel = false) {
+               cudaStream_t st, const void* dres = nullptr, int param_dtype = DT_F32, bool one_kernel = false,
+               void* dzsum = nullptr) {
   const Cfg cfg = pick_cfg(d);
   const int grid = bwd_grid(rows, cfg);
   const int P = grid;
   // one-kernel mode: `scratch` is the zeroed accumulator [2][d] followed by the arrival counter
-  FinishArgs fin{nullptr, nullptr, dgamma, dbeta, param_dtype};
-  if (one_kernel) { fin.acc = scratch; fin.counter = reinterpret_cast<unsigned*>(scratch + 2 * d); }
+  FinishArgs fin{nullptr, nullptr, dgamma, dbeta, dzsum, param_dtype};
+  if (one_kernel) { fin.acc = scratch; fin.counter = reinterpret_cast<unsigned*>(scratch + 3 * d); }
 #define HYP_NORM_BWD(TPR, CH, BLOCK)                                                                                \
   norm_bwd_kernel<TT, TPR, CH, BLOCK><<<grid, BLOCK, 0, st>>>((const TT*)dy, (const TT*)z, (const TT*)gamma, mean, rstd, \
                                                               (const TT*)dres, (TT*)dz, scratch, rows, d, rms, fin)
@@ -470,23 +492,25 @@ HYP_API int hyp_norm_bwd(const void* dy, const void* z, const void* gamma, const
 //  * `dres` (same shape/dtype as dz, may be null) is added to dz -- the gradient that reaches the norm's input through
 //    the skip connection of a pre-norm block, which autograd would otherwise add with a separate elementwise pass;
 //  * dgamma / dbeta are written in `param_dtype` (DT_F32, or the parameters' 16-bit dtype so they can land directly in
-//    the flat gradient buffer);
+//    the flat gradient buffer); `dz_colsum` (may be null; d <= 2048) receives the column sums of dz in the same dtype --
+//    the bias gradient of the linear layer that produced this norm's input;
 //  * there is no second kernel: blocks add their partial sums into the fp32 accumulator at the start of `ws`, and the
 //    last block to finish rounds it into dgamma / dbeta.  `ws` (hyp_norm_bwd_fused_ws_bytes(d) bytes) must be all zero
 //    on entry and is all zero again on return, so one persistent workspace per stream serves every call.  The sums
 //    are accumulated with floating-point atomics, i.e. not bit-reproducible from run to run.
-HYP_API long long hyp_norm_bwd_fused_ws_bytes(int d) { return (2ll * d + 8) * static_cast<long long>(sizeof(float)); }
+HYP_API long long hyp_norm_bwd_fused_ws_bytes(int d) { return (3ll * d + 8) * static_cast<long long>(sizeof(float)); }
 
 HYP_API int hyp_norm_bwd_fused(const void* dy, const void* z, const void* gamma, const float* mean, const float* rstd,
-                               const void* dres, void* dz, void* dgamma, void* dbeta, int param_dtype, void* ws,
-                               long long ws_bytes, int rows, int d, int rms, int dtype, void* stream_) {
+                               const void* dres, void* dz, void* dgamma, void* dbeta, void* dz_colsum, int param_dtype,
+                               void* ws, long long ws_bytes, int rows, int d, int rms, int dtype, void* stream_) {
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
   HYP_REQUIRE(rows > 0 && d > 0 && d % 8 == 0 && d <= 8192, "hyp_norm_bwd_fused: need d %% 8 == 0 and d <= 8192 (d=%d)", d);
   HYP_REQUIRE(param_dtype == DT_F32 || param_dtype == DT_F16 || param_dtype == DT_BF16, "hyp_norm_bwd_fused: bad param dtype");
   HYP_REQUIRE(ws != nullptr && ws_bytes >= hyp_norm_bwd_fused_ws_bytes(d) && reinterpret_cast<uintptr_t>(ws) % 16 == 0,
               "hyp_norm_bwd_fused: workspace too small or misaligned (%lld < %lld bytes)", ws_bytes, hyp_norm_bwd_fused_ws_bytes(d));
+  HYP_REQUIRE(dz_colsum == nullptr || d <= 2048, "hyp_norm_bwd_fused: dz column sums are only produced for d <= 2048 (d=%d)", d);
   return norm::launch_bwd(dy, z, gamma, mean, rstd, dz, dgamma, dbeta, reinterpret_cast<float*>(ws), rows, d, rms,
-                          dtype, 0, st, dres, param_dtype, true);
+                          dtype, 0, st, dres, param_dtype, true, dz_colsum);
 }
 
 // ---------------------------------------------------------------------------------------------------------

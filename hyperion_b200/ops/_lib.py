@@ -34,7 +34,7 @@ _SIGS = {
     "hyp_cast_dscale": "ppliifpp",
     "hyp_norm_fwd": "ppppppppiifiip",
     "hyp_norm_bwd": "pppppppppliiiiip",
-    "hyp_norm_bwd_fused": "pppppppppipliiiip",
+    "hyp_norm_bwd_fused": "ppppppppppipliiiip",
     "hyp_adamw": "ppppplii" + "fffff" + "i" + "f" + "ppppp",
     "hyp_sumsq": "plipp",
     "hyp_ce_fwd_bwd": "plpiilpppfiip",

@@ -94,9 +94,15 @@ def _wgrad(dy2: torch.Tensor, x2: torch.Tensor, out_dtype, slot=None) -> torch.T
     return out if out.is_contiguous() else out.contiguous()
 
 
-def _bias_grad(dy2: torch.Tensor, dtype, slot=None) -> torch.Tensor:
-    """db[N] = column sums of dy2 (fp32 accumulation), rounded into the bias's gradient slot when it can be claimed."""
+def _bias_grad(dy2: torch.Tensor, dtype, slot=None, dy=None) -> torch.Tensor:
+    """db[N] = column sums of dy2 (fp32 accumulation), rounded into the bias's gradient slot when it can be claimed.
+    ``dy``: the gradient tensor as autograd delivered it -- when the norm backward that produced it attached its column
+    sums (``_hyp_colsum``), they are used instead of another pass over the tensor."""
     N = dy2.shape[1]
+    cs = getattr(dy, "_hyp_colsum", None) if dy is not None else None
+    if cs is not None and cs.numel() == N and cs.dtype == dtype and dy.shape[-1] == N:
+        dst = gradslot.claim(slot, dtype)
+        return cs if dst is None else dst.copy_(cs)
     if dtype == dy2.dtype and dtype != torch.float32 and N % 8 == 0 and dy2.stride(0) % 8 == 0 and dy2.data_ptr() % 16 == 0:
         return native.colsum_cast(dy2, out=gradslot.claim(slot, dtype))  # one launch: sum, round, store
     acc = native.colsum(dy2)
@@ -167,7 +173,7 @@ class _LinearFn(torch.autograd.Function):
         if ctx.needs_input_grad[1]:
             dw = _wgrad(dh, x2, w2.dtype, ctx.slots[0])
         if ctx.has_bias and ctx.needs_input_grad[2]:
-            db = _bias_grad(dh, dy.dtype, ctx.slots[1])
+            db = _bias_grad(dh, dy.dtype, ctx.slots[1], dy if dh is dy2 else None)
         if ctx.has_res and ctx.needs_input_grad[3]:
             dres = dy
         return dx, dw, db, dres, None, None
@@ -239,7 +245,7 @@ class _MlpFn(torch.autograd.Function):
         dw1 = _wgrad(dh, x2, w1.dtype, s_w1)
         dx = native.gemm(dh, w1, b_mn_major=True).reshape(ctx.x_shape) if ctx.needs_input_grad[0] else None
         db1 = _bias_grad(dh, dy.dtype, s_b1) if has_b1 else None
-        db2 = _bias_grad(dy2, dy.dtype, s_b2) if has_b2 else None
+        db2 = _bias_grad(dy2, dy.dtype, s_b2, dy) if has_b2 else None
         return dx, dw1, db1, dw2, db2, (dy if has_res else None), None, None, None
 
 
@@ -259,9 +265,16 @@ def _norm_param_grads(ctx, dy, dres):
     s_g, s_b = ctx.slots
     g_out = gradslot.claim(s_g, gamma.dtype)
     b_out = gradslot.claim(s_b, gamma.dtype) if ctx.has_beta else None
+    # dz is usually the output gradient of the linear layer that fed this norm: hand its column sums (= that layer's
+    # bias gradient) along with the tensor so the layer does not have to re-read dz (see _bias_grad)
+    cs = None
+    if g_out is not None and g_out.dtype == z.dtype and z.shape[-1] <= 2048:
+        cs = torch.empty(z.shape[-1], device=z.device, dtype=z.dtype)
     dz, dgamma, dbeta = native.norm_bwd(dy.contiguous(), z, gamma, mean, rstd, rms=ctx.rms, need_beta=ctx.has_beta,
                                         dres=dres.contiguous() if dres is not None else None,
-                                        dgamma_out=g_out, dbeta_out=b_out)
+                                        dgamma_out=g_out, dbeta_out=b_out, dz_colsum_out=cs)
+    if cs is not None:
+        dz._hyp_colsum = cs
     dgamma = dgamma if dgamma.dtype == gamma.dtype else dgamma.to(gamma.dtype)
     if dbeta is not None and dbeta.dtype != gamma.dtype:
         dbeta = dbeta.to(gamma.dtype)

@@ -155,10 +155,11 @@ _norm_ws: dict = {}
 
 
 def norm_bwd(dy, z, gamma, mean, rstd, rms: bool = False, need_beta: bool = True, dres=None, dgamma_out=None,
-             dbeta_out=None):
+             dbeta_out=None, dz_colsum_out=None):
     """dz (+ ``dres``: the skip-connection gradient, added in the same pass), dgamma, dbeta -- one kernel.
     ``dgamma_out`` / ``dbeta_out``: contiguous tensors of gamma's dtype (e.g. flat-gradient slots) that receive the
-    parameter gradients directly; otherwise they come back as fresh fp32 tensors."""
+    parameter gradients directly; otherwise they come back as fresh fp32 tensors.  ``dz_colsum_out`` ([d], same dtype
+    as the parameter gradients, d <= 2048) additionally receives the column sums of dz."""
     d = z.shape[-1]
     rows = z.numel() // d
     dz = torch.empty_like(z)
@@ -172,10 +173,12 @@ def norm_bwd(dy, z, gamma, mean, rstd, rms: bool = False, need_beta: bool = True
         assert dres.shape == z.shape and dres.dtype == z.dtype and dres.is_contiguous()
     ws = _norm_ws.get(z.device)   # persistent accumulator the kernel leaves zeroed
     if ws is None:
-        ws = torch.zeros(2 * 8192 + 8, device=z.device, dtype=torch.float32)
+        ws = torch.zeros(3 * 8192 + 8, device=z.device, dtype=torch.float32)
         _norm_ws[z.device] = ws
+    if dz_colsum_out is not None:
+        assert dz_colsum_out.dtype == pdt and dz_colsum_out.numel() == d and d <= 2048
     call("hyp_norm_bwd_fused", ptr(dy), ptr(z), ptr(gamma), ptr(mean), ptr(rstd), ptr(dres), ptr(dz), ptr(dgamma),
-         ptr(dbeta), DT[pdt], ptr(ws), ws.numel() * 4, rows, d, int(rms), DT[z.dtype], stream_ptr())
+         ptr(dbeta), ptr(dz_colsum_out), DT[pdt], ptr(ws), ws.numel() * 4, rows, d, int(rms), DT[z.dtype], stream_ptr())
     return dz, dgamma, dbeta
 
 

@@ -77,13 +77,14 @@ int hyp_norm_bwd(const void* dy, const void* z, const void* gamma, const float* 
 
 /* hyp_norm_bwd as the framework's ops use it: `dres` (may be NULL) is the gradient reaching the norm's input through
  * the skip connection and is added to dz in the same pass; dgamma / dbeta are written as `param_dtype` (0 fp32,
- * 1 fp16, 2 bf16) so they can be stored straight into a 16-bit flat gradient buffer; and there is no second kernel --
+ * 1 fp16, 2 bf16) so they can be stored straight into a 16-bit flat gradient buffer; `dz_colsum` (may be NULL, d <= 2048)
+ * receives the column sums of dz (the bias gradient of the layer feeding this norm); and there is no second kernel --
  * partial sums are added (fp32 atomics) into the accumulator in `ws`, and the last block rounds it out.  `ws`
  * (hyp_norm_bwd_fused_ws_bytes(d) bytes, 16-byte aligned) must be zero on entry and is zero again on return.
  * No reference counterpart (autograd adds the two branches with a separate elementwise kernel there). */
 long long hyp_norm_bwd_fused_ws_bytes(int d);
 int hyp_norm_bwd_fused(const void* dy, const void* z, const void* gamma, const float* mean, const float* rstd,
-                       const void* dres, void* dz, void* dgamma, void* dbeta, int param_dtype, void* ws,
+                       const void* dres, void* dz, void* dgamma, void* dbeta, void* dz_colsum, int param_dtype, void* ws,
                        long long ws_bytes, int rows, int d, int rms, int dtype, void* stream);
 
 /* hyp_norm_bwd without caller scratch.  It has no counterpart in the reference: it exists for callers that

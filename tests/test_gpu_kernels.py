@@ -175,8 +175,12 @@ def test_norm_fwd_bwd(nat, rows, d, rms, dtype):
     dres = torch.randn(rows, d, device="cuda").to(dtype)
     g_out = torch.empty(d, device="cuda", dtype=dtype)
     b_out = torch.empty(d, device="cuda", dtype=dtype)
-    dz2, dgamma2, dbeta2 = nat.norm_bwd(dy, z, g, mean, rstd, rms=rms, dres=dres, dgamma_out=g_out, dbeta_out=b_out)
+    cs = torch.empty(d, device="cuda", dtype=dtype) if d <= 2048 else None
+    dz2, dgamma2, dbeta2 = nat.norm_bwd(dy, z, g, mean, rstd, rms=rms, dres=dres, dgamma_out=g_out, dbeta_out=b_out,
+                                        dz_colsum_out=cs)
     assert dgamma2.data_ptr() == g_out.data_ptr()
+    if cs is not None:   # column sums of dz ride along (bias gradient of the layer feeding the norm)
+        assert _rel_err(cs, (zq.grad + dres.float()).sum(0)) < (3e-2 if dtype == torch.bfloat16 else 1e-4)
     assert _rel_err(dz2, zq.grad + dres.float()) < tol
     assert _rel_err(dgamma2, gf.grad) < tol
     if not rms:
