@@ -24,9 +24,10 @@ inline EncodeTiledFn tmap_encode_fn() {
 }
 
 // rank-N (<= 5) tiled map, SWIZZLE_128B, zero fill out of bounds.  dims[0] is the contiguous dimension;
-// strides_bytes[i] is the stride of dims[i+1].
+// strides_bytes[i] is the stride of dims[i+1]; elem_strides (optional) are the per-dimension traversal strides.
 inline int make_tmap_nd(CUtensorMap* tm, const void* ptr, int dtype, int rank, const unsigned long long* dims,
-                        const unsigned long long* strides_bytes, const unsigned* box) {
+                        const unsigned long long* strides_bytes, const unsigned* box,
+                        const unsigned* elem_strides = nullptr) {
   EncodeTiledFn enc = tmap_encode_fn();
   HYP_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled is unavailable (driver too old?)");
   // The encoder is a driver-API call: make sure the primary context is bound to THIS thread first (a fresh autograd
@@ -39,7 +40,7 @@ inline int make_tmap_nd(CUtensorMap* tm, const void* ptr, int dtype, int rank, c
   HYP_REQUIRE((reinterpret_cast<uintptr_t>(ptr) & 15) == 0, "TMA operand pointer must be 16-byte aligned");
   cuuint64_t d[5], s[4];
   cuuint32_t b[5], e[5];
-  for (int i = 0; i < rank; ++i) { d[i] = dims[i]; b[i] = box[i]; e[i] = 1; }
+  for (int i = 0; i < rank; ++i) { d[i] = dims[i]; b[i] = box[i]; e[i] = elem_strides ? elem_strides[i] : 1; }
   for (int i = 0; i + 1 < rank; ++i) {
     HYP_REQUIRE(strides_bytes[i] % 16 == 0, "TMA strides must be multiples of 16 bytes (stride %d = %llu)", i, strides_bytes[i]);
     s[i] = strides_bytes[i];

@@ -42,6 +42,7 @@ _SIGS = {
     "hyp_embedding_fwd": "ppplilip",
     "hyp_embedding_bwd": "ppplillip",
     "hyp_rope": "piiiilllpfiip",
+    "hyp_conv2d_fwd": "ppp" + "iiiiiiiii" + "ppp" + "ii" + "p",
 }
 
 DT = {torch.float32: 0, torch.float16: 1, torch.bfloat16: 2}

@@ -1,10 +1,13 @@
 """Conv -> BatchNorm -> ReLU (+ residual) blocks for the ResNets.
 
-Data runs channels-last (NHWC).  The convolution itself is cuDNN's implicit GEMM
-through ``F.conv2d`` for now -- 1x1 convolutions on CUDA are routed to the
-tcgen05 GEMM (an NHWC 1x1 conv *is* ``[N*H*W, Cin] @ W[Cout, Cin]^T``) -- and the
-BatchNorm-apply + ReLU + residual-add tail is one fused pass
-(``csrc/bn_act.cu``) instead of three ATen kernels.
+Data runs channels-last (NHWC).  Convolution forward is the tcgen05 implicit GEMM of
+``csrc/conv_igemm.cu`` (one 4-D TMA box per filter tap, no im2col buffer) whenever the
+input channels are a multiple of 64; 1x1 stride-1 convolutions are routed to the plain
+tcgen05 GEMM (an NHWC 1x1 conv *is* ``[N*H*W, Cin] @ W[Cout, Cin]^T``); the 3-channel
+stem and the conv backward (dgrad / wgrad) stay on cuDNN.  In training the
+BatchNorm-apply + ReLU + residual-add tail is one fused pass (``csrc/bn_act.cu``);
+in eval mode BatchNorm is folded into the convolution's epilogue together with the
+residual add and the ReLU, so a whole Conv-BN-(+res)-ReLU block is one kernel.
 
 Reference call sites: torchvision resnet18/50 Conv2d->BatchNorm2d->ReLU
 (02_development/distributed_utils.py:229; Phase 1/baseline_performance.ipynb c0 L23).
@@ -22,6 +25,51 @@ def to_channels_last(x: torch.Tensor) -> torch.Tensor:
     return x.contiguous(memory_format=torch.channels_last) if x.is_cuda and x.dim() == 4 else x
 
 
+def _igemm_ok(x, conv: nn.Conv2d) -> bool:
+    import os
+
+    return (x.is_cuda and _lib.available() and x.dim() == 4 and x.dtype in (torch.float16, torch.bfloat16)
+            and conv.weight.dtype == x.dtype and conv.groups == 1 and conv.dilation == (1, 1)
+            and conv.stride[0] == conv.stride[1] and conv.stride[0] in (1, 2)
+            and conv.padding[0] == conv.padding[1] and isinstance(conv.padding[0], int)
+            and conv.padding_mode == "zeros" and conv.in_channels % 64 == 0 and conv.out_channels % 32 == 0
+            and x.is_contiguous(memory_format=torch.channels_last)
+            and os.environ.get("HYPERION_CONV", "igemm") == "igemm")
+
+
+def conv2d_igemm(x, weight, stride: int, pad: int, scale=None, shift=None, residual=None, relu: bool = False):
+    """Raw call of ``hyp_conv2d_fwd`` on channels-last tensors (no autograd): returns y [N, K, Ho, Wo] channels-last."""
+    N, C, H, W = x.shape
+    K, _, R, S = weight.shape
+    w = weight.contiguous(memory_format=torch.channels_last)   # memory order [K, R, S, C]
+    Ho, Wo = (H + 2 * pad - R) // stride + 1, (W + 2 * pad - S) // stride + 1
+    y = torch.empty((N, K, Ho, Wo), device=x.device, dtype=x.dtype, memory_format=torch.channels_last)
+    if residual is not None:
+        assert residual.shape == y.shape and residual.is_contiguous(memory_format=torch.channels_last)
+    _lib.call("hyp_conv2d_fwd", _lib.ptr(x), _lib.ptr(w), _lib.ptr(y), N, H, W, C, K, R, S, stride, pad,
+              _lib.ptr(scale), _lib.ptr(shift), _lib.ptr(residual), int(relu), _lib.DT[x.dtype], _lib.stream_ptr())
+    return y
+
+
+class _ConvFn(torch.autograd.Function):
+    """Convolution forward on conv_igemm_tcgen05; dgrad / wgrad through ATen's convolution_backward (cuDNN)."""
+
+    @staticmethod
+    def forward(ctx, x, weight, stride, pad):
+        ctx.save_for_backward(x, weight)
+        ctx.stride, ctx.pad = stride, pad
+        return conv2d_igemm(x, weight, stride, pad)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, weight = ctx.saved_tensors
+        dy = dy.contiguous(memory_format=torch.channels_last)
+        dx, dw, _ = torch.ops.aten.convolution_backward(
+            dy, x, weight, None, [ctx.stride] * 2, [ctx.pad] * 2, [1, 1], False, [0, 0], 1,
+            [ctx.needs_input_grad[0], ctx.needs_input_grad[1], False])
+        return dx, dw, None, None
+
+
 def _conv(x, conv: nn.Conv2d):
     from . import functional as Fn
 
@@ -34,6 +82,9 @@ def _conv(x, conv: nn.Conv2d):
         x2 = x.permute(0, 2, 3, 1).reshape(N * H * W, C)
         y2 = Fn.linear(x2, conv.weight.reshape(conv.out_channels, C), conv.bias)
         return y2.reshape(N, H, W, conv.out_channels).permute(0, 3, 1, 2)
+    if _igemm_ok(x, conv):
+        y = _ConvFn.apply(x, conv.weight, conv.stride[0], conv.padding[0])
+        return y if conv.bias is None else y + conv.bias.view(1, -1, 1, 1)
     return F.conv2d(x, conv.weight, conv.bias, conv.stride, conv.padding, conv.dilation, conv.groups)
 
 
@@ -89,6 +140,15 @@ def _bn_native_ok(y, bn, residual) -> bool:
 
 
 def conv_bn_act(x, conv: nn.Conv2d, bn: nn.BatchNorm2d, relu: bool = True, residual=None):
+    if (not bn.training and not torch.is_grad_enabled() and bn.track_running_stats and _igemm_ok(x, conv)
+            and (residual is None or residual.is_contiguous(memory_format=torch.channels_last))):
+        # inference: BatchNorm folded into the convolution epilogue (+ conv bias, residual, ReLU) -- one kernel per block
+        scale = bn.weight.float() * torch.rsqrt(bn.running_var.float() + bn.eps) if bn.affine else torch.rsqrt(bn.running_var.float() + bn.eps)
+        shift = (bn.bias.float() if bn.affine else 0.0) - bn.running_mean.float() * scale
+        if conv.bias is not None:
+            shift = shift + conv.bias.float() * scale
+        return conv2d_igemm(x, conv.weight, conv.stride[0], conv.padding[0], scale.contiguous(), shift.contiguous(),
+                            residual, relu)
     y = _conv(x, conv)
     if _bn_native_ok(y, bn, residual):
         bn.num_batches_tracked.add_(1)

@@ -197,6 +197,15 @@ int hyp_ipc_open(const unsigned char* handle64, long long* out_ptr);
 int hyp_ipc_close(long long ptr);
 int hyp_ipc_free(long long ptr);
 
+/* ---- conv_igemm_tcgen05 (csrc/conv_igemm.cu) -----------------------------------------
+ * NHWC convolution forward as an implicit GEMM: x [N,H,W,C], w [K,R,S,C], y [N,Ho,Wo,K], all 16-bit (dtype 1/2),
+ * C % 64 == 0, K % 32 == 0, stride 1 or 2, symmetric zero padding.  Optional epilogue: y = conv * scale[k] + shift[k]
+ * (fp32 [K]; a folded eval-mode BatchNorm or a bias), + residual (shaped like y), ReLU.
+ * Reference: torchvision resnet18/50 Conv2d -> BatchNorm2d -> ReLU (distributed_utils.py:229, compilation_optimization.py:89). */
+int hyp_conv2d_fwd(const void* x, const void* w, void* y, int N, int H, int W, int C, int K, int R, int S, int stride,
+                   int pad, const float* scale, const float* shift, const void* residual, int relu, int dtype,
+                   void* stream);
+
 /* ---- bn_act (csrc/bn_act.cu) ------------------------------------------------------
  * Training-mode BatchNorm2d + residual add + ReLU on NHWC-contiguous [rows = N*H*W, C] 16-bit tensors.
  * sums / dsums: fp32 [2*C] scratch ZEROED by the caller (batch statistics / dbeta,dgamma on return).

@@ -298,3 +298,64 @@ def test_gradient_slots_receive_kernel_output_directly():
     finally:
         gradslot.ENABLED = True
     assert _rel(flat.grad, g1) < 1e-2
+
+
+CONV_CASES = [
+    # N, C, H, W, K, R, stride, pad
+    (4, 64, 56, 56, 64, 3, 1, 1),      # ResNet stage-1 3x3
+    (2, 128, 28, 28, 128, 3, 1, 1),
+    (3, 64, 30, 22, 96, 3, 1, 1),      # ragged patches, K not a multiple of 64
+    (8, 256, 8, 8, 512, 3, 1, 1),      # small images: several per tile
+    (2, 64, 56, 56, 128, 3, 2, 1),     # strided 3x3
+    (2, 256, 56, 56, 512, 1, 2, 0),    # strided 1x1 (downsample)
+    (5, 64, 7, 7, 64, 3, 1, 1),        # odd image size
+    (2, 64, 17, 17, 64, 5, 1, 2),      # 5x5
+]
+
+
+@pytest.mark.parametrize("N,C,H,W,K,R,stride,pad", CONV_CASES)
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_conv_igemm_forward_matches_fp32(N, C, H, W, K, R, stride, pad, dtype):
+    from hyperion_b200.ops import conv as convops
+
+    torch.manual_seed(21)
+    x = torch.randn(N, C, H, W, device="cuda").to(dtype).contiguous(memory_format=torch.channels_last)
+    w = (torch.randn(K, C, R, R, device="cuda") / (C * R * R) ** 0.5).to(dtype)
+    ref = F.conv2d(x.float(), w.float(), None, stride, pad)
+    y = convops.conv2d_igemm(x, w, stride, pad)
+    assert y.shape == ref.shape and y.is_contiguous(memory_format=torch.channels_last)
+    assert _rel(y, ref) < 1e-2, _rel(y, ref)
+    # fused epilogue: per-channel affine (folded BN), residual, ReLU
+    scale, shift = torch.rand(K, device="cuda") + 0.5, torch.randn(K, device="cuda")
+    res = torch.randn_like(ref).to(dtype).contiguous(memory_format=torch.channels_last)
+    y2 = convops.conv2d_igemm(x, w, stride, pad, scale, shift, res, relu=True)
+    ref2 = F.relu(ref * scale.view(1, -1, 1, 1) + shift.view(1, -1, 1, 1) + res.float())
+    assert _rel(y2, ref2) < 1e-2, _rel(y2, ref2)
+
+
+def test_conv_bn_act_block_train_and_eval_use_igemm():
+    """conv_bn_act: training forward+backward through the igemm forward (cuDNN backward), eval folds BN into the kernel."""
+    import torch.nn as nn
+
+    from hyperion_b200.ops import conv as convops
+
+    torch.manual_seed(22)
+    conv = nn.Conv2d(64, 128, 3, 2, 1, bias=False).cuda().to(torch.bfloat16).to(memory_format=torch.channels_last)
+    bn = nn.BatchNorm2d(128).cuda()
+    bn.weight.data.uniform_(0.5, 1.5); bn.bias.data.normal_(); bn.running_mean.normal_(); bn.running_var.uniform_(0.5, 2.0)
+    x = torch.randn(4, 64, 28, 28, device="cuda").to(torch.bfloat16).contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    # training: gradients vs the plain torch composition in fp32
+    y = convops.conv_bn_act(x, conv, bn, relu=True)
+    dy = torch.randn_like(y)
+    gx, gw = torch.autograd.grad(y, [x, conv.weight], dy)
+    xr, wr = x.detach().float().requires_grad_(True), conv.weight.detach().float().requires_grad_(True)
+    yr = F.relu(F.batch_norm(F.conv2d(xr, wr, None, 2, 1), None, None, bn.weight.float(), bn.bias.float(), True, 0.1, bn.eps))
+    gxr, gwr = torch.autograd.grad(yr, [xr, wr], dy.float())
+    assert _rel(y, yr) < 3e-2 and _rel(gx, gxr) < 5e-2 and _rel(gw, gwr) < 5e-2
+    # eval: one kernel (BN folded, ReLU fused)
+    bn.eval()
+    with torch.no_grad():
+        ye = convops.conv_bn_act(x, conv, bn, relu=True)
+        yer = F.relu(F.batch_norm(F.conv2d(x.float(), conv.weight.float(), None, 2, 1), bn.running_mean, bn.running_var,
+                                  bn.weight, bn.bias, False, 0.1, bn.eps))
+    assert _rel(ye, yer) < 2e-2
