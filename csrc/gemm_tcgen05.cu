@@ -712,16 +712,22 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 // tcgen05.mma.cta_group::2 (M = 256), which reads both halves of B from the two CTAs' shared memory, so per-SM
 // operand traffic from L2 drops from 48 KB to 32 KB per k-block and the ring deepens to 6 stages.  Each CTA keeps
 // its 128 accumulator rows in its own TMEM and runs its own epilogue.
-constexpr int G2_STAGES = 6;
 constexpr int G2_BN = 256;
-constexpr int G2_STAGE_BYTES = A_STAGE + (G2_BN / 2) * ROW_BYTES;  // 16 KB A + 16 KB B-half
-constexpr int G2_SMEM = G2_STAGES * G2_STAGE_BYTES + 256 + STG_BYTES + 1024;
+// BN = 256: 16 KB A + 16 KB B-half per stage, 6 stages.  BN = 128 (small-M problems: twice the tiles to fill the pairs):
+// 16 KB + 8 KB, 8 stages.
+template <int BN>
+struct G2Cfg {
+  static constexpr int STAGES = (BN == 256) ? 6 : 8;
+  static constexpr int STAGE_BYTES = A_STAGE + (BN / 2) * ROW_BYTES;
+  static constexpr int SMEM = STAGES * STAGE_BYTES + 256 + STG_BYTES + 1024;
+};
 
-template <int EPI, int ACT>
+template <int EPI, int ACT, int BN = G2_BN>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
 gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
              const __grid_constant__ Params p) {
-  constexpr int BN = G2_BN;
+  constexpr int G2_STAGES = G2Cfg<BN>::STAGES;
+  constexpr int G2_STAGE_BYTES = G2Cfg<BN>::STAGE_BYTES;
   constexpr int BH = BN / 2;          // B columns staged by one CTA
   constexpr int BM2 = 2 * BM;         // tile rows of the pair
   extern __shared__ uint8_t smem_raw[];
@@ -989,21 +995,29 @@ static int dispatch_ag(const CUtensorMap& ta, const CUtensorMap& tb, const Param
   return -1;
 }
 
-template <int EPI, int ACT>
+template <int EPI, int ACT, int BN = G2_BN>
 static int launch2(const CUtensorMap& ta, const CUtensorMap& tb, const Params& p, cudaStream_t stream) {
   static bool attr_set[64] = {false};
   int dev = 0;
   cudaGetDevice(&dev);
   if (!attr_set[dev & 63]) {
-    HYP_CHECK_CUDA(cudaFuncSetAttribute(gemm2_kernel<EPI, ACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, G2_SMEM));
+    HYP_CHECK_CUDA(cudaFuncSetAttribute(gemm2_kernel<EPI, ACT, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, G2Cfg<BN>::SMEM));
     attr_set[dev & 63] = true;
   }
-  const int tiles = ((p.M + 2 * BM - 1) / (2 * BM)) * ((p.N + G2_BN - 1) / G2_BN) * p.splits;
+  const int tiles = ((p.M + 2 * BM - 1) / (2 * BM)) * ((p.N + BN - 1) / BN) * p.splits;
   int clusters = num_sms() / 2;
   if (tiles < clusters) clusters = tiles;
-  gemm2_kernel<EPI, ACT><<<2 * clusters, NUM_THREADS, G2_SMEM, stream>>>(ta, tb, p);
+  gemm2_kernel<EPI, ACT, BN><<<2 * clusters, NUM_THREADS, G2Cfg<BN>::SMEM, stream>>>(ta, tb, p);
   HYP_CHECK_CUDA(cudaGetLastError());
   return 0;
+}
+
+// the 256 x 128 pair tile is instantiated for the epilogues small-M problems use (plain, bias/residual, beta)
+static bool pair128_supported(int epi, int act) { return epi == 0 || (epi == 1 && act == 0) || epi == 5; }
+static int dispatch2_n128(const CUtensorMap& ta, const CUtensorMap& tb, const Params& p, int epi, cudaStream_t st) {
+  if (epi == 0) return launch2<0, 0, 128>(ta, tb, p, st);
+  if (epi == 1) return launch2<1, 0, 128>(ta, tb, p, st);
+  return launch2<5, 0, 128>(ta, tb, p, st);
 }
 
 static int dispatch2(const CUtensorMap& ta, const CUtensorMap& tb, const Params& p, int epi, cudaStream_t st) {
@@ -1079,7 +1093,23 @@ static int gemm_impl(const void* A, const void* B, void* D, int M, int N, int K,
   HYP_REQUIRE(in_dtype != DT_F32 || (!a_mn_major && !b_mn_major), "hyp_gemm: fp32/tf32 operands must be K-major");
   const int es = (in_dtype == DT_F32) ? 4 : 2;
   const int epr = gemm::ROW_BYTES / es;
-  const int BN = (N > 128) ? 256 : 128;
+  // 2-CTA (cta_group::2) path: 256 x 256 tiles on CTA pairs; 16-bit operands, large-enough problems
+  static int use_2cta = -1;
+  if (use_2cta < 0) {
+    const char* e = getenv("HYPERION_GEMM_2CTA");
+    use_2cta = e ? atoi(e) : 1;
+  }
+  // Tile shape.  Candidates: 256x256 and 256x128 on a CTA pair, 128x256 and 128x128 on one CTA.  Cost model = waves x relative time
+  // of one tile (a 128x128 tile measures ~1.15x a 256-wide one: half the MMA work, but it is shared-memory-bandwidth bound;
+  // the 1-CTA 128x256 tile runs ~1.35x slower than a pair's 256x256 per SM).  Small-M problems (Llama-7B at 512 tokens:
+  // 32 pair tiles for 74 pairs) fill the machine only with the small tile.
+  static int tile_force = -1;   // HYPERION_GEMM_TILE: 0 auto, 1 pair 256x256, 2 one-CTA 128x256, 3 one-CTA 128x128, 4 pair 256x128
+  if (tile_force < 0) {
+    const char* e = getenv("HYPERION_GEMM_TILE");
+    tile_force = e ? atoi(e) : 0;
+  }
+  const bool pair_ok = use_2cta && !ag && es == 2 && N > 128 && M >= 256;
+  int BN = (N > 128) ? 256 : 128;   // final choice below, once the epilogue kind is known
 
   gemm::Params p;
   p.M = M; p.N = N; p.K = K; p.esize = es; p.a_mn = a_mn_major; p.b_mn = b_mn_major;
@@ -1115,21 +1145,43 @@ static int gemm_impl(const void* A, const void* B, void* D, int M, int N, int K,
   else if (vec && p.splits == 1 && beta != 0.f && mode == 0 && act == 0 && !bias && !aux && !preact_out) epi = 5;
   p.simple = epi;
 
+  bool want_pair = pair_ok;
+  bool pair128 = false;
+  if (N > 128) {
+    const int sms = num_sms();
+    const long long sp = p.splits;
+    auto waves = [](long long tiles, int slots) { return static_cast<double>((tiles + slots - 1) / slots); };
+    const long long tm2 = (M + 255) / 256, tm1 = (M + 127) / 128;
+    const double c_pair = pair_ok ? waves(tm2 * ((N + 255) / 256) * sp, sms / 2) : 1e30;
+    const double c_p128 = (pair_ok && gemm::pair128_supported(epi, act)) ? 0.80 * waves(tm2 * ((N + 127) / 128) * sp, sms / 2) : 1e30;
+    const double c_256 = 1.35 * waves(tm1 * ((N + 255) / 256) * sp, sms);
+    const double c_128 = 1.15 * waves(tm1 * ((N + 127) / 128) * sp, sms);
+    int pick = 1;
+    double best = c_pair;
+    if (c_p128 < best - 1e-9) { best = c_p128; pick = 4; }
+    if (c_256 < best - 1e-9) { best = c_256; pick = 2; }
+    if (c_128 < best - 1e-9) { best = c_128; pick = 3; }
+    if (ag && (pick == 1 || pick == 4)) pick = 2;
+    if (tile_force >= 1 && tile_force <= 4) {
+      const bool ok = (tile_force == 1 && pair_ok) || (tile_force == 4 && pair_ok && gemm::pair128_supported(epi, act)) ||
+                      tile_force == 2 || tile_force == 3;
+      if (ok) pick = tile_force;
+    }
+    want_pair = (pick == 1 || pick == 4);
+    pair128 = (pick == 4);
+    BN = (pick == 3 || pick == 4) ? 128 : 256;
+  }
+  p.idesc = make_idesc(fmt, gemm::BM, BN, a_mn_major != 0, b_mn_major != 0);
+
   CUtensorMap ta, tb;
   int rc;
-  // 2-CTA (cta_group::2) path: 256 x 256 tiles on CTA pairs; 16-bit operands, large-enough problems
-  static int use_2cta = -1;
-  if (use_2cta < 0) {
-    const char* e = getenv("HYPERION_GEMM_2CTA");
-    use_2cta = e ? atoi(e) : 1;
-  }
   p.a_mn_mma = p.a_mn; p.b_mn_mma = p.b_mn;
   static const bool mn3_off = [] { const char* e = getenv("HYPERION_GEMM_MN3"); return e && e[0] == '0'; }();
   // ragged MN is fine when the row padding covers the last chunk's over-read (what it reads there only reaches output
   // rows / columns that are never stored)
   p.a_mn3 = (a_mn_major && es == 2 && (M % 64 == 0 || lda >= (M + 63) / 64 * 64) && !mn3_off) ? 1 : 0;
   p.b_mn3 = (b_mn_major && es == 2 && (N % 64 == 0 || ldb >= (N + 63) / 64 * 64) && !mn3_off) ? 1 : 0;
-  if (use_2cta && !ag && es == 2 && BN == 256 && M >= 256) {
+  if (want_pair) {
     static int dbg = -1;  // timing experiments only (results are wrong): 1 = TMA loads K-major boxes, 2 = MMA assumes K-major
     if (dbg < 0) { const char* e = getenv("HYPERION_GEMM_DBG"); dbg = e ? atoi(e) : 0; }
     if (dbg & 1) { a_mn_major = 0; b_mn_major = 0; p.a_mn = 0; p.b_mn = 0; }
@@ -1143,6 +1195,7 @@ static int gemm_impl(const void* A, const void* B, void* D, int M, int N, int K,
     else if (p.b_mn3)  rc = gemm::make_tmap_mn3(&tb, B, in_dtype, N, K, ldb, BN / 128);
     else               rc = gemm::make_tmap_2d(&tb, B, in_dtype, N, K, ldb, epr, epr);
     if (rc) return rc;
+    if (pair128) return gemm::dispatch2_n128(ta, tb, p, epi, stream);
     return gemm::dispatch2(ta, tb, p, epi, stream);
   }
   if (!a_mn_major)   rc = gemm::make_tmap_2d(&ta, A, in_dtype, K, M, lda, epr, gemm::BM);   // A: [M, K]
