@@ -61,6 +61,13 @@ struct Params {
   int a_mn, b_mn;  // operand majors
   int a_mn_mma, b_mn_mma;  // what the MMA descriptors assume (differs from a_mn/b_mn only under HYPERION_GEMM_DBG)
   int a_mn3, b_mn3;        // MN-major operand addressed through a rank-3 map: one TMA instruction per stage
+  // dual-K (pair kernel only): after the K loop over (A, B), k2_blocks more 64-wide k-blocks come from a second operand
+  // pair (A2 [M, 64*k2], B2 [N, 64*k2], both K-major) and accumulate into the same tile -- a LoRA update
+  // y = x W^T + t B^T runs as one GEMM instead of a second pass over y
+  int k2_blocks;
+  uint32_t idesc2;
+  alignas(64) CUtensorMap tmA2;
+  alignas(64) CUtensorMap tmB2;
   uint32_t idesc;
   int splits;      // split-K factor (fp32 atomic epilogue when > 1)
   // epilogue
@@ -809,6 +816,14 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
           }
           if (++stage == G2_STAGES) { stage = 0; phase ^= 1; }
         }
+        for (int kb2 = 0; kb2 < p.k2_blocks; ++kb2) {   // dual-K tail: second operand pair, K-major
+          mbar_wait(&empty[stage], phase ^ 1);
+          const uint32_t lead_bar = mapa_u32(smem_u32(&full[stage]), 0);
+          if (leader) mbar_expect_tx(&full[stage], 2 * G2_STAGE_BYTES);
+          tma_load_2d_2sm(sA + stage * A_STAGE, &p.tmA2, lead_bar, kb2 * epr, m0);
+          tma_load_2d_2sm(sB + stage * BH * ROW_BYTES, &p.tmB2, lead_bar, kb2 * epr, n0);
+          if (++stage == G2_STAGES) { stage = 0; phase ^= 1; }
+        }
       }
     }
   } else if (warp == 1) {
@@ -838,6 +853,18 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
             const uint64_t bd = make_smem_desc_sw128(b_base + k * b_kstep, b_lbo, 1024);
             umma_f16_2sm(d_tmem, ad, bd, p.idesc, (kb > tc.kb0 || k > 0) ? 1u : 0u);
           }
+          umma_commit_2sm(&empty[stage], 3);
+          if (++stage == G2_STAGES) { stage = 0; phase ^= 1; }
+        }
+        for (int kb2 = 0; kb2 < p.k2_blocks; ++kb2) {
+          mbar_wait(&full[stage], phase);
+          tc_fence_after();
+          const uint32_t a_base = smem_u32(sA + stage * A_STAGE);
+          const uint32_t b_base = smem_u32(sB + stage * BH * ROW_BYTES);
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            umma_f16_2sm(d_tmem, make_smem_desc_sw128(a_base + k * 32, 16, 1024), make_smem_desc_sw128(b_base + k * 32, 16, 1024),
+                         p.idesc2, (tc.kb1 > tc.kb0 || kb2 > 0 || k > 0) ? 1u : 0u);
           umma_commit_2sm(&empty[stage], 3);
           if (++stage == G2_STAGES) { stage = 0; phase ^= 1; }
         }
@@ -1078,10 +1105,13 @@ static int dispatch(const CUtensorMap& ta, const CUtensorMap& tb, const Params& 
 using namespace hyp;
 
 // See include/hyperion_b200.h for the contract.
+struct DualK { const void* A2; const void* B2; int K2; long long lda2, ldb2; };
+
 static int gemm_impl(const void* A, const void* B, void* D, int M, int N, int K, long long lda, long long ldb,
                      long long ldd, int in_dtype, int out_dtype, int a_mn_major, int b_mn_major, const void* bias,
                      int bias_dtype, const void* aux, long long ld_aux, int aux_dtype, void* preact_out, int act, int mode,
-                     float alpha, float beta, int splits, const gemm::AgParams* ag, void* stream_) {
+                     float alpha, float beta, int splits, const gemm::AgParams* ag, void* stream_,
+                     const DualK* dual = nullptr) {
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
   HYP_REQUIRE(M > 0 && N > 0 && K > 0, "hyp_gemm: empty problem %dx%dx%d", M, N, K);
   HYP_REQUIRE(in_dtype >= 0 && in_dtype <= 2 && out_dtype >= 0 && out_dtype <= 2, "hyp_gemm: bad dtype");
@@ -1171,6 +1201,13 @@ static int gemm_impl(const void* A, const void* B, void* D, int M, int N, int K,
     pair128 = (pick == 4);
     BN = (pick == 3 || pick == 4) ? 128 : 256;
   }
+  p.k2_blocks = 0;
+  p.idesc2 = 0;
+  if (dual) {
+    HYP_REQUIRE(pair_ok && p.splits == 1 && dual->K2 > 0 && dual->K2 % 64 == 0,
+                "hyp_gemm_dualk: needs 16-bit operands, M >= 256, N > 128, no split-K and K2 %% 64 == 0 (M=%d N=%d K2=%d)", M, N, dual->K2);
+    want_pair = true; pair128 = false; BN = 256;
+  }
   p.idesc = make_idesc(fmt, gemm::BM, BN, a_mn_major != 0, b_mn_major != 0);
 
   CUtensorMap ta, tb;
@@ -1195,6 +1232,14 @@ static int gemm_impl(const void* A, const void* B, void* D, int M, int N, int K,
     else if (p.b_mn3)  rc = gemm::make_tmap_mn3(&tb, B, in_dtype, N, K, ldb, BN / 128);
     else               rc = gemm::make_tmap_2d(&tb, B, in_dtype, N, K, ldb, epr, epr);
     if (rc) return rc;
+    if (dual) {
+      p.k2_blocks = dual->K2 / 64;
+      p.idesc2 = make_idesc(fmt, 2 * gemm::BM, BN, false, false);
+      rc = gemm::make_tmap_2d(&p.tmA2, dual->A2, in_dtype, dual->K2, M, dual->lda2, epr, gemm::BM);
+      if (rc) return rc;
+      rc = gemm::make_tmap_2d(&p.tmB2, dual->B2, in_dtype, dual->K2, N, dual->ldb2, epr, BN / 2);
+      if (rc) return rc;
+    }
     if (pair128) return gemm::dispatch2_n128(ta, tb, p, epi, stream);
     return gemm::dispatch2(ta, tb, p, epi, stream);
   }
@@ -1256,4 +1301,17 @@ HYP_API int hyp_gemm_ag(const void* A, const void* B, void* D, int M, int N, int
   g.arrived = arrived; g.target = target;
   return gemm_impl(A, B, D, M, N, K, lda, ldb, ldd, in_dtype, out_dtype, 0, 0, bias, bias_dtype, aux, ld_aux, aux_dtype,
                    preact_out, act, 0, alpha, 0.f, 1, &g, stream_);
+}
+
+// D = epilogue(alpha * (A B^T + A2 B2^T)): one GEMM whose reduction runs over two operand pairs (the second K-major,
+// K2 a multiple of 64 -- pad with zero columns).  The LoRA projection y = x W^T + t B_l^T (t = s * x A_l^T) is this
+// with (A, B) = (x, W) and (A2, B2) = (t, B_l): the rank-r update lands in the accumulator tile in TMEM instead of a
+// second read-modify-write pass over y.  Pair kernel only (16-bit, M >= 256, N > 128); bias / residual epilogue.
+HYP_API int hyp_gemm_dualk(const void* A, const void* B, void* D, int M, int N, int K, long long lda, long long ldb,
+                           long long ldd, int in_dtype, int out_dtype, int a_mn_major, int b_mn_major, const void* A2,
+                           const void* B2, int K2, long long lda2, long long ldb2, const void* bias, int bias_dtype,
+                           const void* aux, long long ld_aux, int aux_dtype, float alpha, void* stream_) {
+  DualK d{A2, B2, K2, lda2, ldb2};
+  return gemm_impl(A, B, D, M, N, K, lda, ldb, ldd, in_dtype, out_dtype, a_mn_major, b_mn_major, bias, bias_dtype, aux,
+                   ld_aux, aux_dtype, nullptr, 0, 0, alpha, 0.f, 1, nullptr, stream_, &d);
 }

@@ -24,6 +24,7 @@ _CODES = {"p": _P, "i": _I, "l": _L, "f": _F}
 # name -> argument codes (see the header for the meaning of every argument)
 _SIGS = {
     "hyp_gemm": "pppiiillliiiipiplipiiffip",
+    "hyp_gemm_dualk": "pppiiillliiii" + "ppill" + "pi" + "pli" + "fp",
     "hyp_stream_add": "ppplip",
     "hyp_stream_copy": "pplp",
     "hyp_colsum": "ppiilip",

@@ -552,38 +552,84 @@ def attention(q, k, v, causal: bool = False, key_padding_mask=None, dropout_p: f
 
 
 # --------------------------------------------------------------------------- LoRA
+def _lora_pads(A: torch.Tensor, B: torch.Tensor):
+    """Zero-padded 64-wide copies of the adapter matrices for the dual-K GEMM: A_pad [64, in], At_pad [in, 64],
+    B_pad [out, 64].  The buffers are cached on the parameter (zeros outside the rank-r block) and refreshed by copy."""
+    r = A.shape[0]
+    pads = getattr(A, "_hyp_pads", None)
+    if pads is None or pads[0].shape[1] != A.shape[1] or pads[2].shape[0] != B.shape[0] or pads[0].dtype != A.dtype:
+        pads = (torch.zeros(64, A.shape[1], device=A.device, dtype=A.dtype),
+                torch.zeros(A.shape[1], 64, device=A.device, dtype=A.dtype),
+                torch.zeros(B.shape[0], 64, device=A.device, dtype=A.dtype))
+        try:
+            A._hyp_pads = pads
+        except AttributeError:
+            pass
+    with torch.no_grad():
+        pads[0][:r].copy_(A)
+        pads[1][:, :r].copy_(A.t())
+        pads[2][:, :r].copy_(B)
+    return pads
+
+
 class _LoraLinearFn(torch.autograd.Function):
-    """y = x W^T + b + scaling * (xd A^T) B^T (+ residual); W is usually frozen."""
+    """y = x W^T + b + scaling * (xd A^T) B^T (+ residual); W is usually frozen.
+
+    With enough rows for the pair kernel (M >= 256) the base projection and the rank-r update are ONE dual-K GEMM
+    (``hyp_gemm_dualk``): t = s * xd A^T is computed first (zero-padded to 64 columns), then the reduction of the main
+    GEMM simply continues over (t, B) into the same TMEM accumulator; the backward does the same for
+    dx = dy W + dt A.  Otherwise: three launches of the plain GEMM (beta-accumulate)."""
 
     @staticmethod
     def forward(ctx, x, xd, w, b, A, B, scaling, residual):
         x2, xd2 = _as2d(x), _as2d(xd)
         same = xd is x
-        t = native.gemm(xd2, A, alpha=scaling)  # [M, r], scaling folded in
-        y = torch.empty((x2.shape[0], w.shape[0]), dtype=x.dtype, device=x.device)
-        native.gemm(x2, w, out=y, bias=b, aux=_as2d(residual) if residual is not None else None)
-        native.gemm(t, B, out=y, beta=1.0)  # rank-r update accumulated into the same output tile
+        M, N, r = x2.shape[0], w.shape[0], A.shape[0]
+        res2 = _as2d(residual) if residual is not None else None
+        dual = M >= 256 and N > 128 and r <= 64 and x.dtype != torch.float32 and w.dtype == x.dtype
+        if dual:
+            A_pad, At_pad, B_pad = _lora_pads(A, B)
+            t_pad = native.gemm(xd2, A_pad, alpha=scaling)          # [M, 64], columns >= r are zero
+            y = native.gemm_dualk(x2, w, t_pad, B_pad, bias=b, aux=res2)
+            t = t_pad[:, :r]
+            ctx.pads = (At_pad, B_pad)
+        else:
+            t = native.gemm(xd2, A, alpha=scaling)  # [M, r], scaling folded in
+            y = torch.empty((M, N), dtype=x.dtype, device=x.device)
+            native.gemm(x2, w, out=y, bias=b, aux=res2)
+            native.gemm(t, B, out=y, beta=1.0)  # rank-r update accumulated into the same output tile
+            ctx.pads = None
         ctx.save_for_backward(x2, xd2, w, A, B, t)
         ctx.scaling, ctx.same = scaling, same
         ctx.has_bias, ctx.has_res = b is not None, residual is not None
         ctx.slots = (gradslot.slot_of(A), gradslot.slot_of(B))
         ctx.x_shape = x.shape
-        return y.reshape(*x.shape[:-1], w.shape[0])
+        return y.reshape(*x.shape[:-1], N)
 
     @staticmethod
     def backward(ctx, dy):
         x2, xd2, w, A, B, t = ctx.saved_tensors
         dy2 = _as2d(dy)
         need_x, need_xd, need_w = ctx.needs_input_grad[0], ctx.needs_input_grad[1], ctx.needs_input_grad[2]
-        dt = native.gemm(dy2, B, b_mn_major=True, alpha=ctx.scaling)        # [M, r]
+        r = A.shape[0]
+        if ctx.pads is not None:
+            At_pad, B_pad = ctx.pads
+            dt_pad = native.gemm(dy2, B_pad, b_mn_major=True, alpha=ctx.scaling)   # [M, 64]
+            dt = dt_pad[:, :r]
+        else:
+            dt_pad = None
+            dt = native.gemm(dy2, B, b_mn_major=True, alpha=ctx.scaling)        # [M, r]
         s_A, s_B = ctx.slots
         dB = native.gemm(dy2, t, a_mn_major=True, b_mn_major=True, out=gradslot.claim(s_B, B.dtype))    # [out, r]
         dA = native.gemm(dt, xd2, a_mn_major=True, b_mn_major=True, out=gradslot.claim(s_A, A.dtype))   # [r, in]
         dx = dxd = None
         if need_x or (ctx.same and need_xd):
-            dx = native.gemm(dy2, w, b_mn_major=True)
-            if ctx.same:
-                native.gemm(dt, A, b_mn_major=True, out=dx, beta=1.0)
+            if ctx.same and dt_pad is not None and w.shape[1] > 128:
+                dx = native.gemm_dualk(dy2, w, dt_pad, At_pad, b_mn_major=True)   # dy W + dt A in one launch
+            else:
+                dx = native.gemm(dy2, w, b_mn_major=True)
+                if ctx.same:
+                    native.gemm(dt, A, b_mn_major=True, out=dx, beta=1.0)
             dx = dx.reshape(ctx.x_shape)
         if not ctx.same and need_xd:
             dxd = native.gemm(dt, A, b_mn_major=True).reshape(ctx.x_shape)

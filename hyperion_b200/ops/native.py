@@ -58,6 +58,22 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn_major: bool = False, b_mn_maj
     return out
 
 
+def gemm_dualk(a: torch.Tensor, b: torch.Tensor, a2: torch.Tensor, b2: torch.Tensor, *, b_mn_major: bool = False,
+               out: torch.Tensor | None = None, bias: torch.Tensor | None = None, aux: torch.Tensor | None = None,
+               alpha: float = 1.0) -> torch.Tensor:
+    """``D = alpha * (a @ b^T + a2 @ b2^T) + bias + aux`` in one launch (second pair K-major, K2 % 64 == 0)."""
+    M, K = a.shape
+    N = b.shape[1] if b_mn_major else b.shape[0]
+    K2 = a2.shape[1]
+    assert a2.shape == (M, K2) and b2.shape == (N, K2) and K2 % 64 == 0 and a2.stride(1) == 1 and b2.stride(1) == 1
+    if out is None:
+        out = torch.empty((M, N), device=a.device, dtype=a.dtype)
+    call("hyp_gemm_dualk", ptr(a), ptr(b), ptr(out), M, N, K, _ld(a), _ld(b), _ld(out), DT[a.dtype], DT[out.dtype], 0,
+         int(b_mn_major), ptr(a2), ptr(b2), K2, _ld(a2), _ld(b2), ptr(bias), DT[bias.dtype] if bias is not None else 0,
+         ptr(aux), _ld(aux) if aux is not None else 0, DT[aux.dtype] if aux is not None else 0, float(alpha), stream_ptr())
+    return out
+
+
 def stream_add(x: torch.Tensor, y: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
     if out is None:
         out = torch.empty_like(x)

@@ -42,6 +42,13 @@ int hyp_gemm(const void* A, const void* B, void* D, int M, int N, int K, long lo
              int in_dtype, int out_dtype, int a_mn_major, int b_mn_major, const void* bias, int bias_dtype,
              const void* aux, long long ld_aux, int aux_dtype, void* preact_out, int act, int mode, float alpha,
              float beta, int splits, void* stream);
+/* D = epilogue(alpha * (A B^T + A2 B2^T)): the reduction runs over a second, K-major operand pair as well (K2 % 64 == 0,
+ * zero-pad).  One launch for a LoRA projection (A2 = s * x A_l^T, B2 = B_l).  16-bit, M >= 256, N > 128; bias / residual
+ * epilogue only.  Reference: peft LoRA forward base(x) + B(A(dropout(x))) * alpha/r (distributed_utils.py:469-474). */
+int hyp_gemm_dualk(const void* A, const void* B, void* D, int M, int N, int K, long long lda, long long ldb, long long ldd,
+                   int in_dtype, int out_dtype, int a_mn_major, int b_mn_major, const void* A2, const void* B2, int K2,
+                   long long lda2, long long ldb2, const void* bias, int bias_dtype, const void* aux, long long ld_aux,
+                   int aux_dtype, float alpha, void* stream);
 
 /* ---- streaming kernels (csrc/elementwise.cu) --------------------------------
  * Reference: z = x + y bandwidth sweep, Phase 1/01_hardware_exploration.ipynb c1 L148. */

@@ -51,6 +51,25 @@ def test_gemm_layouts(nat, M, N, K, a_mn, b_mn):
     assert _rel_err(d, ref) < 1e-2, _rel_err(d, ref)
 
 
+@pytest.mark.parametrize("b_mn", [False, True])
+def test_gemm_dual_k(nat, b_mn):
+    """One launch, two operand pairs: D = A B^T + A2 B2^T (+ bias + residual)."""
+    torch.manual_seed(9)
+    M, N, K, K2 = 1000, 640, 320, 64
+    a = torch.randn(M, K, device="cuda", dtype=torch.bfloat16)
+    b = torch.randn(N, K, device="cuda", dtype=torch.bfloat16)
+    a2 = torch.randn(M, K2, device="cuda", dtype=torch.bfloat16)
+    b2 = torch.randn(N, K2, device="cuda", dtype=torch.bfloat16)
+    a2[:, 16:] = 0   # as LoRA uses it: rank 16 zero-padded to 64
+    bias = torch.randn(N, device="cuda", dtype=torch.bfloat16)
+    res = torch.randn(M, N, device="cuda", dtype=torch.bfloat16)
+    ref = a.float() @ b.float().t() + a2.float() @ b2.float().t()
+    bb = b.t().contiguous() if b_mn else b
+    assert _rel_err(nat.gemm_dualk(a, bb, a2, b2, b_mn_major=b_mn), ref) < 1e-2
+    d = nat.gemm_dualk(a, bb, a2, b2, b_mn_major=b_mn, bias=bias, aux=res)
+    assert _rel_err(d, ref + bias.float() + res.float()) < 1e-2
+
+
 def test_gemm_tf32(nat):
     torch.manual_seed(2)
     a = torch.randn(512, 384, device="cuda")

@@ -101,15 +101,21 @@ def test_embedding_and_linear_cross_entropy(ops):
     assert _rel(gt, rt) < 4e-2 and _rel(gw, rw) < 4e-2 and _rel(gb, rb) < 4e-2
 
 
-def test_lora_linear_op(ops):
+@pytest.mark.parametrize("rows", [4 * 128, 48])   # 512 rows: one dual-K GEMM; 48 rows: three plain launches
+@pytest.mark.parametrize("with_bias_res", [False, True])
+def test_lora_linear_op(ops, rows, with_bias_res):
     torch.manual_seed(4)
-    x, w = _leaf(4, 128, 512), _leaf(512, 512, scale=0.05)
-    A, B = _leaf(16, 512, scale=0.05), _leaf(512, 16, scale=0.05)
-    y = ops.lora_linear(x, x, w, None, A, B, 2.0)
+    x, w = _leaf(rows // 16, 16, 512), _leaf(768, 512, scale=0.05)
+    A, B = _leaf(16, 512, scale=0.05), _leaf(768, 16, scale=0.05)
+    b = _leaf(768, scale=0.1) if with_bias_res else None
+    res = _leaf(rows // 16, 16, 768) if with_bias_res else None
+    y = ops.lora_linear(x, x, w, b, A, B, 2.0, residual=res)
     dy = torch.randn_like(y)
     gx, gA, gB = torch.autograd.grad(y, [x, A, B], dy)
     xr, wr, Ar, Br = _ref_copy(x, w, A, B)
-    yr = F.linear(xr, wr) + 2.0 * F.linear(F.linear(xr, Ar), Br)
+    yr = F.linear(xr, wr, b.float() if b is not None else None) + 2.0 * F.linear(F.linear(xr, Ar), Br)
+    if res is not None:
+        yr = yr + res.float()
     rx, rA, rB = torch.autograd.grad(yr, [xr, Ar, Br], dy.float())
     assert _rel(y, yr) < 2e-2
     assert _rel(gx, rx) < 3e-2 and _rel(gA, rA) < 3e-2 and _rel(gB, rB) < 3e-2
