@@ -159,6 +159,12 @@ class HyperionFSDP(nn.Module):
             um.register_forward_pre_hook(self._make_fwd_hook(k))
         # ---- K-C3: units whose first consumer is a GEMM on a known weight gather inside that GEMM
         self._ag_handles: dict[int, _AgHandle] = {}
+        import os
+
+        # HYPERION_FSDP_AG=plain gathers every unit with the stand-alone kernel (queued at the start of the forward, so it
+        # overlaps the forward just the same) and leaves the GEMMs on the faster CTA-pair kernel
+        fuse_allgather_gemm = fuse_allgather_gemm and os.environ.get("HYPERION_FSDP_AG", "fused") == "fused"
+        self._gathers_due = False
         if self.fused and fuse_allgather_gemm and self.flat.dtype in (torch.bfloat16, torch.float16):
             from ..models.transformer import MultiheadSelfAttention
 
@@ -214,7 +220,16 @@ class HyperionFSDP(nn.Module):
                 if ev is not None:
                     cur.wait_event(ev)
 
+    def _start_of_forward(self) -> None:
+        # the parameter gathers of the previous optimizer step are issued here, in forward order on the communication
+        # stream, so they run under this forward (each unit's first use waits for its own event); inside a captured step
+        # this keeps them in the same graph as their consumers instead of serialising them at the end of the step
+        if self._gathers_due:
+            self._gathers_due = False
+            self._queue_gathers()
+
     def forward(self, *args, **kwargs):
+        self._start_of_forward()
         if self.comm_stream is not None:
             self._wait_units_at_start()
         out = self.module(*args, **kwargs)
@@ -223,6 +238,7 @@ class HyperionFSDP(nn.Module):
 
     def loss(self, *args, **kwargs):
         """Forward through ``module.loss`` (fused LM-head + CE) with the same gather waits as ``forward``."""
+        self._start_of_forward()
         if self.comm_stream is not None:
             self._wait_units_at_start()
         out = self.module.loss(*args, **kwargs)
@@ -335,7 +351,9 @@ class HyperionFSDP(nn.Module):
             self.loss_scaler.update()
         self.flat.zero_grad()  # also leaves param.grad undefined so the next backward's kernels write into the slots
         if W > 1:
-            self._queue_gathers()
+            self._gathers_due = True   # issued at the start of the next forward (see _start_of_forward)
+            if self.fused and torch.cuda.is_current_stream_capturing():
+                torch.cuda.current_stream(self.device).wait_stream(self.comm_stream)  # re-join before the capture ends
         if self.arena is not None:
             self.arena.end_step(self.comm_stream)
 
@@ -378,10 +396,6 @@ class HyperionFSDP(nn.Module):
                     gev = torch.cuda.Event()
                     gev.record(self.comm_stream)
                     self._gather_events[ui] = gev
-            if torch.cuda.is_current_stream_capturing():
-                # a captured step must re-join every forked stream before the capture ends
-                torch.cuda.current_stream(self.device).wait_stream(self.comm_stream)
-                self._gather_events = [None] * len(self.units)
         else:
             for ui in order:
                 s, e, _ = self.units[ui]
@@ -390,6 +404,15 @@ class HyperionFSDP(nn.Module):
 
     def zero_grad(self, set_to_none: bool = False) -> None:
         self.flat.zero_grad()
+
+    def sync_params(self) -> None:
+        """Make the resident 16-bit parameters current NOW (the gathers after an optimizer step are otherwise issued
+        lazily at the start of the next forward): call before reading ``module.parameters()`` directly."""
+        if self._gathers_due:
+            self._gathers_due = False
+            self._queue_gathers()
+        if self.comm_stream is not None:
+            torch.cuda.current_stream(self.device).wait_stream(self.comm_stream)
 
     # ------------------------------------------------------------------ checkpoints (K-C6 / K-C7)
     @torch.no_grad()
