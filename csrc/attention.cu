@@ -965,8 +965,9 @@ static int launch_bwd64(const CUtensorMap& tq, const CUtensorMap& tk, const CUte
 // lane, so a row is read as one contiguous 128/256-byte segment) and combine with shuffles.
 template <typename T>
 __global__ void __launch_bounds__(256)
-attn_delta_kernel(const T* __restrict__ o, const T* __restrict__ d_o, float* __restrict__ delta, int B, int H, int S, int D,
-                  long long o_sb, long long o_sh, long long o_ss, long long g_sb, long long g_sh, long long g_ss) {
+attn_delta_kernel(const T* __restrict__ o, const T* __restrict__ d_o, float* __restrict__ delta, float* __restrict__ dq_acc,
+                  int B, int H, int S, int D, long long o_sb, long long o_sh, long long o_ss, long long g_sb, long long g_sh,
+                  long long g_ss) {
   const int lpr = D >> 3;  // lanes per row: 8 or 16
   const long long gid = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   const long long idx = gid / lpr;
@@ -975,6 +976,10 @@ attn_delta_kernel(const T* __restrict__ o, const T* __restrict__ d_o, float* __r
   const bool valid = idx < total;
   float acc = 0.f;
   if (valid) {
+    // the same threads clear the fp32 dQ accumulator the backward kernel reduces into (saves the caller a fill pass)
+    float4* z = reinterpret_cast<float4*>(dq_acc + idx * D + c);
+    z[0] = make_float4(0.f, 0.f, 0.f, 0.f);
+    z[1] = make_float4(0.f, 0.f, 0.f, 0.f);
     const int s = static_cast<int>(idx % S);
     const int h = static_cast<int>((idx / S) % H);
     const int b = static_cast<int>(idx / (static_cast<long long>(S) * H));
@@ -1030,7 +1035,7 @@ static int launch_bwd(const CUtensorMap& tq, const CUtensorMap& tk, const CUtens
 }  // namespace attn
 }  // namespace hyp
 
-// dq_acc: fp32 [B,H,Sq,D] zero-initialised by the caller (accumulated with reductions); delta: fp32 [B,H,Sq] scratch
+// dq_acc: fp32 [B,H,Sq,D], cleared here and then accumulated with reductions; delta: fp32 [B,H,Sq] scratch
 // written here; dk / dv are written in full.  All tensors are indexed [b,h,s,d] through element strides.
 HYP_API int hyp_flash_attn_bwd(const void* q, const void* k, const void* v, const void* o, const void* d_o, const float* lse,
                                float* dq_acc, void* dk, void* dv, float* delta, const unsigned char* key_padding_mask,
@@ -1045,9 +1050,9 @@ HYP_API int hyp_flash_attn_bwd(const void* q, const void* k, const void* v, cons
   const long long rows = static_cast<long long>(B) * H * Sq;
   const int dgrid = static_cast<int>((rows * (D / 8) + 255) / 256);
   if (dtype == DT_BF16)
-    attn::attn_delta_kernel<__nv_bfloat16><<<dgrid, 256, 0, st>>>((const __nv_bfloat16*)o, (const __nv_bfloat16*)d_o, delta, B, H, Sq, D, o_sb, o_sh, o_ss, g_sb, g_sh, g_ss);
+    attn::attn_delta_kernel<__nv_bfloat16><<<dgrid, 256, 0, st>>>((const __nv_bfloat16*)o, (const __nv_bfloat16*)d_o, delta, dq_acc, B, H, Sq, D, o_sb, o_sh, o_ss, g_sb, g_sh, g_ss);
   else
-    attn::attn_delta_kernel<__half><<<dgrid, 256, 0, st>>>((const __half*)o, (const __half*)d_o, delta, B, H, Sq, D, o_sb, o_sh, o_ss, g_sb, g_sh, g_ss);
+    attn::attn_delta_kernel<__half><<<dgrid, 256, 0, st>>>((const __half*)o, (const __half*)d_o, delta, dq_acc, B, H, Sq, D, o_sb, o_sh, o_ss, g_sb, g_sh, g_ss);
   HYP_CHECK_CUDA(cudaGetLastError());
   CUtensorMap tq, tk, tv, tdo;
   int rc;

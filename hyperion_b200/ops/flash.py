@@ -111,7 +111,7 @@ class _FlashPackedFn(torch.autograd.Function):
             do = do.permute(0, 2, 1, 3).contiguous().permute(0, 2, 1, 3)
         dqkv = torch.empty_like(qkv)
         dk, dv = dqkv[:, :, 1].permute(0, 2, 1, 3), dqkv[:, :, 2].permute(0, 2, 1, 3)
-        dq_acc = torch.zeros((B, H, S, D), device=qkv.device, dtype=torch.float32)
+        dq_acc = torch.empty((B, H, S, D), device=qkv.device, dtype=torch.float32)  # cleared by the kernel
         delta = torch.empty((B, H, S), device=qkv.device, dtype=torch.float32)
         call("hyp_flash_attn_bwd", ptr(q), ptr(k), ptr(v), ptr(o), ptr(do), ptr(lse), ptr(dq_acc), ptr(dk), ptr(dv),
              ptr(delta), ptr(kpm), B, H, S, S, D, *_strides_bhs(q), *_strides_bhs(k), *_strides_bhs(v), *_strides_bhs(o),

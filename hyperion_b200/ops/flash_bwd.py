@@ -13,7 +13,7 @@ def flash_bwd(q, k, v, o, lse, do, causal: bool, kpm, scale: float):
     Sk = k.shape[2]
     if not (do.stride(3) == 1 and _tma_ok(do)):
         do = do.permute(0, 2, 1, 3).contiguous().permute(0, 2, 1, 3)  # [B,S,H,D] memory, like o
-    dq_acc = torch.zeros((B, H, Sq, D), device=q.device, dtype=torch.float32)
+    dq_acc = torch.empty((B, H, Sq, D), device=q.device, dtype=torch.float32)  # cleared by the kernel
     dkv = torch.empty((2, B, Sk, H, D), device=q.device, dtype=q.dtype)
     dk, dv = dkv[0].permute(0, 2, 1, 3), dkv[1].permute(0, 2, 1, 3)
     delta = torch.empty((B, H, Sq), device=q.device, dtype=torch.float32)

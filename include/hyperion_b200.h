@@ -146,7 +146,7 @@ int hyp_rope(void* x, int B, int S, int H, int D, long long stride_b, long long 
  * softmax(Q K^T * scale + mask) V on tcgen05 with TMEM accumulators; head dim 64 or 128, fp16 / bf16.
  * q/k/v/o (and d_o, dk, dv) are indexed [b, h, s, d] through ELEMENT strides (unit stride in d; strides multiples of 8),
  * read in place by 4-D TMA descriptors.  key_padding_mask: uint8 [B, Sk], 1 = attend, or NULL.  lse: fp32 [B, H, Sq].
- * Backward: dq_acc is fp32 [B, H, Sq, D], ZEROED by the caller (accumulated with vector reductions); delta is fp32
+ * Backward: dq_acc is fp32 [B, H, Sq, D] scratch (cleared by the entry point, then accumulated with vector reductions); delta is fp32
  * [B, H, Sq] scratch; dk / dv are written in full.
  * Reference: nn.MultiheadAttention in nn.TransformerEncoderLayer (distributed_utils.py:79), HF Llama SDPA (:465). */
 int hyp_flash_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse, int B, int H, int Sq, int Sk, int D,
