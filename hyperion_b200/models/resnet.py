@@ -78,6 +78,9 @@ class ResNet(nn.Module):
         for m in self.modules():
             if isinstance(m, nn.Conv2d):
                 nn.init.kaiming_normal_(m.weight, mode="fan_out", nonlinearity="relu")
+                # weights live in [K, R, S, C] memory order (channels_last), what the NHWC convolution kernels read;
+                # values and state_dict keys/shapes are unchanged
+                m.weight.data = m.weight.data.contiguous(memory_format=torch.channels_last)
 
     def _make_layer(self, block, planes, blocks, stride=1):
         downsample = None

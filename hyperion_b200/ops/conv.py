@@ -139,16 +139,34 @@ def _bn_native_ok(y, bn, residual) -> bool:
             and (residual is None or (residual.shape == y.shape and residual.is_contiguous(memory_format=torch.channels_last))))
 
 
+def _folded_bn(conv: nn.Conv2d, bn: nn.BatchNorm2d):
+    """fp32 per-channel (scale, shift) of an eval-mode BatchNorm (and the conv bias) folded into the convolution;
+    cached on the BatchNorm module until one of its tensors is modified or replaced."""
+    ts = [t for t in (bn.weight, bn.bias, bn.running_mean, bn.running_var, conv.bias) if t is not None]
+    key = tuple((t.data_ptr(), t._version) for t in ts) + (bn.eps,)
+    cached = getattr(bn, "_hyp_folded", None)
+    if cached is not None and cached[0] == key:
+        return cached[1], cached[2]
+    with torch.no_grad():
+        scale = torch.rsqrt(bn.running_var.float() + bn.eps)
+        if bn.affine:
+            scale = scale * bn.weight.float()
+        shift = -bn.running_mean.float() * scale
+        if bn.affine:
+            shift = shift + bn.bias.float()
+        if conv.bias is not None:
+            shift = shift + conv.bias.float() * scale
+        scale, shift = scale.contiguous(), shift.contiguous()
+    bn._hyp_folded = (key, scale, shift)
+    return scale, shift
+
+
 def conv_bn_act(x, conv: nn.Conv2d, bn: nn.BatchNorm2d, relu: bool = True, residual=None):
     if (not bn.training and not torch.is_grad_enabled() and bn.track_running_stats and _igemm_ok(x, conv)
             and (residual is None or residual.is_contiguous(memory_format=torch.channels_last))):
         # inference: BatchNorm folded into the convolution epilogue (+ conv bias, residual, ReLU) -- one kernel per block
-        scale = bn.weight.float() * torch.rsqrt(bn.running_var.float() + bn.eps) if bn.affine else torch.rsqrt(bn.running_var.float() + bn.eps)
-        shift = (bn.bias.float() if bn.affine else 0.0) - bn.running_mean.float() * scale
-        if conv.bias is not None:
-            shift = shift + conv.bias.float() * scale
-        return conv2d_igemm(x, conv.weight, conv.stride[0], conv.padding[0], scale.contiguous(), shift.contiguous(),
-                            residual, relu)
+        scale, shift = _folded_bn(conv, bn)
+        return conv2d_igemm(x, conv.weight, conv.stride[0], conv.padding[0], scale, shift, residual, relu)
     y = _conv(x, conv)
     if _bn_native_ok(y, bn, residual):
         bn.num_batches_tracked.add_(1)

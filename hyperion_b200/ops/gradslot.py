@@ -31,8 +31,9 @@ class GradSlot:
         self.flat, self.spec, self.claimed = flat, spec, False
 
     def view(self) -> torch.Tensor:
-        s = self.spec
-        return self.flat.grad[s.offset:s.offset + s.numel].view(s.param.shape)
+        from ..parallel.flat import shaped_view
+
+        return shaped_view(self.flat.grad, self.spec)
 
 
 def slot_of(param) -> GradSlot | None:

@@ -29,6 +29,16 @@ class ParamSpec:
     param: nn.Parameter
     offset: int   # element offset into the flat buffers
     numel: int
+    channels_last: bool = False   # 4-D conv weight kept in [K, R, S, C] memory order (what the NHWC conv kernels read)
+
+
+def shaped_view(buf: torch.Tensor, s: "ParamSpec") -> torch.Tensor:
+    """The parameter-shaped view of ``s``'s range of a flat buffer, in the parameter's memory format."""
+    flat = buf[s.offset:s.offset + s.numel]
+    if s.channels_last:
+        K, C, R, S = s.param.shape
+        return flat.view(K, R, S, C).permute(0, 3, 1, 2)
+    return flat.view(s.param.shape)
 
 
 class FlatParams:
@@ -64,7 +74,8 @@ class FlatParams:
                     self.units[-1][1] = off
                 self.units.append([off, off, key])
                 prev_key = key
-            self.specs.append(ParamSpec(n, p, off, p.numel()))
+            cl = p.dim() == 4 and p.is_contiguous(memory_format=torch.channels_last) and not p.is_contiguous()
+            self.specs.append(ParamSpec(n, p, off, p.numel(), cl))
             off += (p.numel() + align - 1) // align * align
         pad_to = max(pad_to, unit_align)
         self.numel = (off + pad_to - 1) // pad_to * pad_to
@@ -80,7 +91,7 @@ class FlatParams:
         self.slots: list[GradSlot] = []
         with torch.no_grad():
             for s in self.specs:
-                view = self.data[s.offset:s.offset + s.numel].view(s.param.shape)
+                view = shaped_view(self.data, s)
                 view.copy_(s.param.data.to(self.dtype))
                 s.param.data = view
                 s.param.grad = None
@@ -125,13 +136,13 @@ class FlatParams:
                 data.copy_(self.data)
                 self.data = data
                 for s in self.specs:
-                    s.param.data = data[s.offset:s.offset + s.numel].view(s.param.shape)
+                    s.param.data = shaped_view(data, s)
             if grad is not None:
                 grad.copy_(self.grad)
                 self.grad = grad
                 for s in self.specs:
                     if s.param.grad is not None:
-                        s.param.grad = grad[s.offset:s.offset + s.numel].view(s.param.shape)
+                        s.param.grad = shaped_view(grad, s)
 
     def buckets(self, cap_bytes: int, first_cap_bytes: int | None = None) -> list[tuple[int, int, list[int]]]:
         """Contiguous (start, end, [spec indices]) element ranges of at most ``cap_bytes`` (whole parameters)."""

@@ -324,3 +324,26 @@ def test_flat_params_gradient_slots_cpu():
     flat.zero_grad()
     assert all(p.grad is None for p in m.parameters()) and float(flat.grad.abs().sum()) == 0.0
     assert all(not sl.claimed for sl in flat.slots)
+
+
+def test_flat_params_keep_channels_last_conv_weights():
+    """A channels_last conv weight stays [K, R, S, C]-ordered inside the flat buffers (parameter and gradient)."""
+    from hyperion_b200.parallel.flat import FlatParams
+
+    torch.manual_seed(1)
+    m = nn.Sequential(nn.Conv2d(4, 6, 3, padding=1, bias=False), nn.ReLU(), nn.Conv2d(6, 5, 1, bias=True))
+    m[0].weight.data = m[0].weight.data.contiguous(memory_format=torch.channels_last)
+    ref = copy.deepcopy(m)
+    flat = FlatParams(m.named_parameters())
+    w = m[0].weight
+    assert w.is_contiguous(memory_format=torch.channels_last) and not w.is_contiguous()
+    assert torch.equal(w, ref[0].weight)
+    spec = next(s for s in flat.specs if s.param is w)
+    assert spec.channels_last
+    assert torch.equal(flat.data[spec.offset:spec.offset + spec.numel], ref[0].weight.permute(0, 2, 3, 1).reshape(-1))
+    x = torch.randn(2, 4, 8, 8)
+    m(x).square().mean().backward()
+    ref(x).square().mean().backward()
+    assert torch.allclose(w.grad, ref[0].weight.grad, atol=1e-6)
+    assert w.grad.data_ptr() == flat.grad.data_ptr() + spec.offset * flat.grad.element_size()
+    assert torch.allclose(flat.grad[spec.offset:spec.offset + spec.numel], ref[0].weight.grad.permute(0, 2, 3, 1).reshape(-1), atol=1e-6)
