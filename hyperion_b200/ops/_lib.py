@@ -43,6 +43,7 @@ _SIGS = {
     "hyp_embedding_fwd": "ppplilip",
     "hyp_embedding_bwd": "ppplillip",
     "hyp_rope": "piiiilllpfiip",
+    "hyp_conv2d_wgrad": "ppp" + "iiiiiiiii" + "ip",
     "hyp_conv2d_fwd": "ppp" + "iiiiiiiii" + "ppp" + "ii" + "p",
 }
 

@@ -37,6 +37,18 @@ def _igemm_ok(x, conv: nn.Conv2d) -> bool:
             and os.environ.get("HYPERION_CONV", "igemm") == "igemm")
 
 
+def _igemm_dgrad_on() -> bool:
+    import os
+
+    return os.environ.get("HYPERION_CONV_DGRAD", "igemm") == "igemm"
+
+
+def _igemm_wgrad_on() -> bool:
+    import os
+
+    return os.environ.get("HYPERION_CONV_WGRAD", "igemm") == "igemm"
+
+
 def conv2d_igemm(x, weight, stride: int, pad: int, scale=None, shift=None, residual=None, relu: bool = False):
     """Raw call of ``hyp_conv2d_fwd`` on channels-last tensors (no autograd): returns y [N, K, Ho, Wo] channels-last."""
     N, C, H, W = x.shape
@@ -51,22 +63,64 @@ def conv2d_igemm(x, weight, stride: int, pad: int, scale=None, shift=None, resid
     return y
 
 
+def conv2d_wgrad_igemm(x, dy, weight_shape, stride: int, pad: int, out_flat=None):
+    """dW of ``conv2d(x, w)`` on the tcgen05 implicit GEMM: fp32 accumulation in [K, R, S, C] order, rounded to x's
+    dtype; returns the [K, C, R, S]-shaped channels_last view (backed by ``out_flat`` when given)."""
+    from . import native
+
+    N, C, H, W = x.shape
+    K, _, R, S = weight_shape
+    acc = torch.zeros(K * R * S * C, device=x.device, dtype=torch.float32)
+    _lib.call("hyp_conv2d_wgrad", _lib.ptr(x), _lib.ptr(dy), _lib.ptr(acc), N, H, W, C, K, R, S, stride, pad,
+              _lib.DT[x.dtype], _lib.stream_ptr())
+    flat = native.cast(acc, x.dtype, out=out_flat)
+    return flat.view(K, R, S, C).permute(0, 3, 1, 2)
+
+
 class _ConvFn(torch.autograd.Function):
-    """Convolution forward on conv_igemm_tcgen05; dgrad / wgrad through ATen's convolution_backward (cuDNN)."""
+    """Convolution on conv_igemm_tcgen05: forward, stride-1 dgrad (same kernel, flipped filter) and wgrad (pixel-reduction
+    GEMM with split reduction); stride-2 dgrad and weights that are not channels_last go through ATen (cuDNN)."""
 
     @staticmethod
     def forward(ctx, x, weight, stride, pad):
+        from . import gradslot
+
         ctx.save_for_backward(x, weight)
         ctx.stride, ctx.pad = stride, pad
+        ctx.slot = gradslot.slot_of(weight)
         return conv2d_igemm(x, weight, stride, pad)
 
     @staticmethod
     def backward(ctx, dy):
         x, weight = ctx.saved_tensors
         dy = dy.contiguous(memory_format=torch.channels_last)
-        dx, dw, _ = torch.ops.aten.convolution_backward(
-            dy, x, weight, None, [ctx.stride] * 2, [ctx.pad] * 2, [1, 1], False, [0, 0], 1,
-            [ctx.needs_input_grad[0], ctx.needs_input_grad[1], False])
+        K, C, R, S = weight.shape
+        need_x, need_w = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
+        dx = None
+        if need_x and ctx.stride == 1 and K % 64 == 0 and C % 32 == 0 and R - 1 - ctx.pad >= 0 and _igemm_dgrad_on():
+            # stride-1 dgrad is the same implicit GEMM over dy with the filter flipped and its channel roles swapped:
+            # dx = conv(dy, w'[c, r, s, k] = w[k, R-1-r, S-1-s, c], pad' = R-1-pad)
+            wt = weight.flip(2, 3).transpose(0, 1).contiguous(memory_format=torch.channels_last)
+            dx = conv2d_igemm(dy, wt, 1, R - 1 - ctx.pad)
+            need_x = False
+        dw = None
+        if (need_w and C % 64 == 0 and K % 64 == 0 and weight.is_contiguous(memory_format=torch.channels_last)
+                and _igemm_wgrad_on()):
+            from . import gradslot
+
+            dst = gradslot.claim(ctx.slot, weight.dtype)
+            if dst is not None and not dst.is_contiguous(memory_format=torch.channels_last):
+                dst = None
+            out_flat = dst.permute(0, 2, 3, 1).reshape(-1) if dst is not None else None   # the slot's [K,R,S,C] memory
+            dw = conv2d_wgrad_igemm(x, dy, weight.shape, ctx.stride, ctx.pad, out_flat)
+            if dst is not None:
+                dw = dst
+            need_w = False
+        if need_x or need_w:
+            gx, gw, _ = torch.ops.aten.convolution_backward(
+                dy, x, weight, None, [ctx.stride] * 2, [ctx.pad] * 2, [1, 1], False, [0, 0], 1, [need_x, need_w, False])
+            dx = dx if dx is not None else gx
+            dw = dw if dw is not None else gw
         return dx, dw, None, None
 
 

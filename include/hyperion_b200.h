@@ -213,6 +213,11 @@ int hyp_conv2d_fwd(const void* x, const void* w, void* y, int N, int H, int W, i
                    int pad, const float* scale, const float* shift, const void* residual, int relu, int dtype,
                    void* stream);
 
+/* Weight gradient of the same convolution: dw [K,R,S,C] fp32 (ZEROED by the caller) += sum over output pixels of
+ * dy[pix, k] * x[pix shifted by the tap, c]; x [N,H,W,C], dy [N,Ho,Wo,K] 16-bit NHWC; C % 64 == 0, K % 64 == 0. */
+int hyp_conv2d_wgrad(const void* x, const void* dy, float* dw, int N, int H, int W, int C, int K, int R, int S, int stride,
+                     int pad, int dtype, void* stream);
+
 /* ---- bn_act (csrc/bn_act.cu) ------------------------------------------------------
  * Training-mode BatchNorm2d + residual add + ReLU on NHWC-contiguous [rows = N*H*W, C] 16-bit tensors.
  * sums / dsums: fp32 [2*C] scratch ZEROED by the caller (batch statistics / dbeta,dgamma on return).

@@ -20,4 +20,9 @@ for (C, H, K, R, stride, pad) in [(64, 56, 64, 3, 1, 1), (128, 28, 128, 3, 1, 1)
     fl = 2.0 * B * Ho * Ho * K * C * R * R / 1e9
     t_h = timeit(lambda: convops.conv2d_igemm(x, w, stride, pad))
     t_c = timeit(lambda: F.conv2d(x, w, None, stride, pad))
-    print(f"B{B} C{C} {H}x{H} -> K{K} {R}x{R}/s{stride}: igemm {t_h * 1e3:7.1f} us {fl / t_h:6.0f} TF | cudnn {t_c * 1e3:7.1f} us {fl / t_c:6.0f} TF", flush=True)
+    dy = torch.randn(B, K, Ho, Ho, device="cuda", dtype=dt).contiguous(memory_format=torch.channels_last)
+    t_wh = timeit(lambda: convops.conv2d_wgrad_igemm(x, dy, w.shape, stride, pad))
+    t_wc = timeit(lambda: torch.ops.aten.convolution_backward(dy, x, w, None, [stride] * 2, [pad] * 2, [1, 1], False, [0, 0], 1, [False, True, False]))
+    t_dc = timeit(lambda: torch.ops.aten.convolution_backward(dy, x, w, None, [stride] * 2, [pad] * 2, [1, 1], False, [0, 0], 1, [True, False, False]))
+    print(f"B{B} C{C} {H}x{H} -> K{K} {R}x{R}/s{stride}: fwd igemm {t_h * 1e3:6.1f} us cudnn {t_c * 1e3:6.1f} us | "
+          f"wgrad igemm(+zero,+round) {t_wh * 1e3:6.1f} us cudnn {t_wc * 1e3:6.1f} us | dgrad cudnn {t_dc * 1e3:6.1f} us", flush=True)

@@ -339,6 +339,29 @@ def test_conv_igemm_forward_matches_fp32(N, C, H, W, K, R, stride, pad, dtype):
     assert _rel(y2, ref2) < 1e-2, _rel(y2, ref2)
 
 
+@pytest.mark.parametrize("C,K,R,stride,pad,H", [(64, 64, 3, 1, 1, 28), (128, 64, 3, 1, 1, 14), (64, 128, 1, 1, 0, 9),
+                                                (64, 64, 5, 1, 2, 12), (128, 256, 3, 2, 1, 28), (256, 512, 1, 2, 0, 14),
+                                                (64, 192, 3, 1, 1, 7), (512, 512, 3, 1, 1, 7)])
+def test_conv_backward_on_igemm(C, K, R, stride, pad, H):
+    """dx (stride 1: flipped-filter implicit GEMM; stride 2: ATen) and dw (pixel-reduction implicit GEMM) vs fp32 autograd."""
+    from hyperion_b200.ops import conv as convops
+
+    torch.manual_seed(23)
+    x = torch.randn(3, C, H, H + 3, device="cuda").to(torch.bfloat16).contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    w = (torch.randn(K, C, R, R, device="cuda") / (C * R * R) ** 0.5).to(torch.bfloat16).contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    y = convops._ConvFn.apply(x, w, stride, pad)
+    dy = torch.randn_like(y)
+    gx, gw = torch.autograd.grad(y, [x, w], dy)
+    xr, wr = x.detach().float().requires_grad_(True), w.detach().float().requires_grad_(True)
+    gxr, gwr = torch.autograd.grad(F.conv2d(xr, wr, None, stride, pad), [xr, wr], dy.float())
+    assert gw.shape == w.shape
+    assert _rel(gx, gxr) < 2e-2, _rel(gx, gxr)
+    assert _rel(gw, gwr) < 2e-2, _rel(gw, gwr)
+    # the raw wgrad entry point, twice (fp32 accumulator is allocated per call)
+    g2 = convops.conv2d_wgrad_igemm(x.detach(), dy, w.shape, stride, pad)
+    assert _rel(g2, gwr) < 2e-2
+
+
 def test_conv_bn_act_block_train_and_eval_use_igemm():
     """conv_bn_act: training forward+backward through the igemm forward (cuDNN backward), eval folds BN into the kernel."""
     import torch.nn as nn
