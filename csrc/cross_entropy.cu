@@ -84,6 +84,90 @@ ce_fwd_bwd_kernel(T* __restrict__ logits, long long ld, const long long* __restr
   }
 }
 
+// Same computation for 16-bit rows of up to 512 * 8 * RV elements with the whole row held in registers (RV 16-byte
+// vectors per thread): the logits are read ONCE, the gradient is produced from the registers.  A GPT-2 row (50257
+// bf16) is 13 vectors per thread.
+template <typename T, int RV>
+__global__ void __launch_bounds__(512)
+ce_fwd_bwd_reg_kernel(T* __restrict__ logits, long long ld, const long long* __restrict__ targets, int rows, int V,
+                      long long ignore_index, float* __restrict__ loss_sum_count, float* __restrict__ row_lse,
+                      const float* __restrict__ gscale_ptr, float gscale, int write_grad) {
+  __shared__ float red[32];
+  const int row = blockIdx.x;
+  T* lrow = logits + static_cast<long long>(row) * ld;
+  const long long tgt = targets[row];
+  const bool ignored = (tgt == ignore_index) || tgt < 0 || tgt >= V;
+  const int Vv = (V / 8) * 8;
+  uint4 raw[RV];
+#pragma unroll
+  for (int k = 0; k < RV; ++k) {
+    const int c = (k * 512 + threadIdx.x) * 8;
+    raw[k] = make_uint4(0u, 0u, 0u, 0u);
+    if (c < Vv) raw[k] = *reinterpret_cast<const uint4*>(lrow + c);
+  }
+  float mx = -INFINITY;
+#pragma unroll
+  for (int k = 0; k < RV; ++k) {
+    const int c = (k * 512 + threadIdx.x) * 8;
+    if (c < Vv) {
+      float f[8];
+      unpack8<T>(raw[k], f);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) mx = fmaxf(mx, f[i]);
+    }
+  }
+  float tail = 0.f;  // up to 7 trailing elements: one per thread of the first warp
+  const bool has_tail = threadIdx.x < V - Vv;
+  if (has_tail) { tail = to_f32<T>(lrow[Vv + threadIdx.x]); mx = fmaxf(mx, tail); }
+  const float bmx = block_max(mx, red);
+  const float nb = -bmx * 1.4426950408889634f;
+  float se = 0.f;
+#pragma unroll
+  for (int k = 0; k < RV; ++k) {
+    const int c = (k * 512 + threadIdx.x) * 8;
+    if (c < Vv) {
+      float f[8];
+      unpack8<T>(raw[k], f);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) se += ex2_fast(fmaf(f[i], 1.4426950408889634f, nb));
+    }
+  }
+  if (has_tail) se += ex2_fast(fmaf(tail, 1.4426950408889634f, nb));
+  se = block_sum(se, red);
+  const float lse = bmx + __logf(se);
+  if (threadIdx.x == 0) {
+    if (row_lse) row_lse[row] = lse;
+    if (!ignored) {
+      atomicAdd(loss_sum_count, lse - to_f32<T>(lrow[tgt]));
+      atomicAdd(loss_sum_count + 1, 1.f);
+    }
+  }
+  if (!write_grad) return;
+  __syncthreads();  // the target logit was read above; now overwrite the row
+  const float gs = ignored ? 0.f : (gscale_ptr ? *gscale_ptr * gscale : gscale);
+  const float nl = -lse * 1.4426950408889634f;
+#pragma unroll
+  for (int k = 0; k < RV; ++k) {
+    const int c = (k * 512 + threadIdx.x) * 8;
+    if (c < Vv) {
+      float f[8];
+      unpack8<T>(raw[k], f);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        float gr = ex2_fast(fmaf(f[i], 1.4426950408889634f, nl));
+        if (c + i == tgt) gr -= 1.f;
+        f[i] = gr * gs;
+      }
+      *reinterpret_cast<uint4*>(lrow + c) = pack8<T>(f);
+    }
+  }
+  if (has_tail) {
+    float gr = ex2_fast(fmaf(tail, 1.4426950408889634f, nl));
+    if (Vv + static_cast<int>(threadIdx.x) == tgt) gr -= 1.f;
+    lrow[Vv + threadIdx.x] = from_f32<T>(gr * gs);
+  }
+}
+
 // dlogits *= scale[0] ... used when the mean-reduction denominator (count of
 // non-ignored tokens) is only known after all chunks: out = 1 / max(count, 1)
 __global__ void ce_finalize_kernel(const float* __restrict__ sum_count, float* __restrict__ loss_out,
@@ -103,6 +187,19 @@ HYP_API int hyp_ce_fwd_bwd(void* logits, long long ld, const long long* targets,
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
   HYP_REQUIRE(rows > 0 && V > 0, "hyp_ce_fwd_bwd: empty input");
   const int threads = V >= 8192 ? 512 : 256;
+  // rows that fit in registers (16-bit, 16-byte aligned): single read of the logits
+  const bool aligned = dtype != DT_F32 && (ld * 2) % 16 == 0 && reinterpret_cast<uintptr_t>(logits) % 16 == 0;
+  if (aligned && V >= 8192 && V <= 512 * 8 * 16) {
+    const int rv = (V / 8 + 511) / 512;
+#define HYP_CE_REG(T, RV) ce_fwd_bwd_reg_kernel<T, RV><<<rows, 512, 0, st>>>((T*)logits, ld, targets, rows, V, ignore_index, loss_sum_count, row_lse, gscale_ptr, gscale, write_grad)
+#define HYP_CE_REG_T(T) \
+    if (rv <= 4) HYP_CE_REG(T, 4); else if (rv <= 8) HYP_CE_REG(T, 8); else if (rv <= 13) HYP_CE_REG(T, 13); else HYP_CE_REG(T, 16)
+    if (dtype == DT_BF16) { HYP_CE_REG_T(__nv_bfloat16); } else { HYP_CE_REG_T(__half); }
+#undef HYP_CE_REG_T
+#undef HYP_CE_REG
+    HYP_CHECK_CUDA(cudaGetLastError());
+    return 0;
+  }
   if (dtype == DT_F32)
     ce_fwd_bwd_kernel<float><<<rows, threads, 0, st>>>((float*)logits, ld, targets, rows, V, ignore_index, loss_sum_count, row_lse, gscale_ptr, gscale, write_grad);
   else if (dtype == DT_BF16)
