@@ -66,6 +66,7 @@ struct Params {
   // y = x W^T + t B^T runs as one GEMM instead of a second pass over y
   int k2_blocks;
   uint32_t idesc2;
+  int one_producer;   // HYPERION_GEMM_PRODUCERS=1: warp 0 issues both loads of a stage (A/B timing)
   alignas(64) CUtensorMap tmA2;
   alignas(64) CUtensorMap tmB2;
   uint32_t idesc;
@@ -720,6 +721,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
 // operand traffic from L2 drops from 48 KB to 32 KB per k-block and the ring deepens to 6 stages.  Each CTA keeps
 // its 128 accumulator rows in its own TMEM and runs its own epilogue.
 constexpr int G2_BN = 256;
+// warp 0: TMA producer for A, warp 1: MMA issuer, warps 2-9: epilogue, warp 10: TMA producer for B.  One thread
+// issuing both loads of a stage was the limiter of the main loop (each cp.async.bulk.tensor costs the issuing thread
+// a few hundred cycles: 2 per stage -> ~790 cycles per k-block against 540 of MMA time); two producers issue in parallel.
+constexpr int G2_THREADS = 352;
 // BN = 256: 16 KB A + 16 KB B-half per stage, 6 stages.  BN = 128 (small-M problems: twice the tiles to fill the pairs):
 // 16 KB + 8 KB, 8 stages.
 template <int BN>
@@ -730,7 +735,7 @@ struct G2Cfg {
 };
 
 template <int EPI, int ACT, int BN = G2_BN>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(G2_THREADS, 1)
 gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
              const __grid_constant__ Params p) {
   constexpr int G2_STAGES = G2Cfg<BN>::STAGES;
@@ -783,9 +788,11 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
   tc_fence_after();
   const uint32_t tmem_base = *tmem_holder;
 
-  if (warp == 0) {
-    // ------------------------------------------------------- TMA producer (one per CTA)
-    if (lane == 0) {
+  if (warp == 0 || warp == 10) {
+    // ------------------------------------------------------- TMA producers: warp 0 loads A, warp 10 loads B
+    if (lane == 0 && !(p.one_producer && warp == 10)) {
+      const bool load_a = (warp == 0);
+      const bool load_b = (warp == 10) || p.one_producer;
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = cluster_id; tile < total; tile += num_clusters) {
@@ -795,33 +802,40 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         for (int kb = tc.kb0; kb < tc.kb1; ++kb) {
           mbar_wait(&empty[stage], phase ^ 1);
           const uint32_t lead_bar = mapa_u32(smem_u32(&full[stage]), 0);
-          // the peer only contributes transaction bytes (no arrival: a remote release-arrive per k-block costs a
-          // cluster-scope fence in the single producer thread and halves the throughput)
-          if (leader) mbar_expect_tx(&full[stage], 2 * G2_STAGE_BYTES);
-          uint8_t* a_dst = sA + stage * A_STAGE;
-          uint8_t* b_dst = sB + stage * BH * ROW_BYTES;
-          if (!p.a_mn) {
-            tma_load_2d_2sm(a_dst, &tmA, lead_bar, kb * epr, m0);
-          } else if (p.a_mn3) {
-            tma_load_3d_2sm(a_dst, &tmA, lead_bar, 0, kb * epr, m0 >> 6);
-          } else {
-            for (int j = 0; j < BM / epr; ++j) tma_load_2d_2sm(a_dst + j * epr * ROW_BYTES, &tmA, lead_bar, m0 + j * epr, kb * epr);
+          if (load_a) {
+            // the peer only contributes transaction bytes (no arrival: a remote release-arrive per k-block costs a
+            // cluster-scope fence in the single producer thread and halves the throughput); the A producer of the
+            // leader announces the bytes of all four loads of the stage
+            if (leader) mbar_expect_tx(&full[stage], 2 * G2_STAGE_BYTES);
+            uint8_t* a_dst = sA + stage * A_STAGE;
+            if (!p.a_mn) {
+              tma_load_2d_2sm(a_dst, &tmA, lead_bar, kb * epr, m0);
+            } else if (p.a_mn3) {
+              tma_load_3d_2sm(a_dst, &tmA, lead_bar, 0, kb * epr, m0 >> 6);
+            } else {
+              for (int j = 0; j < BM / epr; ++j) tma_load_2d_2sm(a_dst + j * epr * ROW_BYTES, &tmA, lead_bar, m0 + j * epr, kb * epr);
+            }
           }
-          if (!p.b_mn) {
-            tma_load_2d_2sm(b_dst, &tmB, lead_bar, kb * epr, n0);
-          } else if (p.b_mn3) {
-            tma_load_3d_2sm(b_dst, &tmB, lead_bar, 0, kb * epr, n0 >> 6);
-          } else {
-            for (int j = 0; j < BH / epr; ++j) tma_load_2d_2sm(b_dst + j * epr * ROW_BYTES, &tmB, lead_bar, n0 + j * epr, kb * epr);
+          if (load_b) {
+            uint8_t* b_dst = sB + stage * BH * ROW_BYTES;
+            if (!p.b_mn) {
+              tma_load_2d_2sm(b_dst, &tmB, lead_bar, kb * epr, n0);
+            } else if (p.b_mn3) {
+              tma_load_3d_2sm(b_dst, &tmB, lead_bar, 0, kb * epr, n0 >> 6);
+            } else {
+              for (int j = 0; j < BH / epr; ++j) tma_load_2d_2sm(b_dst + j * epr * ROW_BYTES, &tmB, lead_bar, n0 + j * epr, kb * epr);
+            }
           }
           if (++stage == G2_STAGES) { stage = 0; phase ^= 1; }
         }
         for (int kb2 = 0; kb2 < p.k2_blocks; ++kb2) {   // dual-K tail: second operand pair, K-major
           mbar_wait(&empty[stage], phase ^ 1);
           const uint32_t lead_bar = mapa_u32(smem_u32(&full[stage]), 0);
-          if (leader) mbar_expect_tx(&full[stage], 2 * G2_STAGE_BYTES);
-          tma_load_2d_2sm(sA + stage * A_STAGE, &p.tmA2, lead_bar, kb2 * epr, m0);
-          tma_load_2d_2sm(sB + stage * BH * ROW_BYTES, &p.tmB2, lead_bar, kb2 * epr, n0);
+          if (load_a) {
+            if (leader) mbar_expect_tx(&full[stage], 2 * G2_STAGE_BYTES);
+            tma_load_2d_2sm(sA + stage * A_STAGE, &p.tmA2, lead_bar, kb2 * epr, m0);
+          }
+          if (load_b) tma_load_2d_2sm(sB + stage * BH * ROW_BYTES, &p.tmB2, lead_bar, kb2 * epr, n0);
           if (++stage == G2_STAGES) { stage = 0; phase ^= 1; }
         }
       }
@@ -1034,7 +1048,7 @@ static int launch2(const CUtensorMap& ta, const CUtensorMap& tb, const Params& p
   const int tiles = ((p.M + 2 * BM - 1) / (2 * BM)) * ((p.N + BN - 1) / BN) * p.splits;
   int clusters = num_sms() / 2;
   if (tiles < clusters) clusters = tiles;
-  gemm2_kernel<EPI, ACT, BN><<<2 * clusters, NUM_THREADS, G2Cfg<BN>::SMEM, stream>>>(ta, tb, p);
+  gemm2_kernel<EPI, ACT, BN><<<2 * clusters, G2_THREADS, G2Cfg<BN>::SMEM, stream>>>(ta, tb, p);
   HYP_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -1203,6 +1217,8 @@ static int gemm_impl(const void* A, const void* B, void* D, int M, int N, int K,
   }
   p.k2_blocks = 0;
   p.idesc2 = 0;
+  static const int one_prod = [] { const char* e = getenv("HYPERION_GEMM_PRODUCERS"); return (e && atoi(e) == 1) ? 1 : 0; }();
+  p.one_producer = one_prod;
   if (dual) {
     HYP_REQUIRE(pair_ok && p.splits == 1 && dual->K2 > 0 && dual->K2 % 64 == 0,
                 "hyp_gemm_dualk: needs 16-bit operands, M >= 256, N > 128, no split-K and K2 %% 64 == 0 (M=%d N=%d K2=%d)", M, N, dual->K2);
