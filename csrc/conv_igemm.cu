@@ -30,7 +30,7 @@ constexpr int BM = 128;
 constexpr int ROW_BYTES = 128;
 constexpr int A_STAGE = BM * ROW_BYTES;
 constexpr int STAGES = 6;
-constexpr int THREADS = 192;
+constexpr int THREADS = 224;   // warp 0: TMA producer (activations), warp 1: MMA, warps 2-5: epilogue, warp 6: TMA producer (second operand)
 
 struct Params {
   int N, H, W, C;        // input NHWC
@@ -103,9 +103,11 @@ conv_fwd_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
   tc_fence_after();
   const uint32_t tmem_base = *tmem_holder;
 
-  if (warp == 0) {
-    // ------------------------------------------------------------------ TMA producer
+  if (warp == 0 || warp == 6) {
+    // ------------------------------------------------------------------ TMA producers: warp 0 the input boxes (and the
+    // expect_tx of the stage), warp 6 the weight tiles -- a single issuing thread is the bottleneck of such short k-blocks
     if (lane == 0) {
+      const bool load_a = (warp == 0);
       int stage = 0;
       uint32_t phase = 0;
       for (int t = blockIdx.x; t < total; t += gridDim.x) {
@@ -116,10 +118,13 @@ conv_fwd_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__
           for (int s = 0; s < p.S; ++s) {
             for (int cb = 0; cb < cblocks; ++cb) {
               mbar_wait(&empty[stage], phase ^ 1);
-              mbar_expect_tx(&full[stage], A_STAGE + C::B_STAGE);
-              // the input box of this tap: out-of-image coordinates (padding, ragged patches) are zero-filled
-              tma_load_4d(sA + stage * A_STAGE, &tmX, &full[stage], cb * 64, w_in0 + s, h_in0 + r, tc.pn * p.NB);
-              tma_load_2d(sB + stage * C::B_STAGE, &tmW, &full[stage], (r * p.S + s) * p.C + cb * 64, tc.kb * BN);
+              if (load_a) {
+                mbar_expect_tx(&full[stage], A_STAGE + C::B_STAGE);
+                // the input box of this tap: out-of-image coordinates (padding, ragged patches) are zero-filled
+                tma_load_4d(sA + stage * A_STAGE, &tmX, &full[stage], cb * 64, w_in0 + s, h_in0 + r, tc.pn * p.NB);
+              } else {
+                tma_load_2d(sB + stage * C::B_STAGE, &tmW, &full[stage], (r * p.S + s) * p.C + cb * 64, tc.kb * BN);
+              }
               if (++stage == STAGES) { stage = 0; phase ^= 1; }
             }
           }
@@ -387,9 +392,10 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constan
   tc_fence_after();
   const uint32_t tmem_base = *tmem_holder;
 
-  if (warp == 0) {
-    // ------------------------------------------------------------------ TMA producer
+  if (warp == 0 || warp == 6) {
+    // ------------------------------------------------------------------ TMA producers: warp 0 dy, warp 6 x
     if (lane == 0) {
+      const bool load_a = (warp == 0);
       int stage = 0;
       uint32_t phase = 0;
       for (int t = blockIdx.x; t < total; t += gridDim.x) {
@@ -398,10 +404,13 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constan
         for (int pb = w.pb0; pb < w.pb1; ++pb) {
           const int pw = pb % p.tiles_w, ph = (pb / p.tiles_w) % p.tiles_h, pn = pb / (p.tiles_w * p.tiles_h);
           mbar_wait(&empty[stage], phase ^ 1);
-          mbar_expect_tx(&full[stage], C::A_BYTES + C::B_BYTES);
-          tma_load_5d(sA + stage * C::A_BYTES, &tmDY, &full[stage], 0, pw * p.TW, ph * p.TH, pn * p.NB, w.kb * 2);
-          tma_load_5d(sB + stage * C::B_BYTES, &tmX, &full[stage], 0, pw * p.TW * p.stride + s - p.pad,
-                      ph * p.TH * p.stride + r - p.pad, pn * p.NB, w.cb * (BN / 64));
+          if (load_a) {
+            mbar_expect_tx(&full[stage], C::A_BYTES + C::B_BYTES);
+            tma_load_5d(sA + stage * C::A_BYTES, &tmDY, &full[stage], 0, pw * p.TW, ph * p.TH, pn * p.NB, w.kb * 2);
+          } else {
+            tma_load_5d(sB + stage * C::B_BYTES, &tmX, &full[stage], 0, pw * p.TW * p.stride + s - p.pad,
+                        ph * p.TH * p.stride + r - p.pad, pn * p.NB, w.cb * (BN / 64));
+          }
           if (++stage == WSTAGES) { stage = 0; phase ^= 1; }
         }
       }
