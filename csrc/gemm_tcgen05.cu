@@ -67,7 +67,6 @@ struct Params {
   int k2_blocks;
   uint32_t idesc2;
   int one_producer;   // HYPERION_GEMM_PRODUCERS=1: warp 0 issues both loads of a stage (A/B timing)
-  int cl4;            // clusters of two CTA pairs stacked along M that share every B tile through TMA multicast
   alignas(64) CUtensorMap tmA2;
   alignas(64) CUtensorMap tmB2;
   uint32_t idesc;
@@ -756,22 +755,19 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  // cluster = 1 or 2 CTA pairs (launch attribute); pair p of the cluster takes M tile (2 * super_tile + p) of the same
-  // column block, so with two pairs every B tile is fetched from L2 once and multicast to both
+  // cluster = one CTA pair
   const uint32_t rank = cluster_ctarank();
-  const uint32_t cta = rank & 1u, pair = rank >> 1;
-  const int csize = p.cl4 ? 4 : 2, npairs = csize >> 1;
+  const uint32_t cta = rank & 1u;
+  constexpr int csize = 2;
   const bool leader = cta == 0;
   const int epr = ROW_BYTES / p.esize;
   const int nkb = (p.K + epr - 1) / epr;
-  // M tiles are handed out in groups of npairs ("super tiles"); a missing last tile just computes on zero-filled rows
-  const int tiles_m = ((p.M + BM2 - 1) / BM2 + npairs - 1) / npairs;
+  const int tiles_m = (p.M + BM2 - 1) / BM2;
   const int tiles_n = (p.N + BN - 1) / BN;
   const int total = tiles_m * tiles_n * p.splits;
   const int cluster_id = blockIdx.x / csize, num_clusters = gridDim.x / csize;
-  const uint32_t lead_rank = rank & ~1u;                                   // my pair's leader
-  const uint16_t all_mask = static_cast<uint16_t>((1u << csize) - 1u);     // every CTA of the cluster
-  const uint16_t pair_mask = static_cast<uint16_t>(3u << (pair * 2));      // the two CTAs of my pair
+  const uint32_t lead_rank = 0;                                            // the pair's leader
+  const uint16_t all_mask = 3, pair_mask = 3;                              // both CTAs of the pair
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
@@ -781,8 +777,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     if (lane == 0) {
       for (int i = 0; i < G2_STAGES; ++i) {
         mbar_init(&full[i], 1);    // the leader's arrive.expect_tx covers the bytes of every TMA load into the pair
-        mbar_init(&empty[i], npairs);   // multicast commit from each pair leader's MMA thread (a multicast B slice is
-                                        // written into both pairs' shared memory, so both must have consumed the stage)
+        mbar_init(&empty[i], 1);   // commit from the leader's MMA thread
       }
       for (int i = 0; i < 2; ++i) {
         mbar_init(&tfull[i], 1);
@@ -803,14 +798,11 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     if (lane == 0 && !(p.one_producer && warp == 10)) {
       const bool load_a = (warp == 0);
       const bool load_b = (warp == 10) || p.one_producer;
-      // with two pairs: this CTA fetches one 64-row slice of its B half and multicasts it to the CTA of the other pair
-      // that stages the same half (rank ^ 2); the other slice arrives from there
-      const uint16_t b_mask = static_cast<uint16_t>((1u << rank) | (1u << (rank ^ 2u)));
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = cluster_id; tile < total; tile += num_clusters) {
         const TileCoord tc = decode_tile(tile, tiles_m, tiles_n, nkb, p.splits);
-        const int m0 = (tc.m_blk * npairs + static_cast<int>(pair)) * BM2 + cta * BM;
+        const int m0 = tc.m_blk * BM2 + cta * BM;
         const int n0 = tc.n_blk * BN + cta * BH;
         for (int kb = tc.kb0; kb < tc.kb1; ++kb) {
           mbar_wait(&empty[stage], phase ^ 1);
@@ -831,12 +823,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
           }
           if (load_b) {
             uint8_t* b_dst = sB + stage * BH * ROW_BYTES;
-            if (p.cl4) {
-              const uint32_t own_bar = smem_u32(&full[stage]) & 0xFEFFFFFFu;   // pair-peer bit cleared: the pair leader's copy
-              const int sl = static_cast<int>(pair);                           // my slice: rows [64 sl, 64 sl + 64) of the half
-              if (!p.b_mn) tma_load_2d_2sm_mc(b_dst + sl * 64 * ROW_BYTES, &tmB, own_bar, kb * epr, n0 + sl * 64, b_mask);
-              else tma_load_3d_2sm_mc(b_dst + sl * epr * ROW_BYTES, &tmB, own_bar, 0, kb * epr, (n0 >> 6) + sl, b_mask);
-            } else if (!p.b_mn) {
+            if (!p.b_mn) {
               tma_load_2d_2sm(b_dst, &tmB, lead_bar, kb * epr, n0);
             } else if (p.b_mn3) {
               tma_load_3d_2sm(b_dst, &tmB, lead_bar, 0, kb * epr, n0 >> 6);
@@ -846,7 +833,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
           }
           if (++stage == G2_STAGES) { stage = 0; phase ^= 1; }
         }
-        for (int kb2 = 0; kb2 < p.k2_blocks; ++kb2) {   // dual-K tail: second operand pair, K-major (never with cl4)
+        for (int kb2 = 0; kb2 < p.k2_blocks; ++kb2) {   // dual-K tail: second operand pair, K-major
           mbar_wait(&empty[stage], phase ^ 1);
           const uint32_t lead_bar = mapa_u32(smem_u32(&full[stage]), lead_rank);
           if (load_a) {
@@ -914,7 +901,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     uint32_t acc_phase = 0;
     for (int tile = cluster_id; tile < total; tile += num_clusters) {
       const TileCoord tc = decode_tile(tile, tiles_m, tiles_n, nkb, p.splits);
-      const int row = (tc.m_blk * npairs + static_cast<int>(pair)) * BM2 + cta * BM + quarter * 32 + lane;
+      const int row = tc.m_blk * BM2 + cta * BM + quarter * 32 + lane;
       const bool has_k = tc.kb1 > tc.kb0;
       constexpr bool kStageable = (EPI == 0 || EPI == 1 || EPI == 2 || EPI == 5);
       constexpr int NCH = BN / 64;   // 32-column chunks per warp
@@ -1057,28 +1044,17 @@ static int dispatch_ag(const CUtensorMap& ta, const CUtensorMap& tb, const Param
 template <int EPI, int ACT, int BN = G2_BN>
 static int launch2(const CUtensorMap& ta, const CUtensorMap& tb, const Params& p, cudaStream_t stream) {
   static bool attr_set[64] = {false};
-  static int max_cl4[64] = {0};   // co-resident 4-CTA clusters (GPC boundaries leave some SMs without a full cluster)
   int dev = 0;
   cudaGetDevice(&dev);
   auto kernel = gemm2_kernel<EPI, ACT, BN>;
   if (!attr_set[dev & 63]) {
     HYP_CHECK_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G2Cfg<BN>::SMEM));
-    cudaLaunchConfig_t q = {};
-    q.gridDim = dim3(4 * (num_sms() / 4)); q.blockDim = dim3(G2_THREADS); q.dynamicSmemBytes = G2Cfg<BN>::SMEM;
-    cudaLaunchAttribute qa[1];
-    qa[0].id = cudaLaunchAttributeClusterDimension;
-    qa[0].val.clusterDim.x = 4; qa[0].val.clusterDim.y = 1; qa[0].val.clusterDim.z = 1;
-    q.attrs = qa; q.numAttrs = 1;
-    int n = 0;
-    if (cudaOccupancyMaxActiveClusters(&n, kernel, &q) != cudaSuccess) { n = 0; cudaGetLastError(); }
-    max_cl4[dev & 63] = n;
     attr_set[dev & 63] = true;
   }
-  const int csize = p.cl4 ? 4 : 2, npairs = csize / 2;
-  const int tiles_m = ((p.M + 2 * BM - 1) / (2 * BM) + npairs - 1) / npairs;
+  const int csize = 2;
+  const int tiles_m = (p.M + 2 * BM - 1) / (2 * BM);
   const int tiles = tiles_m * ((p.N + BN - 1) / BN) * p.splits;
-  int clusters = p.cl4 ? max_cl4[dev & 63] : num_sms() / 2;
-  HYP_REQUIRE(clusters > 0, "gemm2: no co-resident cluster of %d CTAs on this device", csize);
+  int clusters = num_sms() / 2;
   if (tiles < clusters) clusters = tiles;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(csize * clusters);
@@ -1092,29 +1068,6 @@ static int launch2(const CUtensorMap& ta, const CUtensorMap& tb, const Params& p
   cfg.numAttrs = 1;
   HYP_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kernel, ta, tb, p));
   return 0;
-}
-
-// co-resident clusters of four CTAs for the pair kernel (0 when unknown): drives the cl4 decision
-static int gemm2_max_cl4() {
-  static int cached[64];
-  static bool have[64] = {false};
-  int dev = 0;
-  cudaGetDevice(&dev);
-  if (!have[dev & 63]) {
-    auto kernel = gemm2_kernel<0, 0, G2_BN>;
-    cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G2Cfg<G2_BN>::SMEM);
-    cudaLaunchConfig_t q = {};
-    q.gridDim = dim3(4 * (num_sms() / 4)); q.blockDim = dim3(G2_THREADS); q.dynamicSmemBytes = G2Cfg<G2_BN>::SMEM;
-    cudaLaunchAttribute qa[1];
-    qa[0].id = cudaLaunchAttributeClusterDimension;
-    qa[0].val.clusterDim.x = 4; qa[0].val.clusterDim.y = 1; qa[0].val.clusterDim.z = 1;
-    q.attrs = qa; q.numAttrs = 1;
-    int n = 0;
-    if (cudaOccupancyMaxActiveClusters(&n, kernel, &q) != cudaSuccess) { n = 0; cudaGetLastError(); }
-    cached[dev & 63] = n;
-    have[dev & 63] = true;
-  }
-  return cached[dev & 63];
 }
 
 // the 256 x 128 pair tile is instantiated for the epilogues small-M problems use (plain, bias/residual, beta)
@@ -1308,23 +1261,8 @@ static int gemm_impl(const void* A, const void* B, void* D, int M, int N, int K,
     else if (p.a_mn3)  rc = gemm::make_tmap_mn3(&ta, A, in_dtype, M, K, lda, gemm::BM / 64);
     else               rc = gemm::make_tmap_2d(&ta, A, in_dtype, M, K, lda, epr, epr);
     if (rc) return rc;
-    // clusters of two pairs sharing B through multicast (HYPERION_GEMM_CL4: 0 off, 1 on whenever possible, 2 = by the
-    // wave model): each CTA then fetches 64-row slices of its B half
-    static int cl4_mode = -1;
-    if (cl4_mode < 0) { const char* e = getenv("HYPERION_GEMM_CL4"); cl4_mode = e ? atoi(e) : 0; }
-    p.cl4 = 0;
-    if (cl4_mode > 0 && !pair128 && BN == 256 && !dual && (!b_mn_major || p.b_mn3) && M > 256) {
-      const int ncl = gemm::gemm2_max_cl4();
-      if (ncl > 0) {
-        const long long tm2 = (M + 255) / 256, tn = (N + 255) / 256;
-        const long long w_pair = (tm2 * tn * p.splits + num_sms() / 2 - 1) / (num_sms() / 2);
-        const long long w_cl4 = (((tm2 + 1) / 2) * tn * p.splits + ncl - 1) / ncl;
-        // a cl4 wave does two tiles per cluster; model its tile time as 0.8 of a pair tile (less L2 traffic)
-        if (cl4_mode == 1 || 0.8 * static_cast<double>(w_cl4) < static_cast<double>(w_pair)) p.cl4 = 1;
-      }
-    }
-    if (!b_mn_major)   rc = gemm::make_tmap_2d(&tb, B, in_dtype, K, N, ldb, epr, p.cl4 ? BN / 4 : BN / 2);
-    else if (p.b_mn3)  rc = gemm::make_tmap_mn3(&tb, B, in_dtype, N, K, ldb, p.cl4 ? 1 : BN / 128);
+    if (!b_mn_major)   rc = gemm::make_tmap_2d(&tb, B, in_dtype, K, N, ldb, epr, BN / 2);
+    else if (p.b_mn3)  rc = gemm::make_tmap_mn3(&tb, B, in_dtype, N, K, ldb, BN / 128);
     else               rc = gemm::make_tmap_2d(&tb, B, in_dtype, N, K, ldb, epr, epr);
     if (rc) return rc;
     if (dual) {
