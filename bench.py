@@ -10,11 +10,11 @@ synthetic tokens, sequence length 1024, weak scaling (fixed per-GPU batch); metr
 with CUDA events, max over ranks.  ``--config resnet50_ddp | vit_ddp | lm_ddp | llama_lora`` select the other
 BASELINE configs.  Prints ONE JSON line on rank 0.
 
-``--impl reference`` must run the unmodified reference from ``baseline/_ref``; the reference is a set of notebooks
-and scripts without ``setup.py`` / ``pyproject.toml`` and pip refuses to install it, so that arm prints
-``{"impl": "reference", "unavailable": ...}``.  ``--impl torch`` runs the stock-PyTorch restatement
-(torch FSDP/DDP + NCCL + cuBLAS, ``baseline/torch_baseline.py``) for the same config -- the operative baseline of
-BASELINE.md section 3.
+``--impl reference`` drives the UNMODIFIED reference trainers installed in ``baseline/_ref``
+(``baseline/install_reference.sh``, ``baseline/reference_arm.py``) for the jobs the reference contains and this image
+can import: ``--config lm_ddp | lm_fsdp | cifar_ddp``.  Its GPT-2 / Llama path needs ``accelerate`` and ``peft`` (absent),
+so for ``gpt2_fsdp`` / ``llama_*`` / ``resnet50_ddp`` / ``vit_ddp`` that arm prints ``{"impl": "reference", "unavailable": ...}``
+and ``--impl torch`` (stock torch FSDP/DDP + NCCL + cuBLAS, ``baseline/torch_baseline.py``) is the operative baseline.
 """
 from __future__ import annotations
 
@@ -34,7 +34,7 @@ def parse():
     ap.add_argument("--steps", type=int, default=8)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", choices=["hyperion", "reference", "torch"], default="hyperion")
-    ap.add_argument("--config", default="gpt2_fsdp", choices=["gpt2_fsdp", "resnet50_ddp", "vit_ddp", "lm_ddp", "llama_lora"])
+    ap.add_argument("--config", default="gpt2_fsdp", choices=["gpt2_fsdp", "resnet50_ddp", "vit_ddp", "lm_ddp", "lm_fsdp", "cifar_ddp", "llama_lora", "llama_fsdp"])
     ap.add_argument("--batch", type=int, default=None, help="per-GPU batch")
     ap.add_argument("--seq", type=int, default=None)
     ap.add_argument("--size", default=None, help="model size override (gpt2: medium/small/tiny; llama: 7b/tiny)")
@@ -47,10 +47,9 @@ def parse():
 def main() -> int:
     args = parse()
     if args.impl == "reference":
-        print(json.dumps({"impl": "reference", "unavailable":
-                          "pip cannot install /root/reference (no setup.py/pyproject.toml; notebooks + scripts that "
-                          "import matplotlib/peft and download from the network); see DESIGN.md"}))
-        return 0
+        from baseline.reference_arm import run as run_reference
+
+        return run_reference(args)
     if args.impl == "torch":
         from baseline.torch_baseline import run as run_torch
 

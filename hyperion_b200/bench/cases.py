@@ -125,6 +125,57 @@ class LMDDP(Case):
         return self.eng.model.loss(ids[:, :-1].contiguous(), ids[:, 1:].contiguous(), ignore_index=synth.GPT2_PAD)
 
 
+class LMFSDP(LMDDP):
+    """The reference's own FSDP job: SimpleTransformerLM, FULL_SHARD, size-based wrap (100 k), bf16, AdamW 1e-4, clip 1.0,
+    bs 32/GPU (distributed_utils.py:290-352)."""
+    dtype = "bf16"
+
+    def __init__(self, dev, rank, world, batch=None, seq=None, size=None, fused_comm=None):
+        Case.__init__(self, dev, rank, world)
+        from ..models import SimpleTransformerLM
+
+        self.bs, self.seq = batch or 32, seq or 128
+        model = SimpleTransformerLM(synth.GPT2_VOCAB)
+        self.eng = build_engine(model, strategy="fsdp", precision="bf16", lr=1e-4, clip=1.0, device=dev, fused_comm=fused_comm,
+                                fsdp_min_num_params=100_000)
+        self.items_per_step = self.bs * (self.seq - 1)
+        for k in range(4):
+            ids, _ = synth.wikitext2_like_arrays(self.bs, self.seq, seed=1000 * rank + k)
+            self.batches.append((torch.from_numpy(ids).to(dev),))
+        self.metric = "SimpleTransformerLM FSDP tokens/s"
+        self.config = {"model": "SimpleTransformerLM(50257,256,4,2)", "global_batch": self.bs * world, "seq_len": self.seq - 1,
+                       "parallelism": f"fsdp{world}", "l2": "bf16 weights 57 MB + logits chunks exceed L2"}
+
+
+class CifarDDP(Case):
+    """The reference's own vision job: ResNet-18 (10 classes) on CIFAR-shaped 32x32 images, DDP, fp16 AMP, AdamW 1e-3,
+    bs 64/GPU (distributed_utils.py:207-279)."""
+    unit = "samples/s"
+    dtype = "fp16"
+
+    def __init__(self, dev, rank, world, batch=None, fused_comm=None):
+        super().__init__(dev, rank, world)
+        from .. import ops
+        from ..models import resnet18
+
+        self.ops = ops
+        self.bs = batch or 64
+        model = resnet18(num_classes=10)
+        self.eng = build_engine(model, strategy="ddp", precision="fp16", lr=1e-3, device=dev, fused_comm=fused_comm)
+        self.items_per_step = self.bs
+        for k in range(4):
+            x, y = synth.image_batch(self.bs, 32, 10, dev, seed=1000 * rank + k, dtype=torch.float32)
+            self.batches.append((x, y))
+        self.metric = "ResNet-18 CIFAR DDP samples/s"
+        self.config = {"model": "resnet18(num_classes=10)", "global_batch": self.bs * world, "image": 32,
+                       "parallelism": f"dp{world}", "input": "fp32 images, cast to fp16 on the device inside the step",
+                       "l2": "small working set; 256 MB L2 flush not applied (launch-bound job)"}
+
+    def loss_fn(self, batch):
+        x, y = batch
+        return self.ops.cross_entropy(self.eng.model(x.to(torch.float16)), y)
+
+
 class VisionDDP(Case):
     """BASELINE configs 2 / 3: ResNet-50 DDP bf16, ViT-B/16 DDP bf16 with activation checkpointing (224x224)."""
     unit = "samples/s"
@@ -143,21 +194,22 @@ class VisionDDP(Case):
         self.eng = build_engine(model, strategy="ddp", precision="bf16", lr=1e-3, device=dev, fused_comm=fused_comm)
         self.items_per_step = self.bs
         for k in range(2):
-            x, y = synth.image_batch(self.bs, 224, 1000, dev, seed=1000 * rank + k, dtype=torch.bfloat16)
+            x, y = synth.image_batch(self.bs, 224, 1000, dev, seed=1000 * rank + k, dtype=torch.float32)
             self.batches.append((x, y))
         self.metric = f"{'ResNet-50' if arch == 'resnet50' else 'ViT-B/16'} DDP samples/s"
         self.config = {"model": arch, "global_batch": self.bs * world, "image": 224, "parallelism": f"dp{world}",
-                       "checkpointing": arch == "vit", "l2": "activations per step exceed the 126 MB L2"}
+                       "checkpointing": arch == "vit", "input": "fp32 images (as the torch arm), cast to bf16 on the device inside the step",
+                       "l2": "activations per step exceed the 126 MB L2"}
 
     def loss_fn(self, batch):
         x, y = batch
-        return self.ops.cross_entropy(self.eng.model(x), y)
+        return self.ops.cross_entropy(self.eng.model(x.to(torch.bfloat16)), y)
 
 
 class LlamaLoRA(Case):
     """BASELINE config 5: Llama-2-7B LoRA (r=16, q/k/v/o) under FSDP, bf16, seq 128."""
 
-    def __init__(self, dev, rank, world, batch=None, seq=None, size=None, fused_comm=None):
+    def __init__(self, dev, rank, world, batch=None, seq=None, size=None, fused_comm=None, lora=True):
         super().__init__(dev, rank, world)
         from ..lora import inject_lora
         from ..models import LlamaConfig, LlamaForCausalLM
@@ -173,7 +225,8 @@ class LlamaLoRA(Case):
                 model = LlamaForCausalLM(cfg)
         finally:
             torch.set_default_dtype(prev)
-        inject_lora(model, r=16, alpha=32, dropout=0.05)
+        if lora:
+            inject_lora(model, r=16, alpha=32, dropout=0.05)
         units = [m for m in model.modules() if isinstance(m, LlamaDecoderLayer)]
         self.eng = build_engine(model, strategy="fsdp", precision="bf16", lr=1e-5, weight_decay=0.01, clip=1.0, device=dev,
                                 fused_comm=fused_comm, fsdp_units=units)
@@ -182,8 +235,8 @@ class LlamaLoRA(Case):
             ids, mask = synth.token_batch(self.bs, self.seq, cfg.vocab_size, dev, seed=1000 * rank + k, pad_id=cfg.pad_token_id,
                                           pad_fraction=0.3)
             self.batches.append((ids, mask))
-        self.metric = f"Llama-2 {size} LoRA FSDP tokens/s"
-        self.config = {"model": f"llama2-{size}", "lora": "r16 a32 qkvo", "global_batch": self.bs * world, "seq_len": self.seq,
+        self.metric = f"Llama-2 {size} LoRA FSDP tokens/s" if lora else f"Llama-2 {size} FSDP tokens/s"
+        self.config = {"model": f"llama2-{size}", "lora": "r16 a32 qkvo" if lora else None, "global_batch": self.bs * world, "seq_len": self.seq,
                        "parallelism": f"fsdp{world}", "l2": "13.5 GB bf16 weights exceed L2"}
 
     def loss_fn(self, batch):
@@ -196,10 +249,16 @@ def make_case(name: str, dev, rank, world, batch=None, seq=None, size=None, fuse
         return GPT2FSDP(dev, rank, world, batch, seq, size, fused_comm)
     if name == "lm_ddp":
         return LMDDP(dev, rank, world, batch, seq, size, fused_comm)
+    if name == "lm_fsdp":
+        return LMFSDP(dev, rank, world, batch, seq, size, fused_comm)
+    if name == "cifar_ddp":
+        return CifarDDP(dev, rank, world, batch, fused_comm)
     if name == "resnet50_ddp":
         return VisionDDP(dev, rank, world, "resnet50", batch, fused_comm)
     if name == "vit_ddp":
         return VisionDDP(dev, rank, world, "vit", batch, fused_comm)
     if name == "llama_lora":
         return LlamaLoRA(dev, rank, world, batch, seq, size, fused_comm)
+    if name == "llama_fsdp":
+        return LlamaLoRA(dev, rank, world, batch, seq, size, fused_comm, lora=False)
     raise ValueError(name)
