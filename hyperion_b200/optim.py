@@ -94,6 +94,30 @@ class FusedAdamW:
         self.flat.zero_grad()
 
     # -- checkpointing ---------------------------------------------------------------------------
+    @torch.no_grad()
+    def refresh_master(self, sd: dict | None = None) -> None:
+        """Re-seed the fp32 master from the module's (just loaded) parameters; fp32 values in ``sd`` (an unwrapped
+        state_dict) overlay it so nothing is lost through the 16-bit copy.  Call after ANY weights-only load: otherwise
+        the next step writes the stale master back over the loaded weights."""
+        if self.master is None:
+            return
+        self.master.copy_(self.flat.data[self.start:self.end].to(torch.float32))
+        if sd is not None and self.start == 0 and self.end == self.flat.numel:
+            from .parallel.flat import shaped_view
+
+            for sp in self.flat.specs:
+                v = sd.get(sp.name)
+                if v is not None and tuple(v.shape) == tuple(sp.param.shape):
+                    shaped_view(self.master, sp).copy_(v.to(device=self.master.device, dtype=torch.float32))
+
+    def master_state_overlay(self) -> dict:
+        """{parameter name: fp32 master view} for checkpoint export (true fp32 weights, as the reference's AMP keeps)."""
+        if self.master is None or self.start != 0 or self.end != self.flat.numel:
+            return {}
+        from .parallel.flat import shaped_view
+
+        return {sp.name: shaped_view(self.master, sp) for sp in self.flat.specs}
+
     def state_dict(self) -> dict:
         return {"step": int(self.step_t.item()), "exp_avg": self.exp_avg, "exp_avg_sq": self.exp_avg_sq, "master": self.master,
                 "lr": self.lr, "betas": self.betas, "eps": self.eps, "weight_decay": self.weight_decay}

@@ -113,8 +113,18 @@ class HyperionDDP(nn.Module):
             self._handles.append((h, view))
 
     def _finalize(self) -> None:
-        """Runs once at the end of backward: join the communication with the compute stream."""
+        """Runs once at the end of backward: join the communication with the compute stream.
+
+        A bucket whose counter did not reach zero holds a parameter that received no gradient this step (unused branch).
+        The model is the same on every rank, so the same buckets are short everywhere: they are reduced here anyway (the
+        missing slots are zeros from ``zero_grad``), which keeps the ranks' collective sequences identical instead of
+        silently skipping the bucket (torch DDP raises in that situation; see ``unused`` for the names)."""
         self._callback_queued = False
+        self.unused = []
+        for b, (_, _, idxs) in enumerate(self.buckets):
+            if 0 < self._pending[b] < len(idxs) or (self._pending[b] == len(idxs) and self._require_sync):
+                self.unused += [self.flat.specs[i].name for i in idxs if self.flat.specs[i].param.grad is None]
+                self._reduce_bucket(b)
         if self.fused:
             torch.cuda.current_stream(self.device).wait_stream(self.comm_stream)
         else:

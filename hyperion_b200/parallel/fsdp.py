@@ -79,8 +79,9 @@ class HyperionFSDP(nn.Module):
     def __init__(self, module: nn.Module, units: list[nn.Module] | None = None, min_num_params: int = 100_000,
                  lr: float = 1e-4, betas=(0.9, 0.999), eps: float = 1e-8, weight_decay: float = 0.01,
                  max_norm: float = 0.0, fused: bool | None = None, process_group=None, loss_scaler=None,
-                 sync_params: bool = True, fuse_allgather_gemm: bool = True):
+                 sync_params: bool = True, fuse_allgather_gemm: bool = True, reshard_after_forward: bool | None = None):
         super().__init__()
+        self.reshard = False
         self.module = module
         self.rank, self.world_size = world()
         self.group = process_group
@@ -289,6 +290,14 @@ class HyperionFSDP(nn.Module):
 
     def _end_of_backward(self) -> None:
         self._callback_queued = False
+        # units holding a parameter that received no gradient this step never reach pending == 0: reduce them here (zeros
+        # in the missing slots), on every rank alike, so neither a stale gshard is re-applied nor a unit left un-updated
+        self.unused = []
+        for ui, n in enumerate(self._unit_nparams):
+            if self._pending[ui] > 0 and n > 0:
+                self.unused += [self.flat.specs[i].name for i, u in self._spec_unit.items()
+                                if u == ui and self.flat.specs[i].param.grad is None]
+                self._reduce_unit(ui)
         if self.fused:
             torch.cuda.current_stream(self.device).wait_stream(self.comm_stream)
         self._pending = list(self._unit_nparams)
@@ -376,8 +385,9 @@ class HyperionFSDP(nn.Module):
         if p16 is not master:
             p16.copy_(master.to(p16.dtype))
 
-    def _queue_gathers(self) -> None:
-        """Gather every unit's new 16-bit shard into the resident flat buffer, in forward order."""
+    def _queue_gathers(self, force_plain: bool = False) -> None:
+        """Gather every unit's new 16-bit shard into the resident flat buffer, in forward order.  ``force_plain`` also
+        gathers the GEMM-gathered units with the stand-alone kernel (``sync_params``)."""
         W = self.world_size
         order = sorted(range(len(self.units)), key=lambda ui: (self.units[ui][2] != -1, -self.units[ui][0]))
         if self.fused:
@@ -386,7 +396,7 @@ class HyperionFSDP(nn.Module):
             self.comm_stream.wait_event(ev)
             with torch.cuda.stream(self.comm_stream):
                 for ui in order:
-                    if ui in self._ag_handles:  # gathered later, inside the unit's first GEMM (K-C3)
+                    if ui in self._ag_handles and not force_plain:  # gathered later, inside the unit's first GEMM (K-C3)
                         self._ag_handles[ui].pending = True
                         self._gather_events[ui] = None
                         continue
@@ -396,6 +406,8 @@ class HyperionFSDP(nn.Module):
                     gev = torch.cuda.Event()
                     gev.record(self.comm_stream)
                     self._gather_events[ui] = gev
+                    if ui in self._ag_handles:
+                        self._ag_handles[ui].pending = False
         else:
             for ui in order:
                 s, e, _ = self.units[ui]
@@ -410,9 +422,24 @@ class HyperionFSDP(nn.Module):
         lazily at the start of the next forward): call before reading ``module.parameters()`` directly."""
         if self._gathers_due:
             self._gathers_due = False
-            self._queue_gathers()
+            self._queue_gathers(force_plain=True)
+        elif any(h.pending for h in self._ag_handles.values()):
+            self._gather_pending_ag_units()
         if self.comm_stream is not None:
             torch.cuda.current_stream(self.device).wait_stream(self.comm_stream)
+
+    def _gather_pending_ag_units(self) -> None:
+        """Stand-alone gather of the units that were waiting for their first GEMM (collective: every rank calls)."""
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(self.device))
+        self.comm_stream.wait_event(ev)
+        with torch.cuda.stream(self.comm_stream):
+            for ui, h in sorted(self._ag_handles.items()):
+                if h.pending:
+                    s, e, _ = self.units[ui]
+                    a, b = self._shard_range(ui)
+                    self.arena.allgather(self.shard16, a, b - a, self.flat.data[s:e])
+                    h.pending = False
 
     # ------------------------------------------------------------------ checkpoints (K-C6 / K-C7)
     @torch.no_grad()
@@ -451,5 +478,48 @@ class HyperionFSDP(nn.Module):
     def state_dict(self, *a, **kw):
         return self.module.state_dict(*a, **kw)
 
+    def load_state_dict(self, sd, strict: bool = True, *a, **kw):
+        """Load an unwrapped full state_dict: the resident 16-bit copy, THEN the local 16-bit shard and the fp32 master
+        shard (taken from the fp32 values in ``sd`` where present, so no precision is lost through the 16-bit copy)."""
+        res = self.module.load_state_dict(sd, strict=strict, *a, **kw)
+        self.refresh_shards(sd)
+        return res
+
+    @torch.no_grad()
+    def refresh_shards(self, sd: dict | None = None) -> None:
+        """Re-derive ``shard16`` / ``master`` from the resident parameters (after any weights-only load)."""
+        full32 = self.flat.data.to(torch.float32)
+        if sd is not None:
+            for sp in self.flat.specs:
+                v = sd.get(sp.name)
+                if v is not None and tuple(v.shape) == tuple(sp.param.shape):
+                    from .flat import shaped_view
+
+                    shaped_view(full32, sp).copy_(v.to(device=self.device, dtype=torch.float32))
+        self._copy_local_shards(self.flat.data, self.shard16)
+        if self.master is not None:
+            self._copy_local_shards(full32, self.master)
+        self._gathers_due = False
+        for h in self._ag_handles.values():
+            h.pending = False
+
     def optimizer_state_dict(self) -> dict:
-        return {"step": self.step_count, "exp_avg": self.exp_avg, "exp_avg_sq": self.exp_avg_sq, "master": self.master}
+        """This rank's shard of the optimizer state (fp32 master, exp_avg, exp_avg_sq) plus the step count."""
+        # the device-side counter is the truth: a CUDA-graph replay advances it without running the Python above
+        return {"step": int(self.step_t.item()) - 1, "exp_avg": self.exp_avg, "exp_avg_sq": self.exp_avg_sq, "master": self.master,
+                "rank": self.rank, "world_size": self.world_size, "shard_numel": self.shard_numel}
+
+    @torch.no_grad()
+    def load_optimizer_state_dict(self, sd: dict) -> None:
+        if int(sd.get("world_size", self.world_size)) != self.world_size or int(sd.get("shard_numel", self.shard_numel)) != self.shard_numel:
+            raise ValueError(f"optimizer shard was saved with world_size={sd.get('world_size')} / shard_numel={sd.get('shard_numel')}; "
+                             f"this engine has {self.world_size} / {self.shard_numel}")
+        self.step_count = int(sd["step"])
+        self.step_t.fill_(float(self.step_count + 1))
+        self.exp_avg.copy_(sd["exp_avg"])
+        self.exp_avg_sq.copy_(sd["exp_avg_sq"])
+        if self.master is not None and sd.get("master") is not None:
+            self.master.copy_(sd["master"])
+            self.shard16.copy_(self.master.to(self.shard16.dtype))
+            if self.world_size > 1:
+                self._gathers_due = True

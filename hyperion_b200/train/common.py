@@ -78,3 +78,61 @@ def mean_over_ranks(t: torch.Tensor) -> float:
         dist.all_reduce(t)
         t /= W
     return float(t.item())
+
+
+def graph_default(device) -> bool:
+    """CUDA-graph the step unless ``HYPERION_GRAPH=0`` (needs a CUDA device and the native library)."""
+    from ..ops import _lib
+
+    return torch.device(device).type == "cuda" and _lib.available() and os.environ.get("HYPERION_GRAPH", "1") != "0"
+
+
+class StepRunner:
+    """What every trainer calls per batch: ``loss = runner(batch_tuple)``.
+
+    With ``graph=True`` the whole step (forward, backward, communication kernels, optimizer) is captured in a CUDA graph
+    (``GraphedStep``) after ``eager_steps`` ordinary steps and replayed from then on -- the headline configuration of
+    ``bench.py``, reachable from ``run_distributed.py --graph`` (default on CUDA).  Batches whose shapes differ from
+    the captured ones (the ragged last batch of an epoch) run eagerly.  ``loss_fn(batch)`` returns the loss or
+    ``(loss, *extras)``; the same structure comes back (detached).  Without a graph it is just
+    ``eng.backward_and_step(loss_fn(batch))``.
+    """
+
+    def __init__(self, eng, loss_fn, graph: bool | None = None, eager_steps: int = 2):
+        self.eng, self.loss_fn = eng, loss_fn
+        dev = getattr(eng.flat, "device", "cpu")
+        self.graph = graph_default(dev) if graph is None else (graph and torch.device(dev).type == "cuda")
+        self.eager_steps, self.n, self.graphed, self.shapes = eager_steps, 0, None, None
+        self.replays = 0
+
+    def _eager(self, batch):
+        out = self.loss_fn(batch)
+        loss = out[0] if isinstance(out, (tuple, list)) else out
+        self.eng.backward_and_step(loss)
+        return tuple(t.detach() for t in out) if isinstance(out, (tuple, list)) else loss.detach()
+
+    def __call__(self, batch):
+        self.n += 1
+        if not self.graph:
+            return self._eager(batch)
+        shapes = tuple((tuple(t.shape), t.dtype) for t in batch)
+        if self.graphed is None:
+            if self.n <= self.eager_steps:
+                return self._eager(batch)
+            from .engine import GraphedStep
+
+            try:
+                # the eager steps above were the warm-up; the capture itself performs no optimizer step
+                self.graphed = GraphedStep(self.eng, self.loss_fn, batch, warmup=0)
+                self.shapes = shapes
+            except Exception as e:  # noqa: BLE001
+                import warnings
+
+                warnings.warn(f"CUDA-graph capture failed ({e!r}); continuing eagerly")
+                torch.cuda.synchronize()
+                self.graph = False
+                return self._eager(batch)
+        if shapes != self.shapes:
+            return self._eager(batch)
+        self.replays += 1
+        return self.graphed(batch)

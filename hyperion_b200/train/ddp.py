@@ -23,7 +23,7 @@ from ..models import SimpleTransformerLM, resnet18, resnet50, vit_b_16
 from ..parallel.runtime import cleanup, setup
 from ..utils.checkpoint import load_training_state, save_model, save_training_state
 from ..utils.metrics import CsvLogger
-from .common import EpochTimer, load_cifar_tensors, load_wikitext_tensors, mean_over_ranks
+from .common import EpochTimer, StepRunner, load_cifar_tensors, load_wikitext_tensors, mean_over_ranks
 from .engine import build_engine
 
 
@@ -31,7 +31,8 @@ def train_language_model_ddp(rank: int, world_size: int, epochs: int = 5, base_d
                              precision: str | None = None, synthetic: bool = True, steps_per_epoch: int | None = None,
                              batch_size: int = 32, rows: int | None = None, fused_comm: bool | None = None,
                              seed: int = 0, resume: str | None = None, save: bool = True, model_kwargs: dict | None = None,
-                             vocab_size: int = synth.GPT2_VOCAB, pad_id: int = synth.GPT2_PAD, strategy: str = "ddp"):
+                             vocab_size: int = synth.GPT2_VOCAB, pad_id: int = synth.GPT2_PAD, strategy: str = "ddp",
+                             graph: bool | None = None):
     dev = setup(rank, world_size, backend, seed=seed)
     precision = precision or ("fp16" if dev.type == "cuda" else "fp32")
     out_dir = os.path.join(base_dir, "data/distributed")
@@ -41,19 +42,19 @@ def train_language_model_ddp(rank: int, world_size: int, epochs: int = 5, base_d
     model = SimpleTransformerLM(vocab_size, **(model_kwargs or {}))
     eng = build_engine(model, strategy=strategy, precision=precision, lr=2e-4, device=dev, fused_comm=fused_comm)
     start_epoch = load_training_state(resume, eng.model, eng.optimizer, eng.scaler) if resume else 0
+    eng.model.train()
+    runner = StepRunner(eng, lambda b: eng.model.loss(b[0][:, :-1].contiguous(), b[0][:, 1:].contiguous(), ignore_index=pad_id),
+                        graph=graph)
     timer = EpochTimer(dev)
     history = []
     for ep in range(start_epoch, epochs):
         loader.set_epoch(ep)
-        eng.model.train()
         total = torch.zeros((), device=dev)
         nsteps = 0
         timer.start()
-        for (batch,) in loader:
-            x, y = batch[:, :-1].contiguous(), batch[:, 1:].contiguous()
-            loss = eng.model.loss(x, y, ignore_index=pad_id)
-            eng.backward_and_step(loss)
-            total += loss.detach().float()
+        for batch in loader:
+            loss = runner(batch)
+            total += loss.float()
             nsteps += 1
             if steps_per_epoch and nsteps >= steps_per_epoch:
                 break
@@ -67,7 +68,7 @@ def train_language_model_ddp(rank: int, world_size: int, epochs: int = 5, base_d
         logger.log_device(ep + 1, nsteps, dev_ms / max(nsteps, 1), toks / (dev_ms / 1e3), "tokens/s",
                           torch.cuda.max_memory_allocated(dev) / 2 ** 20 if dev.type == "cuda" else 0.0, world_size)
     if save:
-        save_model(eng.model, os.path.join(out_dir, f"{logger.run_id}_model.pt"), rank)
+        save_model(eng.model, os.path.join(out_dir, f"{logger.run_id}_model.pt"), rank, optimizer=eng.optimizer)
         save_training_state(os.path.join(out_dir, f"{logger.run_id}_train_state.pt"), eng.model, eng.optimizer,
                             epochs - 1, eng.scaler, rank)
     cleanup()
@@ -84,7 +85,8 @@ VISION_MODELS = {
 def train_cifar_model_ddp(rank: int, world_size: int, epochs: int = 5, base_dir: str = ".", *, backend: str | None = None,
                           precision: str | None = None, synthetic: bool = True, steps_per_epoch: int | None = None,
                           batch_size: int = 64, rows: int | None = None, fused_comm: bool | None = None, seed: int = 0,
-                          arch: str = "resnet18", checkpointing: bool = False, save: bool = True):
+                          arch: str = "resnet18", checkpointing: bool = False, save: bool = True, resume: str | None = None,
+                          graph: bool | None = None):
     """ResNet-18 on CIFAR-10-shaped data (the reference job); ``arch`` generalises it to ResNet-50 / ViT-B/16
     at 224x224 (BASELINE configs 2 and 3)."""
     dev = setup(rank, world_size, backend, seed=seed)
@@ -105,22 +107,28 @@ def train_cifar_model_ddp(rank: int, world_size: int, epochs: int = 5, base_dir:
     eng = build_engine(model, strategy="ddp", precision=precision, lr=1e-3, device=dev, fused_comm=fused_comm)
     x_all = x_all.to(eng.precision.dtype)
     loader = DeviceResidentLoader((x_all, y_all), batch_size, rank, world_size, shuffle=True, seed=seed)
+    start_epoch = load_training_state(resume, eng.model, eng.optimizer, eng.scaler) if resume else 0
+    eng.model.train()
+
+    def loss_fn(b):
+        out = eng.model(b[0])
+        with torch.no_grad():
+            correct = (out.argmax(1) == b[1]).sum()
+        return ops.cross_entropy(out, b[1]), correct
+
+    runner = StepRunner(eng, loss_fn, graph=graph)
     timer = EpochTimer(dev)
     history = []
-    for ep in range(epochs):
+    for ep in range(start_epoch, epochs):
         loader.set_epoch(ep)
-        eng.model.train()
         stats = torch.zeros(3, device=dev)  # loss sum, correct, total
         nsteps = 0
         timer.start()
-        for x, y in loader:
-            out = eng.model(x)
-            loss = ops.cross_entropy(out, y)
-            eng.backward_and_step(loss)
-            with torch.no_grad():
-                stats[0] += loss.detach().float()
-                stats[1] += (out.argmax(1) == y).sum()
-                stats[2] += y.numel()
+        for batch in loader:
+            loss, correct = runner(batch)
+            stats[0] += loss.float()
+            stats[1] += correct
+            stats[2] += batch[1].numel()
             nsteps += 1
             if steps_per_epoch and nsteps >= steps_per_epoch:
                 break
@@ -137,6 +145,8 @@ def train_cifar_model_ddp(rank: int, world_size: int, epochs: int = 5, base_dir:
         logger.log_device(ep + 1, nsteps, dev_ms / max(nsteps, 1), nsteps * batch_size * world_size / (dev_ms / 1e3),
                           "samples/s", torch.cuda.max_memory_allocated(dev) / 2 ** 20 if dev.type == "cuda" else 0.0, world_size)
     if save:
-        save_model(eng.model, os.path.join(out_dir, f"{logger.run_id}_model.pt"), rank)
+        save_model(eng.model, os.path.join(out_dir, f"{logger.run_id}_model.pt"), rank, optimizer=eng.optimizer)
+        save_training_state(os.path.join(out_dir, f"{logger.run_id}_train_state.pt"), eng.model, eng.optimizer,
+                            epochs - 1, eng.scaler, rank)
     cleanup()
     return history

@@ -9,6 +9,8 @@ zero the flat gradient.  Nothing in it synchronises the host.
 """
 from __future__ import annotations
 
+import contextlib
+
 import torch
 import torch.nn as nn
 
@@ -73,7 +75,8 @@ class Engine:
 def build_engine(model: nn.Module, *, strategy: str = "single", precision: str = "bf16", lr: float = 1e-3,
                  betas=(0.9, 0.999), eps: float = 1e-8, weight_decay: float = 0.01, clip: float = 0.0, device=None,
                  fused_comm: bool | None = None, bucket_cap_mb: float = 25.0, fsdp_units=None,
-                 fsdp_min_num_params: int = 100_000, broadcast_buffers: bool = False) -> Engine:
+                 fsdp_min_num_params: int = 100_000, broadcast_buffers: bool = False,
+                 reshard_after_forward: bool | None = None) -> Engine:
     rank, W = world()
     pol = policy(precision)
     device = torch.device(device) if device is not None else next(model.parameters()).device
@@ -84,7 +87,8 @@ def build_engine(model: nn.Module, *, strategy: str = "single", precision: str =
     scaler = DynamicLossScaler(device, enabled=True) if pol.needs_scaler else None
     if strategy == "fsdp":
         wrapped = HyperionFSDP(model, units=fsdp_units, min_num_params=fsdp_min_num_params, lr=lr, betas=betas, eps=eps,
-                               weight_decay=weight_decay, max_norm=clip, fused=fused_comm, loss_scaler=scaler)
+                               weight_decay=weight_decay, max_norm=clip, fused=fused_comm, loss_scaler=scaler,
+                               reshard_after_forward=reshard_after_forward)
         return Engine(model, wrapped, wrapped.flat, None, scaler, strategy, pol, clip)
     if strategy == "ddp" and W > 1:
         wrapped = HyperionDDP(model, bucket_cap_mb=bucket_cap_mb, fused=fused_comm, loss_scaler=scaler,
@@ -112,6 +116,8 @@ class GraphedStep:
         loss = step(batch)            # copies the batch into the static input, replays, returns the static loss tensor
 
     ``warmup`` eager steps run first (they are real optimizer steps).  Shapes are fixed by ``example_batch``.
+    ``StepRunner`` (train/common.py) is the wrapper the trainers use: it captures lazily, counts the warm-up steps as
+    training steps on their own batches and falls back to eager for a ragged last batch.
     """
 
     def __init__(self, eng: Engine, loss_fn, example_batch, warmup: int = 2):
@@ -121,9 +127,10 @@ class GraphedStep:
         dev = self.static_batch[0].device
         side = torch.cuda.Stream(dev)
         side.wait_stream(torch.cuda.current_stream(dev))
-        with torch.cuda.stream(side):
-            for _ in range(max(1, warmup)):
-                eng.backward_and_step(loss_fn(self.static_batch))
+        with torch.cuda.stream(side) if warmup > 0 else contextlib.nullcontext():
+            for _ in range(warmup):
+                out = loss_fn(self.static_batch)
+                eng.backward_and_step(out[0] if isinstance(out, (tuple, list)) else out)
         torch.cuda.current_stream(dev).wait_stream(side)
         torch.cuda.synchronize(dev)
         # events recorded by the eager warm-up steps (pending parameter gathers) are complete after the synchronize;
@@ -135,9 +142,15 @@ class GraphedStep:
         n0 = _lib.launch_count()
         self.graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(self.graph, capture_error_mode="thread_local"):  # other threads (NCCL watchdog) may poll events
-            self.loss = loss_fn(self.static_batch)
+            out = loss_fn(self.static_batch)
+            # ``loss_fn`` may return ``loss`` or ``(loss, *extras)`` (e.g. a correct-prediction count): the extras are
+            # static graph outputs too and come back from every replay
+            self.loss = out[0] if isinstance(out, (tuple, list)) else out
             eng.backward_and_step(self.loss)
-        self.loss = self.loss.detach()
+        if isinstance(out, (tuple, list)):
+            self.loss = tuple(t.detach() for t in out)
+        else:
+            self.loss = self.loss.detach()
         self.kernels_per_replay = _lib.launch_count() - n0  # library kernels recorded in the graph
         self._add_launches = _lib.add_launches
 

@@ -17,9 +17,9 @@ from ..data import DeviceResidentLoader, synth
 from ..models import GPT2Config, GPT2LMHeadModel, SimpleTransformerLM
 from ..models.gpt2 import Block as GPT2Block
 from ..parallel.runtime import cleanup, setup
-from ..utils.checkpoint import save_model, save_sharded
+from ..utils.checkpoint import load_training_state, save_model, save_sharded, save_training_state
 from ..utils.metrics import CsvLogger
-from .common import EpochTimer, load_wikitext_tensors, mean_over_ranks
+from .common import EpochTimer, StepRunner, load_wikitext_tensors, mean_over_ranks
 from .engine import build_engine
 
 
@@ -28,7 +28,8 @@ def train_language_model_fsdp(rank: int, world_size: int, epochs: int = 5, base_
                               steps_per_epoch: int | None = None, batch_size: int = 32, rows: int | None = None,
                               fused_comm: bool | None = None, seed: int = 0, save: bool = True, clip: float = 1.0,
                               model_kwargs: dict | None = None, vocab_size: int = synth.GPT2_VOCAB,
-                              pad_id: int = synth.GPT2_PAD, min_num_params: int = 100_000):
+                              pad_id: int = synth.GPT2_PAD, min_num_params: int = 100_000, resume: str | None = None,
+                              graph: bool | None = None, reshard_after_forward: bool | None = None):
     dev = setup(rank, world_size, backend, seed=seed)
     precision = precision or ("bf16" if dev.type == "cuda" else "fp32")
     out_dir = os.path.join(base_dir, "data/distributed")
@@ -37,20 +38,21 @@ def train_language_model_fsdp(rank: int, world_size: int, epochs: int = 5, base_
     loader = DeviceResidentLoader((ids,), batch_size, rank, world_size, shuffle=True, seed=seed)
     model = SimpleTransformerLM(vocab_size, **(model_kwargs or {}))
     eng = build_engine(model, strategy="fsdp", precision=precision, lr=1e-4, clip=clip, device=dev,
-                       fused_comm=fused_comm, fsdp_min_num_params=min_num_params)
+                       fused_comm=fused_comm, fsdp_min_num_params=min_num_params, reshard_after_forward=reshard_after_forward)
+    start_epoch = load_training_state(resume, eng.model, None, eng.scaler) if resume else 0
+    eng.model.train()
+    runner = StepRunner(eng, lambda b: eng.model.loss(b[0][:, :-1].contiguous(), b[0][:, 1:].contiguous(), ignore_index=pad_id),
+                        graph=graph)
     timer = EpochTimer(dev)
     history = []
-    for ep in range(epochs):
+    for ep in range(start_epoch, epochs):
         loader.set_epoch(ep)
-        eng.model.train()
         total = torch.zeros((), device=dev)
         nsteps = 0
         timer.start()
-        for (batch,) in loader:
-            x, y = batch[:, :-1].contiguous(), batch[:, 1:].contiguous()
-            loss = eng.model.loss(x, y, ignore_index=pad_id)
-            eng.backward_and_step(loss)
-            total += loss.detach().float()
+        for batch in loader:
+            loss = runner(batch)
+            total += loss.float()
             nsteps += 1
             if steps_per_epoch and nsteps >= steps_per_epoch:
                 break
@@ -66,6 +68,8 @@ def train_language_model_fsdp(rank: int, world_size: int, epochs: int = 5, base_
     if save:
         save_model(eng.model, os.path.join(out_dir, f"{logger.run_id}_model.pt"), rank)          # all ranks gather
         save_sharded(eng.model, None, os.path.join(out_dir, f"{logger.run_id}_model_sharded"), rank)
+        save_training_state(os.path.join(out_dir, f"{logger.run_id}_train_state.pt"), eng.model, None, epochs - 1,
+                            eng.scaler, rank)     # + one optimizer shard file per rank
     cleanup()
     return history
 
@@ -73,7 +77,8 @@ def train_language_model_fsdp(rank: int, world_size: int, epochs: int = 5, base_
 def train_gpt2_fsdp(rank: int, world_size: int, epochs: int = 1, base_dir: str = ".", *, backend: str | None = None,
                     precision: str = "bf16", size: str = "medium", seq_len: int = 1024, batch_size: int = 8,
                     steps_per_epoch: int = 20, fused_comm: bool | None = None, seed: int = 0, clip: float = 1.0,
-                    save: bool = False, checkpointing: bool = False):
+                    save: bool = False, checkpointing: bool = False, resume: str | None = None, graph: bool | None = None,
+                    reshard_after_forward: bool | None = None):
     """GPT-2 (medium by default) under HyperionFSDP on WikiText-2-shaped synthetic tokens, seq 1024 (config 4)."""
     dev = setup(rank, world_size, backend, seed=seed)
     cfg = {"medium": GPT2Config.medium, "small": GPT2Config.small, "tiny": GPT2Config.tiny}[size]()
@@ -84,21 +89,22 @@ def train_gpt2_fsdp(rank: int, world_size: int, epochs: int = 1, base_dir: str =
     model.use_checkpoint = checkpointing
     units = [m for m in model.modules() if isinstance(m, GPT2Block)]
     eng = build_engine(model, strategy="fsdp", precision=precision if dev.type == "cuda" else "fp32", lr=1e-4, clip=clip,
-                       device=dev, fused_comm=fused_comm, fsdp_units=units)
+                       device=dev, fused_comm=fused_comm, fsdp_units=units, reshard_after_forward=reshard_after_forward)
+    start_epoch = load_training_state(resume, eng.model, None, eng.scaler) if resume else 0
+    runner = StepRunner(eng, lambda b: eng.model.loss(b[0]), graph=graph)
     n = batch_size * world_size * steps_per_epoch
     ids, _ = synth.token_batch(n, seq_len, cfg.vocab_size, dev, seed)
     loader = DeviceResidentLoader((ids,), batch_size, rank, world_size, shuffle=True, seed=seed)
     timer = EpochTimer(dev)
     history = []
-    for ep in range(epochs):
+    for ep in range(start_epoch, epochs):
         loader.set_epoch(ep)
         total = torch.zeros((), device=dev)
         nsteps = 0
         timer.start()
-        for (batch,) in loader:
-            loss = eng.model.loss(batch)
-            eng.backward_and_step(loss)
-            total += loss.detach().float()
+        for batch in loader:
+            loss = runner(batch)
+            total += loss.float()
             nsteps += 1
         wall_s, dev_ms = timer.stop()
         avg = mean_over_ranks(total / max(nsteps, 1))
@@ -111,5 +117,7 @@ def train_gpt2_fsdp(rank: int, world_size: int, epochs: int = 1, base_dir: str =
                           torch.cuda.max_memory_allocated(dev) / 2 ** 20 if dev.type == "cuda" else 0.0, world_size)
     if save:
         save_model(eng.model, os.path.join(out_dir, f"{logger.run_id}_model.pt"), rank)
+        save_training_state(os.path.join(out_dir, f"{logger.run_id}_train_state.pt"), eng.model, None, epochs - 1,
+                            eng.scaler, rank)
     cleanup()
     return history

@@ -21,9 +21,9 @@ from ..lora import inject_lora, save_pretrained, trainable_parameters
 from ..models import LlamaConfig, LlamaForCausalLM
 from ..models.llama import LlamaDecoderLayer
 from ..parallel.runtime import cleanup, setup
-from ..utils.checkpoint import save_model
+from ..utils.checkpoint import load_training_state, save_model, save_training_state
 from ..utils.metrics import CsvLogger
-from .common import EpochTimer, mean_over_ranks
+from .common import EpochTimer, StepRunner, mean_over_ranks
 from .engine import build_engine
 
 CONFIGS = {"7b": LlamaConfig.llama2_7b, "tiny": LlamaConfig.tiny}
@@ -33,7 +33,8 @@ def train_llama_fsdp(rank: int, world_size: int, epochs: int = 1, base_dir: str 
                      model_id: str = "NousResearch/Llama-2-7b-hf", lora: bool = False, batch_size: int = 1,
                      progress_every: int = 50, *, backend: str | None = None, size: str = "7b", seq_len: int = 128,
                      steps_per_epoch: int | None = 50, lora_strategy: str = "fsdp", fused_comm: bool | None = None,
-                     seed: int = 0, save: bool = True, checkpointing: bool = False, config: LlamaConfig | None = None):
+                     seed: int = 0, save: bool = True, checkpointing: bool = False, config: LlamaConfig | None = None,
+                     resume: str | None = None, graph: bool | None = None, reshard_after_forward: bool | None = None):
     dev = setup(rank, world_size, backend, seed=seed)
     cfg = config or CONFIGS[size]()
     mode = "lora_bf16" if lora else "fsdp_bf16"
@@ -57,24 +58,24 @@ def train_llama_fsdp(rank: int, world_size: int, epochs: int = 1, base_dir: str 
     units = [m for m in model.modules() if isinstance(m, LlamaDecoderLayer)]
     strategy = ("fsdp" if lora_strategy == "fsdp" else "ddp") if lora else "fsdp"
     eng = build_engine(model, strategy=strategy, precision=precision, lr=1e-5, weight_decay=0.01, clip=1.0, device=dev,
-                       fused_comm=fused_comm, fsdp_units=units)
+                       fused_comm=fused_comm, fsdp_units=units, reshard_after_forward=reshard_after_forward)
+    start_epoch = load_training_state(resume, eng.model, eng.optimizer, eng.scaler) if resume else 0
+    eng.model.train()
+    runner = StepRunner(eng, lambda b: eng.model(input_ids=b[0], attention_mask=b[1], labels=b[0].clone()).loss, graph=graph)
     steps = steps_per_epoch or (synth.WIKITEXT2_ROWS["train"] // (batch_size * world_size))
     n = batch_size * world_size * steps
     ids, mask = synth.token_batch(n, seq_len, cfg.vocab_size, dev, seed, pad_id=cfg.pad_token_id, pad_fraction=0.4)
     loader = DeviceResidentLoader((ids, mask), batch_size, rank, world_size, shuffle=True, seed=seed)
     timer = EpochTimer(dev)
     history = []
-    for ep in range(epochs):
+    for ep in range(start_epoch, epochs):
         loader.set_epoch(ep)
-        eng.model.train()
         total = torch.zeros((), device=dev)
         nsteps = 0
         timer.start()
-        for step, (x, m) in enumerate(loader):
-            labels = x.clone()
-            loss = eng.model(input_ids=x, attention_mask=m, labels=labels).loss
-            eng.backward_and_step(loss)
-            total += loss.detach().float()
+        for step, batch in enumerate(loader):
+            loss = runner(batch)
+            total += loss.float()
             nsteps += 1
             if rank == 0 and progress_every and (step + 1) % progress_every == 0:
                 print(f"[Llama] epoch {ep + 1} step {step + 1}/{len(loader)}", flush=True)
@@ -95,5 +96,7 @@ def train_llama_fsdp(rank: int, world_size: int, epochs: int = 1, base_dir: str 
                 save_pretrained(eng.raw_model, os.path.join(out_dir, f"{logger.run_id}_{mode}"), model_id)
         else:
             save_model(eng.model, os.path.join(out_dir, f"{logger.run_id}_{mode}.pt"), rank, dtype=None)
+        save_training_state(os.path.join(out_dir, f"{logger.run_id}_train_state.pt"), eng.model, eng.optimizer, epochs - 1,
+                            eng.scaler, rank)
     cleanup()
     return history

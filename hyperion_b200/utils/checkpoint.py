@@ -26,14 +26,23 @@ def unwrap(model):
     return getattr(model, "module", model)
 
 
-def full_state_dict(model, to_cpu: bool = True, dtype: torch.dtype | None = torch.float32) -> dict:
-    """Unwrapped state_dict (all ranks may call; for HyperionFSDP every rank must call -- it gathers)."""
+def full_state_dict(model, to_cpu: bool = True, dtype: torch.dtype | None = torch.float32, optimizer=None) -> dict:
+    """Unwrapped state_dict (all ranks may call; for HyperionFSDP every rank must call -- it gathers).  With
+    ``optimizer`` (a ``FusedAdamW``) the fp32 master weights replace the upcast 16-bit compute copy, so the file holds
+    true fp32 parameters like the reference's AMP checkpoints."""
     if hasattr(model, "sync_buffers"):
         model.sync_buffers()
     if hasattr(model, "gather_full_state_dict"):
         sd = model.gather_full_state_dict()
     else:
-        sd = unwrap(model).state_dict()
+        sd = dict(unwrap(model).state_dict())
+        overlay = optimizer.master_state_overlay() if hasattr(optimizer, "master_state_overlay") else {}
+        if overlay:
+            by_ptr = {p.data_ptr(): n for n, p in unwrap(model).named_parameters()}
+            for k, v in list(sd.items()):
+                n = by_ptr.get(v.data_ptr(), k)   # tied parameters share storage
+                if n in overlay and overlay[n].shape == v.shape:
+                    sd[k] = overlay[n]
     out = {}
     for k, v in sd.items():
         t = v.detach()
@@ -59,9 +68,9 @@ def verify(path) -> bool:
     return man["bytes"] == path.stat().st_size and man["sha256"] == h
 
 
-def save_model(model, path, rank: int = 0, wrap: bool = True, scaler=None, dtype=torch.float32) -> None:
+def save_model(model, path, rank: int = 0, wrap: bool = True, scaler=None, dtype=torch.float32, optimizer=None) -> None:
     """All ranks call (collective for FSDP); rank 0 writes ``{"model_state_dict": ...}``."""
-    sd = full_state_dict(model, dtype=dtype)
+    sd = full_state_dict(model, dtype=dtype, optimizer=optimizer)
     if rank == 0:
         path = Path(path)
         path.parent.mkdir(parents=True, exist_ok=True)
@@ -74,10 +83,22 @@ def save_model(model, path, rank: int = 0, wrap: bool = True, scaler=None, dtype
         dist.barrier()
 
 
-def load_model(model, path, strict: bool = True):
+def _load_weights(model, sd, optimizer=None, strict: bool = True):
+    """Weights into the module AND into every derived copy: FSDP's local 16-bit / fp32 master shards, or the
+    optimizer's fp32 master (otherwise the first step would write the stale master back over the loaded weights)."""
+    if hasattr(model, "refresh_shards"):          # HyperionFSDP
+        return model.load_state_dict(sd, strict=strict)
+    res = unwrap(model).load_state_dict(sd, strict=strict)
+    if optimizer is not None and hasattr(optimizer, "refresh_master"):
+        optimizer.refresh_master(sd)
+    return res
+
+
+def load_model(model, path, strict: bool = True, optimizer=None):
+    """Weights-only load.  Pass the engine's ``optimizer`` (``FusedAdamW``) so its fp32 master follows the file."""
     obj = torch.load(path, map_location="cpu", weights_only=False)
     sd = obj["model_state_dict"] if isinstance(obj, dict) and "model_state_dict" in obj else obj
-    return unwrap(model).load_state_dict(sd, strict=strict)
+    return _load_weights(model, sd, optimizer, strict)
 
 
 def save_sharded(model, optimizer, path_prefix, rank: int) -> Path:
@@ -91,8 +112,18 @@ def save_sharded(model, optimizer, path_prefix, rank: int) -> Path:
     return p
 
 
+def _opt_shard_path(path, rank: int) -> Path:
+    return Path(f"{path}.optshard_rank{rank}.pt")
+
+
 def save_training_state(path, model, optimizer, epoch: int, scaler=None, rank: int = 0, extra: dict | None = None) -> None:
-    sd = full_state_dict(model, dtype=None)
+    """Collective.  Rank 0 writes model + (replicated) optimizer + scaler + epoch + RNG; under HyperionFSDP every rank
+    also writes its optimizer shard next to it (``<path>.optshard_rank<r>.pt``)."""
+    sd = full_state_dict(model, dtype=None, optimizer=optimizer)
+    if hasattr(model, "optimizer_state_dict"):    # HyperionFSDP: sharded state, one file per rank
+        Path(path).parent.mkdir(parents=True, exist_ok=True)
+        torch.save({k: (v.detach().cpu() if torch.is_tensor(v) else v) for k, v in model.optimizer_state_dict().items()},
+                   _opt_shard_path(path, rank))
     if rank == 0:
         path = Path(path)
         path.parent.mkdir(parents=True, exist_ok=True)
@@ -109,15 +140,35 @@ def save_training_state(path, model, optimizer, epoch: int, scaler=None, rank: i
 
 def load_training_state(path, model, optimizer=None, scaler=None) -> int:
     """Returns the epoch to resume from (saved epoch + 1)."""
+    import warnings
+
     obj = torch.load(path, map_location="cpu", weights_only=False)
-    unwrap(model).load_state_dict(obj["model_state_dict"])
+    _load_weights(model, obj["model_state_dict"], optimizer)
     if optimizer is not None and obj.get("optimizer_state_dict") is not None:
         try:
             optimizer.load_state_dict(obj["optimizer_state_dict"])
-        except Exception:
-            pass  # a different world size changes shard shapes; weights are still restored
+        except Exception as e:  # noqa: BLE001 -- e.g. a different flat layout; weights + re-seeded master are still right
+            warnings.warn(f"optimizer state in {path} could not be loaded ({e!r}); moments start from zero")
+            if hasattr(optimizer, "refresh_master"):
+                optimizer.refresh_master(obj["model_state_dict"])
+    if hasattr(model, "load_optimizer_state_dict"):   # HyperionFSDP: this rank's shard
+        rank = dist.get_rank() if dist.is_available() and dist.is_initialized() else 0
+        sp = _opt_shard_path(path, rank)
+        if sp.exists():
+            try:
+                model.load_optimizer_state_dict(torch.load(sp, map_location="cpu", weights_only=False))
+            except ValueError as e:
+                warnings.warn(f"{e}; moments start from zero, weights are restored")
+                model.refresh_shards(obj["model_state_dict"])
+        else:
+            warnings.warn(f"no optimizer shard {sp.name}; moments start from zero")
     if scaler is not None and obj.get("scaler_state_dict") is not None:
         scaler.load_state_dict(obj["scaler_state_dict"])
     if obj.get("rng_cpu") is not None:
         torch.set_rng_state(obj["rng_cpu"])
+    if obj.get("rng_cuda") is not None and torch.cuda.is_available():
+        try:
+            torch.cuda.set_rng_state_all(obj["rng_cuda"][:torch.cuda.device_count()])
+        except Exception as e:  # noqa: BLE001
+            warnings.warn(f"CUDA RNG state not restored: {e!r}")
     return int(obj["epoch"]) + 1

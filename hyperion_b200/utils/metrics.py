@@ -31,12 +31,28 @@ def make_run_id(kind: str, world_size: int, now: datetime.datetime | None = None
     return f"{kind}_{world_size}gpus_{now.strftime('%Y%m%d_%H%M%S')}"
 
 
+def shared_run_id(kind: str, world_size: int) -> str:
+    """Rank 0's run id on every rank (each rank reading its own clock can straddle a second boundary, and the per-rank
+    shard files of one run would then carry different names)."""
+    rid = make_run_id(kind, world_size)
+    try:
+        import torch.distributed as dist
+
+        if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+            box = [rid]
+            dist.broadcast_object_list(box, src=0)
+            rid = box[0]
+    except Exception:  # noqa: BLE001 -- logging must never take a run down
+        pass
+    return rid
+
+
 class CsvLogger:
     def __init__(self, out_dir, kind: str, world_size: int, rank: int = 0, header: list[str] | None = None,
                  run_id: str | None = None):
         self.kind, self.rank, self.world_size = kind, rank, world_size
         self.out_dir = Path(out_dir)
-        self.run_id = run_id or make_run_id(kind, world_size)
+        self.run_id = run_id or shared_run_id(kind, world_size)
         self.header = header or HEADERS[kind]
         self.path = self.out_dir / f"{self.run_id}_metrics.csv"
         self.device_path = self.out_dir / f"{self.run_id}_device_metrics.csv"

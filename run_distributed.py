@@ -7,7 +7,8 @@
 Reference flags kept: --model {language_ddp,cifar,language_fsdp,llama,all,scaling} --epochs --base_dir --hf_token
 --model_id --lora --batch_size --progress_every --scaling_gpus.  Additions: --model {resnet50,vit,gpt2}
 (BASELINE configs 2-4), --precision, --synthetic / --real-data, --steps, --backend (gloo runs on CPU),
---no-fused-comm (NCCL baseline path), --lora-strategy {fsdp,ddp}, --llama-size, --checkpointing, --seed, --config.
+--no-fused-comm (NCCL baseline path), --lora-strategy {fsdp,ddp}, --llama-size, --checkpointing, --seed, --config,
+--graph / --no-graph (whole-step CUDA graph, default on CUDA), --resume <train_state.pt>, --reshard (FSDP FULL_SHARD).
 
 Unlike the reference (A-15), ``--model scaling`` is an ordinary launcher: run it WITHOUT torchrun; it spawns one
 torchrun per GPU count and then writes the scaling report.
@@ -49,6 +50,17 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--seed", type=int, default=0)
     p.add_argument("--config", type=str, default=None, help="JSON file with the default_config.json schema")
     p.add_argument("--no-save", dest="save", action="store_false", default=True)
+    p.add_argument("--save", dest="save_gpt2", action="store_true", default=False,
+                   help="--model gpt2 only: also write the 1.4 GB model file + resumable train state (the other jobs save by default)")
+    p.add_argument("--graph", dest="graph", action="store_true", default=None,
+                   help="capture the whole training step in a CUDA graph (default on CUDA; HYPERION_GRAPH=0 also disables it)")
+    p.add_argument("--no-graph", dest="graph", action="store_false")
+    p.add_argument("--resume", type=str, default=None,
+                   help="a <run_id>_train_state.pt written by an earlier run: weights, optimizer state (sharded under FSDP), "
+                        "loss scaler, RNG and epoch are restored and training continues at the next epoch")
+    p.add_argument("--reshard", dest="reshard", action="store_true", default=None,
+                   help="FSDP: free each unit's gathered parameters after its forward and re-gather them in backward "
+                        "(FULL_SHARD semantics; default keeps the 16-bit copy resident)")
     return p
 
 
@@ -56,7 +68,7 @@ def run_selected(which: str, args, rank: int, world: int) -> None:
     from hyperion_b200 import train
 
     common = dict(backend=args.backend, synthetic=args.synthetic, steps_per_epoch=args.steps, fused_comm=args.fused_comm,
-                  seed=args.seed, save=args.save)
+                  seed=args.seed, save=args.save, resume=args.resume, graph=args.graph)
     bs = {} if args.batch_size is None else {"batch_size": args.batch_size}
     if which == "language_ddp":
         train.train_language_model_ddp(rank, world, epochs=args.epochs, base_dir=args.base_dir, precision=args.precision,
@@ -70,19 +82,21 @@ def run_selected(which: str, args, rank: int, world: int) -> None:
                                     **common, **bs)
     elif which == "language_fsdp":
         train.train_language_model_fsdp(rank, world, epochs=args.epochs, base_dir=args.base_dir, precision=args.precision,
-                                        **common, **bs)
+                                        reshard_after_forward=args.reshard, **common, **bs)
     elif which == "gpt2":
         train.train_gpt2_fsdp(rank, world, epochs=args.epochs, base_dir=args.base_dir, backend=args.backend,
                               precision=args.precision or "bf16", size=args.gpt2_size, seq_len=args.seq_len or 1024,
                               steps_per_epoch=args.steps or 20, fused_comm=args.fused_comm, seed=args.seed,
-                              checkpointing=args.checkpointing, save=False, **bs)
+                              checkpointing=args.checkpointing, save=args.save_gpt2,
+                              resume=args.resume, graph=args.graph, reshard_after_forward=args.reshard, **bs)
     elif which == "llama":
         train.train_llama_fsdp(rank, world, epochs=args.epochs, base_dir=args.base_dir, hf_token=args.hf_token,
                                model_id=args.model_id, lora=args.lora, batch_size=args.batch_size or 1,
                                progress_every=args.progress_every, backend=args.backend, size=args.llama_size,
                                seq_len=args.seq_len or 128, steps_per_epoch=args.steps or 50,
                                lora_strategy=args.lora_strategy, fused_comm=args.fused_comm, seed=args.seed,
-                               save=args.save, checkpointing=args.checkpointing)
+                               save=args.save, checkpointing=args.checkpointing, resume=args.resume, graph=args.graph,
+                               reshard_after_forward=args.reshard)
     else:
         raise ValueError(f"unknown model: {which}")
 
