@@ -17,6 +17,14 @@ distributed_utils.py:318-332, 488-499) is re-designed for a GPU with 180 GB of H
   (two-phase, exact global norm -- the reference computes a per-rank local norm, SURVEY.md A-4);
 * parameter path (K-C3): after the optimizer step the all-gathers of all units are queued on the comm stream
   in forward order; each unit's forward waits only for its own event, so gathers overlap earlier compute;
+* ``reshard_after_forward=True`` (``run_distributed.py --reshard``, ``HYPERION_FSDP_RESHARD=1``) gives the reference's
+  ``ShardingStrategy.FULL_SHARD`` memory behaviour instead: a unit's gathered parameters live in one of two slot
+  buffers only while the unit computes; they are gathered before its forward (the next unit is prefetched into the
+  other slot), dropped, and gathered again before its backward -- twice the all-gather traffic, parameter memory =
+  1/W shard + two unit-sized slots + the root unit.  Frozen parameters inside such units (the LoRA base weights) are
+  sharded and gathered the same way, so "LoRA under FSDP" shards the 13.5 GB base and not only the adapters.  Units whose
+  module is a leaf that the model code reads without calling it (``nn.Linear`` / ``nn.Embedding`` / norms) and the root
+  parameters stay resident, like FSDP1's root unit;
 * world size 1 degrades to NO_SHARD (no communication kernels at all), as FSDP1 does;
 * gloo / CPU: the same algorithm with ``dist.all_reduce`` / ``dist.all_gather_into_tensor`` (test path).
 """
@@ -81,7 +89,11 @@ class HyperionFSDP(nn.Module):
                  max_norm: float = 0.0, fused: bool | None = None, process_group=None, loss_scaler=None,
                  sync_params: bool = True, fuse_allgather_gemm: bool = True, reshard_after_forward: bool | None = None):
         super().__init__()
-        self.reshard = False
+        import os as _os
+
+        if reshard_after_forward is None:
+            reshard_after_forward = _os.environ.get("HYPERION_FSDP_RESHARD", "0") == "1"
+        self.reshard = bool(reshard_after_forward)
         self.module = module
         self.rank, self.world_size = world()
         self.group = process_group
@@ -90,6 +102,7 @@ class HyperionFSDP(nn.Module):
         p0 = next(p for p in module.parameters() if p.requires_grad)
         self.device = p0.device
         W = self.world_size
+        self.reshard = self.reshard and W > 1
         want_fused = fused if fused is not None else True
         self.fused = bool(want_fused and self.device.type == "cuda" and W > 1)
         self.arena = None
@@ -158,14 +171,18 @@ class HyperionFSDP(nn.Module):
             sp.param.register_post_accumulate_grad_hook(self._make_grad_hook(i))
         for k, um in enumerate(unit_modules):
             um.register_forward_pre_hook(self._make_fwd_hook(k))
+        self._gathers_due = False
+        self._rs_units: list[int] = []
+        if self.reshard:
+            self._setup_reshard(sync_params)
         # ---- K-C3: units whose first consumer is a GEMM on a known weight gather inside that GEMM
         self._ag_handles: dict[int, _AgHandle] = {}
         import os
 
         # HYPERION_FSDP_AG=plain gathers every unit with the stand-alone kernel (queued at the start of the forward, so it
         # overlaps the forward just the same) and leaves the GEMMs on the faster CTA-pair kernel
-        fuse_allgather_gemm = fuse_allgather_gemm and os.environ.get("HYPERION_FSDP_AG", "fused") == "fused"
-        self._gathers_due = False
+        fuse_allgather_gemm = (fuse_allgather_gemm and os.environ.get("HYPERION_FSDP_AG", "fused") == "fused"
+                               and not self.reshard)
         if self.fused and fuse_allgather_gemm and self.flat.dtype in (torch.bfloat16, torch.float16):
             from ..models.transformer import MultiheadSelfAttention
 
@@ -189,11 +206,168 @@ class HyperionFSDP(nn.Module):
         return s // W, e // W
 
     def _copy_local_shards(self, flat_src: torch.Tensor, shard_dst: torch.Tensor) -> None:
+        """``flat_src`` is a full-size flat buffer (flat offsets)."""
         W, r = self.world_size, self.rank
         for ui, (s, e, _) in enumerate(self.units):
             per = (e - s) // W
             a, b = self._shard_range(ui)
             shard_dst[a:b].copy_(flat_src[s + r * per: s + (r + 1) * per].to(shard_dst.dtype))
+
+    # ------------------------------------------------------------------ FULL_SHARD mode (reshard_after_forward)
+    _LEAF_TYPES = (nn.Linear, nn.Embedding, nn.LayerNorm, nn.Conv2d, nn.modules.batchnorm._BatchNorm)
+
+    @staticmethod
+    def _view_at(buf: torch.Tensor, off: int, numel: int, shape, channels_last: bool = False) -> torch.Tensor:
+        flat = buf[off:off + numel]
+        if channels_last:
+            K, C, R, S = shape
+            return flat.view(K, R, S, C).permute(0, 3, 1, 2)
+        return flat.view(shape)
+
+    def _dst(self, ui: int) -> torch.Tensor:
+        """Where unit ``ui``'s full 16-bit parameters live when gathered."""
+        s, e, _ = self.units[ui]
+        if not self.reshard:
+            return self.flat.data[s:e]
+        buf, off = self._unit_base[ui]
+        return buf[off:off + (e - s)]
+
+    @torch.no_grad()
+    def _setup_reshard(self, sync_params: bool) -> None:
+        W, r, dev, dt = self.world_size, self.rank, self.device, self.flat.dtype
+        K = 2
+        # forward order of the units: root first, then decreasing flat offset (the flat buffer is in reverse registration order)
+        order = sorted(range(len(self.units)), key=lambda ui: (self.units[ui][2] != -1, -self.units[ui][0]))
+        self._rs_units = [ui for ui in order if self.units[ui][2] != -1
+                          and not isinstance(self.unit_modules[self.units[ui][2]], self._LEAF_TYPES)]
+        rs = set(self._rs_units)
+        self._rs_pos = {ui: i for i, ui in enumerate(self._rs_units)}
+        self._slot_of = {ui: i % K for i, ui in enumerate(self._rs_units)}
+        self._slot_owner: list = [None] * K
+        max_unit = max((self.units[ui][1] - self.units[ui][0] for ui in self._rs_units), default=0)
+        self._slots = [torch.empty(max_unit, dtype=dt, device=dev) for _ in range(K)] if max_unit else []
+        # resident buffer: root + leaf units, compacted
+        self._unit_base: dict[int, tuple[torch.Tensor, int]] = {}
+        roff = 0
+        for ui in range(len(self.units)):
+            if ui not in rs:
+                self._unit_base[ui] = (None, roff)
+                roff += self.units[ui][1] - self.units[ui][0]
+        self._resident = torch.empty(max(roff, 1), dtype=dt, device=dev)
+        for ui in range(len(self.units)):
+            s, e, _ = self.units[ui]
+            if ui in rs:
+                self._unit_base[ui] = (self._slots[self._slot_of[ui]], 0)
+            else:
+                off = self._unit_base[ui][1]
+                self._unit_base[ui] = (self._resident, off)
+                self._resident[off:off + (e - s)].copy_(self.flat.data[s:e])
+        for i, sp in enumerate(self.flat.specs):
+            ui = self._spec_unit[i]
+            buf, off = self._unit_base[ui]
+            sp.param.data = self._view_at(buf, off + sp.offset - self.units[ui][0], sp.numel, sp.param.shape, sp.channels_last)
+        self.flat.data = torch.empty(0, dtype=dt, device=dev)   # the full-size 16-bit copy is gone
+        # ---- frozen parameters inside reshardable units (LoRA base weights): sharded too
+        self._frozen: dict[int, list] = {}       # ui -> [(name, param, offset in unit, numel)]
+        self._frozen_range: dict[int, tuple[int, int, int]] = {}  # ui -> (shard start, per-rank elems, unit elems)
+        names = {id(p_): n for n, p_ in self.module.named_parameters()}
+        seen: set = set()
+        foff = 0
+        max_f = 0
+        for ui in self._rs_units:
+            um = self.unit_modules[self.units[ui][2]]
+            lst, off = [], 0
+            for p_ in um.parameters():
+                if p_.requires_grad or id(p_) in seen or p_.dtype != dt or p_.device != dev:
+                    continue
+                seen.add(id(p_))
+                lst.append((names.get(id(p_), ""), p_, off, p_.numel()))
+                off += (p_.numel() + 127) // 128 * 128
+            if not lst:
+                continue
+            size = (off + W * 128 - 1) // (W * 128) * (W * 128)
+            self._frozen[ui] = lst
+            self._frozen_range[ui] = (foff, size // W, size)
+            foff += size // W
+            max_f = max(max_f, size)
+        self.fshard16 = None
+        self._fslots = []
+        if self._frozen:
+            alloc16 = self.arena.alloc if self.fused else (lambda n, d, dv: torch.zeros(n, dtype=d, device=dv))
+            self.fshard16 = alloc16(foff, dt, dev)
+            tmp = torch.empty(max_f, dtype=dt, device=dev)
+            for ui, lst in self._frozen.items():
+                fa, per, size = self._frozen_range[ui]
+                tmp.zero_()
+                for _n, p_, off, n in lst:
+                    tmp[off:off + n].copy_(p_.data.reshape(-1))
+                if sync_params:
+                    dist.broadcast(tmp[:size], src=0, group=self.group)
+                self.fshard16[fa:fa + per].copy_(tmp[r * per:(r + 1) * per])
+            del tmp
+            self._fslots = [torch.empty(max_f, dtype=dt, device=dev) for _ in range(K)]
+            for ui, lst in self._frozen.items():
+                slot = self._fslots[self._slot_of[ui]]
+                for _n, p_, off, n in lst:
+                    p_.data = slot[off:off + n].view(p_.shape)
+        if dev.type == "cuda":
+            torch.cuda.synchronize(dev)
+            torch.cuda.empty_cache()
+        for ui in self._rs_units:
+            um = self.unit_modules[self.units[ui][2]]
+            um.register_forward_pre_hook(self._make_rs_hook(ui))
+            um.register_full_backward_pre_hook(self._make_rs_bwd_hook(ui))
+
+    def _gather_unit(self, ui: int) -> None:
+        """All-gather unit ``ui`` (trainable and frozen parts) into its slot; ordered after everything already enqueued on
+        the compute stream, which includes the last use of the slot's previous owner."""
+        a, b = self._shard_range(ui)
+        dst = self._dst(ui)
+        fr = self._frozen_range.get(ui)
+        if self.fused:
+            ev = torch.cuda.Event()
+            ev.record(torch.cuda.current_stream(self.device))
+            self.comm_stream.wait_event(ev)
+            with torch.cuda.stream(self.comm_stream):
+                self.arena.allgather(self.shard16, a, b - a, dst)
+                if fr is not None:
+                    self.arena.allgather(self.fshard16, fr[0], fr[1], self._fslots[self._slot_of[ui]][:fr[2]])
+                gev = torch.cuda.Event()
+                gev.record(self.comm_stream)
+            self._gather_events[ui] = gev
+        else:
+            dist.all_gather_into_tensor(dst, self.shard16[a:b].contiguous(), group=self.group)
+            if fr is not None:
+                dist.all_gather_into_tensor(self._fslots[self._slot_of[ui]][:fr[2]], self.fshard16[fr[0]:fr[0] + fr[1]].contiguous(),
+                                            group=self.group)
+        self.gathers_issued = getattr(self, "gathers_issued", 0) + 1
+
+    def _ensure_unit(self, ui: int, wait: bool) -> None:
+        slot = self._slot_of[ui]
+        if self._slot_owner[slot] != ui:
+            self._slot_owner[slot] = ui
+            self._gather_unit(ui)
+        if wait and self.fused:
+            ev = self._gather_events[ui]
+            if ev is not None:
+                torch.cuda.current_stream(self.device).wait_event(ev)
+
+    def _rs_touch(self, ui: int, backward: bool) -> None:
+        self._ensure_unit(ui, wait=True)
+        nxt = self._rs_pos[ui] + (-1 if backward else 1)
+        if 0 <= nxt < len(self._rs_units):
+            self._ensure_unit(self._rs_units[nxt], wait=False)   # prefetch into the other slot
+
+    def _make_rs_hook(self, ui: int):
+        def hook(_m, _args):
+            # a forward that runs inside backward is an activation-checkpoint recompute: prefetch in backward direction
+            self._rs_touch(ui, backward=torch._C._current_graph_task_id() != -1)
+        return hook
+
+    def _make_rs_bwd_hook(self, ui: int):
+        def hook(_m, _grad_out):
+            self._rs_touch(ui, backward=True)
+        return hook
 
     # ------------------------------------------------------------------ forward: wait for gathered units
     def _make_fwd_hook(self, key: int):
@@ -359,6 +533,8 @@ class HyperionFSDP(nn.Module):
         if self.loss_scaler is not None:
             self.loss_scaler.update()
         self.flat.zero_grad()  # also leaves param.grad undefined so the next backward's kernels write into the slots
+        if self.reshard:
+            self._slot_owner = [None] * len(self._slot_owner)   # the slots hold pre-update parameters now
         if W > 1:
             self._gathers_due = True   # issued at the start of the next forward (see _start_of_forward)
             if self.fused and torch.cuda.is_current_stream_capturing():
@@ -396,13 +572,15 @@ class HyperionFSDP(nn.Module):
             self.comm_stream.wait_event(ev)
             with torch.cuda.stream(self.comm_stream):
                 for ui in order:
+                    if ui in self._slot_of_or_empty():   # FULL_SHARD unit: gathered on demand into its slot
+                        continue
                     if ui in self._ag_handles and not force_plain:  # gathered later, inside the unit's first GEMM (K-C3)
                         self._ag_handles[ui].pending = True
                         self._gather_events[ui] = None
                         continue
                     s, e, _ = self.units[ui]
                     a, b = self._shard_range(ui)
-                    self.arena.allgather(self.shard16, a, b - a, self.flat.data[s:e])
+                    self.arena.allgather(self.shard16, a, b - a, self._dst(ui))
                     gev = torch.cuda.Event()
                     gev.record(self.comm_stream)
                     self._gather_events[ui] = gev
@@ -410,9 +588,13 @@ class HyperionFSDP(nn.Module):
                         self._ag_handles[ui].pending = False
         else:
             for ui in order:
-                s, e, _ = self.units[ui]
+                if ui in self._slot_of_or_empty():
+                    continue
                 a, b = self._shard_range(ui)
-                dist.all_gather_into_tensor(self.flat.data[s:e], self.shard16[a:b].contiguous(), group=self.group)
+                dist.all_gather_into_tensor(self._dst(ui), self.shard16[a:b].contiguous(), group=self.group)
+
+    def _slot_of_or_empty(self) -> dict:
+        return self._slot_of if self.reshard else {}
 
     def zero_grad(self, set_to_none: bool = False) -> None:
         self.flat.zero_grad()
@@ -438,7 +620,7 @@ class HyperionFSDP(nn.Module):
                 if h.pending:
                     s, e, _ = self.units[ui]
                     a, b = self._shard_range(ui)
-                    self.arena.allgather(self.shard16, a, b - a, self.flat.data[s:e])
+                    self.arena.allgather(self.shard16, a, b - a, self._dst(ui))
                     h.pending = False
 
     # ------------------------------------------------------------------ checkpoints (K-C6 / K-C7)
@@ -460,15 +642,23 @@ class HyperionFSDP(nn.Module):
             for q in range(W):
                 full[s + q * per: s + (q + 1) * per] = gathered[q * self.shard_numel + a: q * self.shard_numel + a + per]
         sd = {k: v.detach().clone() for k, v in self.module.state_dict().items()}
-        by_ptr = {sp.param.data_ptr(): sp for sp in self.flat.specs}
-        for name, p in self.module.named_parameters():
-            sp = by_ptr.get(p.data_ptr())
+        by_id = {id(sp.param): sp for sp in self.flat.specs}
+        for name, p in self.module.named_parameters(remove_duplicate=False):   # tied parameters appear under every name
+            sp = by_id.get(id(p))
             if sp is not None and name in sd:
-                sd[name] = full[sp.offset: sp.offset + sp.numel].view(p.shape).clone()
-        for k, v in self.module.state_dict().items():  # tied parameters share storage
-            sp = by_ptr.get(v.data_ptr())
-            if sp is not None:
-                sd[k] = full[sp.offset: sp.offset + sp.numel].view(v.shape).clone()
+                from .flat import shaped_view
+
+                sd[name] = shaped_view(full, sp).clone()
+        if self.reshard and self._frozen:     # sharded frozen parameters (their slots hold whichever unit ran last)
+            F = self.fshard16.numel()
+            gf = torch.empty(W * F, device=self.device, dtype=self.fshard16.dtype)
+            dist.all_gather_into_tensor(gf, self.fshard16.contiguous(), group=self.group)
+            for ui, lst in self._frozen.items():
+                fa, per, size = self._frozen_range[ui]
+                unit = torch.cat([gf[q * F + fa: q * F + fa + per] for q in range(W)])
+                for name, p_, off, n in lst:
+                    if name in sd:
+                        sd[name] = unit[off:off + n].view(p_.shape).clone()
         return sd
 
     def local_shard_state(self) -> dict:
@@ -481,13 +671,63 @@ class HyperionFSDP(nn.Module):
     def load_state_dict(self, sd, strict: bool = True, *a, **kw):
         """Load an unwrapped full state_dict: the resident 16-bit copy, THEN the local 16-bit shard and the fp32 master
         shard (taken from the fp32 values in ``sd`` where present, so no precision is lost through the 16-bit copy)."""
+        if self.reshard:
+            return self._load_state_dict_resharded(sd, strict)
         res = self.module.load_state_dict(sd, strict=strict, *a, **kw)
         self.refresh_shards(sd)
         return res
 
     @torch.no_grad()
+    def _load_state_dict_resharded(self, sd, strict: bool):
+        from .flat import shaped_view
+
+        W, r = self.world_size, self.rank
+        full32 = torch.zeros(self.flat.numel, device=self.device, dtype=torch.float32)
+        handled, missing = set(), []
+        for sp in self.flat.specs:
+            v = sd.get(sp.name)
+            if v is None:
+                missing.append(sp.name)
+                continue
+            shaped_view(full32, sp).copy_(v.to(device=self.device, dtype=torch.float32))
+            handled.add(sp.name)
+        self._copy_local_shards(full32, self.shard16)
+        if self.master is not None:
+            self._copy_local_shards(full32, self.master)
+        for ui in range(len(self.units)):
+            if ui not in self._slot_of:
+                s, e, _ = self.units[ui]
+                self._dst(ui).copy_(full32[s:e].to(self.flat.dtype))
+        del full32
+        for ui, lst in self._frozen.items():
+            fa, per, size = self._frozen_range[ui]
+            tmp = torch.zeros(size, device=self.device, dtype=self.fshard16.dtype)
+            for name, p_, off, n in lst:
+                v = sd.get(name)
+                if v is None:
+                    missing.append(name)
+                    continue
+                tmp[off:off + n].copy_(v.reshape(-1).to(device=self.device, dtype=tmp.dtype))
+                handled.add(name)
+            self.fshard16[fa:fa + per].copy_(tmp[r * per:(r + 1) * per])
+        if strict and missing:
+            raise KeyError(f"state_dict is missing {missing[:5]}{'...' if len(missing) > 5 else ''}")
+        tied = {n for n, p_ in self.module.named_parameters(remove_duplicate=False)
+                if id(p_) in {id(sp.param) for sp in self.flat.specs}}
+        rest = {k: v for k, v in sd.items() if k not in handled and k not in tied}
+        res = self.module.load_state_dict(rest, strict=False)
+        self._slot_owner = [None] * len(self._slot_owner)
+        self._gathers_due = False
+        return res
+
+    @torch.no_grad()
     def refresh_shards(self, sd: dict | None = None) -> None:
         """Re-derive ``shard16`` / ``master`` from the resident parameters (after any weights-only load)."""
+        if self.reshard:
+            if sd is None:
+                raise RuntimeError("FULL_SHARD mode keeps no resident copy to refresh from: pass the state_dict")
+            self._load_state_dict_resharded(sd, strict=False)
+            return
         full32 = self.flat.data.to(torch.float32)
         if sd is not None:
             for sp in self.flat.specs:

@@ -26,8 +26,13 @@ def _worker(rank, world, port, strategy, out):
     dev = setup(rank, world, "gloo", seed=0)
     torch.manual_seed(0)
     model = SimpleTransformerLM(300, 32, 2, 2, 64, dropout=0.0)
+    reshard = strategy == "fsdp_reshard"
+    strategy = "fsdp" if reshard else strategy
     eng = build_engine(model, strategy=strategy, precision="fp32", lr=1e-2, clip=1.0 if strategy == "fsdp" else 0.0,
-                       device=dev, fsdp_min_num_params=2000)
+                       device=dev, fsdp_min_num_params=2000, reshard_after_forward=reshard,
+                       fsdp_units=list(model.tr.layers) if reshard else None)
+    if reshard:
+        assert eng.model.reshard and len(eng.model._rs_units) == 2 and eng.model.flat.data.numel() == 0
     g = torch.Generator().manual_seed(1)
     data = torch.randint(0, 300, (3, 2 * world, 12), generator=g)
     losses = []
@@ -36,6 +41,9 @@ def _worker(rank, world, port, strategy, out):
         loss = eng.model.loss(b[:, :-1].contiguous(), b[:, 1:].contiguous())
         eng.backward_and_step(loss)
         losses.append(float(loss.detach()))
+    if reshard:
+        # every step gathers each layer for forward; backward finds both layers still in their slots (2 slots, 2 layers)
+        assert eng.model.gathers_issued == 3 * 2, eng.model.gathers_issued
     from hyperion_b200.utils.checkpoint import full_state_dict
 
     sd = full_state_dict(eng.model)
@@ -58,13 +66,13 @@ def _single(strategy):
         # mean of the two rank-local mean losses == what DDP / FSDP average
         loss = 0.5 * (model.loss(b[:2, :-1].contiguous(), b[:2, 1:].contiguous()) + model.loss(b[2:, :-1].contiguous(), b[2:, 1:].contiguous()))
         loss.backward()
-        if strategy == "fsdp":
+        if strategy.startswith("fsdp"):
             torch.nn.utils.clip_grad_norm_(model.parameters(), 1.0)
         opt.step()
     return model.state_dict()
 
 
-@pytest.mark.parametrize("strategy", ["ddp", "fsdp"])
+@pytest.mark.parametrize("strategy", ["ddp", "fsdp", "fsdp_reshard"])
 def test_gloo_world2_matches_single_process(tmp_path, strategy):
     out = str(tmp_path / "r0.pt")
     mp.spawn(_worker, args=(2, _free_port(), strategy, out), nprocs=2, join=True)
@@ -79,3 +87,95 @@ def test_gloo_world2_matches_single_process(tmp_path, strategy):
             e = a.numel() // 3
             a, b = torch.cat([a[:e], a[2 * e:]]), torch.cat([b[:e], b[2 * e:]])
         assert torch.allclose(a, b, atol=1e-4, rtol=1e-3), k
+
+
+def _lora_worker(rank, world, port, reshard, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    from hyperion_b200.lora import inject_lora
+    from hyperion_b200.models import LlamaConfig, LlamaForCausalLM
+    from hyperion_b200.models.llama import LlamaDecoderLayer
+    from hyperion_b200.parallel.runtime import cleanup, setup
+    from hyperion_b200.train.engine import build_engine
+    from hyperion_b200.utils.checkpoint import full_state_dict
+
+    torch.set_num_threads(1)
+    dev = setup(rank, world, "gloo", seed=0)
+    torch.manual_seed(0)
+    cfg = LlamaConfig.tiny()
+    cfg.num_hidden_layers = 3
+    model = LlamaForCausalLM(cfg)
+    inject_lora(model, r=4, alpha=8, dropout=0.0)
+    units = [m for m in model.modules() if isinstance(m, LlamaDecoderLayer)]
+    eng = build_engine(model, strategy="fsdp", precision="fp32", lr=1e-2, clip=1.0, device=dev, fsdp_units=units,
+                       reshard_after_forward=reshard)
+    if reshard:
+        f = eng.model
+        assert f.reshard and len(f._rs_units) == 3 and f._frozen and f.fshard16 is not None
+        # the frozen base of the layers lives in two slots + a 1/W shard, not in 3 full copies
+        per_layer = sum(p.numel() for p in units[0].parameters() if not p.requires_grad)
+        assert f.fshard16.numel() * world >= 3 * per_layer and f._fslots[0].numel() >= per_layer
+    g = torch.Generator().manual_seed(1)
+    data = torch.randint(0, cfg.vocab_size, (4, 2 * world, 16), generator=g)
+    losses = []
+    for step in range(4):
+        b = data[step, rank * 2:(rank + 1) * 2]
+        loss = eng.model(input_ids=b, labels=b.clone()).loss
+        eng.backward_and_step(loss)
+        losses.append(float(loss.detach()))
+    sd = full_state_dict(eng.model)
+    if rank == 0:
+        torch.save({"sd": sd, "losses": losses}, out)
+    cleanup()
+
+
+def test_gloo_lora_fsdp_reshard_shards_frozen_base(tmp_path):
+    """FULL_SHARD mode (reshard_after_forward) with LoRA: the frozen base weights are sharded and gathered per layer; the
+    run must match the params-resident mode step for step and export the same full state_dict."""
+    outs = []
+    for reshard in (False, True):
+        out = str(tmp_path / f"r{int(reshard)}.pt")
+        mp.spawn(_lora_worker, args=(2, _free_port(), reshard, out), nprocs=2, join=True)
+        outs.append(torch.load(out, weights_only=False))
+    a, b = outs
+    assert a["losses"][-1] < a["losses"][0]
+    assert torch.allclose(torch.tensor(a["losses"]), torch.tensor(b["losses"]), atol=1e-5), (a["losses"], b["losses"])
+    assert set(a["sd"]) == set(b["sd"])
+    for k in a["sd"]:
+        assert torch.allclose(a["sd"][k], b["sd"][k], atol=1e-5), k
+
+
+def _resume_worker(rank, world, port, base, phase, strategy):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    import glob
+
+    from hyperion_b200 import train
+
+    torch.set_num_threads(1)
+    kw = dict(backend="gloo", precision="fp32", synthetic=True, rows=32, batch_size=4, seed=0, save=True,
+              model_kwargs=dict(emb_dim=32, n_heads=2, n_layers=1, dim_feedforward=64, dropout=0.0), vocab_size=300, pad_id=299)
+    fn = train.train_language_model_ddp if strategy == "ddp" else train.train_language_model_fsdp
+    if strategy == "fsdp":
+        kw["min_num_params"] = 2000
+    if phase == "full":
+        hist = fn(rank, world, epochs=3, base_dir=os.path.join(base, "full"), **kw)
+    elif phase == "first":
+        hist = fn(rank, world, epochs=2, base_dir=os.path.join(base, "part"), **kw)
+    else:
+        state = sorted(glob.glob(os.path.join(base, "part", "data/distributed/*_train_state.pt")))[-1]
+        hist = fn(rank, world, epochs=3, base_dir=os.path.join(base, "part"), resume=state, **kw)
+    if rank == 0:
+        torch.save(hist, os.path.join(base, f"hist_{phase}.pt"))
+
+
+@pytest.mark.parametrize("strategy", ["ddp", "fsdp"])
+def test_gloo_kill_and_resume_reproduces_the_loss_curve(tmp_path, strategy):
+    """Three epochs in one go == two epochs, process exit, ``resume=<train_state.pt>`` in fresh processes for the third
+    (weights, fp32 master, optimizer moments -- sharded per rank under FSDP -- and epoch are restored)."""
+    base = str(tmp_path)
+    for phase in ("full", "first", "resume"):
+        mp.spawn(_resume_worker, args=(2, _free_port(), base, phase, strategy), nprocs=2, join=True)
+    full = torch.load(os.path.join(base, "hist_full.pt"))
+    first = torch.load(os.path.join(base, "hist_first.pt"))
+    resumed = torch.load(os.path.join(base, "hist_resume.pt"))
+    assert len(full) == 3 and len(first) == 2 and len(resumed) == 1
+    assert abs(full[2] - resumed[0]) < 1e-4 * max(1.0, abs(full[2])), (full, first, resumed)
