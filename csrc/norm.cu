@@ -10,6 +10,7 @@
 // Reference call sites: nn.LayerNorm inside nn.TransformerEncoderLayer
 // (02_development/distributed_utils.py:79; post-norm with residual) and the
 // HF LlamaRMSNorm reached through distributed_utils.py:465.
+#include <atomic>
 #include "common/ptx.cuh"
 #include "common/util.cuh"
 
@@ -539,19 +540,21 @@ HYP_API int hyp_norm_bwd_fused(const void* dy, const void* z, const void* gamma,
 namespace hyp { namespace norm {
 constexpr long long kNoAllocScratchBytes = 8ll << 20;
 static __device__ __align__(256) unsigned char g_bwd_scratch[kNoAllocScratchBytes];
-// device address of g_bwd_scratch per device ordinal; the symbol itself is only a host-side stand-in
-static void* g_bwd_scratch_addr[64] = {nullptr};
+// device address of g_bwd_scratch per device ordinal; the symbol itself is only a host-side stand-in.  Two host threads
+// making their first call on one device at the same time both look the address up and store the same value, hence atomics
+// (relaxed is enough: the value is a constant of the device).
+static std::atomic<void*> g_bwd_scratch_addr[64];
 
 static int resolve_scratch(float** out) {
   int dev = 0;
   HYP_CHECK_CUDA(cudaGetDevice(&dev));
   HYP_REQUIRE(dev >= 0 && dev < 64, "hyp_norm_bwd_noalloc: device ordinal %d out of range", dev);
-  if (g_bwd_scratch_addr[dev] == nullptr) {
-    void* p = nullptr;
+  void* p = g_bwd_scratch_addr[dev].load(std::memory_order_relaxed);
+  if (p == nullptr) {
     HYP_CHECK_CUDA(cudaGetSymbolAddress(&p, g_bwd_scratch));
-    g_bwd_scratch_addr[dev] = p;
+    g_bwd_scratch_addr[dev].store(p, std::memory_order_relaxed);
   }
-  *out = reinterpret_cast<float*>(g_bwd_scratch_addr[dev]);
+  *out = reinterpret_cast<float*>(p);
   return 0;
 }
 }}  // namespace hyp::norm

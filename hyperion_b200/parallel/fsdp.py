@@ -443,6 +443,9 @@ class HyperionFSDP(nn.Module):
         return 1.0 / self.world_size
 
     def _reduce_unit(self, ui: int) -> None:
+        from ..utils import nvtx
+
+        nvtx.mark(f"hyperion/comm/reduce_scatter unit {ui}")
         s, e, _ = self.units[ui]
         W = self.world_size
         per = (e - s) // W

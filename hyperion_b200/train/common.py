@@ -106,7 +106,10 @@ class StepRunner:
         self.replays = 0
 
     def _eager(self, batch):
-        out = self.loss_fn(batch)
+        from ..utils import nvtx
+
+        with nvtx.range("hyperion/forward"):
+            out = self.loss_fn(batch)
         loss = out[0] if isinstance(out, (tuple, list)) else out
         self.eng.backward_and_step(loss)
         return tuple(t.detach() for t in out) if isinstance(out, (tuple, list)) else loss.detach()
@@ -135,4 +138,7 @@ class StepRunner:
         if shapes != self.shapes:
             return self._eager(batch)
         self.replays += 1
-        return self.graphed(batch)
+        from ..utils import nvtx
+
+        with nvtx.range("hyperion/graph_replay"):
+            return self.graphed(batch)

@@ -20,6 +20,7 @@ from ..parallel.ddp import HyperionDDP
 from ..parallel.flat import FlatParams
 from ..parallel.fsdp import HyperionFSDP
 from ..parallel.runtime import world
+from ..utils import nvtx
 
 
 def cast_trainable(model: nn.Module, dtype: torch.dtype) -> nn.Module:
@@ -44,10 +45,16 @@ class Engine:
 
     def backward_and_step(self, loss: torch.Tensor) -> None:
         scaler = self.scaler
-        (scaler.scale_loss(loss) if scaler is not None else loss).backward()
+        with nvtx.range("hyperion/backward+comm"):   # reduce-scatter / all-reduce kernels fire from autograd hooks in here
+            (scaler.scale_loss(loss) if scaler is not None else loss).backward()
         if self.strategy == "fsdp":
-            self.model.step()
+            with nvtx.range("hyperion/optimizer(fsdp)"):
+                self.model.step()
             return
+        with nvtx.range("hyperion/optimizer"):
+            self._optimizer_phase(scaler)
+
+    def _optimizer_phase(self, scaler) -> None:
         inv_scale = found_inf = sumsq = None
         fused_ddp = self.strategy == "ddp" and getattr(self.model, "fused", False)
         if scaler is not None and scaler.enabled:

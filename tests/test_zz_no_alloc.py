@@ -75,7 +75,16 @@ def _case(lib, rows, d, dtype, rms, seed):
                                   DT[dtype], 0, st)
     assert rc == 0, lib.hyp_last_error()
     torch.cuda.synchronize()
-    return (dz0, dg0, None if rms else db0), (dz1, dg1, None if rms else db1)
+    # fp32 oracle of the same op (plain PyTorch autograd on upcast inputs)
+    xf = x.float().requires_grad_(True)
+    gf, bf = g.float().requires_grad_(True), b.float().requires_grad_(True)
+    if rms:
+        yo = xf * torch.rsqrt(xf.pow(2).mean(-1, keepdim=True) + 1e-5) * gf
+    else:
+        yo = torch.nn.functional.layer_norm(xf, (d,), gf, bf, 1e-5)
+    yo.backward(dy.float())
+    oracle = (xf.grad, gf.grad, None if rms else bf.grad)
+    return (dz0, dg0, None if rms else db0), (dz1, dg1, None if rms else db1), oracle
 
 
 def _rel(a, b):
@@ -87,18 +96,25 @@ def _rel(a, b):
 def test_noalloc_matches_existing_entry_point_two_calls_in_a_row(lib, dtype):
     tol = 2e-2 if dtype == torch.bfloat16 else 1e-5  # the tolerances of tests/test_gpu_kernels.py
     assert lib.hyp_norm_bwd_noalloc_max_scratch_bytes() == 8 << 20
+
+    def check(ref, got, oracle):
+        # dz is computed row by row with no cross-block arithmetic: both entry points run the same code on the same
+        # inputs, so it must agree bit for bit.  dgamma / dbeta are fp32 atomic accumulations over row blocks (order
+        # varies from run to run), so they agree to rounding of an fp32 sum, far inside the suite's tolerance.
+        assert torch.equal(got[0], ref[0])
+        for r, o in zip(ref[1:], got[1:]):
+            if r is not None:
+                assert _rel(o, r) < 1e-5
+        for want, o in zip(oracle, got):
+            if want is not None:
+                assert _rel(o, want) < tol
+
     # call 1: a big LayerNorm problem fills a large part of the built-in array
-    ref, got = _case(lib, 8192, 1024, dtype, rms=False, seed=11)
-    for r, o in zip(ref, got):
-        assert _rel(o, r) < tol
+    check(*_case(lib, 8192, 1024, dtype, rms=False, seed=11))
     # call 2, straight after: smaller RMSNorm problem; stale partial sums from call 1 must not leak in
-    ref, got = _case(lib, 333, 256, dtype, rms=True, seed=12)
-    for r, o in zip(ref[:2], got[:2]):
-        assert _rel(o, r) < tol
+    check(*_case(lib, 333, 256, dtype, rms=True, seed=12))
     # and a wide row (one block per row path)
-    ref, got = _case(lib, 64, 4096, dtype, rms=False, seed=13)
-    for r, o in zip(ref, got):
-        assert _rel(o, r) < tol
+    check(*_case(lib, 64, 4096, dtype, rms=False, seed=13))
 
 
 def test_noalloc_rejects_shapes_beyond_builtin_scratch(lib):
