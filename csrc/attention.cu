@@ -18,6 +18,7 @@
 // Reference call sites: nn.MultiheadAttention inside nn.TransformerEncoderLayer (02_development/
 // distributed_utils.py:79; the reference ran the *math* SDPA path that materialises the scores)
 // and HF Llama SDPA with causal + padding mask (distributed_utils.py:465).
+#include "common/philox.cuh"
 #include "common/ptx.cuh"
 #include "common/tmap.cuh"
 #include "common/util.cuh"
@@ -38,6 +39,7 @@ struct FwdParams {
   long long o_sb, o_sh, o_ss;
   float* lse;                // [B, H, Sq] natural-log LSE, or null
   int dtype;
+  DropoutArgs drop;          // dropout on the attention probabilities (state == nullptr: none)
 };
 
 template <int D>
@@ -92,7 +94,7 @@ __device__ __forceinline__ float fwd_chunk_exp(const uint32_t (&v)[32], float (&
   return l2.x + l2.y;
 }
 
-template <typename T, int D>
+template <typename T, int D, bool DROP>
 __global__ void __launch_bounds__(THREADS, (D == 64) ? 2 : 1)
 flash_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                  const __grid_constant__ CUtensorMap tmV, const __grid_constant__ FwdParams p) {
@@ -212,6 +214,8 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
 #pragma unroll
     for (int i = 0; i < D; ++i) o_acc[i] = 0.f;
     float m_run = -INFINITY, l_run = 0.f;
+    uint2 dkey = make_uint2(0u, 0u);
+    if constexpr (DROP) dkey = dropout_key(p.drop.state);
     for (int j = 0; j < nblk; ++j) {
       const int k0 = j * BKV;
       const bool need_mask = (k0 + BKV > p.Sk) || (p.causal && (k0 + BKV - 1 > q0 + shift)) || (p.kpm != nullptr);
@@ -249,6 +253,14 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
         if (!need_mask) l_blk += fwd_chunk_exp<false, false>(v, pr, p.scale_log2, neg_m, 0, 0, nullptr);
         else if (p.kpm) l_blk += fwd_chunk_exp<true, true>(v, pr, p.scale_log2, neg_m, k0 + c * 32, k_limit, s_kpm + c * 32);
         else l_blk += fwd_chunk_exp<true, false>(v, pr, p.scale_log2, neg_m, k0 + c * 32, k_limit, nullptr);
+        if constexpr (DROP) {
+          // the row sum above is of the un-dropped probabilities (softmax normalisation); dropped entries contribute
+          // nothing to O, survivors are rescaled once at the end through inv_l
+          const uint32_t km = dropout_keep32(dkey, p.drop.salt, static_cast<uint32_t>(k0 + c * 32), static_cast<uint32_t>(qi),
+                                             static_cast<uint32_t>(b * p.H + h), p.drop.thresh);
+#pragma unroll
+          for (int i = 0; i < 32; ++i) pr[i] = ((km >> i) & 1u) ? pr[i] : 0.f;
+        }
         uint8_t* prow = sP + (c >> 1) * 16384 + r * 128;
 #pragma unroll
         for (int t = 0; t < 4; ++t) {
@@ -284,7 +296,7 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
       tc_fence_before();
     }
     if (qi < p.Sq) {
-      const float inv_l = l_run > 0.f ? 1.f / l_run : 0.f;
+      const float inv_l = (l_run > 0.f ? 1.f / l_run : 0.f) * (DROP ? p.drop.scale : 1.f);
       T* orow = reinterpret_cast<T*>(p.o) + b * p.o_sb + h * p.o_sh + static_cast<long long>(qi) * p.o_ss;
 #pragma unroll
       for (int g = 0; g < D / 8; ++g) {
@@ -313,20 +325,25 @@ static int make_qkv_map(CUtensorMap* tm, const void* ptr, int dtype, int B, int 
   return make_tmap_nd(tm, ptr, dtype, 4, dims, strides, box);
 }
 
-template <typename T, int D>
-static int launch_fwd(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const FwdParams& p, cudaStream_t st) {
+template <typename T, int D, bool DROP>
+static int launch_fwd_t(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const FwdParams& p, cudaStream_t st) {
   using L = Smem<D>;
   static bool attr_set[64] = {false};
   int dev = 0;
   cudaGetDevice(&dev);
   if (!attr_set[dev & 63]) {
-    HYP_CHECK_CUDA(cudaFuncSetAttribute(flash_fwd_kernel<T, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
+    HYP_CHECK_CUDA(cudaFuncSetAttribute(flash_fwd_kernel<T, D, DROP>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
     attr_set[dev & 63] = true;
   }
   dim3 grid(static_cast<unsigned>((p.Sq + BQ - 1) / BQ) * p.H * p.B);
-  flash_fwd_kernel<T, D><<<grid, THREADS, L::TOTAL, st>>>(tq, tk, tv, p);
+  flash_fwd_kernel<T, D, DROP><<<grid, THREADS, L::TOTAL, st>>>(tq, tk, tv, p);
   HYP_CHECK_CUDA(cudaGetLastError());
   return 0;
+}
+// the dropout instantiation is a separate kernel, so the plain one carries none of its registers
+template <typename T, int D>
+static int launch_fwd(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const FwdParams& p, cudaStream_t st) {
+  return p.drop.state ? launch_fwd_t<T, D, true>(tq, tk, tv, p, st) : launch_fwd_t<T, D, false>(tq, tk, tv, p, st);
 }
 
 }  // namespace attn
@@ -335,11 +352,25 @@ static int launch_fwd(const CUtensorMap& tq, const CUtensorMap& tk, const CUtens
 using namespace hyp;
 
 // q/k/v/o are indexed [b, h, s, d] through element strides (unit stride in d); see include/hyperion_b200.h.
-HYP_API int hyp_flash_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse, int B, int H, int Sq, int Sk,
+namespace hyp { namespace attn {
+// p in (0, 1) -> 8-bit threshold and survivor scale (see common/philox.cuh); p == 0 or a null state -> no dropout
+static int make_dropout(DropoutArgs* d, const unsigned long long* state, unsigned salt, float p, const char* who) {
+  d->state = nullptr; d->salt = salt; d->thresh = 0; d->scale = 1.f;
+  if (state == nullptr || p <= 0.f) return 0;
+  HYP_REQUIRE(p < 1.f, "%s: dropout probability must be in [0, 1) (got %f)", who, p);
+  int t = static_cast<int>(p * 256.f + 0.5f);
+  t = t < 1 ? 1 : (t > 255 ? 255 : t);
+  d->state = state; d->thresh = static_cast<unsigned>(t); d->scale = 256.f / static_cast<float>(256 - t);
+  return 0;
+}
+}}  // namespace hyp::attn
+
+static int flash_attn_fwd_impl(const void* q, const void* k, const void* v, void* o, float* lse, int B, int H, int Sq, int Sk,
                                int D, long long q_sb, long long q_sh, long long q_ss, long long k_sb, long long k_sh,
                                long long k_ss, long long v_sb, long long v_sh, long long v_ss, long long o_sb,
                                long long o_sh, long long o_ss, const unsigned char* key_padding_mask, int causal,
-                               float scale, int dtype, void* stream_) {
+                               float scale, int dtype, const unsigned long long* rng_state, unsigned salt, float dropout_p,
+                               void* stream_) {
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
   HYP_REQUIRE(dtype == DT_F16 || dtype == DT_BF16, "hyp_flash_attn_fwd: 16-bit dtypes only");
   HYP_REQUIRE(D == 64 || D == 128, "hyp_flash_attn_fwd: head dim must be 64 or 128 (got %d)", D);
@@ -356,8 +387,31 @@ HYP_API int hyp_flash_attn_fwd(const void* q, const void* k, const void* v, void
   p.scale_log2 = scale * attn::LOG2E;
   p.kpm = key_padding_mask;
   p.o = o; p.o_sb = o_sb; p.o_sh = o_sh; p.o_ss = o_ss; p.lse = lse; p.dtype = dtype;
+  if ((rc = attn::make_dropout(&p.drop, rng_state, salt, dropout_p, "hyp_flash_attn_fwd_drop"))) return rc;
   if (dtype == DT_BF16) return D == 64 ? attn::launch_fwd<__nv_bfloat16, 64>(tq, tk, tv, p, st) : attn::launch_fwd<__nv_bfloat16, 128>(tq, tk, tv, p, st);
   return D == 64 ? attn::launch_fwd<__half, 64>(tq, tk, tv, p, st) : attn::launch_fwd<__half, 128>(tq, tk, tv, p, st);
+}
+
+HYP_API int hyp_flash_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse, int B, int H, int Sq, int Sk,
+                               int D, long long q_sb, long long q_sh, long long q_ss, long long k_sb, long long k_sh,
+                               long long k_ss, long long v_sb, long long v_sh, long long v_ss, long long o_sb,
+                               long long o_sh, long long o_ss, const unsigned char* key_padding_mask, int causal,
+                               float scale, int dtype, void* stream_) {
+  return flash_attn_fwd_impl(q, k, v, o, lse, B, H, Sq, Sk, D, q_sb, q_sh, q_ss, k_sb, k_sh, k_ss, v_sb, v_sh, v_ss, o_sb, o_sh,
+                             o_ss, key_padding_mask, causal, scale, dtype, nullptr, 0u, 0.f, stream_);
+}
+
+// Same, with dropout on the attention probabilities: rng_state -> device [seed, step] (see common/philox.cuh), salt
+// identifies this call within the step; the backward must be given the same three values.
+HYP_API int hyp_flash_attn_fwd_drop(const void* q, const void* k, const void* v, void* o, float* lse, int B, int H, int Sq,
+                                    int Sk, int D, long long q_sb, long long q_sh, long long q_ss, long long k_sb,
+                                    long long k_sh, long long k_ss, long long v_sb, long long v_sh, long long v_ss,
+                                    long long o_sb, long long o_sh, long long o_ss, const unsigned char* key_padding_mask,
+                                    int causal, float scale, int dtype, const unsigned long long* rng_state, int salt,
+                                    float dropout_p, void* stream_) {
+  return flash_attn_fwd_impl(q, k, v, o, lse, B, H, Sq, Sk, D, q_sb, q_sh, q_ss, k_sb, k_sh, k_ss, v_sb, v_sh, v_ss, o_sb, o_sh,
+                             o_ss, key_padding_mask, causal, scale, dtype, rng_state, static_cast<unsigned>(salt), dropout_p,
+                             stream_);
 }
 
 // =====================================================================================================
@@ -383,6 +437,7 @@ struct BwdParams {
   void* dk; void* dv;  // element strides below (unit stride in D)
   long long dk_sb, dk_sh, dk_ss, dv_sb, dv_sh, dv_ss;
   int dtype;
+  DropoutArgs drop;    // the forward's dropout (state, salt, thresh): the mask is regenerated, never stored
 };
 
 template <int D>
@@ -398,7 +453,7 @@ struct BwdSmem {
   static constexpr int TOTAL = BAR_OFF + 384 + 1024;
 };
 
-template <typename T, int D>
+template <typename T, int D, bool DROP>
 __global__ void __launch_bounds__(THREADS, 1)
 flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                  const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmDO,
@@ -538,6 +593,8 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
       named_bar_sync(1, 128);
     }
     const long long bh = static_cast<long long>(b) * p.H + h;
+    uint2 dkey = make_uint2(0u, 0u);
+    if constexpr (DROP) dkey = dropout_key(p.drop.state);
     for (int it = 0; it < niter; ++it) {
       const int q0 = (i_start + it) * BQ;
       const int qi = q0 + r;
@@ -558,6 +615,11 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
         tmem_ld_32x32(tDP + lane_off + c * 32, vd);
         tmem_ld_wait();
         float pr[32], ds[32];
+        uint32_t km = 0xFFFFFFFFu;
+        if constexpr (DROP)
+          km = dropout_keep32(dkey, p.drop.salt, static_cast<uint32_t>(k0 + c * 32), static_cast<uint32_t>(qi),
+                              static_cast<uint32_t>(bh), p.drop.thresh);
+        const float ksc = DROP ? p.drop.scale : 1.f;
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
           bool ok = !dead;
@@ -567,8 +629,15 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
             if (p.kpm) ok = ok & (s_kpm[c * 32 + i] != 0);
           }
           const float pv = ok ? ex2_fast(fmaf(__uint_as_float(vs[i]), p.scale_log2, -lse2)) : 0.f;
-          pr[i] = pv;
-          ds[i] = pv * (__uint_as_float(vd[i]) - delta) * p.scale;
+          // with dropout: dV takes the dropped/rescaled P, and dP = mask * scale * (dO V^T)
+          if constexpr (DROP) {
+            const float mk = ((km >> i) & 1u) ? ksc : 0.f;
+            pr[i] = pv * mk;
+            ds[i] = pv * (__uint_as_float(vd[i]) * mk - delta) * p.scale;
+          } else {
+            pr[i] = pv;
+            ds[i] = pv * (__uint_as_float(vd[i]) - delta) * p.scale;
+          }
         }
         uint8_t* prow = sP + (c >> 1) * 16384 + r * 128;
         uint8_t* drow = sDS + (c >> 1) * 16384 + r * 128;
@@ -669,11 +738,11 @@ struct Bwd64Smem {
 };
 
 // One 32-column chunk of a query row: P and dS from S and dP.  lse2 is +inf for rows that must produce zeros.
-template <typename T, bool MASK>
+template <typename T, bool MASK, bool DROP = false>
 __device__ __forceinline__ void bwd_softmax_chunk(const uint32_t (&vs)[32], const uint32_t (&vd)[32], uint8_t* prow,
                                                   uint8_t* drow, int chunk_in_row, int r, float scale_log2, float scale,
                                                   float lse2, float delta_s, int kcol0, int k_limit,
-                                                  const uint8_t* s_kpm_chunk) {
+                                                  const uint8_t* s_kpm_chunk, uint32_t keep = 0xFFFFFFFFu, float ksc = 1.f) {
   const float2 sc2 = splat2(scale_log2), nl2 = splat2(-lse2), s2 = splat2(scale), nd2 = splat2(-delta_s);
 #pragma unroll
   for (int t = 0; t < 4; ++t) {
@@ -689,9 +758,18 @@ __device__ __forceinline__ void bwd_softmax_chunk(const uint32_t (&vs)[32], cons
         x.y = ok1 ? x.y : -INFINITY;
       }
       const float2 pv = make_float2(ex2_fast(x.x), ex2_fast(x.y));
-      const float2 ds = fmul2(pv, ffma2(make_float2(__uint_as_float(vd[e]), __uint_as_float(vd[e + 1])), s2, nd2));
-      f[i] = pv.x; f[i + 1] = pv.y;
-      g[i] = ds.x; g[i + 1] = ds.y;
+      if constexpr (DROP) {
+        // dV takes the dropped / rescaled P; dP = mask * keep_scale * (dO V^T)
+        const float2 mk = make_float2(((keep >> e) & 1u) ? ksc : 0.f, ((keep >> (e + 1)) & 1u) ? ksc : 0.f);
+        const float2 ds = fmul2(pv, ffma2(fmul2(make_float2(__uint_as_float(vd[e]), __uint_as_float(vd[e + 1])), mk), s2, nd2));
+        const float2 pd = fmul2(pv, mk);
+        f[i] = pd.x; f[i + 1] = pd.y;
+        g[i] = ds.x; g[i + 1] = ds.y;
+      } else {
+        const float2 ds = fmul2(pv, ffma2(make_float2(__uint_as_float(vd[e]), __uint_as_float(vd[e + 1])), s2, nd2));
+        f[i] = pv.x; f[i + 1] = pv.y;
+        g[i] = ds.x; g[i + 1] = ds.y;
+      }
     }
     const int cc = (chunk_in_row * 4 + t) ^ (r & 7);
     *reinterpret_cast<uint4*>(prow + (cc << 4)) = pack8<T>(f);
@@ -699,7 +777,7 @@ __device__ __forceinline__ void bwd_softmax_chunk(const uint32_t (&vs)[32], cons
   }
 }
 
-template <typename T>
+template <typename T, bool DROP>
 __global__ void __launch_bounds__(BWD64_THREADS, 1)
 flash_bwd64_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                    const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmDO,
@@ -852,6 +930,8 @@ flash_bwd64_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       named_bar_sync(1, 256);
     }
     const long long bh = static_cast<long long>(b) * p.H + h;
+    uint2 dkey = make_uint2(0u, 0u);
+    if constexpr (DROP) dkey = dropout_key(p.drop.state);
     auto drain_dq = [&](int it_prev) {
       const int qi = (i_start + it_prev) * BQ + r;
       mbar_wait(dq_full, it_prev & 1);
@@ -900,7 +980,19 @@ flash_bwd64_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       tmem_ld_wait();
       tc_fence_before();
       mbar_arrive(sdp_read);
-      if (need_mask) {
+      if constexpr (DROP) {
+        int k_limit = p.Sk;
+        if (p.causal) k_limit = min(k_limit, qi + shift + 1);
+        const int col = half * 64;
+        const uint32_t km0 = dropout_keep32(dkey, p.drop.salt, static_cast<uint32_t>(k0 + col), static_cast<uint32_t>(qi),
+                                            static_cast<uint32_t>(bh), p.drop.thresh);
+        const uint32_t km1 = dropout_keep32(dkey, p.drop.salt, static_cast<uint32_t>(k0 + col + 32), static_cast<uint32_t>(qi),
+                                            static_cast<uint32_t>(bh), p.drop.thresh);
+        bwd_softmax_chunk<T, true, true>(vs0, vd0, prow, drow, 0, r, p.scale_log2, p.scale, lse2, delta_s, k0 + col, k_limit,
+                                         p.kpm ? s_kpm + col : nullptr, km0, p.drop.scale);
+        bwd_softmax_chunk<T, true, true>(vs1, vd1, prow, drow, 1, r, p.scale_log2, p.scale, lse2, delta_s, k0 + col + 32,
+                                         k_limit, p.kpm ? s_kpm + col + 32 : nullptr, km1, p.drop.scale);
+      } else if (need_mask) {
         int k_limit = p.Sk;
         if (p.causal) k_limit = min(k_limit, qi + shift + 1);
         const int col = half * 64;
@@ -952,21 +1044,26 @@ flash_bwd64_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
   if (warp == 1) tmem_dealloc<512>(tmem_base);
 }
 
-template <typename T>
-static int launch_bwd64(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const CUtensorMap& tdo,
-                        const BwdParams& p, cudaStream_t st) {
+template <typename T, bool DROP>
+static int launch_bwd64_t(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const CUtensorMap& tdo,
+                          const BwdParams& p, cudaStream_t st) {
   using L = Bwd64Smem;
   static bool attr_set[64] = {false};
   int dev = 0;
   cudaGetDevice(&dev);
   if (!attr_set[dev & 63]) {
-    HYP_CHECK_CUDA(cudaFuncSetAttribute(flash_bwd64_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
+    HYP_CHECK_CUDA(cudaFuncSetAttribute(flash_bwd64_kernel<T, DROP>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
     attr_set[dev & 63] = true;
   }
   dim3 grid(static_cast<unsigned>((p.Sk + BKV - 1) / BKV) * p.H * p.B);
-  flash_bwd64_kernel<T><<<grid, BWD64_THREADS, L::TOTAL, st>>>(tq, tk, tv, tdo, p);
+  flash_bwd64_kernel<T, DROP><<<grid, BWD64_THREADS, L::TOTAL, st>>>(tq, tk, tv, tdo, p);
   HYP_CHECK_CUDA(cudaGetLastError());
   return 0;
+}
+template <typename T>
+static int launch_bwd64(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const CUtensorMap& tdo,
+                        const BwdParams& p, cudaStream_t st) {
+  return p.drop.state ? launch_bwd64_t<T, true>(tq, tk, tv, tdo, p, st) : launch_bwd64_t<T, false>(tq, tk, tv, tdo, p, st);
 }
 
 // delta[b,h,q] = sum_d dO[b,h,q,d] * O[b,h,q,d]; D/8 adjacent lanes share a row (one 16-byte load of each operand per
@@ -1023,21 +1120,27 @@ dq_convert_kernel(const float* __restrict__ acc, T* __restrict__ dq, int B, int 
   *reinterpret_cast<uint4*>(dq + b * sb + h * sh + static_cast<long long>(s) * ss + c) = pack8<T>(f);
 }
 
-template <typename T, int D>
-static int launch_bwd(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const CUtensorMap& tdo,
+template <typename T, int D, bool DROP>
+static int launch_bwd_t(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const CUtensorMap& tdo,
                       const BwdParams& p, cudaStream_t st) {
   using L = BwdSmem<D>;
   static bool attr_set[64] = {false};
   int dev = 0;
   cudaGetDevice(&dev);
   if (!attr_set[dev & 63]) {
-    HYP_CHECK_CUDA(cudaFuncSetAttribute(flash_bwd_kernel<T, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
+    HYP_CHECK_CUDA(cudaFuncSetAttribute(flash_bwd_kernel<T, D, DROP>, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
     attr_set[dev & 63] = true;
   }
   dim3 grid(static_cast<unsigned>((p.Sk + BKV - 1) / BKV) * p.H * p.B);
-  flash_bwd_kernel<T, D><<<grid, THREADS, L::TOTAL, st>>>(tq, tk, tv, tdo, p);
+  flash_bwd_kernel<T, D, DROP><<<grid, THREADS, L::TOTAL, st>>>(tq, tk, tv, tdo, p);
   HYP_CHECK_CUDA(cudaGetLastError());
   return 0;
+}
+
+template <typename T, int D>
+static int launch_bwd(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const CUtensorMap& tdo,
+                      const BwdParams& p, cudaStream_t st) {
+  return p.drop.state ? launch_bwd_t<T, D, true>(tq, tk, tv, tdo, p, st) : launch_bwd_t<T, D, false>(tq, tk, tv, tdo, p, st);
 }
 
 }  // namespace attn
@@ -1045,13 +1148,13 @@ static int launch_bwd(const CUtensorMap& tq, const CUtensorMap& tk, const CUtens
 
 // dq_acc: fp32 [B,H,Sq,D], cleared here and then accumulated with reductions; delta: fp32 [B,H,Sq] scratch
 // written here; dk / dv are written in full.  All tensors are indexed [b,h,s,d] through element strides.
-HYP_API int hyp_flash_attn_bwd(const void* q, const void* k, const void* v, const void* o, const void* d_o, const float* lse,
+static int flash_attn_bwd_impl(const void* q, const void* k, const void* v, const void* o, const void* d_o, const float* lse,
                                float* dq_acc, void* dk, void* dv, float* delta, const unsigned char* key_padding_mask,
                                int B, int H, int Sq, int Sk, int D, long long q_sb, long long q_sh, long long q_ss,
                                long long k_sb, long long k_sh, long long k_ss, long long v_sb, long long v_sh, long long v_ss,
                                long long o_sb, long long o_sh, long long o_ss, long long g_sb, long long g_sh, long long g_ss,
                                long long dkv_sb, long long dkv_sh, long long dkv_ss, int causal, float scale, int dtype,
-                               void* stream_) {
+                               const unsigned long long* rng_state, unsigned salt, float dropout_p, void* stream_) {
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
   HYP_REQUIRE(dtype == DT_F16 || dtype == DT_BF16, "hyp_flash_attn_bwd: 16-bit dtypes only");
   HYP_REQUIRE(D == 64 || D == 128, "hyp_flash_attn_bwd: head dim must be 64 or 128 (got %d)", D);
@@ -1074,6 +1177,7 @@ HYP_API int hyp_flash_attn_bwd(const void* q, const void* k, const void* v, cons
   p.kpm = key_padding_mask; p.lse = lse; p.delta = delta; p.dq_acc = dq_acc; p.dk = dk; p.dv = dv;
   p.dk_sb = dkv_sb; p.dk_sh = dkv_sh; p.dk_ss = dkv_ss; p.dv_sb = dkv_sb; p.dv_sh = dkv_sh; p.dv_ss = dkv_ss;
   p.dtype = dtype;
+  if ((rc = attn::make_dropout(&p.drop, rng_state, salt, dropout_p, "hyp_flash_attn_bwd_drop"))) return rc;
   // HYPERION_FLASH_BWD=v1 keeps D = 64 on the non-pipelined kernel (A/B timing only)
   static const bool v1 = [] { const char* e = getenv("HYPERION_FLASH_BWD"); return e && e[0] == 'v' && e[1] == '1'; }();
   if (D == 64 && !v1)
@@ -1081,6 +1185,33 @@ HYP_API int hyp_flash_attn_bwd(const void* q, const void* k, const void* v, cons
                             : attn::launch_bwd64<__half>(tq, tk, tv, tdo, p, st);
   if (dtype == DT_BF16) return D == 64 ? attn::launch_bwd<__nv_bfloat16, 64>(tq, tk, tv, tdo, p, st) : attn::launch_bwd<__nv_bfloat16, 128>(tq, tk, tv, tdo, p, st);
   return D == 64 ? attn::launch_bwd<__half, 64>(tq, tk, tv, tdo, p, st) : attn::launch_bwd<__half, 128>(tq, tk, tv, tdo, p, st);
+}
+
+HYP_API int hyp_flash_attn_bwd(const void* q, const void* k, const void* v, const void* o, const void* d_o, const float* lse,
+                               float* dq_acc, void* dk, void* dv, float* delta, const unsigned char* key_padding_mask,
+                               int B, int H, int Sq, int Sk, int D, long long q_sb, long long q_sh, long long q_ss,
+                               long long k_sb, long long k_sh, long long k_ss, long long v_sb, long long v_sh, long long v_ss,
+                               long long o_sb, long long o_sh, long long o_ss, long long g_sb, long long g_sh, long long g_ss,
+                               long long dkv_sb, long long dkv_sh, long long dkv_ss, int causal, float scale, int dtype,
+                               void* stream_) {
+  return flash_attn_bwd_impl(q, k, v, o, d_o, lse, dq_acc, dk, dv, delta, key_padding_mask, B, H, Sq, Sk, D, q_sb, q_sh, q_ss,
+                             k_sb, k_sh, k_ss, v_sb, v_sh, v_ss, o_sb, o_sh, o_ss, g_sb, g_sh, g_ss, dkv_sb, dkv_sh, dkv_ss,
+                             causal, scale, dtype, nullptr, 0u, 0.f, stream_);
+}
+
+// Backward of hyp_flash_attn_fwd_drop: same arguments plus the forward's (rng_state, salt, dropout_p); must run before the
+// engine advances the step word of rng_state.
+HYP_API int hyp_flash_attn_bwd_drop(const void* q, const void* k, const void* v, const void* o, const void* d_o,
+                                    const float* lse, float* dq_acc, void* dk, void* dv, float* delta,
+                                    const unsigned char* key_padding_mask, int B, int H, int Sq, int Sk, int D, long long q_sb,
+                                    long long q_sh, long long q_ss, long long k_sb, long long k_sh, long long k_ss,
+                                    long long v_sb, long long v_sh, long long v_ss, long long o_sb, long long o_sh,
+                                    long long o_ss, long long g_sb, long long g_sh, long long g_ss, long long dkv_sb,
+                                    long long dkv_sh, long long dkv_ss, int causal, float scale, int dtype,
+                                    const unsigned long long* rng_state, int salt, float dropout_p, void* stream_) {
+  return flash_attn_bwd_impl(q, k, v, o, d_o, lse, dq_acc, dk, dv, delta, key_padding_mask, B, H, Sq, Sk, D, q_sb, q_sh, q_ss,
+                             k_sb, k_sh, k_ss, v_sb, v_sh, v_ss, o_sb, o_sh, o_ss, g_sb, g_sh, g_ss, dkv_sb, dkv_sh, dkv_ss,
+                             causal, scale, dtype, rng_state, static_cast<unsigned>(salt), dropout_p, stream_);
 }
 
 // dq (16-bit, [b,h,s,d] through element strides, unit stride in d) = dq_acc (fp32 contiguous [B,H,S,D]).

@@ -5,6 +5,7 @@
 // Reference call sites: `z = x + y` in the bandwidth sweep
 // (Phase 1/01_hardware_exploration.ipynb c1 L148), autocast casts
 // (02_development/distributed_utils.py:175).
+#include "common/philox.cuh"
 #include "common/ptx.cuh"
 #include "common/util.cuh"
 
@@ -450,4 +451,66 @@ HYP_API int hyp_cast(const void* x, void* y, long long n, int in_dtype, int out_
 HYP_API int hyp_cast_dscale(const void* x, void* y, long long n, int in_dtype, int out_dtype, float scale,
                             const float* scale_ptr, void* stream_) {
   return cast_impl(x, y, n, in_dtype, out_dtype, scale, scale_ptr, reinterpret_cast<cudaStream_t>(stream_));
+}
+
+
+// ------------------------------------------------------------------------------------------------ dropout
+// y[row, col] = x[row, col] * keep(row, col) * scale, mask from common/philox.cuh (2-D plane).  The same call with the
+// same (rng_state, salt, p) applied to a gradient is the backward.  Replaces F.dropout on the FFN hidden activation
+// (nn.TransformerEncoderLayer, 02_development/distributed_utils.py:79) and LoRA's lora_dropout (:469-473), and undoes
+// the dropout folded into hyp_norm_fwd_drop for that op's gradient.  In place (y == x) is fine.
+namespace hyp { namespace ew {
+template <typename T>
+__global__ void __launch_bounds__(256) dropout_kernel(const T* __restrict__ x, T* __restrict__ y, long long rows, int cols,
+                                                       DropoutArgs drop) {
+  const int groups = (cols + 15) >> 4;                    // 16-column groups per row
+  const long long total = rows * groups;
+  const uint2 key = dropout_key(drop.state);
+  for (long long idx = blockIdx.x * 256ll + threadIdx.x; idx < total; idx += 256ll * gridDim.x) {
+    const long long row = idx / groups;
+    const int g = static_cast<int>(idx - row * groups);
+    const uint4 by = dropout_bytes16(key, drop.salt, static_cast<uint32_t>(g), static_cast<uint32_t>(row), kDropoutPlane2D);
+    const uint32_t w[4] = {by.x, by.y, by.z, by.w};
+    const int c0 = g * 16;
+    const T* xr = x + row * cols + c0;
+    T* yr = y + row * cols + c0;
+    if (c0 + 16 <= cols && sizeof(T) == 2 && (cols & 7) == 0) {
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        float f[8];
+        unpack8<T>(*reinterpret_cast<const uint4*>(xr + h * 8), f);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const uint32_t byte = (w[h * 2 + (i >> 2)] >> ((i & 3) * 8)) & 0xFFu;
+          f[i] = byte >= drop.thresh ? f[i] * drop.scale : 0.f;
+        }
+        *reinterpret_cast<uint4*>(yr + h * 8) = pack8<T>(f);
+      }
+    } else {
+      for (int i = 0; i < 16 && c0 + i < cols; ++i) {
+        const uint32_t byte = (w[i >> 2] >> ((i & 3) * 8)) & 0xFFu;
+        yr[i] = byte >= drop.thresh ? from_f32<T>(to_f32<T>(xr[i]) * drop.scale) : from_f32<T>(0.f);
+      }
+    }
+  }
+}
+}}  // namespace hyp::ew
+
+HYP_API int hyp_dropout(const void* x, void* y, long long rows, int cols, int dtype, const unsigned long long* rng_state,
+                        int salt, float dropout_p, void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  HYP_REQUIRE(rows > 0 && cols > 0, "hyp_dropout: empty tensor");
+  HYP_REQUIRE(rng_state != nullptr && dropout_p > 0.f && dropout_p < 1.f, "hyp_dropout: need an rng state and 0 < p < 1 (p=%f)", dropout_p);
+  int t = static_cast<int>(dropout_p * 256.f + 0.5f);
+  t = t < 1 ? 1 : (t > 255 ? 255 : t);
+  DropoutArgs drop{rng_state, static_cast<unsigned>(salt), static_cast<unsigned>(t), 256.f / static_cast<float>(256 - t)};
+  const long long total = rows * ((cols + 15) >> 4);
+  long long blocks = (total + 255) / 256;
+  const long long cap = 148ll * 16;
+  const int grid = static_cast<int>(blocks < cap ? blocks : cap);
+  if (dtype == DT_F32) ew::dropout_kernel<float><<<grid, 256, 0, st>>>((const float*)x, (float*)y, rows, cols, drop);
+  else if (dtype == DT_BF16) ew::dropout_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y, rows, cols, drop);
+  else ew::dropout_kernel<__half><<<grid, 256, 0, st>>>((const __half*)x, (__half*)y, rows, cols, drop);
+  HYP_CHECK_CUDA(cudaGetLastError());
+  return 0;
 }

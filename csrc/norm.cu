@@ -11,6 +11,7 @@
 // (02_development/distributed_utils.py:79; post-norm with residual) and the
 // HF LlamaRMSNorm reached through distributed_utils.py:465.
 #include <atomic>
+#include "common/philox.cuh"
 #include "common/ptx.cuh"
 #include "common/util.cuh"
 
@@ -102,11 +103,13 @@ __device__ __forceinline__ float2 group_sum2(float2 v, float2* red, int sub, int
   }
 }
 
-template <typename T, int TPR, int CH, int BLOCK>
+// DROP: z = dropout(x) + residual -- the dropout of a residual branch (nn.TransformerEncoderLayer's dropout1 / dropout2)
+// folded into the add + norm pass; mask addressed by (row, col), see common/philox.cuh.
+template <typename T, int TPR, int CH, int BLOCK, bool DROP = false>
 __global__ void __launch_bounds__(BLOCK)
 norm_fwd_kernel(const T* __restrict__ x, const T* __restrict__ residual, const T* __restrict__ gamma,
                 const T* __restrict__ beta, T* __restrict__ y, T* __restrict__ sum_out, float* __restrict__ mean_out,
-                float* __restrict__ rstd_out, int rows, int d, float eps, int rms) {
+                float* __restrict__ rstd_out, int rows, int d, float eps, int rms, DropoutArgs drop = DropoutArgs{}) {
   __shared__ float2 red[2 * MAX_RPB * 8];
   constexpr int RPB = BLOCK / TPR;
   static_assert(RPB <= MAX_RPB && TPR / 32 <= 8, "bad norm config");
@@ -133,6 +136,16 @@ norm_fwd_kernel(const T* __restrict__ x, const T* __restrict__ residual, const T
       const int c = (t + k * TPR) * 8;
       if (c < d) {
         load8<T>(x + base + c, v[k]);
+        if constexpr (DROP) {
+          const uint4 by = dropout_bytes16(dropout_key(drop.state), drop.salt, static_cast<uint32_t>(c) >> 4,
+                                           static_cast<uint32_t>(row), kDropoutPlane2D);
+          const uint32_t w0 = (c & 8) ? by.z : by.x, w1 = (c & 8) ? by.w : by.y;
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const uint32_t byte = ((i < 4 ? w0 : w1) >> ((i & 3) * 8)) & 0xFFu;
+            v[k][i] = byte >= drop.thresh ? v[k][i] * drop.scale : 0.f;
+          }
+        }
         if (residual) {
           float r[8];
           load8<T>(residual + base + c, r);
@@ -427,9 +440,9 @@ inline int fwd_grid(int rows, const Cfg& c) {
 
 using namespace hyp;
 
-HYP_API int hyp_norm_fwd(const void* x, const void* residual, const void* gamma, const void* beta, void* y,
+static int norm_fwd_impl(const void* x, const void* residual, const void* gamma, const void* beta, void* y,
                          void* sum_out, float* mean, float* rstd, int rows, int d, float eps, int rms, int dtype,
-                         void* stream_) {
+                         const DropoutArgs& drop, void* stream_) {
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
   HYP_REQUIRE(rows > 0 && d > 0 && d % 8 == 0 && d <= 8192, "hyp_norm_fwd: need d %% 8 == 0 and d <= 8192 (d=%d)", d);
   const norm::Cfg cfg = norm::pick_cfg(d);
@@ -438,12 +451,45 @@ HYP_API int hyp_norm_fwd(const void* x, const void* residual, const void* gamma,
   norm::norm_fwd_kernel<TT, TPR, CH, BLOCK><<<grid, BLOCK, 0, st>>>((const TT*)x, (const TT*)residual, (const TT*)gamma, \
                                                                      (const TT*)beta, (TT*)y, (TT*)sum_out, mean, rstd, \
                                                                      rows, d, eps, rms)
-  if (dtype == DT_F32) { using TT = float; HYP_NORM_FWD_SWITCH(cfg.idx, HYP_NORM_FWD) }
-  else if (dtype == DT_BF16) { using TT = __nv_bfloat16; HYP_NORM_FWD_SWITCH(cfg.idx, HYP_NORM_FWD) }
-  else { using TT = __half; HYP_NORM_FWD_SWITCH(cfg.idx, HYP_NORM_FWD) }
+#define HYP_NORM_FWD_DROP(TPR, CH, BLOCK)                                                                             \
+  norm::norm_fwd_kernel<TT, TPR, CH, BLOCK, true><<<grid, BLOCK, 0, st>>>((const TT*)x, (const TT*)residual,          \
+                                                                           (const TT*)gamma, (const TT*)beta, (TT*)y, \
+                                                                           (TT*)sum_out, mean, rstd, rows, d, eps, rms, drop)
+  if (drop.state) {
+    if (dtype == DT_F32) { using TT = float; HYP_NORM_FWD_SWITCH(cfg.idx, HYP_NORM_FWD_DROP) }
+    else if (dtype == DT_BF16) { using TT = __nv_bfloat16; HYP_NORM_FWD_SWITCH(cfg.idx, HYP_NORM_FWD_DROP) }
+    else { using TT = __half; HYP_NORM_FWD_SWITCH(cfg.idx, HYP_NORM_FWD_DROP) }
+  } else {
+    if (dtype == DT_F32) { using TT = float; HYP_NORM_FWD_SWITCH(cfg.idx, HYP_NORM_FWD) }
+    else if (dtype == DT_BF16) { using TT = __nv_bfloat16; HYP_NORM_FWD_SWITCH(cfg.idx, HYP_NORM_FWD) }
+    else { using TT = __half; HYP_NORM_FWD_SWITCH(cfg.idx, HYP_NORM_FWD) }
+  }
 #undef HYP_NORM_FWD
+#undef HYP_NORM_FWD_DROP
   HYP_CHECK_CUDA(cudaGetLastError());
   return 0;
+}
+
+HYP_API int hyp_norm_fwd(const void* x, const void* residual, const void* gamma, const void* beta, void* y,
+                         void* sum_out, float* mean, float* rstd, int rows, int d, float eps, int rms, int dtype,
+                         void* stream_) {
+  return norm_fwd_impl(x, residual, gamma, beta, y, sum_out, mean, rstd, rows, d, eps, rms, dtype, DropoutArgs{}, stream_);
+}
+
+// z = dropout(x, p) + residual, then the norm: the residual-branch dropout fused into the add + norm pass.  The gradient of
+// x is hyp_dropout(dz) with the same (rng_state, salt, p); the gradient of `residual` is dz itself.
+HYP_API int hyp_norm_fwd_drop(const void* x, const void* residual, const void* gamma, const void* beta, void* y,
+                              void* sum_out, float* mean, float* rstd, int rows, int d, float eps, int rms, int dtype,
+                              const unsigned long long* rng_state, int salt, float dropout_p, void* stream_) {
+  DropoutArgs drop{};
+  if (rng_state != nullptr && dropout_p > 0.f) {
+    HYP_REQUIRE(dropout_p < 1.f, "hyp_norm_fwd_drop: dropout probability must be in [0, 1) (got %f)", dropout_p);
+    int t = static_cast<int>(dropout_p * 256.f + 0.5f);
+    t = t < 1 ? 1 : (t > 255 ? 255 : t);
+    drop.state = rng_state; drop.salt = static_cast<unsigned>(salt); drop.thresh = static_cast<unsigned>(t);
+    drop.scale = 256.f / static_cast<float>(256 - t);
+  }
+  return norm_fwd_impl(x, residual, gamma, beta, y, sum_out, mean, rstd, rows, d, eps, rms, dtype, drop, stream_);
 }
 
 // Bytes of fp32 scratch hyp_norm_bwd needs for (rows, d).

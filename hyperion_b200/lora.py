@@ -51,7 +51,7 @@ class LoRALinear(nn.Module):
         return self.base_layer.bias
 
     def lora_forward(self, x, residual=None):
-        xd = F.dropout(x, self.p, True) if (self.training and self.p > 0) else x
+        xd = ops.dropout(x, self.p, True) if (self.training and self.p > 0) else x
         return ops.lora_linear(x, xd, self.base_layer.weight, self.base_layer.bias, self.lora_A.weight,
                                self.lora_B.weight, self.scaling, residual=residual)
 

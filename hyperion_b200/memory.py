@@ -16,10 +16,31 @@ import torch
 from torch.utils.checkpoint import checkpoint
 
 
+class _SaltKeeper:
+    """Runs ``fn`` for the forward, and again for the recompute in backward with the dropout salt counter rewound to where
+    the forward started, so the native Philox dropout kernels (ops/rng.py) regenerate the forward's masks."""
+
+    def __init__(self, fn):
+        self.fn, self.salt = fn, None
+
+    def __call__(self, *a, **k):
+        from .ops import rng
+
+        if self.salt is None:
+            self.salt = rng.get_salt()
+            return self.fn(*a, **k)
+        cur = rng.get_salt()
+        rng.set_salt(self.salt)
+        try:
+            return self.fn(*a, **k)
+        finally:
+            rng.set_salt(cur)
+
+
 def checkpoint_layers(layers, x, **kwargs):
     """Checkpoint every layer of an iterable (one segment per layer)."""
     for layer in layers:
-        x = checkpoint(layer, x, use_reentrant=False, **kwargs)
+        x = checkpoint(_SaltKeeper(layer), x, use_reentrant=False, **kwargs)
     return x
 
 
@@ -38,7 +59,7 @@ def checkpoint_sequential(functions, segments: int, input, **kwargs):
 
     x = input
     for s in range(0, n, per):
-        x = checkpoint(run(s, min(n, s + per)), x, use_reentrant=False)
+        x = checkpoint(_SaltKeeper(run(s, min(n, s + per))), x, use_reentrant=False)
     return x
 
 

@@ -57,11 +57,15 @@ class TransformerEncoderLayer(nn.Module):
         self.activation = activation
         self.norm_first = norm_first
 
-    def _ffn(self, x, residual=None):
+    def _ffn(self, x, residual=None, out_dropout: bool = True):
+        """linear2(dropout(act(linear1(x)))) [+ dropout2 + residual].  ``out_dropout=False``: the caller folds dropout2
+        into the norm kernel that consumes the result (post-norm)."""
         if self.training and self.p > 0.0:
             h = ops.linear(x, self.linear1.weight, self.linear1.bias, act=self.activation)
-            h = F.dropout(h, self.p, True)
-            y = F.dropout(ops.linear(h, self.linear2.weight, self.linear2.bias), self.p, True)
+            h = ops.dropout(h, self.p, True)
+            y = ops.linear(h, self.linear2.weight, self.linear2.bias)
+            if out_dropout:
+                y = ops.dropout(y, self.p, True)
             return y if residual is None else y + residual
         return ops.mlp(x, self.linear1.weight, self.linear1.bias, self.linear2.weight, self.linear2.bias,
                        act=self.activation, residual=residual)
@@ -71,18 +75,18 @@ class TransformerEncoderLayer(nn.Module):
         if self.norm_first:
             h, skip = ops.layer_norm_fork(x, self.norm1.weight, self.norm1.bias, self.norm1.eps)
             if drop:
-                x = skip + F.dropout(self.self_attn(h, causal, key_padding_mask), self.p, True)
+                x = skip + ops.dropout(self.self_attn(h, causal, key_padding_mask), self.p, True)
             else:
                 x = self.self_attn(h, causal, key_padding_mask, residual=skip)
             h, skip = ops.layer_norm_fork(x, self.norm2.weight, self.norm2.bias, self.norm2.eps)
             return self._ffn(h, residual=skip)
         # post-norm: x = LN(x + sublayer(x)); the residual add is fused into the norm kernel
+        # dropout1 / dropout2 of the residual branches ride inside the add + norm kernels (z = dropout(branch) + x)
+        pd = self.p if drop else 0.0
         a = self.self_attn(x, causal, key_padding_mask)
-        if drop:
-            a = F.dropout(a, self.p, True)
-        x = ops.layer_norm(a, self.norm1.weight, self.norm1.bias, self.norm1.eps, residual=x)
-        f = self._ffn(x)
-        return ops.layer_norm(f, self.norm2.weight, self.norm2.bias, self.norm2.eps, residual=x)
+        x = ops.layer_norm(a, self.norm1.weight, self.norm1.bias, self.norm1.eps, residual=x, dropout_p=pd)
+        f = self._ffn(x, out_dropout=False)
+        return ops.layer_norm(f, self.norm2.weight, self.norm2.bias, self.norm2.eps, residual=x, dropout_p=pd)
 
 
 class TransformerEncoder(nn.Module):

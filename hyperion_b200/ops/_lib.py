@@ -34,6 +34,8 @@ _SIGS = {
     "hyp_cast": "ppliifp",
     "hyp_cast_dscale": "ppliifpp",
     "hyp_norm_fwd": "ppppppppiifiip",
+    "hyp_norm_fwd_drop": "ppppppppiifii" + "pif" + "p",
+    "hyp_dropout": "pplii" + "pif" + "p",
     "hyp_norm_bwd": "pppppppppliiiiip",
     "hyp_norm_bwd_fused": "ppppppppppipliiiip",
     "hyp_adamw": "ppppplii" + "fffff" + "i" + "f" + "ppppp",

@@ -4,7 +4,8 @@
 or 128 and a 16-bit dtype it runs the hand-written tcgen05 flash kernels
 (``csrc/attention.cu``: S = QK^T and O += PV on the tensor cores with TMEM
 accumulators, online softmax in registers, variants none / causal /
-causal+key-padding).  Elsewhere (CPU, fp32, odd head dims) it evaluates the same
+causal+key-padding, optional Philox dropout on the probabilities that the backward
+regenerates instead of storing).  Elsewhere (CPU, fp32, odd head dims) it evaluates the same
 maths with plain PyTorch ops -- the oracle for the kernel tests.
 
 Reference call sites: nn.MultiheadAttention inside nn.TransformerEncoderLayer
@@ -44,7 +45,12 @@ def _flash_supported(q, k, v, dropout_p) -> bool:
     lib = _lib.raw()
     if lib is None or not hasattr(lib, "hyp_flash_attn_fwd"):
         return False
-    return q.dtype in (torch.float16, torch.bfloat16) and q.shape[-1] in (64, 128) and dropout_p == 0.0
+    if dropout_p > 0.0:
+        from .functional import native_dropout_enabled
+
+        if not (native_dropout_enabled() and hasattr(lib, "hyp_flash_attn_fwd_drop")):
+            return False
+    return q.dtype in (torch.float16, torch.bfloat16) and q.shape[-1] in (64, 128)
 
 
 def attention_qkvpacked(qkv, causal=False, key_padding_mask=None, dropout_p=0.0, scale=None):
@@ -55,7 +61,8 @@ def attention_qkvpacked(qkv, causal=False, key_padding_mask=None, dropout_p=0.0,
             and os.environ.get("HYPERION_ATTN", "flash") == "flash"):
         from .flash import flash_attention_qkvpacked
 
-        return flash_attention_qkvpacked(qkv, causal=causal, key_padding_mask=key_padding_mask, scale=scale)
+        return flash_attention_qkvpacked(qkv, causal=causal, key_padding_mask=key_padding_mask, scale=scale,
+                                         dropout_p=dropout_p)
     q, k, v = (qkv[:, :, i].permute(0, 2, 1, 3) for i in range(3))
     return attention(q, k, v, causal, key_padding_mask, dropout_p, scale)
 
@@ -66,7 +73,7 @@ def attention(q, k, v, causal=False, key_padding_mask=None, dropout_p=0.0, scale
     if _flash_supported(q, k, v, dropout_p) and os.environ.get("HYPERION_ATTN", "flash") == "flash":
         from .flash import flash_attention
 
-        return flash_attention(q, k, v, causal=causal, key_padding_mask=key_padding_mask, scale=scale)
+        return flash_attention(q, k, v, causal=causal, key_padding_mask=key_padding_mask, scale=scale, dropout_p=dropout_p)
     if q.is_cuda:
         # Library fallback (cuDNN / flash SDPA) for shapes the native kernel does not cover yet.
         mask = None

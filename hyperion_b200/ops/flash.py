@@ -10,7 +10,7 @@ import math
 
 import torch
 
-from . import _lib
+from . import _lib, rng
 from ._lib import DT, call, ptr, stream_ptr
 
 _declared = False
@@ -25,6 +25,9 @@ def _declare():
     if hasattr(lib, "hyp_flash_attn_bwd"):
         _lib.declare("hyp_flash_attn_bwd", "pppppp" + "ppp" + "pp" + "iiiii" + "l" * 18 + "ifip")
         _lib.declare("hyp_flash_dq_convert", "pp" + "iiii" + "lll" + "ip")
+    if hasattr(lib, "hyp_flash_attn_fwd_drop"):
+        _lib.declare("hyp_flash_attn_fwd_drop", "ppppp" + "iiiii" + "l" * 12 + "p" + "i" + "f" + "i" + "pif" + "p")
+        _lib.declare("hyp_flash_attn_bwd_drop", "pppppp" + "ppp" + "pp" + "iiiii" + "l" * 18 + "ifi" + "pif" + "p")
     _declared = True
 
 
@@ -37,8 +40,21 @@ def _tma_ok(t: torch.Tensor) -> bool:
     return t.data_ptr() % 16 == 0 and all(s % 8 == 0 for s in t.stride()[:3])
 
 
-def flash_fwd(q, k, v, causal: bool, key_padding_mask, scale: float):
-    """Returns (o as [B,H,S,D] view over [B,S,H,D] memory, lse [B,H,Sq] fp32)."""
+def make_drop(device, dropout_p: float):
+    """``(rng_state, salt, p)`` of one dropout call, or None (see ops/rng.py)."""
+    return (rng.state(device), rng.next_salt(), float(dropout_p)) if dropout_p > 0.0 else None
+
+
+def bwd_call(args_before_stream, drop):
+    """hyp_flash_attn_bwd / _drop with the forward's dropout triple."""
+    if drop is None:
+        call("hyp_flash_attn_bwd", *args_before_stream, stream_ptr())
+    else:
+        call("hyp_flash_attn_bwd_drop", *args_before_stream, ptr(drop[0]), int(drop[1]), float(drop[2]), stream_ptr())
+
+
+def flash_fwd(q, k, v, causal: bool, key_padding_mask, scale: float, drop=None):
+    """Returns (o as [B,H,S,D] view over [B,S,H,D] memory, lse [B,H,Sq] fp32).  ``drop``: see :func:`make_drop`."""
     _declare()
     B, H, Sq, D = q.shape
     Sk = k.shape[2]
@@ -49,16 +65,20 @@ def flash_fwd(q, k, v, causal: bool, key_padding_mask, scale: float):
     kpm = None
     if key_padding_mask is not None:
         kpm = key_padding_mask.to(torch.uint8).contiguous()
-    call("hyp_flash_attn_fwd", ptr(q), ptr(k), ptr(v), ptr(o_mem), ptr(lse), B, H, Sq, Sk, D, *_strides_bhs(q),
-         *_strides_bhs(k), *_strides_bhs(v), *_strides_bhs(o), ptr(kpm), int(causal), float(scale), DT[q.dtype],
-         stream_ptr())
+    args = (ptr(q), ptr(k), ptr(v), ptr(o_mem), ptr(lse), B, H, Sq, Sk, D, *_strides_bhs(q),
+            *_strides_bhs(k), *_strides_bhs(v), *_strides_bhs(o), ptr(kpm), int(causal), float(scale), DT[q.dtype])
+    if drop is None:
+        call("hyp_flash_attn_fwd", *args, stream_ptr())
+    else:
+        call("hyp_flash_attn_fwd_drop", *args, ptr(drop[0]), int(drop[1]), float(drop[2]), stream_ptr())
     return o, lse, (q, k, v, kpm)
 
 
 class _FlashFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, q, k, v, causal, key_padding_mask, scale):
-        o, lse, (qc, kc, vc, kpm) = flash_fwd(q, k, v, causal, key_padding_mask, scale)
+    def forward(ctx, q, k, v, causal, key_padding_mask, scale, dropout_p=0.0):
+        ctx.drop = make_drop(q.device, dropout_p)
+        o, lse, (qc, kc, vc, kpm) = flash_fwd(q, k, v, causal, key_padding_mask, scale, ctx.drop)
         ctx.save_for_backward(qc, kc, vc, o, lse, kpm if kpm is not None else torch.empty(0, device=q.device))
         ctx.causal, ctx.scale, ctx.has_kpm = causal, scale, kpm is not None
         return o
@@ -71,8 +91,8 @@ class _FlashFn(torch.autograd.Function):
         if hasattr(lib, "hyp_flash_attn_bwd"):
             from .flash_bwd import flash_bwd
 
-            dq, dk, dv = flash_bwd(q, k, v, o, lse, do, ctx.causal, kpm, ctx.scale)
-            return dq, dk, dv, None, None, None
+            dq, dk, dv = flash_bwd(q, k, v, o, lse, do, ctx.causal, kpm, ctx.scale, ctx.drop)
+            return dq, dk, dv, None, None, None, None
         # recompute-based backward in plain PyTorch (only used when the backward kernel is not built)
         from .attn import attention_reference
 
@@ -80,12 +100,13 @@ class _FlashFn(torch.autograd.Function):
             qq, kk, vv = (t.detach().requires_grad_(True) for t in (q, k, v))
             out = attention_reference(qq, kk, vv, ctx.causal, kpm.bool() if kpm is not None else None, 0.0, ctx.scale)
             dq, dk, dv = torch.autograd.grad(out, (qq, kk, vv), do)
-        return dq, dk, dv, None, None, None
+        return dq, dk, dv, None, None, None, None
 
 
-def flash_attention(q, k, v, causal: bool = False, key_padding_mask=None, scale: float | None = None):
+def flash_attention(q, k, v, causal: bool = False, key_padding_mask=None, scale: float | None = None,
+                    dropout_p: float = 0.0):
     scale = scale if scale is not None else 1.0 / math.sqrt(q.shape[-1])
-    return _FlashFn.apply(q, k, v, causal, key_padding_mask, scale)
+    return _FlashFn.apply(q, k, v, causal, key_padding_mask, scale, dropout_p)
 
 
 class _FlashPackedFn(torch.autograd.Function):
@@ -93,9 +114,10 @@ class _FlashPackedFn(torch.autograd.Function):
     into one ``[B, S, 3, H, D]`` gradient buffer (no per-slice zero-fill + copy + add in autograd)."""
 
     @staticmethod
-    def forward(ctx, qkv, causal, key_padding_mask, scale):
+    def forward(ctx, qkv, causal, key_padding_mask, scale, dropout_p=0.0):
         q, k, v = (qkv[:, :, i].permute(0, 2, 1, 3) for i in range(3))
-        o, lse, (_, _, _, kpm) = flash_fwd(q, k, v, causal, key_padding_mask, scale)
+        ctx.drop = make_drop(qkv.device, dropout_p)
+        o, lse, (_, _, _, kpm) = flash_fwd(q, k, v, causal, key_padding_mask, scale, ctx.drop)
         ctx.save_for_backward(qkv, o, lse, kpm if kpm is not None else torch.empty(0, device=qkv.device))
         ctx.causal, ctx.scale, ctx.has_kpm = causal, scale, kpm is not None
         return o
@@ -113,15 +135,16 @@ class _FlashPackedFn(torch.autograd.Function):
         dk, dv = dqkv[:, :, 1].permute(0, 2, 1, 3), dqkv[:, :, 2].permute(0, 2, 1, 3)
         dq_acc = torch.empty((B, H, S, D), device=qkv.device, dtype=torch.float32)  # cleared by the kernel
         delta = torch.empty((B, H, S), device=qkv.device, dtype=torch.float32)
-        call("hyp_flash_attn_bwd", ptr(q), ptr(k), ptr(v), ptr(o), ptr(do), ptr(lse), ptr(dq_acc), ptr(dk), ptr(dv),
-             ptr(delta), ptr(kpm), B, H, S, S, D, *_strides_bhs(q), *_strides_bhs(k), *_strides_bhs(v), *_strides_bhs(o),
-             *_strides_bhs(do), *_strides_bhs(dk), int(ctx.causal), float(ctx.scale), DT[qkv.dtype], stream_ptr())
+        bwd_call((ptr(q), ptr(k), ptr(v), ptr(o), ptr(do), ptr(lse), ptr(dq_acc), ptr(dk), ptr(dv),
+                  ptr(delta), ptr(kpm), B, H, S, S, D, *_strides_bhs(q), *_strides_bhs(k), *_strides_bhs(v), *_strides_bhs(o),
+                  *_strides_bhs(do), *_strides_bhs(dk), int(ctx.causal), float(ctx.scale), DT[qkv.dtype]), ctx.drop)
         dq = dqkv[:, :, 0].permute(0, 2, 1, 3)
         call("hyp_flash_dq_convert", ptr(dq_acc), ptr(dq), B, H, S, D, *_strides_bhs(dq), DT[qkv.dtype], stream_ptr())
-        return dqkv, None, None, None
+        return dqkv, None, None, None, None
 
 
-def flash_attention_qkvpacked(qkv, causal: bool = False, key_padding_mask=None, scale: float | None = None):
+def flash_attention_qkvpacked(qkv, causal: bool = False, key_padding_mask=None, scale: float | None = None,
+                              dropout_p: float = 0.0):
     """``qkv``: ``[B, S, 3, H, D]`` (contiguous).  Returns ``[B, H, S, D]`` (a view over ``[B, S, H, D]`` memory)."""
     scale = scale if scale is not None else 1.0 / math.sqrt(qkv.shape[-1])
-    return _FlashPackedFn.apply(qkv, causal, key_padding_mask, scale)
+    return _FlashPackedFn.apply(qkv, causal, key_padding_mask, scale, dropout_p)

@@ -13,7 +13,7 @@ import math
 import torch
 import torch.nn.functional as F
 
-from . import _lib, gradslot, native
+from . import _lib, gradslot, native, rng
 
 _SUPPORTED = (torch.float32, torch.float16, torch.bfloat16)
 
@@ -283,10 +283,14 @@ def _norm_param_grads(ctx, dy, dres):
 
 class _NormFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, gamma, beta, residual, eps, rms):
+    def forward(ctx, x, gamma, beta, residual, eps, rms, dropout_p=0.0):
         xc = x.contiguous()
         rc = residual.contiguous() if residual is not None else None
-        y, z, mean, rstd = native.norm_fwd(xc, gamma, beta, residual=rc, eps=eps, rms=rms)
+        ctx.drop = None
+        if dropout_p > 0.0:
+            # z = dropout(x) + residual in the norm kernel's own pass; the mask is regenerated in backward
+            ctx.drop = (rng.state(x.device), rng.next_salt(), float(dropout_p))
+        y, z, mean, rstd = native.norm_fwd(xc, gamma, beta, residual=rc, eps=eps, rms=rms, drop=ctx.drop)
         ctx.save_for_backward(z, gamma, mean, rstd)
         ctx.rms = rms
         ctx.has_beta = beta is not None
@@ -297,7 +301,40 @@ class _NormFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, dy):
         dz, dgamma, dbeta = _norm_param_grads(ctx, dy, None)
-        return dz, dgamma, dbeta, dz if ctx.has_res else None, None, None
+        dx = dz
+        if ctx.drop is not None:
+            st, salt, p = ctx.drop
+            dx = native.dropout(dz.contiguous(), st, salt, p)
+        return dx, dgamma, dbeta, dz if ctx.has_res else None, None, None, None
+
+
+class _DropoutFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, p):
+        ctx.drop = (rng.state(x.device), rng.next_salt(), float(p))
+        return native.dropout(x.contiguous(), *ctx.drop)
+
+    @staticmethod
+    def backward(ctx, dy):
+        return native.dropout(dy.contiguous(), *ctx.drop), None
+
+
+def native_dropout_enabled() -> bool:
+    """The Philox dropout kernels (attention probabilities, residual branches, FFN hidden, LoRA input) are the default;
+    ``HYPERION_DROPOUT=torch`` selects the library path (F.dropout / SDPA) for A/B runs."""
+    import os
+
+    return os.environ.get("HYPERION_DROPOUT", "native") == "native"
+
+
+def dropout(x, p: float, training: bool = True):
+    """``F.dropout`` on the native Philox kernel (mask regenerated in backward, nothing stored).  The effective drop
+    probability is ``round(256 p) / 256`` and survivors are scaled accordingly (unbiased)."""
+    if not training or p <= 0.0:
+        return x
+    if _native(x) and native_dropout_enabled() and x.dim() >= 1 and x.numel() > 0:
+        return _DropoutFn.apply(x, p)
+    return F.dropout(x, p, True)
 
 
 class _NormForkFn(torch.autograd.Function):
@@ -323,11 +360,16 @@ class _NormForkFn(torch.autograd.Function):
         return dz, dgamma, dbeta, None, None
 
 
-def layer_norm(x, gamma, beta, eps: float = 1e-5, residual=None):
-    """LayerNorm(x + residual) in one pass (post-norm residual add fused)."""
+def layer_norm(x, gamma, beta, eps: float = 1e-5, residual=None, dropout_p: float = 0.0):
+    """LayerNorm(dropout(x) + residual) in one pass: the post-norm residual add -- and, in training, the dropout of the
+    residual branch (``dropout_p``) -- are fused into the norm kernel."""
     d = x.shape[-1]
     if _native(x, gamma) and d % 8 == 0 and d <= 8192:
-        return _NormFn.apply(x, gamma, beta, residual, eps, False)
+        if dropout_p > 0.0 and not native_dropout_enabled():
+            x, dropout_p = F.dropout(x, dropout_p, True), 0.0
+        return _NormFn.apply(x, gamma, beta, residual, eps, False, dropout_p)
+    if dropout_p > 0.0:
+        x = F.dropout(x, dropout_p, True)
     z = x if residual is None else x + residual
     return F.layer_norm(z, (d,), gamma, beta, eps)
 
@@ -352,7 +394,7 @@ def rms_norm_fork(x, gamma, eps: float = 1e-6):
 def rms_norm(x, gamma, eps: float = 1e-6, residual=None):
     d = x.shape[-1]
     if _native(x, gamma) and d % 8 == 0 and d <= 8192:
-        return _NormFn.apply(x, gamma, None, residual, eps, True)
+        return _NormFn.apply(x, gamma, None, residual, eps, True, 0.0)
     z = x if residual is None else x + residual
     zf = z.float()
     return (zf * torch.rsqrt(zf.pow(2).mean(-1, keepdim=True) + eps)).to(x.dtype) * gamma

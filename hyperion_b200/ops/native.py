@@ -143,16 +143,33 @@ def cast(x: torch.Tensor, dtype: torch.dtype, scale: float = 1.0, out: torch.Ten
     return out
 
 
-def norm_fwd(x, gamma, beta=None, residual=None, eps: float = 1e-5, rms: bool = False, want_sum: bool = False):
+def norm_fwd(x, gamma, beta=None, residual=None, eps: float = 1e-5, rms: bool = False, want_sum: bool = False,
+             drop=None):
+    """``drop = (rng_state, salt, p)``: ``z = dropout(x) + residual`` inside the same pass (hyp_norm_fwd_drop)."""
     d = x.shape[-1]
     rows = x.numel() // d
     y = torch.empty_like(x)
-    z = torch.empty_like(x) if (want_sum or residual is not None) else None
+    z = torch.empty_like(x) if (want_sum or residual is not None or drop is not None) else None
     mean = torch.empty(rows, device=x.device, dtype=torch.float32)
     rstd = torch.empty(rows, device=x.device, dtype=torch.float32)
-    call("hyp_norm_fwd", ptr(x), ptr(residual), ptr(gamma), ptr(beta), ptr(y), ptr(z), ptr(mean), ptr(rstd), rows, d,
-         float(eps), int(rms), DT[x.dtype], stream_ptr())
+    if drop is not None:
+        st, salt, p = drop
+        call("hyp_norm_fwd_drop", ptr(x), ptr(residual), ptr(gamma), ptr(beta), ptr(y), ptr(z), ptr(mean), ptr(rstd), rows, d,
+             float(eps), int(rms), DT[x.dtype], ptr(st), int(salt), float(p), stream_ptr())
+    else:
+        call("hyp_norm_fwd", ptr(x), ptr(residual), ptr(gamma), ptr(beta), ptr(y), ptr(z), ptr(mean), ptr(rstd), rows, d,
+             float(eps), int(rms), DT[x.dtype], stream_ptr())
     return y, (z if z is not None else x), mean, rstd
+
+
+def dropout(x: torch.Tensor, rng_state: torch.Tensor, salt: int, p: float, out: torch.Tensor | None = None) -> torch.Tensor:
+    """``x * keep * 1/(1-p_eff)`` with the (row, col) Philox mask of common/philox.cuh over ``x`` viewed as
+    ``[-1, last dim]`` (contiguous); the same call on a gradient is the backward."""
+    assert x.is_contiguous()
+    cols = x.shape[-1]
+    out = torch.empty_like(x) if out is None else out
+    call("hyp_dropout", ptr(x), ptr(out), x.numel() // cols, cols, DT[x.dtype], ptr(rng_state), int(salt), float(p), stream_ptr())
+    return out
 
 
 _scratch: dict = {}

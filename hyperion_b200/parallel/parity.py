@@ -13,7 +13,7 @@ import torch
 import torch.distributed as dist
 
 
-def run(strategy: str, precision: str, steps: int) -> int:
+def run(strategy: str, precision: str, steps: int, reshard: bool = False) -> int:
     from hyperion_b200.models import SimpleTransformerLM
     from hyperion_b200.parallel.runtime import cleanup, setup
     from hyperion_b200.train.engine import build_engine
@@ -27,11 +27,17 @@ def run(strategy: str, precision: str, steps: int) -> int:
     results = {}
     for fused in (True, False):
         model = copy.deepcopy(base)
+        # --reshard: the fused arm runs FULL_SHARD (encoder layers as units, gathered into two slots before forward and again
+        # before backward); the NCCL arm keeps the parameters resident -- the two must still agree
+        rs = reshard and fused
         eng = build_engine(model, strategy=strategy, precision=precision, lr=1e-3, clip=1.0 if strategy == "fsdp" else 0.0,
-                           device=dev, fused_comm=fused)
+                           device=dev, fused_comm=fused, reshard_after_forward=rs,
+                           fsdp_units=list(model.tr.layers) if (reshard and strategy == "fsdp") else None)
         assert getattr(eng.model, "fused", None) == fused, "requested comm path was not taken"
-        if strategy == "fsdp" and fused:
+        if strategy == "fsdp" and fused and not reshard:
             assert len(eng.model._ag_handles) > 0, "no unit uses the all-gather-fused GEMM"
+        if rs:
+            assert eng.model.reshard and len(eng.model._rs_units) == 2 and eng.model.flat.data.numel() == 0
         losses = []
         for s in range(steps):
             b = data[s, rank]
@@ -69,8 +75,9 @@ def main():
     ap.add_argument("--strategy", default="ddp", choices=["ddp", "fsdp"])
     ap.add_argument("--precision", default="bf16")
     ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--reshard", action="store_true")
     a = ap.parse_args()
-    sys.exit(1 if run(a.strategy, a.precision, a.steps) else 0)
+    sys.exit(1 if run(a.strategy, a.precision, a.steps, a.reshard) else 0)
 
 
 if __name__ == "__main__":

@@ -47,12 +47,16 @@ class Engine:
         scaler = self.scaler
         with nvtx.range("hyperion/backward+comm"):   # reduce-scatter / all-reduce kernels fire from autograd hooks in here
             (scaler.scale_loss(loss) if scaler is not None else loss).backward()
+        from ..ops import rng
+
         if self.strategy == "fsdp":
             with nvtx.range("hyperion/optimizer(fsdp)"):
                 self.model.step()
+            rng.advance(self.flat.device)   # next step draws new dropout masks (device-side: replays of a graph advance too)
             return
         with nvtx.range("hyperion/optimizer"):
             self._optimizer_phase(scaler)
+        rng.advance(self.flat.device)
 
     def _optimizer_phase(self, scaler) -> None:
         inv_scale = found_inf = sumsq = None

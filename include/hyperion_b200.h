@@ -54,6 +54,11 @@ int hyp_gemm_dualk(const void* A, const void* B, void* D, int M, int N, int K, l
  * Reference: z = x + y bandwidth sweep, Phase 1/01_hardware_exploration.ipynb c1 L148. */
 int hyp_stream_add(const void* x, const void* y, void* z, long long n, int dtype, void* stream);
 int hyp_stream_copy(const void* x, void* z, long long nbytes, void* stream);
+/* y = x * keep * 1/(1-p_eff) over a row-major [rows, cols] tensor, Philox mask as described at hyp_norm_fwd_drop; applying
+ * it to a gradient with the same (rng_state, salt, p) is the backward.  y == x is allowed.
+ * Reference: nn.Dropout inside nn.TransformerEncoderLayer (distributed_utils.py:79), lora_dropout (:469-473). */
+int hyp_dropout(const void* x, void* y, long long rows, int cols, int dtype, const unsigned long long* rng_state, int salt,
+                float dropout_p, void* stream);
 /* out[c] += sum_r x[r,c]; out is fp32 and must be initialised by the caller. */
 int hyp_colsum(const void* x, float* out, int M, int N, long long ld, int dtype, void* stream);
 /* Column sums of a 16-bit matrix rounded to the same dtype in one launch.  acc_ws (>= N fp32) and counter (one
@@ -75,6 +80,14 @@ int hyp_cast_dscale(const void* x, void* y, long long n, int in_dtype, int out_d
  * LlamaRMSNorm via distributed_utils.py:465. */
 int hyp_norm_fwd(const void* x, const void* residual, const void* gamma, const void* beta, void* y, void* sum_out,
                  float* mean, float* rstd, int rows, int d, float eps, int rms, int dtype, void* stream);
+/* Same with z = dropout(x, p) + residual: the residual-branch dropout (nn.TransformerEncoderLayer dropout1 / dropout2,
+ * distributed_utils.py:79) folded into the add + norm pass.  rng_state: device uint64[2] = (seed, step); salt tells the
+ * dropout calls of one step apart; the mask is a Philox4x32-10 function of (seed, step, salt, row, col) with 8 bits per
+ * element (effective p = round(256 p) / 256, survivors scaled by 1 / (1 - p_eff)).  Gradient of x: hyp_dropout(dz) with
+ * the same three values; gradient of residual: dz. */
+int hyp_norm_fwd_drop(const void* x, const void* residual, const void* gamma, const void* beta, void* y, void* sum_out,
+                      float* mean, float* rstd, int rows, int d, float eps, int rms, int dtype,
+                      const unsigned long long* rng_state, int salt, float dropout_p, void* stream);
 long long hyp_norm_bwd_scratch_bytes(int rows, int d);
 /* dz, and fp32 dgamma / dbeta (either may be NULL); `scratch` is caller-owned
  * global memory of at least hyp_norm_bwd_scratch_bytes(rows, d) bytes. */
@@ -159,6 +172,22 @@ int hyp_flash_attn_bwd(const void* q, const void* k, const void* v, const void* 
                        long long k_ss, long long v_sb, long long v_sh, long long v_ss, long long o_sb, long long o_sh,
                        long long o_ss, long long g_sb, long long g_sh, long long g_ss, long long dkv_sb, long long dkv_sh,
                        long long dkv_ss, int causal, float scale, int dtype, void* stream);
+/* The same two entry points with dropout on the attention probabilities (attention dropout 0.1 of
+ * nn.TransformerEncoderLayer, distributed_utils.py:79).  The forward drops P after the softmax normalisation; the backward
+ * regenerates the mask from (rng_state, salt, dropout_p) -- pass the forward's values, and run it before the step word of
+ * rng_state is advanced.  Mask element = Philox(seed, step, salt, b * H + h, query, key), see hyp_norm_fwd_drop. */
+int hyp_flash_attn_fwd_drop(const void* q, const void* k, const void* v, void* o, float* lse, int B, int H, int Sq, int Sk,
+                            int D, long long q_sb, long long q_sh, long long q_ss, long long k_sb, long long k_sh,
+                            long long k_ss, long long v_sb, long long v_sh, long long v_ss, long long o_sb, long long o_sh,
+                            long long o_ss, const unsigned char* key_padding_mask, int causal, float scale, int dtype,
+                            const unsigned long long* rng_state, int salt, float dropout_p, void* stream);
+int hyp_flash_attn_bwd_drop(const void* q, const void* k, const void* v, const void* o, const void* d_o, const float* lse,
+                            float* dq_acc, void* dk, void* dv, float* delta, const unsigned char* key_padding_mask, int B,
+                            int H, int Sq, int Sk, int D, long long q_sb, long long q_sh, long long q_ss, long long k_sb,
+                            long long k_sh, long long k_ss, long long v_sb, long long v_sh, long long v_ss, long long o_sb,
+                            long long o_sh, long long o_ss, long long g_sb, long long g_sh, long long g_ss, long long dkv_sb,
+                            long long dkv_sh, long long dkv_ss, int causal, float scale, int dtype,
+                            const unsigned long long* rng_state, int salt, float dropout_p, void* stream);
 /* Rounds the fp32 dQ accumulator ([B,H,S,D] contiguous) into a 16-bit tensor addressed [b,h,s,d] through element
  * strides (e.g. the q slice of the packed [B,S,3,H,D] gradient buffer). */
 int hyp_flash_dq_convert(const float* dq_acc, void* dq, int B, int H, int S, int D, long long sb, long long sh,

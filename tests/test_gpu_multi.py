@@ -32,3 +32,10 @@ def test_comm_kernels_match_nccl():
 def test_fused_training_matches_nccl_path(strategy, precision):
     out = _torchrun(_n(), "hyperion_b200.parallel.parity", "--strategy", strategy, "--precision", precision)
     assert "PASS" in out and "FAIL" not in out
+
+
+def test_full_shard_mode_matches_nccl_path():
+    """reshard_after_forward=True (FULL_SHARD: slots, gather before forward and again before backward) on the fused NVLink
+    kernels vs the params-resident NCCL path."""
+    out = _torchrun(_n(), "hyperion_b200.parallel.parity", "--strategy", "fsdp", "--precision", "bf16", "--reshard")
+    assert "PASS" in out and "FAIL" not in out
