@@ -6,7 +6,8 @@ h.N.attn.c_attn ...``) but weights use the ``nn.Linear`` ``[out, in]`` layout.
 
 Pre-norm blocks; every residual add is fused into the epilogue of the GEMM that
 produces the branch output; GELU(tanh) and its derivative live in GEMM epilogues;
-the tied LM head + cross-entropy never materialise the logits.
+the tied LM head + cross-entropy run as one op that produces the loss and all gradients in the forward
+(16-bit logits are held while it runs, see ops.functional._LinearCEFn).
 """
 from __future__ import annotations
 

@@ -13,7 +13,7 @@ Three divergent definitions exist in the reference:
   layers, ff 3072, sequence-first input ``idx[T, B]``.
 
 The output head is exposed separately (``features`` + ``fc``) so trainers can use
-the fused linear+cross-entropy op and never materialise ``[tokens, vocab]`` logits.
+the fused linear+cross-entropy op (loss and gradients in one pass over L2-sized slices of the logits).
 """
 from __future__ import annotations
 

@@ -61,11 +61,11 @@ class TransformerEncoderLayer(nn.Module):
         """linear2(dropout(act(linear1(x)))) [+ dropout2 + residual].  ``out_dropout=False``: the caller folds dropout2
         into the norm kernel that consumes the result (post-norm)."""
         if self.training and self.p > 0.0:
-            h = ops.linear(x, self.linear1.weight, self.linear1.bias, act=self.activation)
-            h = ops.dropout(h, self.p, True)
-            y = ops.linear(h, self.linear2.weight, self.linear2.bias)
-            if out_dropout:
-                y = ops.dropout(y, self.p, True)
+            if not out_dropout:
+                return ops.mlp(x, self.linear1.weight, self.linear1.bias, self.linear2.weight, self.linear2.bias,
+                               act=self.activation, residual=residual, dropout_p=self.p)
+            y = ops.dropout(ops.mlp(x, self.linear1.weight, self.linear1.bias, self.linear2.weight, self.linear2.bias,
+                                    act=self.activation, dropout_p=self.p), self.p, True)
             return y if residual is None else y + residual
         return ops.mlp(x, self.linear1.weight, self.linear1.bias, self.linear2.weight, self.linear2.bias,
                        act=self.activation, residual=residual)

@@ -9,6 +9,7 @@ raises (see :func:`_native`).
 from __future__ import annotations
 
 import math
+import os
 
 import torch
 import torch.nn.functional as F
@@ -62,6 +63,16 @@ _SM_COUNT = 148
 _CE_LOGITS_BUDGET = 2 << 30  # bytes of logits linear_cross_entropy may hold at once
 
 
+def _ce_l2_rows(vocab: int, es: int) -> int:
+    """Rows per slice of the logits in linear_cross_entropy; 0 (default) = one slice.  ``HYPERION_CE_L2_ROWS=n`` processes
+    the head in n-row slices so a slice stays in the 126 MB L2 between the GEMM that writes it, the CE kernel and the
+    dgrad / bias-sum passes.  Measured on the reference LM (4064 tokens x 50257, fp16; step 1.55 ms unsliced): 1024-row
+    slices 1.71 ms, 256-row slices 2.32 ms -- the small-M GEMMs and the extra launches cost more than the HBM traffic they
+    save, so slicing stays off."""
+    v = os.environ.get("HYPERION_CE_L2_ROWS")
+    return int(v) if v is not None else 0
+
+
 def _wgrad(dy2: torch.Tensor, x2: torch.Tensor, out_dtype, slot=None) -> torch.Tensor:
     """dW[N, K] = dy2[M, N]^T @ x2[M, K] (both operands MN-major).  When the output has few tiles (N*K is small next
     to the token count M) the reduction is split across SMs: split-K partial tiles are reduced with vector fp32
@@ -74,7 +85,10 @@ def _wgrad(dy2: torch.Tensor, x2: torch.Tensor, out_dtype, slot=None) -> torch.T
         # GPT-2-medium shapes: 48 tiles run as fast unsplit, 16 tiles are 1.7x faster with 4 splits)
         tiles, pairs = ((N + 255) // 256) * ((K + 255) // 256), _SM_COUNT // 2
         if 2 * tiles <= pairs and dy2.shape[0] >= 2048:
-            splits = max(1, min(4, pairs // tiles, dy2.shape[0] // 1024))
+            # up to 4 splits at GPT-2 sizes (tuned there); a handful of tiles (the 256-wide layers of the reference LM,
+            # 1-8 tiles over 4064 tokens) were latency-bound at ~17 us whatever their size: give each split ~512 tokens
+            cap = 4 if tiles >= 9 else 8
+            splits = max(1, min(cap, pairs // tiles, dy2.shape[0] // (1024 if tiles >= 9 else 512)))
     else:
         tiles = ((N + 127) // 128) * ((K + 255) // 256 if K > 128 else 1)
         if tiles < 120 and dy2.shape[0] >= 2048:
@@ -92,6 +106,26 @@ def _wgrad(dy2: torch.Tensor, x2: torch.Tensor, out_dtype, slot=None) -> torch.T
     out = dst if dst is not None else _padded_empty(N, K, out_dtype, dy2.device)
     native.gemm(dy2, x2, a_mn_major=True, b_mn_major=True, out=out)
     return out if out.is_contiguous() else out.contiguous()
+
+
+def _dgrad(dh2: torch.Tensor, w2: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
+    """dx[M, K] = dh2[M, N] @ w2[N, K].  When the output has few tiles and the reduction dimension N is long (the
+    vocabulary projection of a narrow model: 4064 x 256 outputs reduced over 50257 columns ran on 32 of 74 CTA pairs),
+    the reduction is split across SMs into an fp32 accumulator and rounded once."""
+    M, N = dh2.shape
+    K = w2.shape[1]
+    bn = 256 if K >= 256 else 128
+    tiles, pairs = ((M + 255) // 256) * ((K + bn - 1) // bn), _SM_COUNT // 2
+    splits = 1
+    if 2 * tiles <= pairs and N >= 8192 and (K * 4) % 16 == 0:
+        splits = max(1, min(8, pairs // tiles, N // 4096))
+    if splits > 1:
+        acc = torch.zeros((M, K), device=dh2.device, dtype=torch.float32)
+        native.gemm(dh2, w2, b_mn_major=True, out=acc, splits=splits)
+        return native.cast(acc, dh2.dtype, out=out)
+    if out is None:
+        out = _padded_empty(M, K, dh2.dtype, dh2.device)
+    return native.gemm(dh2, w2, b_mn_major=True, out=out)
 
 
 def _bias_grad(dy2: torch.Tensor, dtype, slot=None, dy=None) -> torch.Tensor:
@@ -168,8 +202,7 @@ class _LinearFn(torch.autograd.Function):
             dh = dy2
         dx = dw = db = dres = None
         if ctx.needs_input_grad[0]:
-            dx = native.gemm(dh, w2, b_mn_major=True, out=_padded_empty(dh.shape[0], w2.shape[1], dh.dtype, dh.device))
-            dx = dx.reshape(ctx.x_shape)
+            dx = _dgrad(dh, w2).reshape(ctx.x_shape)
         if ctx.needs_input_grad[1]:
             dw = _wgrad(dh, x2, w2.dtype, ctx.slots[0])
         if ctx.has_bias and ctx.needs_input_grad[2]:
@@ -208,10 +241,11 @@ def linear(x, w, b=None, act: str | None = None, residual=None):
 
 # --------------------------------------------------------------------------- fused MLP
 class _MlpFn(torch.autograd.Function):
-    """y = act(x W1^T + b1) W2^T + b2 (+ residual); backward fuses act' into the dgrad GEMM epilogue."""
+    """y = dropout(act(x W1^T + b1)) W2^T + b2 (+ residual); backward fuses act' into the dgrad GEMM epilogue and
+    re-applies the regenerated dropout mask in place (mask and act' are both element-wise, so the order is free)."""
 
     @staticmethod
-    def forward(ctx, x, w1, b1, w2, b2, residual, act, ag1=None, ag2=None):
+    def forward(ctx, x, w1, b1, w2, b2, residual, act, ag1=None, ag2=None, dropout_p=0.0):
         x2 = _as2d(x)
         M = x2.shape[0]
         h = torch.empty((M, w1.shape[0]), dtype=x.dtype, device=x.device)
@@ -220,6 +254,10 @@ class _MlpFn(torch.autograd.Function):
             ag1.run(x2, w1, a, bias=b1, act=act, preact_out=h)
         else:
             native.gemm(x2, w1, out=a, bias=b1, act=act, preact_out=h)
+        ctx.drop = None
+        if dropout_p > 0.0:
+            ctx.drop = (rng.state(x.device), rng.next_salt(), float(dropout_p))
+            native.dropout(a, *ctx.drop, out=a)      # in place: only the dropped activation is needed again (wgrad of W2)
         y = torch.empty((M, w2.shape[0]), dtype=x.dtype, device=x.device)
         res2 = _as2d(residual) if residual is not None else None
         if ag2 is not None and ag2.pending:
@@ -240,21 +278,31 @@ class _MlpFn(torch.autograd.Function):
         has_b1, has_b2, has_res = ctx.flags
         # dh = (dy @ W2) * act'(h): activation derivative applied in the GEMM epilogue
         dh = native.gemm(dy2, w2, b_mn_major=True, aux=h, act=ctx.act, mode=1)
+        if ctx.drop is not None:
+            native.dropout(dh, *ctx.drop, out=dh)
         s_w1, s_b1, s_w2, s_b2 = ctx.slots
         dw2 = _wgrad(dy2, a, w2.dtype, s_w2)
         dw1 = _wgrad(dh, x2, w1.dtype, s_w1)
         dx = native.gemm(dh, w1, b_mn_major=True).reshape(ctx.x_shape) if ctx.needs_input_grad[0] else None
         db1 = _bias_grad(dh, dy.dtype, s_b1) if has_b1 else None
         db2 = _bias_grad(dy2, dy.dtype, s_b2, dy) if has_b2 else None
-        return dx, dw1, db1, dw2, db2, (dy if has_res else None), None, None, None
+        return dx, dw1, db1, dw2, db2, (dy if has_res else None), None, None, None, None
 
 
-def mlp(x, w1, b1, w2, b2, act: str = "relu", residual=None):
-    """Two-layer feed-forward block (the FFN of every transformer in the model zoo)."""
+def mlp(x, w1, b1, w2, b2, act: str = "relu", residual=None, dropout_p: float = 0.0):
+    """Two-layer feed-forward block (the FFN of every transformer in the model zoo); ``dropout_p`` drops the hidden
+    activation (``dropout`` inside ``nn.TransformerEncoderLayer``'s FFN) without leaving the fused op."""
     es = x.element_size()
     if _native(x, w1) and x.shape[-1] % (16 // es) == 0 and w1.shape[0] % (16 // es) == 0 and w2.shape[0] % (16 // es) == 0:
-        return _MlpFn.apply(x, w1, b1, w2, b2, residual, act, getattr(w1, "_hyp_ag", None), getattr(w2, "_hyp_ag", None))
-    y = F.linear(_act_ref(F.linear(x, w1, b1), act), w2, b2)
+        if dropout_p > 0.0 and not native_dropout_enabled():
+            h = F.dropout(linear(x, w1, b1, act=act), dropout_p, True)
+            return linear(h, w2, b2, residual=residual)
+        return _MlpFn.apply(x, w1, b1, w2, b2, residual, act, getattr(w1, "_hyp_ag", None), getattr(w2, "_hyp_ag", None),
+                            dropout_p)
+    h = _act_ref(F.linear(x, w1, b1), act)
+    if dropout_p > 0.0:
+        h = F.dropout(h, dropout_p, True)
+    y = F.linear(h, w2, b2)
     return y if residual is None else y + residual
 
 
@@ -429,11 +477,12 @@ def embedding(idx, table, padding_idx=None):
 
 # --------------------------------------------------------------------------- linear + cross-entropy
 class _LinearCEFn(torch.autograd.Function):
-    """mean CE(x @ W^T + b, targets) without ever holding the [tokens, vocab] logits.
+    """mean CE(x @ W^T + b, targets) with the loss AND all three gradients produced in the forward.
 
-    The vocabulary projection runs in row chunks; each chunk's logits are turned
-    into their gradient in place by the fused CE kernel and immediately consumed
-    by the dgrad / wgrad GEMMs (wgrad accumulates across chunks in fp32).
+    The vocabulary projection writes 16-bit logits, the fused CE kernel turns them into their gradient in place, and the
+    dgrad / wgrad GEMMs consume that gradient right away.  The [tokens, vocab] matrix is held while that happens (up to
+    ``_CE_LOGITS_BUDGET``; beyond it the rows are processed in chunks with an fp32 wgrad accumulator) -- see the comment
+    in ``forward`` for why the recompute variant that avoids it is not used, and for the L2-resident row slices.
     """
 
     @staticmethod
@@ -447,29 +496,37 @@ class _LinearCEFn(torch.autograd.Function):
         sum_count = torch.zeros(2, device=dev, dtype=torch.float32)
         inv_cnt = (tgt != ignore_index).sum().clamp(min=1).to(torch.float32).reciprocal().reshape(1)
         dx = torch.empty_like(x2)
-        # one chunk when the whole logits matrix is affordable (<= 2 GiB): the head's wgrad is then a single GEMM with a
-        # 16-bit output instead of fp32 accumulation across chunks (which reads and writes V x K fp32 per chunk)
-        if M * V * x.element_size() <= _CE_LOGITS_BUDGET:
+        # The logits matrix (tokens x vocab, 16-bit) IS held when it is affordable (<= 2 GiB; 0.8 GB for GPT-2 medium at 8 x
+        # 1024 tokens): the head's wgrad is then a single GEMM with a 16-bit output instead of fp32 accumulation across
+        # chunks (which reads and writes V x K fp32 per chunk).  A recompute design (online LSE in the forward epilogue,
+        # logits rebuilt in backward) would save that memory but costs a second vocabulary GEMM (0.6 ms at GPT-2-medium
+        # size) to save ~0.25 ms of HBM traffic, so it is not what runs.  Optional L2-sized row slices: see _ce_l2_rows.
+        single = M * V * x.element_size() <= _CE_LOGITS_BUDGET
+        if single:
             chunk_rows = M
-        single = chunk_rows >= M
         dw = None if single else torch.zeros((V, K), device=dev, dtype=torch.float32)
         db = torch.zeros(V, device=dev, dtype=torch.float32) if b is not None else None
         ag = getattr(w, "_hyp_ag", None)
+        l2_rows = _ce_l2_rows(V, x.element_size())
         for r0 in range(0, M, chunk_rows):
             r1 = min(M, r0 + chunk_rows)
             logits = _padded_empty(r1 - r0, V, x.dtype, dev)
-            if ag is not None and ag.pending:
-                ag.run(x2[r0:r1], w2, logits, bias=b)  # first chunk gathers the head's unit inside its GEMM
-            else:
-                native.gemm(x2[r0:r1], w2, out=logits, bias=b)
-            native.ce_fwd_bwd(logits, tgt[r0:r1], ignore_index, sum_count, gscale_ptr=inv_cnt, n_classes=V)
-            native.gemm(logits, w2, b_mn_major=True, out=dx[r0:r1])
+            step = l2_rows if (single and 0 < l2_rows < r1 - r0) else (r1 - r0)
+            for q0 in range(r0, r1, step):
+                q1 = min(r1, q0 + step)
+                lg = logits[q0 - r0:q1 - r0]
+                if ag is not None and ag.pending:
+                    ag.run(x2[q0:q1], w2, lg, bias=b)  # first slice gathers the head's unit inside its GEMM
+                else:
+                    native.gemm(x2[q0:q1], w2, out=lg, bias=b)
+                native.ce_fwd_bwd(lg, tgt[q0:q1], ignore_index, sum_count, gscale_ptr=inv_cnt, n_classes=V)
+                _dgrad(lg, w2, out=dx[q0:q1])
+                if db is not None:
+                    native.colsum(lg, out=db)
             if single:
                 dw = _wgrad(logits, x2, w.dtype)
             else:
                 native.gemm(logits, x2[r0:r1], a_mn_major=True, b_mn_major=True, out=dw, beta=1.0)
-            if db is not None:
-                native.colsum(logits, out=db)
         loss = torch.empty((), device=dev, dtype=torch.float32)
         native.ce_finalize(sum_count, loss)
         ctx.save_for_backward(dx, dw, db)

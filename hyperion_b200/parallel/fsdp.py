@@ -115,11 +115,24 @@ class HyperionFSDP(nn.Module):
                 self.fused = False
         # ---- units
         unit_modules = units if units is not None else size_based_units(module, min_num_params)
+        import os
+
+        # K-C3 on composite units (a transformer block, a decoder layer): the unit is gathered by warps riding inside the
+        # GEMM that consumes its first weight matrix.  What the block reads BEFORE that GEMM -- its norm scale / shift
+        # vectors -- would still be stale, so those few KB are carved out into the root unit (gathered up front).
+        want_ag = (fuse_allgather_gemm and os.environ.get("HYPERION_FSDP_AG", "fused") == "fused" and self.fused
+                   and not self.reshard and os.environ.get("HYPERION_FSDP_AG_BLOCKS", "1") == "1")
         owner: dict[str, int] = {}
         for ui, um in enumerate(unit_modules):
             prefix = next((n for n, m in module.named_modules() if m is um), None)
+            carve = set()
+            if want_ag and not isinstance(um, self._LEAF_TYPES):
+                for sn, sm in um.named_modules():
+                    if sm is not um and "norm" in type(sm).__name__.lower():
+                        carve |= {f"{sn}.{pn}" for pn, _ in sm.named_parameters(recurse=False)}
             for pn, _ in um.named_parameters():
-                owner[f"{prefix}.{pn}" if prefix else pn] = ui
+                if pn not in carve:
+                    owner[f"{prefix}.{pn}" if prefix else pn] = ui
         self.unit_modules = unit_modules
         galloc = self.arena.alloc if self.fused else None
         self.flat = FlatParams(module.named_parameters(), device=self.device, unit_key=lambda n: owner.get(n, -1),
@@ -177,7 +190,6 @@ class HyperionFSDP(nn.Module):
             self._setup_reshard(sync_params)
         # ---- K-C3: units whose first consumer is a GEMM on a known weight gather inside that GEMM
         self._ag_handles: dict[int, _AgHandle] = {}
-        import os
 
         # HYPERION_FSDP_AG=plain gathers every unit with the stand-alone kernel (queued at the start of the forward, so it
         # overlaps the forward just the same) and leaves the GEMMs on the faster CTA-pair kernel
@@ -187,17 +199,28 @@ class HyperionFSDP(nn.Module):
             from ..models.transformer import MultiheadSelfAttention
 
             flat_ids = {id(sp.param) for sp in self.flat.specs}
+            blocks_ok = os.environ.get("HYPERION_FSDP_AG_BLOCKS", "1") == "1"
+
+            def first_gemm_weight(um):
+                """The weight of the first GEMM a unit's forward runs (registration order == call order in the models here)."""
+                for sm in um.modules():
+                    if isinstance(sm, MultiheadSelfAttention):
+                        return sm.in_proj_weight
+                    if isinstance(sm, nn.Linear):
+                        return sm.weight
+                    if sm is not um and not blocks_ok:
+                        return None
+                return None
+
             for k, um in enumerate(unit_modules):
-                target = None
-                if isinstance(um, nn.Linear):
-                    target = um.weight
-                elif isinstance(um, MultiheadSelfAttention):
-                    target = um.in_proj_weight
+                target = first_gemm_weight(um) if (blocks_ok or isinstance(um, (nn.Linear, MultiheadSelfAttention))) else None
                 uis = self._key_to_units.get(k, [])
                 if target is not None and id(target) in flat_ids and len(uis) == 1 and target.shape[1] % 8 == 0:
                     h = _AgHandle(self, uis[0])
                     target._hyp_ag = h
                     self._ag_handles[uis[0]] = h
+                    if not isinstance(um, (nn.Linear, MultiheadSelfAttention)):
+                        um.register_forward_hook(self._make_ag_check_hook(h, k))
 
     # ------------------------------------------------------------------ shard <-> flat index helpers
     def _shard_range(self, ui: int) -> tuple[int, int]:
@@ -369,6 +392,15 @@ class HyperionFSDP(nn.Module):
             self._rs_touch(ui, backward=True)
         return hook
 
+    def _make_ag_check_hook(self, handle: "_AgHandle", key: int):
+        def hook(_m, _args, _out):
+            # the unit's first GEMM must have run (and gathered the unit) inside this forward; anything else would have
+            # computed with last step's weights
+            if handle.pending:
+                raise RuntimeError(f"FSDP unit {key}: its forward finished without running the GEMM that gathers it "
+                                   "(HYPERION_FSDP_AG_BLOCKS=0 or HYPERION_FSDP_AG=plain selects stand-alone gathers)")
+        return hook
+
     # ------------------------------------------------------------------ forward: wait for gathered units
     def _make_fwd_hook(self, key: int):
         def hook(_m, _args):
@@ -402,6 +434,14 @@ class HyperionFSDP(nn.Module):
         if self._gathers_due:
             self._gathers_due = False
             self._queue_gathers()
+            if self._ag_handles and self.comm_stream is not None:
+                # Co-residency invariant: a GEMM with gather warps (one CTA per SM, spinning on its peers' flags) must never
+                # share the GPU with a communication kernel of this engine (512 threads x 128 registers = a whole SM each, also
+                # spinning on peers): neither fits beside the other, and across two ranks the waits could form a cycle.  So
+                # every stand-alone gather of this step is complete before the first forward kernel is issued; during the
+                # forward the comm stream stays idle (all remaining units gather inside GEMMs), and in backward the
+                # reduce-scatters only ever run beside ordinary kernels, which never wait for a peer.
+                torch.cuda.current_stream(self.device).wait_stream(self.comm_stream)
 
     def forward(self, *args, **kwargs):
         self._start_of_forward()

@@ -13,7 +13,7 @@ import torch
 import torch.distributed as dist
 
 
-def run(strategy: str, precision: str, steps: int, reshard: bool = False) -> int:
+def run(strategy: str, precision: str, steps: int, reshard: bool = False, model_name: str = "lm") -> int:
     from hyperion_b200.models import SimpleTransformerLM
     from hyperion_b200.parallel.runtime import cleanup, setup
     from hyperion_b200.train.engine import build_engine
@@ -22,8 +22,18 @@ def run(strategy: str, precision: str, steps: int, reshard: bool = False) -> int
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     dev = setup(rank, world, "nccl", seed=0)
     torch.manual_seed(0)
-    base = SimpleTransformerLM(50257, dropout=0.0)
-    data = torch.randint(0, 50256, (steps, world, 8, 64), generator=torch.Generator().manual_seed(7)).to(dev)
+    gpt2 = model_name == "gpt2"
+    if gpt2:
+        # block-sized units: every Block is gathered inside its c_attn GEMM (K-C3 on composite units), the root unit (wte,
+        # wpe, ln_f and the carved-out block norms) by the stand-alone kernel -- the mix the BASELINE GPT-2 config runs
+        from hyperion_b200.models import GPT2Config, GPT2LMHeadModel
+        from hyperion_b200.models.gpt2 import Block
+
+        base = GPT2LMHeadModel(GPT2Config(vocab_size=1024, n_positions=128, n_embd=256, n_layer=3, n_head=4))
+        data = torch.randint(0, 1024, (steps, world, 4, 128), generator=torch.Generator().manual_seed(7)).to(dev)
+    else:
+        base = SimpleTransformerLM(50257, dropout=0.0)
+        data = torch.randint(0, 50256, (steps, world, 8, 64), generator=torch.Generator().manual_seed(7)).to(dev)
     results = {}
     for fused in (True, False):
         model = copy.deepcopy(base)
@@ -32,16 +42,20 @@ def run(strategy: str, precision: str, steps: int, reshard: bool = False) -> int
         rs = reshard and fused
         eng = build_engine(model, strategy=strategy, precision=precision, lr=1e-3, clip=1.0 if strategy == "fsdp" else 0.0,
                            device=dev, fused_comm=fused, reshard_after_forward=rs,
-                           fsdp_units=list(model.tr.layers) if (reshard and strategy == "fsdp") else None)
+                           fsdp_units=([m for m in model.modules() if isinstance(m, Block)] if gpt2 else
+                                       list(model.tr.layers) if (reshard and strategy == "fsdp") else None))
         assert getattr(eng.model, "fused", None) == fused, "requested comm path was not taken"
         if strategy == "fsdp" and fused and not reshard:
             assert len(eng.model._ag_handles) > 0, "no unit uses the all-gather-fused GEMM"
         if rs:
-            assert eng.model.reshard and len(eng.model._rs_units) == 2 and eng.model.flat.data.numel() == 0
+            assert eng.model.reshard and len(eng.model._rs_units) == (3 if gpt2 else 2) and eng.model.flat.data.numel() == 0
+        if gpt2 and fused and not reshard and strategy == "fsdp":
+            assert len(eng.model._ag_handles) == 3, "the three Block units must gather inside their first GEMM"
         losses = []
         for s in range(steps):
             b = data[s, rank]
-            loss = eng.model.loss(b[:, :-1].contiguous(), b[:, 1:].contiguous(), ignore_index=50256)
+            loss = (eng.model.loss(b) if gpt2 else
+                    eng.model.loss(b[:, :-1].contiguous(), b[:, 1:].contiguous(), ignore_index=50256))
             eng.backward_and_step(loss)
             losses.append(loss.detach().float())
         torch.cuda.synchronize()
@@ -76,8 +90,9 @@ def main():
     ap.add_argument("--precision", default="bf16")
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--reshard", action="store_true")
+    ap.add_argument("--model", default="lm", choices=["lm", "gpt2"])
     a = ap.parse_args()
-    sys.exit(1 if run(a.strategy, a.precision, a.steps, a.reshard) else 0)
+    sys.exit(1 if run(a.strategy, a.precision, a.steps, a.reshard, a.model) else 0)
 
 
 if __name__ == "__main__":

@@ -39,3 +39,12 @@ def test_full_shard_mode_matches_nccl_path():
     kernels vs the params-resident NCCL path."""
     out = _torchrun(_n(), "hyperion_b200.parallel.parity", "--strategy", "fsdp", "--precision", "bf16", "--reshard")
     assert "PASS" in out and "FAIL" not in out
+
+
+@pytest.mark.parametrize("reshard", [False, True])
+def test_block_units_gather_inside_their_first_gemm(reshard):
+    """GPT-2-shaped model with one FSDP unit per Block: fused path = all-gather warps inside each block's c_attn GEMM plus
+    stand-alone gathers for the root unit (and, with --reshard, FULL_SHARD slots) vs the NCCL path."""
+    args = ["--strategy", "fsdp", "--precision", "bf16", "--model", "gpt2"] + (["--reshard"] if reshard else [])
+    out = _torchrun(_n(), "hyperion_b200.parallel.parity", *args)
+    assert "PASS" in out and "FAIL" not in out
