@@ -40,6 +40,7 @@ def parse():
     ap.add_argument("--size", default=None, help="model size override (gpt2: medium/small/tiny; llama: 7b/tiny)")
     ap.add_argument("--no-fused-comm", dest="fused_comm", action="store_false", default=None)
     ap.add_argument("--no-e2e", dest="e2e", action="store_false", default=True)
+    ap.add_argument("--ag-blocks", action="store_true", help="FSDP: block-sized units gather inside their first GEMM (K-C3 A/B)")
     ap.add_argument("--reshard", action="store_true", help="FSDP configs: FULL_SHARD semantics (free after forward, re-gather in backward)")
     ap.add_argument("--no-graph", dest="graph", action="store_false", default=True, help="do not capture the step in a CUDA graph")
     return ap.parse_args()
@@ -82,8 +83,13 @@ def main() -> int:
 
     if args.reshard:
         os.environ["HYPERION_FSDP_RESHARD"] = "1"
+    if args.ag_blocks:
+        os.environ["HYPERION_FSDP_AG_BLOCKS"] = "1"
     case = make_case(args.config, dev, rank, world, batch=args.batch, seq=args.seq, size=args.size,
                      fused_comm=args.fused_comm)
+    if getattr(case.eng.model, "fused", False) and hasattr(case.eng.model, "_ag_handles"):
+        case.config["comm"] = (f"fused NVLink kernels: reduce-scatter(+AdamW), all-gather, "
+                               f"ag_gemm x{len(case.eng.model._ag_handles)} units")
     if hasattr(case.eng.model, "reshard"):
         case.config["fsdp_mode"] = ("full_shard(reshard_after_forward)" if case.eng.model.reshard else
                                     "shard optimizer state + gradients, 16-bit parameters resident (one all-gather per step)")

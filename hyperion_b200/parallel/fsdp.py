@@ -121,8 +121,10 @@ class HyperionFSDP(nn.Module):
         # GEMM that consumes its first weight matrix.  What the block reads BEFORE that GEMM -- its norm scale / shift
         # vectors -- would still be stale, so those few KB are carved out into the root unit (gathered up front).
         want_ag = (fuse_allgather_gemm and os.environ.get("HYPERION_FSDP_AG", "fused") == "fused" and self.fused
-                   and not self.reshard and os.environ.get("HYPERION_FSDP_AG_BLOCKS", "1") == "1")
+                   and not self.reshard and os.environ.get("HYPERION_FSDP_AG_BLOCKS", "0") == "1")
+        want_ag = want_ag or os.environ.get("HYPERION_FSDP_AG_CARVE") == "1"   # layout-only switch for the CPU unit test
         owner: dict[str, int] = {}
+        carved_names: set = set()
         for ui, um in enumerate(unit_modules):
             prefix = next((n for n, m in module.named_modules() if m is um), None)
             carve = set()
@@ -133,9 +135,15 @@ class HyperionFSDP(nn.Module):
             for pn, _ in um.named_parameters():
                 if pn not in carve:
                     owner[f"{prefix}.{pn}" if prefix else pn] = ui
+                else:
+                    carved_names.add(f"{prefix}.{pn}" if prefix else pn)
         self.unit_modules = unit_modules
         galloc = self.arena.alloc if self.fused else None
-        self.flat = FlatParams(module.named_parameters(), device=self.device, unit_key=lambda n: owner.get(n, -1),
+        # units are runs of consecutive parameters with the same key: the carved-out vectors go to the front of the list (=
+        # the tail of the reversed flat layout, next to the embeddings) so that they do not cut a block's run in two
+        named = list(module.named_parameters())
+        named = [np_ for np_ in named if np_[0] in carved_names] + [np_ for np_ in named if np_[0] not in carved_names]
+        self.flat = FlatParams(named, device=self.device, unit_key=lambda n: owner.get(n, -1),
                                unit_align=W * 128, grad_allocator=galloc)
         self.units = [(s, e, k) for s, e, k in self.flat.units]
         N = self.flat.numel
@@ -199,7 +207,11 @@ class HyperionFSDP(nn.Module):
             from ..models.transformer import MultiheadSelfAttention
 
             flat_ids = {id(sp.param) for sp in self.flat.specs}
-            blocks_ok = os.environ.get("HYPERION_FSDP_AG_BLOCKS", "1") == "1"
+            # HYPERION_FSDP_AG_BLOCKS=1: composite units (GPT-2 Block, Llama decoder layer) gather inside their first GEMM
+            # too.  Off by default: with resident parameters the stand-alone gathers already hide completely under the
+            # forward, and the gather GEMM runs on the one-CTA kernel -- GPT-2 medium at N=2: 28.1 ms/step fused vs 27.4
+            # plain (profiles/bench/r2); leaf units (nn.Linear / attention in-projection) keep the fused path.
+            blocks_ok = os.environ.get("HYPERION_FSDP_AG_BLOCKS", "0") == "1"
 
             def first_gemm_weight(um):
                 """The weight of the first GEMM a unit's forward runs (registration order == call order in the models here)."""

@@ -347,3 +347,26 @@ def test_flat_params_keep_channels_last_conv_weights():
     assert torch.allclose(w.grad, ref[0].weight.grad, atol=1e-6)
     assert w.grad.data_ptr() == flat.grad.data_ptr() + spec.offset * flat.grad.element_size()
     assert torch.allclose(flat.grad[spec.offset:spec.offset + spec.numel], ref[0].weight.grad.permute(0, 2, 3, 1).reshape(-1), atol=1e-6)
+
+
+def test_fsdp_block_units_stay_whole_when_norm_vectors_are_carved_out(monkeypatch):
+    """K-C3 on composite units: the block's norm vectors move to the root unit (they are read before the GEMM that gathers
+    the block); that must not split a block's parameters into several units."""
+    monkeypatch.setenv("HYPERION_FSDP_AG_CARVE", "1")
+    from hyperion_b200.models import GPT2Config, GPT2LMHeadModel
+    from hyperion_b200.models.gpt2 import Block
+    from hyperion_b200.parallel.fsdp import HyperionFSDP
+
+    torch.manual_seed(0)
+    m = GPT2LMHeadModel(GPT2Config(vocab_size=512, n_positions=64, n_embd=64, n_layer=3, n_head=2))
+    f = HyperionFSDP(m, units=[x for x in m.modules() if isinstance(x, Block)], lr=1e-3)
+    assert all(len(f._key_to_units[k]) == 1 for k in range(3))
+    root = [sp.name for i, sp in enumerate(f.flat.specs) if f.units[f._spec_unit[i]][2] == -1]
+    assert "h.0.ln_1.weight" in root and "h.2.ln_2.bias" in root and "wte.weight" in root
+    ids = torch.randint(0, 512, (2, 32))
+    l0 = float(f.loss(ids).detach())
+    for _ in range(3):
+        loss = f.loss(ids)
+        loss.backward()
+        f.step()
+    assert float(loss.detach()) < l0

@@ -15,7 +15,12 @@ def _torchrun(n, module, *args, timeout=600):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--standalone", "--local-addr", "127.0.0.1",
            f"--nproc-per-node={n}", "-m", module, *args]
     r = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=timeout)
-    assert r.returncode == 0, (r.stdout[-3000:], r.stderr[-3000:])
+    if r.returncode != 0:   # keep the whole log where a gpurun call brings it back
+        out = ROOT / "gpurun_out"
+        out.mkdir(exist_ok=True)
+        (out / ("multi_fail_" + "_".join(a.strip("-") for a in args) + ".log")).write_text(r.stdout + "\n---- stderr ----\n" + r.stderr)
+    rank0 = "\n".join(l for l in r.stderr.splitlines() if "[rank1]" not in l)
+    assert r.returncode == 0, (r.stdout[-2000:], rank0[-4000:])
     return r.stdout
 
 
@@ -46,5 +51,11 @@ def test_block_units_gather_inside_their_first_gemm(reshard):
     """GPT-2-shaped model with one FSDP unit per Block: fused path = all-gather warps inside each block's c_attn GEMM plus
     stand-alone gathers for the root unit (and, with --reshard, FULL_SHARD slots) vs the NCCL path."""
     args = ["--strategy", "fsdp", "--precision", "bf16", "--model", "gpt2"] + (["--reshard"] if reshard else [])
-    out = _torchrun(_n(), "hyperion_b200.parallel.parity", *args)
+    import os
+
+    os.environ["HYPERION_FSDP_AG_BLOCKS"] = "1"   # inherited by the ranks
+    try:
+        out = _torchrun(_n(), "hyperion_b200.parallel.parity", *args)
+    finally:
+        os.environ.pop("HYPERION_FSDP_AG_BLOCKS", None)
     assert "PASS" in out and "FAIL" not in out
