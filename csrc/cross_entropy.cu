@@ -98,6 +98,17 @@ ce_fwd_bwd_reg_kernel(T* __restrict__ logits, long long ld, const long long* __r
   const long long tgt = targets[row];
   const bool ignored = (tgt == ignore_index) || tgt < 0 || tgt >= V;
   const int Vv = (V / 8) * 8;
+  if (ignored && write_grad && row_lse == nullptr) {
+    // a padding position (ignore_index) adds nothing to the loss and its gradient row is zero: store the zeros without
+    // reading the logits (about 40 % of the rows of WikiText-2-shaped batches)
+#pragma unroll
+    for (int k = 0; k < RV; ++k) {
+      const int c = (k * 512 + threadIdx.x) * 8;
+      if (c < Vv) *reinterpret_cast<uint4*>(lrow + c) = make_uint4(0u, 0u, 0u, 0u);
+    }
+    if (threadIdx.x < V - Vv) lrow[Vv + threadIdx.x] = from_f32<T>(0.f);
+    return;
+  }
   uint4 raw[RV];
 #pragma unroll
   for (int k = 0; k < RV; ++k) {

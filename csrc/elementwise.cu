@@ -338,7 +338,10 @@ HYP_API int hyp_stream_copy(const void* x, void* z, long long nbytes, void* stre
 HYP_API int hyp_colsum(const void* x, float* out, int M, int N, long long ld, int dtype, void* stream_) {
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
   HYP_REQUIRE(M > 0 && N > 0, "hyp_colsum: empty input");
-  const bool vec = dtype != DT_F32 && N % 8 == 0 && ld % 8 == 0 && reinterpret_cast<uintptr_t>(x) % 16 == 0;
+  // 16-byte loads need aligned rows; a ragged N is fine as long as the last 8-column group stays inside the row pitch
+  // (the padded logits of a 50257-word vocabulary: N = 50257, ld = 50304) -- columns >= N are summed but never stored
+  const bool vec = dtype != DT_F32 && ld % 8 == 0 && reinterpret_cast<uintptr_t>(x) % 16 == 0 &&
+                   (static_cast<long long>(N) + 7) / 8 * 8 <= ld;
   const int cpb = vec ? 256 : 64;  // columns per block
   const int gx = (N + cpb - 1) / cpb;
   int gy = (num_sms() * 4 + gx - 1) / gx;

@@ -153,6 +153,25 @@ def _declare_bn():
         _bn_declared = True
 
 
+# BatchNorm ``num_batches_tracked`` counters: one fused add for all layers instead of one tiny kernel per layer and step.
+_pending_nbt: list = []
+
+
+def _count_batch(bn) -> None:
+    if bn.num_batches_tracked is not None:
+        _pending_nbt.append(bn.num_batches_tracked)
+        if len(_pending_nbt) >= 512:
+            flush_bn_counters()
+
+
+def flush_bn_counters() -> None:
+    """Apply the pending ``num_batches_tracked += 1`` of every BatchNorm that ran since the last flush (one multi-tensor
+    kernel).  The training engine calls it once per step; checkpoint export calls it before reading the buffers."""
+    if _pending_nbt:
+        torch._foreach_add_(list(_pending_nbt), 1)
+        _pending_nbt.clear()
+
+
 class _BnActFn(torch.autograd.Function):
     """Training-mode BatchNorm2d + (residual add) + ReLU on a channels-last tensor: csrc/bn_act.cu."""
 
@@ -162,7 +181,9 @@ class _BnActFn(torch.autograd.Function):
         N, C, H, W = x.shape
         rows = N * H * W
         y = torch.empty_like(x, memory_format=torch.channels_last)
-        sums = torch.zeros(2 * C, device=x.device, dtype=torch.float32)
+        # one zero-fill serves the forward statistics and, later, the backward reductions of this layer
+        zbuf = torch.zeros(4 * C, device=x.device, dtype=torch.float32)
+        sums, ctx.dsums = zbuf[:2 * C], zbuf[2 * C:]
         mean = torch.empty(C, device=x.device, dtype=torch.float32)
         rstd = torch.empty(C, device=x.device, dtype=torch.float32)
         gf, bf = gamma.float(), beta.float()
@@ -180,7 +201,7 @@ class _BnActFn(torch.autograd.Function):
         dy = dy.contiguous(memory_format=torch.channels_last)
         dx = torch.empty_like(x, memory_format=torch.channels_last)
         dres = torch.empty_like(x, memory_format=torch.channels_last) if ctx.has_res else None
-        dsums = torch.zeros(2 * C, device=x.device, dtype=torch.float32)
+        dsums = ctx.dsums
         _lib.call("hyp_bn_act_bwd", _lib.ptr(dy), _lib.ptr(x), _lib.ptr(y), _lib.ptr(mean), _lib.ptr(rstd), _lib.ptr(gf),
                   _lib.ptr(dsums), _lib.ptr(dx), _lib.ptr(dres), N * H * W, C, int(ctx.relu), _lib.DT[x.dtype], _lib.stream_ptr())
         return dx, dsums[C:].to(ctx.pdtype), dsums[:C].to(ctx.pdtype), dres, None, None, None, None, None
@@ -223,7 +244,7 @@ def conv_bn_act(x, conv: nn.Conv2d, bn: nn.BatchNorm2d, relu: bool = True, resid
         return conv2d_igemm(x, conv.weight, conv.stride[0], conv.padding[0], scale, shift, residual, relu)
     y = _conv(x, conv)
     if _bn_native_ok(y, bn, residual):
-        bn.num_batches_tracked.add_(1)
+        _count_batch(bn)
         return _BnActFn.apply(y, bn.weight, bn.bias, residual, bn.running_mean, bn.running_var, bn.eps, bn.momentum, relu)
     if bn.training:
         if bn.num_batches_tracked is not None:

@@ -24,6 +24,7 @@ def run(strategy: str, precision: str, steps: int, reshard: bool = False, model_
     torch.manual_seed(0)
     gpt2 = model_name == "gpt2"
     if gpt2:
+        os.environ.setdefault("HYPERION_FSDP_AG_BLOCKS", "1")   # exercise the gather-inside-GEMM path on block units
         # block-sized units: every Block is gathered inside its c_attn GEMM (K-C3 on composite units), the root unit (wte,
         # wpe, ln_f and the carved-out block norms) by the stand-alone kernel -- the mix the BASELINE GPT-2 config runs
         from hyperion_b200.models import GPT2Config, GPT2LMHeadModel

@@ -48,7 +48,9 @@ class Engine:
         with nvtx.range("hyperion/backward+comm"):   # reduce-scatter / all-reduce kernels fire from autograd hooks in here
             (scaler.scale_loss(loss) if scaler is not None else loss).backward()
         from ..ops import rng
+        from ..ops.conv import flush_bn_counters
 
+        flush_bn_counters()
         if self.strategy == "fsdp":
             with nvtx.range("hyperion/optimizer(fsdp)"):
                 self.model.step()

@@ -30,6 +30,9 @@ def full_state_dict(model, to_cpu: bool = True, dtype: torch.dtype | None = torc
     """Unwrapped state_dict (all ranks may call; for HyperionFSDP every rank must call -- it gathers).  With
     ``optimizer`` (a ``FusedAdamW``) the fp32 master weights replace the upcast 16-bit compute copy, so the file holds
     true fp32 parameters like the reference's AMP checkpoints."""
+    from ..ops.conv import flush_bn_counters
+
+    flush_bn_counters()
     if hasattr(model, "sync_buffers"):
         model.sync_buffers()
     if hasattr(model, "gather_full_state_dict"):
