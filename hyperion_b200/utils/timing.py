@@ -65,15 +65,58 @@ def time_fn(fn, iters: int = 20, warmup: int = 5, flush_l2: bool = True):
 
 
 class ClockSampler:
-    """Samples nvidia-smi clocks / throttle reasons in a background thread during a timed region."""
+    """Samples SM clock, power and throttle reasons in a background thread during a timed region.
+
+    NVML (``pynvml``) is polled every few milliseconds, so even a 30 ms region (20 steps of the 1.4 ms reference LM) gets
+    samples *during* the region; when NVML is not importable it falls back to ``nvidia-smi -lms``."""
+
+    _REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap",
+                0x80: "hw_power_brake_slowdown"}
 
     def __init__(self, gpu_index: int = 0, period_ms: int = 200):
         self.gpu_index, self.period_ms = gpu_index, period_ms
         self.proc = None
         self.lines: list[str] = []
         self._thr = None
+        self._stop = threading.Event()
+        self._nvml = None
+        self._samples: list[tuple[float, float, int]] = []   # (sm MHz, W, reasons bitmask)
+        self._max_mhz = None
+
+    def _nvml_handle(self):
+        import pynvml
+
+        pynvml.nvmlInit()
+        try:
+            uuid = torch.cuda.get_device_properties(self.gpu_index).uuid
+            return pynvml, pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + str(uuid)).encode())
+        except Exception:  # noqa: BLE001 -- older torch / masked devices: index order
+            return pynvml, pynvml.nvmlDeviceGetHandleByIndex(self.gpu_index)
 
     def start(self):
+        try:
+            nv, h = self._nvml_handle()
+            self._max_mhz = float(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM))
+            self._nvml = (nv, h)
+
+            def poll():
+                while not self._stop.is_set():
+                    try:
+                        mhz = float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM))
+                        watts = nv.nvmlDeviceGetPowerUsage(h) / 1e3
+                        try:
+                            reasons = int(nv.nvmlDeviceGetCurrentClocksEventReasons(h))
+                        except AttributeError:
+                            reasons = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(h))
+                        self._samples.append((mhz, watts, reasons))
+                    except Exception:  # noqa: BLE001
+                        pass
+                    self._stop.wait(0.003)
+            self._thr = threading.Thread(target=poll, daemon=True)
+            self._thr.start()
+            return self
+        except Exception:  # noqa: BLE001 -- no NVML: nvidia-smi below
+            self._nvml = None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.gpu_index}", f"--query-gpu={_QUERY}",
                                           "--format=csv,noheader,nounits", "-lms", str(self.period_ms)],
@@ -90,6 +133,18 @@ class ClockSampler:
         return self
 
     def stop(self) -> dict:
+        if self._nvml is not None:
+            self._stop.set()
+            self._thr.join(timeout=1.0)
+            sm = [s[0] for s in self._samples]
+            reasons = set()
+            for _, _, bits in self._samples:
+                for bit, name in self._REASONS.items():
+                    if bits & bit:
+                        reasons.add(name)
+            return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": self._max_mhz,
+                    "power_w_max": max((s[1] for s in self._samples), default=None), "samples": len(sm),
+                    "reasons": sorted(reasons), "source": "nvml"}
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()
@@ -111,4 +166,5 @@ class ClockSampler:
                 if val.lower().startswith("active"):
                     reasons.add(nm)
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(smax) if smax else None,
-                "power_w_max": max(power) if power else None, "samples": len(sm), "reasons": sorted(reasons)}
+                "power_w_max": max(power) if power else None, "samples": len(sm), "reasons": sorted(reasons),
+                "source": "nvidia-smi"}

@@ -370,3 +370,14 @@ def test_fsdp_block_units_stay_whole_when_norm_vectors_are_carved_out(monkeypatc
         loss.backward()
         f.step()
     assert float(loss.detach()) < l0
+
+
+def test_device_prefetcher_preserves_order_and_values():
+    from hyperion_b200.data import DevicePrefetcher
+
+    bs = [(torch.arange(4) + i, torch.ones(2) * i) for i in range(5)]
+    got = list(DevicePrefetcher(iter(bs), "cpu"))
+    assert len(got) == 5
+    for i, (a, b) in enumerate(got):
+        assert torch.equal(a, torch.arange(4) + i) and torch.equal(b, torch.ones(2) * i)
+    assert list(DevicePrefetcher(iter([]), "cpu")) == []
