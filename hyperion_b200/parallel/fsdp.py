@@ -39,6 +39,16 @@ from .flat import FlatParams
 from .runtime import world
 
 
+# HYPERION_COMM_POISON=1: the race-detection build of the parameter path.  compute-sanitizer is closed on the pod this
+# project is developed on, so ordering bugs between the communication stream and the compute stream are hunted this way
+# instead: every gather destination is filled with NaN on the communication stream right before the gather kernel, so a
+# kernel that reads parameters before its gather event has fired -- or a slot that is reused while its previous owner is
+# still computing -- turns the loss into NaN, which the parity tests assert against (tests/test_gpu_multi.py).
+import os as _os_mod
+
+_POISON = _os_mod.environ.get("HYPERION_COMM_POISON", "0") == "1"
+
+
 def size_based_units(module: nn.Module, min_num_params: int = 100_000) -> list[nn.Module]:
     """Innermost modules holding >= ``min_num_params`` parameters (mirrors size_based_auto_wrap_policy)."""
     units = []
@@ -364,6 +374,8 @@ class HyperionFSDP(nn.Module):
             ev.record(torch.cuda.current_stream(self.device))
             self.comm_stream.wait_event(ev)
             with torch.cuda.stream(self.comm_stream):
+                if _POISON:
+                    dst.fill_(float("nan"))   # debug build: a consumer that runs ahead of the gather event computes NaNs
                 self.arena.allgather(self.shard16, a, b - a, dst)
                 if fr is not None:
                     self.arena.allgather(self.fshard16, fr[0], fr[1], self._fslots[self._slot_of[ui]][:fr[2]])
@@ -635,6 +647,8 @@ class HyperionFSDP(nn.Module):
                         continue
                     s, e, _ = self.units[ui]
                     a, b = self._shard_range(ui)
+                    if _POISON:
+                        self._dst(ui).fill_(float("nan"))
                     self.arena.allgather(self.shard16, a, b - a, self._dst(ui))
                     gev = torch.cuda.Event()
                     gev.record(self.comm_stream)

@@ -64,7 +64,7 @@ def run(strategy: str, precision: str, steps: int, reshard: bool = False, model_
         del eng, model
     lf, sf = results[True]
     ln, sn = results[False]
-    ok = True
+    ok = bool(torch.isfinite(lf).all() and torch.isfinite(ln).all())   # NaN = a poisoned (not yet gathered) buffer was read
     ldiff = (lf - ln).abs().max().item()
     if ldiff > 5e-2:
         ok = False

@@ -59,3 +59,18 @@ def test_block_units_gather_inside_their_first_gemm(reshard):
     finally:
         os.environ.pop("HYPERION_FSDP_AG_BLOCKS", None)
     assert "PASS" in out and "FAIL" not in out
+
+
+@pytest.mark.parametrize("extra", [[], ["--reshard"], ["--model", "gpt2", "--reshard"]])
+def test_no_kernel_reads_a_parameter_before_its_gather_landed(extra):
+    """Race-detection build (HYPERION_COMM_POISON=1): gather destinations are NaN-filled right before each gather kernel,
+    so any consumer that is not ordered after its gather event -- resident units, FULL_SHARD slots being reused, block
+    units -- produces a NaN loss and fails the parity run."""
+    import os
+
+    os.environ["HYPERION_COMM_POISON"] = "1"
+    try:
+        out = _torchrun(_n(), "hyperion_b200.parallel.parity", "--strategy", "fsdp", "--precision", "bf16", *extra)
+    finally:
+        os.environ.pop("HYPERION_COMM_POISON", None)
+    assert "PASS" in out and "FAIL" not in out
