@@ -170,3 +170,43 @@ HYP_API int hyp_sumsq(const void* x, long long n, int dtype, float* out2, void* 
   HYP_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
+
+// ------------------------------------------------------------------------------------------------ loss scaler
+// GradScaler's bookkeeping as two one-thread kernels instead of ~15 tiny elementwise launches per step
+// (torch.cuda.amp.GradScaler in the reference's DDP trainers, 02_development/distributed_utils.py:163, 178-180).
+namespace hyp {
+__global__ void scaler_note_kernel(float* __restrict__ found_inf, const float* __restrict__ sumsq_flag) {
+  // sumsq_flag: (sum of squares, non-finite flag) from the norm / reduce kernels
+  const float s = sumsq_flag[0], f = sumsq_flag[1];
+  if (f != 0.f || !isfinite(s)) found_inf[0] = 1.f;
+}
+__global__ void scaler_update_kernel(float* __restrict__ scale, float* __restrict__ inv_scale, float* __restrict__ growth_tracker,
+                                     float* __restrict__ found_inf, float growth, float backoff, float interval) {
+  float sc = scale[0], gt = growth_tracker[0];
+  if (found_inf[0] != 0.f) {
+    sc *= backoff;
+    gt = 0.f;
+  } else {
+    gt += 1.f;
+    if (gt >= interval) { sc *= growth; gt = 0.f; }
+  }
+  scale[0] = sc;
+  inv_scale[0] = 1.f / sc;
+  growth_tracker[0] = gt;
+  found_inf[0] = 0.f;
+}
+}  // namespace hyp
+
+HYP_API int hyp_scaler_note(float* found_inf, const float* sumsq_flag, void* stream_) {
+  hyp::scaler_note_kernel<<<1, 1, 0, reinterpret_cast<cudaStream_t>(stream_)>>>(found_inf, sumsq_flag);
+  HYP_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+HYP_API int hyp_scaler_update(float* scale, float* inv_scale, float* growth_tracker, float* found_inf, float growth_factor,
+                              float backoff_factor, float growth_interval, void* stream_) {
+  hyp::scaler_update_kernel<<<1, 1, 0, reinterpret_cast<cudaStream_t>(stream_)>>>(scale, inv_scale, growth_tracker, found_inf,
+                                                                                   growth_factor, backoff_factor, growth_interval);
+  HYP_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}

@@ -8,7 +8,7 @@ inside the kernels, so no per-op autocast casts remain on the hot path.
 
 ``DynamicLossScaler`` is the GradScaler equivalent with all state on the device: ``scale``,
 ``growth_tracker`` and ``found_inf`` are tensors; unscale + inf check happen inside the gradient
-all-reduce kernel (multi-GPU) or the AdamW kernel (1 GPU); ``update()`` is three tiny device ops.
+all-reduce kernel (multi-GPU) or the AdamW kernel (1 GPU); ``update()`` is one one-thread kernel (``hyp_scaler_update``).
 ``state_dict`` uses GradScaler's keys so ``{"model_state_dict", "scaler_state_dict"}`` checkpoints
 (02_development/mixed_precision.ipynb c5 L7-15) keep their layout.
 """
@@ -50,8 +50,18 @@ class DynamicLossScaler:
     def scale_loss(self, loss: torch.Tensor) -> torch.Tensor:
         return loss * self.scale.to(loss.dtype).reshape(()) if self.enabled else loss
 
+    def _native(self) -> bool:
+        from .ops import _lib
+
+        return self.scale.is_cuda and _lib.available() and hasattr(_lib.raw(), "hyp_scaler_update")
+
     def note_overflow(self, sumsq_flag: torch.Tensor) -> None:
         """``sumsq_flag``: fp32[2] from the norm kernel; element 1 (or a non-finite sum) marks an overflow."""
+        if self._native() and sumsq_flag.dtype == torch.float32 and sumsq_flag.is_contiguous():
+            from .ops import _lib
+
+            _lib.call("hyp_scaler_note", _lib.ptr(self.found_inf), _lib.ptr(sumsq_flag), _lib.stream_ptr(self.scale.device))
+            return
         bad = (sumsq_flag[1] != 0) | ~torch.isfinite(sumsq_flag[0])
         self.found_inf.copy_(torch.maximum(self.found_inf, bad.float().reshape(1)))
 
@@ -59,6 +69,13 @@ class DynamicLossScaler:
     def update(self) -> None:
         """GradScaler.update(): back off on overflow, grow after ``growth_interval`` clean steps (device-side)."""
         if not self.enabled:
+            return
+        if self._native():
+            from .ops import _lib
+
+            _lib.call("hyp_scaler_update", _lib.ptr(self.scale), _lib.ptr(self.inv_scale), _lib.ptr(self.growth_tracker),
+                      _lib.ptr(self.found_inf), float(self.growth_factor), float(self.backoff_factor),
+                      float(self.growth_interval), _lib.stream_ptr(self.scale.device))
             return
         overflow = self.found_inf != 0
         grown = self.growth_tracker + 1

@@ -28,7 +28,7 @@ from ..models import FallbackCNN, create_custom_transformer, create_resnet50, cr
 from ..train.engine import build_engine
 
 COLUMNS = ["Model", "Forward Time (ms)", "Backward Time (ms)", "Optimizer Time (ms)", "Total Time (ms)",
-           "Memory Usage (MB)", "Throughput (samples/s)"]
+           "Memory Usage (MB)", "Throughput (samples/s)", "Math"]   # the reference's seven columns + the arithmetic used
 
 
 def _loop_ms(fn, iters: int, device) -> float:
@@ -52,6 +52,15 @@ def benchmark_model(model_fn, input_shape, target_shape, num_iterations: int = 5
                     precision: str = "fp32", device=None, name: str | None = None) -> dict:
     device = torch.device(device or ("cuda" if torch.cuda.is_available() else "cpu"))
     model = model_fn()
+    # "fp32" is true IEEE fp32 as in the reference's run (fp32 tensors stay on the library path with TF32 off); "tf32" is
+    # fp32 storage on the tensor cores (tcgen05 kind::tf32)
+    from ..ops.functional import fp32_math, set_fp32_math
+
+    prev_math = fp32_math()
+    if precision in ("fp32", "tf32"):
+        set_fp32_math("ieee" if precision == "fp32" else "tf32")
+    math_label = {"fp32": "fp32 (IEEE)", "tf32": "tf32 (fp32 storage, tensor cores)"}.get(precision, precision)
+    precision = "fp32" if precision == "tf32" else precision
     eng = build_engine(model, strategy="single", precision=precision if device.type == "cuda" else "fp32", lr=1e-3,
                        weight_decay=0.0, device=device)
     dt = eng.precision.dtype
@@ -81,11 +90,14 @@ def benchmark_model(model_fn, input_shape, target_shape, num_iterations: int = 5
     if device.type == "cuda":
         torch.cuda.synchronize(device)
     bwd = max(fb - f, 0.0)
-    opt = max(t - fb, 0.0)
+    # the optimizer is timed on its own (the gradients of the last backward are still in the flat buffer): the difference
+    # of two loop timings used before was noise for models whose step is a single 1 ms kernel
+    opt = _loop_ms(lambda: eng.optimizer.step(), num_iterations, device) if eng.optimizer is not None else max(t - fb, 0.0)
     total = f + bwd + opt
+    set_fp32_math(prev_math)
     return {"Model": name or getattr(model_fn, "__name__", "model"), "Forward Time (ms)": f, "Backward Time (ms)": bwd,
             "Optimizer Time (ms)": opt, "Total Time (ms)": total, "Memory Usage (MB)": mem.sample().peak_mb,
-            "Throughput (samples/s)": input_shape[0] / (total / 1e3)}
+            "Throughput (samples/s)": input_shape[0] / (total / 1e3), "Math": math_label}
 
 
 def run_baseline_benchmarks(batch: int = 32, precision: str = "fp32", out_dir: str | None = None, iters: int = 50,
@@ -125,7 +137,7 @@ def test_batch_size_scaling(model_fn=create_resnet50, input_hw=(3, 224, 224), ou
 def main(argv=None) -> int:
     ap = argparse.ArgumentParser(prog="hyperion baseline")
     ap.add_argument("--out", default="results/benchmarks")
-    ap.add_argument("--precision", default="fp32", choices=["fp32", "fp16", "bf16"])
+    ap.add_argument("--precision", default="fp32", choices=["fp32", "tf32", "fp16", "bf16"])
     ap.add_argument("--batch", type=int, default=32)
     ap.add_argument("--iters", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=10)

@@ -53,16 +53,19 @@ def test_precision_formats(device, sizes=(1024, 2048, 4096, 8192), iters: int = 
     from ..ops import _lib, native
 
     rows = []
-    dts = [(torch.float32, "FP32"), (torch.float16, "FP16"), (torch.bfloat16, "BF16")]
+    # FP32 = true IEEE fp32 like the reference's sweep (library matmul, TF32 off; the tensor-core GEMM has no such mode, so
+    # its column stays empty); TF32 = fp32 storage on the tensor cores, library with allow_tf32 vs tcgen05 kind::tf32
+    dts = [(torch.float32, "FP32"), (torch.float32, "TF32"), (torch.float16, "FP16"), (torch.bfloat16, "BF16")]
     for n in sizes:
         for dt, name in dts:
             x = torch.rand(n, n, device=device).to(dt)
             y = torch.rand(n, n, device=device).to(dt)
             out = torch.empty(n, n, device=device, dtype=dt)
-            torch.backends.cuda.matmul.allow_tf32 = True  # the own GEMM runs fp32 as tf32; compare like with like
+            torch.backends.cuda.matmul.allow_tf32 = (name == "TF32")
             _, t_torch = time_fn(lambda: torch.matmul(x, y, out=out), iters, 3)
+            torch.backends.cuda.matmul.allow_tf32 = False
             row = {"Size": n, "Precision": name, "Time (s)": t_torch / 1e3, "TFLOPS": 2 * n ** 3 / (t_torch / 1e3) / 1e12}
-            if torch.device(device).type == "cuda" and _lib.available():
+            if torch.device(device).type == "cuda" and _lib.available() and name != "FP32":
                 yt = y.t().contiguous()  # the own GEMM takes B as [N, K]
                 _, t_own = time_fn(lambda: native.gemm(x, yt, out=out), iters, 3)
                 row["Time tcgen05 (s)"] = t_own / 1e3

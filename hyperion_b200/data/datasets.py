@@ -20,9 +20,18 @@ class WikiText2TorchDataset(Dataset):
             ids, mask = data
             self.ids, self.mask = torch.as_tensor(ids, dtype=torch.long), torch.as_tensor(mask, dtype=torch.long)
         else:
-            data = data.with_format("torch")
-            self.ids = data["input_ids"][:].long()
-            self.mask = data["attention_mask"][:].long()
+            # straight from the arrow table (fixed-length lists -> one reshape), no datasets formatter: both its torch and
+            # numpy formatters import torchvision.io.VideoReader whenever torchvision is loaded, which this image lacks
+            import numpy as np
+
+            def column(name):
+                if getattr(data, "_indices", None) is None:
+                    col = data.data.column(name).combine_chunks()
+                    return col.values.to_numpy(zero_copy_only=False).reshape(len(col), -1).astype(np.int64)
+                return np.asarray(data.with_format(None)[name], dtype=np.int64)
+
+            self.ids = torch.from_numpy(column("input_ids"))
+            self.mask = torch.from_numpy(column("attention_mask"))
 
     def __len__(self):
         return self.ids.shape[0]

@@ -40,6 +40,8 @@ _SIGS = {
     "hyp_norm_bwd_fused": "ppppppppppipliiiip",
     "hyp_adamw": "ppppplii" + "fffff" + "i" + "f" + "ppppp",
     "hyp_sumsq": "plipp",
+    "hyp_scaler_note": "ppp",
+    "hyp_scaler_update": "ppppfffp",
     "hyp_ce_fwd_bwd": "plpiilpppfiip",
     "hyp_ce_finalize": "pppp",
     "hyp_embedding_fwd": "ppplilip",

@@ -18,6 +18,23 @@ from . import _lib, gradslot, native, rng
 
 _SUPPORTED = (torch.float32, torch.float16, torch.bfloat16)
 
+# fp32 tensors: "tf32" runs them on the tensor cores (tcgen05 kind::tf32, 10-bit mantissa products, fp32 accumulation);
+# "ieee" keeps true fp32 arithmetic by leaving fp32 tensors to the library path with TF32 off -- what the reference's fp32
+# baseline benchmark computes (baseline_performance.ipynb c0 L92-101).  HYPERION_FP32 / set_fp32_math() select it.
+_FP32_MATH = os.environ.get("HYPERION_FP32", "tf32")
+
+
+def set_fp32_math(mode: str) -> None:
+    global _FP32_MATH
+    assert mode in ("tf32", "ieee")
+    _FP32_MATH = mode
+    if mode == "ieee":
+        torch.backends.cuda.matmul.allow_tf32 = False
+
+
+def fp32_math() -> str:
+    return _FP32_MATH
+
 
 def _native(*tensors) -> bool:
     """True -> run the sm_100a kernels.  CUDA tensors without the library are an error."""
@@ -27,6 +44,8 @@ def _native(*tensors) -> bool:
     if not _lib.available():
         if torch.cuda.is_available() and _lib.raw() is None:
             raise RuntimeError("CUDA tensor given but libhyperion_b200.so is not built; run `python -m hyperion_b200.build`")
+        return False
+    if t0.dtype == torch.float32 and _FP32_MATH == "ieee":
         return False
     return t0.dtype in _SUPPORTED
 

@@ -131,6 +131,12 @@ int hyp_adamw(float* p, const void* g, float* m, float* v, void* p_copy, long lo
               const float* sumsq, const float* inv_scale, const float* found_inf, const float* step_ptr, void* stream);
 /* out2[0] += sum(x^2); out2[1] = 1 if a non-finite value was seen. */
 int hyp_sumsq(const void* x, long long n, int dtype, float* out2, void* stream);
+/* Loss-scaler bookkeeping on the device (GradScaler of the reference's DDP trainers, distributed_utils.py:163, 178-180):
+ * note = raise found_inf when the (sum of squares, non-finite flag) pair reports an overflow; update = back off on overflow,
+ * grow after growth_interval clean steps, refresh inv_scale, clear found_inf.  All arguments are device fp32 scalars. */
+int hyp_scaler_note(float* found_inf, const float* sumsq_flag, void* stream);
+int hyp_scaler_update(float* scale, float* inv_scale, float* growth_tracker, float* found_inf, float growth_factor,
+                      float backoff_factor, float growth_interval, void* stream);
 
 /* ---- fused cross-entropy (csrc/cross_entropy.cu) -------------------------------
  * Per row: lse, NLL (accumulated into loss_sum_count[0], count into [1]) and, when

@@ -18,12 +18,12 @@ def test_probe_csv_schemas(tmp_path):
     assert probe.main(["--out", str(tmp_path), "--sizes", "256", "--bw-sizes", "10"]) == 0
     prec = pd.read_csv(tmp_path / "precision_results.csv")
     assert list(prec.columns)[:4] == ["Size", "Precision", "Time (s)", "TFLOPS"]
-    assert set(prec["Precision"]) == {"FP32", "FP16", "BF16"}
+    assert set(prec["Precision"]) == {"FP32", "TF32", "FP16", "BF16"}
     bw = pd.read_csv(tmp_path / "bandwidth_results.csv")
     assert list(bw.columns)[:2] == ["Size (M elements)", "Bandwidth (GB/s)"]
 
 
-def test_benchmark_utils_return_keys():
+def test_benchmark_utils_return_keys(tmp_path):
     from hyperion_b200.bench.utils import (benchmark_forward_pass, benchmark_training_step, compare_precision_formats,
                                            save_benchmark_results)
 
@@ -33,6 +33,16 @@ def test_benchmark_utils_return_keys():
     assert set(benchmark_training_step(net(), (16,), (16,), 4, 3, 1)) == keys
     df = compare_precision_formats(net, (16,), (16,), batch_sizes=(2, 4), precisions=("fp32",), iterations=2, warmup=1)
     assert len(df) == 2 and {"batch_size", "precision", "throughput"} <= set(df.columns)
+    # the reference's own call forms (Phase 1/benchmarking.py:12-17, 57-66, 153-158, 223-227)
+    m = net()
+    x, y = torch.rand(4, 16), torch.rand(4, 16)
+    assert set(benchmark_forward_pass(m, x, num_iterations=3, warmup=1)) == keys
+    opt = torch.optim.Adam(m.parameters(), lr=3e-3)
+    assert set(benchmark_training_step(m, x, y, opt, torch.nn.MSELoss(), num_iterations=3, warmup=1)) == keys
+    df2 = compare_precision_formats(net, (16,), batch_sizes=[2], num_iterations=2, warmup=1, precisions=("fp32",))
+    assert len(df2) == 1
+    p = save_benchmark_results(df2, "ref_form.csv", results_dir=str(tmp_path))
+    assert p.endswith("ref_form.csv") and (tmp_path / "ref_form.csv").exists()
 
 
 def test_baseline_benchmark_columns(tmp_path):
@@ -41,7 +51,7 @@ def test_baseline_benchmark_columns(tmp_path):
 
     r = benchmark_model(create_custom_transformer, (2, 16, 512), (2, 16, 512), 2, 1)
     assert set(COLUMNS) <= set(r)
-    assert COLUMNS == ["Model", "Forward Time (ms)", "Backward Time (ms)", "Optimizer Time (ms)", "Total Time (ms)",
+    assert COLUMNS[:7] == ["Model", "Forward Time (ms)", "Backward Time (ms)", "Optimizer Time (ms)", "Total Time (ms)",
                        "Memory Usage (MB)", "Throughput (samples/s)"]
     tiny = lambda: nn.Sequential(nn.Flatten(), nn.Linear(3 * 8 * 8, 10))
     tiny.__name__ = "tiny"
