@@ -45,10 +45,10 @@ __global__ void __launch_bounds__(256) stats_kernel(const T* __restrict__ x, flo
 }
 
 // y = relu?((x - mean) * rstd * gamma + beta (+ res)); also writes mean / rstd and updates the running statistics.
-template <typename T>
+template <typename T, typename P = float>
 __global__ void __launch_bounds__(256)
-apply_kernel(const T* __restrict__ x, const T* __restrict__ res, const float* __restrict__ sums, const float* __restrict__ gamma,
-             const float* __restrict__ beta, T* __restrict__ y, float* __restrict__ mean_out, float* __restrict__ rstd_out,
+apply_kernel(const T* __restrict__ x, const T* __restrict__ res, const float* __restrict__ sums, const P* __restrict__ gamma,
+             const P* __restrict__ beta, T* __restrict__ y, float* __restrict__ mean_out, float* __restrict__ rstd_out,
              float* __restrict__ running_mean, float* __restrict__ running_var, long long rows, int C, float eps,
              float momentum, int relu) {
   const long long total = rows * C / 8;
@@ -63,7 +63,7 @@ apply_kernel(const T* __restrict__ x, const T* __restrict__ res, const float* __
     for (int k = 0; k < 8; ++k) {
       const float m = sums[c0 + k] * inv_n;
       const float var = fmaxf(sums[C + c0 + k] * inv_n - m * m, 0.f);
-      const float t = (v[k] - m) * rsqrtf(var + eps) * gamma[c0 + k] + beta[c0 + k] + (res ? r[k] : 0.f);
+      const float t = (v[k] - m) * rsqrtf(var + eps) * to_f32<P>(gamma[c0 + k]) + to_f32<P>(beta[c0 + k]) + (res ? r[k] : 0.f);
       o[k] = relu ? fmaxf(t, 0.f) : t;
     }
     *reinterpret_cast<uint4*>(y + i * 8) = pack8<T>(o);
@@ -121,10 +121,10 @@ bwd_reduce_kernel(const T* __restrict__ dy, const T* __restrict__ x, const T* __
   }
 }
 
-template <typename T>
+template <typename T, typename P = float>
 __global__ void __launch_bounds__(256)
 bwd_dx_kernel(const T* __restrict__ dy, const T* __restrict__ x, const T* __restrict__ y, const float* __restrict__ mean,
-              const float* __restrict__ rstd, const float* __restrict__ gamma, const float* __restrict__ dsums,
+              const float* __restrict__ rstd, const P* __restrict__ gamma, const float* __restrict__ dsums,
               T* __restrict__ dx, T* __restrict__ dres, long long rows, int C, int relu) {
   const long long total = rows * C / 8;
   const float inv_n = 1.f / static_cast<float>(rows);
@@ -140,7 +140,7 @@ bwd_dx_kernel(const T* __restrict__ dy, const T* __restrict__ x, const T* __rest
       const float g = (relu && !(yv[k] > 0.f)) ? 0.f : d[k];
       d[k] = g;
       const float xh = (xv[k] - mean[c0 + k]) * rstd[c0 + k];
-      o[k] = gamma[c0 + k] * rstd[c0 + k] * (g - dsums[c0 + k] * inv_n - xh * dsums[C + c0 + k] * inv_n);
+      o[k] = to_f32<P>(gamma[c0 + k]) * rstd[c0 + k] * (g - dsums[c0 + k] * inv_n - xh * dsums[C + c0 + k] * inv_n);
     }
     *reinterpret_cast<uint4*>(dx + i * 8) = pack8<T>(o);
     if (dres) *reinterpret_cast<uint4*>(dres + i * 8) = pack8<T>(d);
@@ -206,6 +206,54 @@ HYP_API int hyp_bn_act_bwd(const void* dy, const void* x, const void* y, const f
   } else {
     bn::bwd_reduce_kernel<__half><<<grid, 256, 0, st>>>((const __half*)dy, (const __half*)x, (const __half*)y, mean, rstd, dsums, rows, C, rpb, relu);
     bn::bwd_dx_kernel<__half><<<eg, 256, 0, st>>>((const __half*)dy, (const __half*)x, (const __half*)y, mean, rstd, gamma, dsums, (__half*)dx, (__half*)dres, rows, C, relu);
+  }
+  HYP_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+
+// Same two entry points with gamma / beta in the activations' 16-bit dtype (the layout a mixed-precision module holds them
+// in), so the caller does not launch two cast kernels per layer and step.
+HYP_API int hyp_bn_act_fwd_p16(const void* x, const void* res, const void* gamma, const void* beta, void* y, float* sums,
+                               float* mean, float* rstd, float* running_mean, float* running_var, long long rows, int C,
+                               float eps, float momentum, int relu, int dtype, void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  HYP_REQUIRE(dtype == DT_BF16 || dtype == DT_F16, "hyp_bn_act_fwd_p16: 16-bit dtypes only");
+  HYP_REQUIRE(rows > 0 && C > 0 && C % 8 == 0, "hyp_bn_act_fwd_p16: need C %% 8 == 0 (C=%d)", C);
+  dim3 grid; long long rpb;
+  bn::reduce_grid(rows, C, &grid, &rpb);
+  const int eg = bn::ew_grid(rows * C / 8);
+  const int eg2 = eg * 256 < C ? (C + 255) / 256 : eg;
+  if (dtype == DT_BF16) {
+    using T = __nv_bfloat16;
+    bn::stats_kernel<T><<<grid, 256, 0, st>>>((const T*)x, sums, rows, C, rpb);
+    bn::apply_kernel<T, T><<<eg2, 256, 0, st>>>((const T*)x, (const T*)res, sums, (const T*)gamma, (const T*)beta, (T*)y, mean, rstd, running_mean, running_var, rows, C, eps, momentum, relu);
+  } else {
+    using T = __half;
+    bn::stats_kernel<T><<<grid, 256, 0, st>>>((const T*)x, sums, rows, C, rpb);
+    bn::apply_kernel<T, T><<<eg2, 256, 0, st>>>((const T*)x, (const T*)res, sums, (const T*)gamma, (const T*)beta, (T*)y, mean, rstd, running_mean, running_var, rows, C, eps, momentum, relu);
+  }
+  HYP_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+HYP_API int hyp_bn_act_bwd_p16(const void* dy, const void* x, const void* y, const float* mean, const float* rstd,
+                               const void* gamma, float* dsums, void* dx, void* dres, long long rows, int C, int relu,
+                               int dtype, void* stream_) {
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
+  HYP_REQUIRE(dtype == DT_BF16 || dtype == DT_F16, "hyp_bn_act_bwd_p16: 16-bit dtypes only");
+  HYP_REQUIRE(rows > 0 && C > 0 && C % 8 == 0, "hyp_bn_act_bwd_p16: need C %% 8 == 0 (C=%d)", C);
+  dim3 grid; long long rpb;
+  bn::reduce_grid(rows, C, &grid, &rpb);
+  const int eg = bn::ew_grid(rows * C / 8);
+  if (dtype == DT_BF16) {
+    using T = __nv_bfloat16;
+    bn::bwd_reduce_kernel<T><<<grid, 256, 0, st>>>((const T*)dy, (const T*)x, (const T*)y, mean, rstd, dsums, rows, C, rpb, relu);
+    bn::bwd_dx_kernel<T, T><<<eg, 256, 0, st>>>((const T*)dy, (const T*)x, (const T*)y, mean, rstd, (const T*)gamma, dsums, (T*)dx, (T*)dres, rows, C, relu);
+  } else {
+    using T = __half;
+    bn::bwd_reduce_kernel<T><<<grid, 256, 0, st>>>((const T*)dy, (const T*)x, (const T*)y, mean, rstd, dsums, rows, C, rpb, relu);
+    bn::bwd_dx_kernel<T, T><<<eg, 256, 0, st>>>((const T*)dy, (const T*)x, (const T*)y, mean, rstd, (const T*)gamma, dsums, (T*)dx, (T*)dres, rows, C, relu);
   }
   HYP_CHECK_CUDA(cudaGetLastError());
   return 0;

@@ -11,67 +11,52 @@
 
 namespace hyp {
 
+// One block streams a contiguous run of 4 x 512 sixteen-byte vectors: every thread issues its four loads of both operands
+// (8 x 16 B in flight) before the first add, and consecutive blocks touch consecutive DRAM pages.  A persistent
+// grid-stride version with two loads in flight per operand reached 6.36 TB/s on 500 M fp32 elements where
+// torch's elementwise kernel reached 7.0; this shape closes that gap.
 template <typename T>
 __global__ void __launch_bounds__(512) stream_add_kernel(const T* __restrict__ x, const T* __restrict__ y,
                                                          T* __restrict__ z, long long n) {
   constexpr int V = 16 / sizeof(T);
+  constexpr int U = 4;
   const long long nv = n / V;
-  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
   const uint4* x4 = reinterpret_cast<const uint4*>(x);
   const uint4* y4 = reinterpret_cast<const uint4*>(y);
   uint4* z4 = reinterpret_cast<uint4*>(z);
-  long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
-  // two independent 16-byte loads per operand in flight per thread
-  for (; i + stride < nv; i += 2 * stride) {
-    const uint4 a0 = ld_nc_v4(x4 + i), b0 = ld_nc_v4(y4 + i);
-    const uint4 a1 = ld_nc_v4(x4 + i + stride), b1 = ld_nc_v4(y4 + i + stride);
-    uint4 r0, r1;
-    if constexpr (sizeof(T) == 4) {
-      const float* fa = reinterpret_cast<const float*>(&a0);
-      const float* fb = reinterpret_cast<const float*>(&b0);
-      float* fr = reinterpret_cast<float*>(&r0);
+  const long long base = static_cast<long long>(blockIdx.x) * (U * 512) + threadIdx.x;
+  uint4 a[U], b[U];
 #pragma unroll
-      for (int k = 0; k < 4; ++k) fr[k] = fa[k] + fb[k];
-      fa = reinterpret_cast<const float*>(&a1);
-      fb = reinterpret_cast<const float*>(&b1);
-      fr = reinterpret_cast<float*>(&r1);
-#pragma unroll
-      for (int k = 0; k < 4; ++k) fr[k] = fa[k] + fb[k];
-    } else {
-      float fa[8], fb[8];
-      unpack8<T>(a0, fa); unpack8<T>(b0, fb);
-#pragma unroll
-      for (int k = 0; k < 8; ++k) fa[k] += fb[k];
-      r0 = pack8<T>(fa);
-      unpack8<T>(a1, fa); unpack8<T>(b1, fb);
-#pragma unroll
-      for (int k = 0; k < 8; ++k) fa[k] += fb[k];
-      r1 = pack8<T>(fa);
-    }
-    z4[i] = r0;
-    z4[i + stride] = r1;
+  for (int k = 0; k < U; ++k) {
+    const long long i = base + k * 512;
+    if (i < nv) { a[k] = ld_nc_v4(x4 + i); b[k] = ld_nc_v4(y4 + i); }
   }
-  for (; i < nv; i += stride) {
-    const uint4 a0 = ld_nc_v4(x4 + i), b0 = ld_nc_v4(y4 + i);
-    uint4 r0;
-    if constexpr (sizeof(T) == 4) {
-      const float* fa = reinterpret_cast<const float*>(&a0);
-      const float* fb = reinterpret_cast<const float*>(&b0);
-      float* fr = reinterpret_cast<float*>(&r0);
 #pragma unroll
-      for (int k = 0; k < 4; ++k) fr[k] = fa[k] + fb[k];
-    } else {
-      float fa[8], fb[8];
-      unpack8<T>(a0, fa); unpack8<T>(b0, fb);
+  for (int k = 0; k < U; ++k) {
+    const long long i = base + k * 512;
+    if (i < nv) {
+      uint4 r;
+      if constexpr (sizeof(T) == 4) {
+        const float* fa = reinterpret_cast<const float*>(&a[k]);
+        const float* fb = reinterpret_cast<const float*>(&b[k]);
+        float* fr = reinterpret_cast<float*>(&r);
 #pragma unroll
-      for (int k = 0; k < 8; ++k) fa[k] += fb[k];
-      r0 = pack8<T>(fa);
+        for (int e = 0; e < 4; ++e) fr[e] = fa[e] + fb[e];
+      } else {
+        float fa[8], fb[8];
+        unpack8<T>(a[k], fa); unpack8<T>(b[k], fb);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) fa[e] += fb[e];
+        r = pack8<T>(fa);
+      }
+      z4[i] = r;
     }
-    z4[i] = r0;
   }
-  // scalar tail
-  const long long t = nv * V + static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (t < n) z[t] = from_f32<T>(to_f32<T>(x[t]) + to_f32<T>(y[t]));
+  // scalar tail (fewer than V elements): first block
+  if (blockIdx.x == 0) {
+    const long long t = nv * V + threadIdx.x;
+    if (t < n) z[t] = from_f32<T>(to_f32<T>(x[t]) + to_f32<T>(y[t]));
+  }
 }
 
 __global__ void __launch_bounds__(512) stream_copy_kernel(const uint4* __restrict__ x, uint4* __restrict__ z,
@@ -313,13 +298,14 @@ HYP_API int hyp_stream_add(const void* x, const void* y, void* z, long long n, i
   if (n == 0) return 0;
   HYP_REQUIRE(((uintptr_t)x | (uintptr_t)y | (uintptr_t)z) % 16 == 0, "hyp_stream_add: pointers must be 16B aligned");
   const int threads = 512;
+  auto add_grid = [](long long nv) { return static_cast<unsigned>((nv + 2047) / 2048 > 0 ? (nv + 2047) / 2048 : 1); };
   if (dtype == DT_F32) {
-    stream_add_kernel<float><<<stream_grid(n / 8 + 1, threads), threads, 0, st>>>((const float*)x, (const float*)y, (float*)z, n);
+    stream_add_kernel<float><<<add_grid(n / 4), threads, 0, st>>>((const float*)x, (const float*)y, (float*)z, n);
   } else if (dtype == DT_BF16) {
-    stream_add_kernel<__nv_bfloat16><<<stream_grid(n / 16 + 1, threads), threads, 0, st>>>(
+    stream_add_kernel<__nv_bfloat16><<<add_grid(n / 8), threads, 0, st>>>(
         (const __nv_bfloat16*)x, (const __nv_bfloat16*)y, (__nv_bfloat16*)z, n);
   } else {
-    stream_add_kernel<__half><<<stream_grid(n / 16 + 1, threads), threads, 0, st>>>((const __half*)x, (const __half*)y, (__half*)z, n);
+    stream_add_kernel<__half><<<add_grid(n / 8), threads, 0, st>>>((const __half*)x, (const __half*)y, (__half*)z, n);
   }
   HYP_CHECK_CUDA(cudaGetLastError());
   return 0;

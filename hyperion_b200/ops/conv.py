@@ -3,8 +3,9 @@
 Data runs channels-last (NHWC).  Convolution forward is the tcgen05 implicit GEMM of
 ``csrc/conv_igemm.cu`` (one 4-D TMA box per filter tap, no im2col buffer) whenever the
 input channels are a multiple of 64; 1x1 stride-1 convolutions are routed to the plain
-tcgen05 GEMM (an NHWC 1x1 conv *is* ``[N*H*W, Cin] @ W[Cout, Cin]^T``); the 3-channel
-stem and the conv backward (dgrad / wgrad) stay on cuDNN.  In training the
+tcgen05 GEMM (an NHWC 1x1 conv *is* ``[N*H*W, Cin] @ W[Cout, Cin]^T``); the weight gradient is the
+pixel-reduction implicit GEMM ``conv_wgrad_kernel``; the 3-channel stem and -- by default, see ``_igemm_dgrad_on`` --
+the data gradient are on cuDNN (a native stride-1 dgrad exists: ``HYPERION_CONV_DGRAD=igemm``).  In training the
 BatchNorm-apply + ReLU + residual-add tail is one fused pass (``csrc/bn_act.cu``);
 in eval mode BatchNorm is folded into the convolution's epilogue together with the
 residual add and the ReLU, so a whole Conv-BN-(+res)-ReLU block is one kernel.
@@ -40,7 +41,11 @@ def _igemm_ok(x, conv: nn.Conv2d) -> bool:
 def _igemm_dgrad_on() -> bool:
     import os
 
-    return os.environ.get("HYPERION_CONV_DGRAD", "igemm") == "igemm"
+    # default cuDNN: measured per part on the step benches (profiles/bench/r2/r2n_*): ResNet-50 14.93 ms all-native,
+    # 14.64 with cuDNN dgrad, 14.72 with cuDNN wgrad, 14.44 with both; ResNet-18/CIFAR 1.41 / 1.19 / 1.48 / 1.26 -- the native
+    # dgrad (forward kernel over dy with a filter that has to be flipped and re-laid-out every step, stride 1 only) loses
+    # on both, the native wgrad wins on the small model and is within 1.4 % on the large one, so it stays the default
+    return os.environ.get("HYPERION_CONV_DGRAD", "cudnn") == "igemm"
 
 
 def _igemm_wgrad_on() -> bool:
@@ -150,6 +155,9 @@ def _declare_bn():
     if not _bn_declared:
         _lib.declare("hyp_bn_act_fwd", "pppppppppp" + "li" + "ff" + "ii" + "p")
         _lib.declare("hyp_bn_act_bwd", "ppppppppp" + "li" + "ii" + "p")
+        if hasattr(_lib.raw(), "hyp_bn_act_fwd_p16"):
+            _lib.declare("hyp_bn_act_fwd_p16", "pppppppppp" + "li" + "ff" + "ii" + "p")
+            _lib.declare("hyp_bn_act_bwd_p16", "ppppppppp" + "li" + "ii" + "p")
         _bn_declared = True
 
 
@@ -186,8 +194,11 @@ class _BnActFn(torch.autograd.Function):
         sums, ctx.dsums = zbuf[:2 * C], zbuf[2 * C:]
         mean = torch.empty(C, device=x.device, dtype=torch.float32)
         rstd = torch.empty(C, device=x.device, dtype=torch.float32)
-        gf, bf = gamma.float(), beta.float()
-        _lib.call("hyp_bn_act_fwd", _lib.ptr(x), _lib.ptr(residual), _lib.ptr(gf), _lib.ptr(bf), _lib.ptr(y), _lib.ptr(sums),
+        # 16-bit gamma / beta go to the kernels as they are (hyp_bn_act_*_p16); fp32 ones take the original entry points
+        p16 = gamma.dtype == x.dtype and beta.dtype == x.dtype and hasattr(_lib.raw(), "hyp_bn_act_fwd_p16")
+        gf, bf = (gamma.detach(), beta.detach()) if p16 else (gamma.float(), beta.float())
+        ctx.p16 = p16
+        _lib.call("hyp_bn_act_fwd_p16" if p16 else "hyp_bn_act_fwd", _lib.ptr(x), _lib.ptr(residual), _lib.ptr(gf), _lib.ptr(bf), _lib.ptr(y), _lib.ptr(sums),
                   _lib.ptr(mean), _lib.ptr(rstd), _lib.ptr(running_mean), _lib.ptr(running_var), rows, C, float(eps),
                   float(momentum), int(relu), _lib.DT[x.dtype], _lib.stream_ptr())
         ctx.save_for_backward(x, y, mean, rstd, gf)
@@ -202,7 +213,7 @@ class _BnActFn(torch.autograd.Function):
         dx = torch.empty_like(x, memory_format=torch.channels_last)
         dres = torch.empty_like(x, memory_format=torch.channels_last) if ctx.has_res else None
         dsums = ctx.dsums
-        _lib.call("hyp_bn_act_bwd", _lib.ptr(dy), _lib.ptr(x), _lib.ptr(y), _lib.ptr(mean), _lib.ptr(rstd), _lib.ptr(gf),
+        _lib.call("hyp_bn_act_bwd_p16" if ctx.p16 else "hyp_bn_act_bwd", _lib.ptr(dy), _lib.ptr(x), _lib.ptr(y), _lib.ptr(mean), _lib.ptr(rstd), _lib.ptr(gf),
                   _lib.ptr(dsums), _lib.ptr(dx), _lib.ptr(dres), N * H * W, C, int(ctx.relu), _lib.DT[x.dtype], _lib.stream_ptr())
         return dx, dsums[C:].to(ctx.pdtype), dsums[:C].to(ctx.pdtype), dres, None, None, None, None, None
 

@@ -262,6 +262,12 @@ int hyp_bn_act_fwd(const void* x, const void* res, const float* gamma, const flo
                    int relu, int dtype, void* stream);
 int hyp_bn_act_bwd(const void* dy, const void* x, const void* y, const float* mean, const float* rstd, const float* gamma,
                    float* dsums, void* dx, void* dres, long long rows, int C, int relu, int dtype, void* stream);
+/* The same pair with gamma / beta in the activations' 16-bit dtype (no per-layer cast launches in a mixed-precision module). */
+int hyp_bn_act_fwd_p16(const void* x, const void* res, const void* gamma, const void* beta, void* y, float* sums, float* mean,
+                       float* rstd, float* running_mean, float* running_var, long long rows, int C, float eps, float momentum,
+                       int relu, int dtype, void* stream);
+int hyp_bn_act_bwd_p16(const void* dy, const void* x, const void* y, const float* mean, const float* rstd, const void* gamma,
+                       float* dsums, void* dx, void* dres, long long rows, int C, int relu, int dtype, void* stream);
 
 #ifdef __cplusplus
 }

@@ -342,10 +342,13 @@ def test_conv_igemm_forward_matches_fp32(N, C, H, W, K, R, stride, pad, dtype):
 @pytest.mark.parametrize("C,K,R,stride,pad,H", [(64, 64, 3, 1, 1, 28), (128, 64, 3, 1, 1, 14), (64, 128, 1, 1, 0, 9),
                                                 (64, 64, 5, 1, 2, 12), (128, 256, 3, 2, 1, 28), (256, 512, 1, 2, 0, 14),
                                                 (64, 192, 3, 1, 1, 7), (512, 512, 3, 1, 1, 7)])
-def test_conv_backward_on_igemm(C, K, R, stride, pad, H):
-    """dx (stride 1: flipped-filter implicit GEMM; stride 2: ATen) and dw (pixel-reduction implicit GEMM) vs fp32 autograd."""
+@pytest.mark.parametrize("dgrad", ["igemm", "cudnn"])
+def test_conv_backward_on_igemm(C, K, R, stride, pad, H, dgrad, monkeypatch):
+    """dx (stride 1: flipped-filter implicit GEMM when HYPERION_CONV_DGRAD=igemm, cuDNN by default; stride 2: ATen) and dw
+    (pixel-reduction implicit GEMM) vs fp32 autograd."""
     from hyperion_b200.ops import conv as convops
 
+    monkeypatch.setenv("HYPERION_CONV_DGRAD", dgrad)
     torch.manual_seed(23)
     x = torch.randn(3, C, H, H + 3, device="cuda").to(torch.bfloat16).contiguous(memory_format=torch.channels_last).requires_grad_(True)
     w = (torch.randn(K, C, R, R, device="cuda") / (C * R * R) ** 0.5).to(torch.bfloat16).contiguous(memory_format=torch.channels_last).requires_grad_(True)
