@@ -86,9 +86,10 @@ ce_fwd_bwd_kernel(T* __restrict__ logits, long long ld, const long long* __restr
 
 // Same computation for 16-bit rows of up to 512 * 8 * RV elements with the whole row held in registers (RV 16-byte
 // vectors per thread): the logits are read ONCE, the gradient is produced from the registers.  A GPT-2 row (50257
-// bf16) is 13 vectors per thread.
-template <typename T, int RV>
-__global__ void __launch_bounds__(512)
+// bf16) is 13 vectors per thread at 512 threads (108 registers: one 16-warp block per SM) or 7 vectors at 1024 threads
+// (<= 64 registers: 32 warps per SM, twice the loads in flight) -- the latter is used whenever the row fits.
+template <typename T, int RV, int BLOCK = 512>
+__global__ void __launch_bounds__(BLOCK)
 ce_fwd_bwd_reg_kernel(T* __restrict__ logits, long long ld, const long long* __restrict__ targets, int rows, int V,
                       long long ignore_index, float* __restrict__ loss_sum_count, float* __restrict__ row_lse,
                       const float* __restrict__ gscale_ptr, float gscale, int write_grad) {
@@ -103,7 +104,7 @@ ce_fwd_bwd_reg_kernel(T* __restrict__ logits, long long ld, const long long* __r
     // reading the logits (about 40 % of the rows of WikiText-2-shaped batches)
 #pragma unroll
     for (int k = 0; k < RV; ++k) {
-      const int c = (k * 512 + threadIdx.x) * 8;
+      const int c = (k * BLOCK + threadIdx.x) * 8;
       if (c < Vv) *reinterpret_cast<uint4*>(lrow + c) = make_uint4(0u, 0u, 0u, 0u);
     }
     if (threadIdx.x < V - Vv) lrow[Vv + threadIdx.x] = from_f32<T>(0.f);
@@ -112,14 +113,14 @@ ce_fwd_bwd_reg_kernel(T* __restrict__ logits, long long ld, const long long* __r
   uint4 raw[RV];
 #pragma unroll
   for (int k = 0; k < RV; ++k) {
-    const int c = (k * 512 + threadIdx.x) * 8;
+    const int c = (k * BLOCK + threadIdx.x) * 8;
     raw[k] = make_uint4(0u, 0u, 0u, 0u);
     if (c < Vv) raw[k] = *reinterpret_cast<const uint4*>(lrow + c);
   }
   float mx = -INFINITY;
 #pragma unroll
   for (int k = 0; k < RV; ++k) {
-    const int c = (k * 512 + threadIdx.x) * 8;
+    const int c = (k * BLOCK + threadIdx.x) * 8;
     if (c < Vv) {
       float f[8];
       unpack8<T>(raw[k], f);
@@ -135,7 +136,7 @@ ce_fwd_bwd_reg_kernel(T* __restrict__ logits, long long ld, const long long* __r
   float se = 0.f;
 #pragma unroll
   for (int k = 0; k < RV; ++k) {
-    const int c = (k * 512 + threadIdx.x) * 8;
+    const int c = (k * BLOCK + threadIdx.x) * 8;
     if (c < Vv) {
       float f[8];
       unpack8<T>(raw[k], f);
@@ -159,7 +160,7 @@ ce_fwd_bwd_reg_kernel(T* __restrict__ logits, long long ld, const long long* __r
   const float nl = -lse * 1.4426950408889634f;
 #pragma unroll
   for (int k = 0; k < RV; ++k) {
-    const int c = (k * 512 + threadIdx.x) * 8;
+    const int c = (k * BLOCK + threadIdx.x) * 8;
     if (c < Vv) {
       float f[8];
       unpack8<T>(raw[k], f);
@@ -202,6 +203,15 @@ HYP_API int hyp_ce_fwd_bwd(void* logits, long long ld, const long long* targets,
   const bool aligned = dtype != DT_F32 && (ld * 2) % 16 == 0 && reinterpret_cast<uintptr_t>(logits) % 16 == 0;
   if (aligned && V >= 8192 && V <= 512 * 8 * 16) {
     const int rv = (V / 8 + 511) / 512;
+    static const bool wide = [] { const char* e = getenv("HYPERION_CE_BLOCK"); return !(e && atoi(e) == 512); }();
+    if (wide && (V / 8 + 1023) / 1024 <= 7) {
+      if (dtype == DT_BF16)
+        ce_fwd_bwd_reg_kernel<__nv_bfloat16, 7, 1024><<<rows, 1024, 0, st>>>((__nv_bfloat16*)logits, ld, targets, rows, V, ignore_index, loss_sum_count, row_lse, gscale_ptr, gscale, write_grad);
+      else
+        ce_fwd_bwd_reg_kernel<__half, 7, 1024><<<rows, 1024, 0, st>>>((__half*)logits, ld, targets, rows, V, ignore_index, loss_sum_count, row_lse, gscale_ptr, gscale, write_grad);
+      HYP_CHECK_CUDA(cudaGetLastError());
+      return 0;
+    }
 #define HYP_CE_REG(T, RV) ce_fwd_bwd_reg_kernel<T, RV><<<rows, 512, 0, st>>>((T*)logits, ld, targets, rows, V, ignore_index, loss_sum_count, row_lse, gscale_ptr, gscale, write_grad)
 #define HYP_CE_REG_T(T) \
     if (rv <= 4) HYP_CE_REG(T, 4); else if (rv <= 8) HYP_CE_REG(T, 8); else if (rv <= 13) HYP_CE_REG(T, 13); else HYP_CE_REG(T, 16)
