@@ -81,6 +81,8 @@ struct Params {
   long long ld_aux;
   int aux_dtype;
   void* preact_out;  // optional: alpha*acc + bias before the activation (same ld / dtype as D)
+  float* colsum;     // optional, EPI 2 only: fp32 [N], column sums of the ROUNDED output tile are added to it (the bias
+                     // gradient of the layer whose pre-activation gradient this GEMM produces), so no kernel re-reads D
   int act;   // 0 none, 1 relu, 2 gelu(erf), 3 gelu(tanh), 4 silu
   int mode;  // 0: D = act(alpha*acc + bias) + aux ; 1: D = alpha*acc * act'(aux)
   float alpha, beta;
@@ -271,7 +273,7 @@ __device__ __forceinline__ void epi_prefetch(const Params& p, uint4 (&pre)[4], i
   }
 }
 __device__ __forceinline__ void stage_store_tile(uint8_t* stg, const float (&v)[32], int out_dtype, void* dst, long long ld,
-                                                 int row0, int lane, int col0, int M) {
+                                                 int row0, int lane, int col0, int M, float* colsum = nullptr) {
 #pragma unroll
   for (int g = 0; g < 4; ++g) {
     float t[8];
@@ -280,6 +282,17 @@ __device__ __forceinline__ void stage_store_tile(uint8_t* stg, const float (&v)[
     *reinterpret_cast<uint4*>(stg + lane * STG_ROW + g * 16) = (out_dtype == DT_BF16) ? pack8<__nv_bfloat16>(t) : pack8<__half>(t);
   }
   __syncwarp();
+  if (colsum != nullptr) {
+    // lane j adds up column j of the staged 32 x 32 tile (the 16-bit values that are stored, so the result equals a
+    // column sum over D); rows past M hold zeros here (zero-filled operand rows times act' of a zero-filled aux row)
+    float cs = 0.f;
+#pragma unroll
+    for (int rr = 0; rr < 32; ++rr) {
+      const uint16_t h = *reinterpret_cast<const uint16_t*>(stg + rr * STG_ROW + lane * 2);
+      cs += (out_dtype == DT_BF16) ? __uint_as_float(static_cast<uint32_t>(h) << 16) : __half2float(__ushort_as_half(h));
+    }
+    atomicAdd(colsum + col0 + lane, cs);
+  }
   uint16_t* d = reinterpret_cast<uint16_t*>(dst);
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
@@ -354,7 +367,7 @@ __device__ __forceinline__ void epilogue32s(const Params& p, const uint32_t (&r)
     }
     __syncwarp();
   }
-  stage_store_tile(stg, v, p.out_dtype, p.D, p.ldd, row0, lane, col0, p.M);
+  stage_store_tile(stg, v, p.out_dtype, p.D, p.ldd, row0, lane, col0, p.M, EPI == 2 ? p.colsum : nullptr);
 }
 
 template <int EPI, int ACT>
@@ -1183,7 +1196,12 @@ static int gemm_impl(const void* A, const void* B, void* D, int M, int N, int K,
   p.D = D; p.ldd = ldd; p.out_dtype = out_dtype;
   p.bias = bias; p.bias_dtype = bias_dtype;
   p.aux = aux; p.ld_aux = ld_aux; p.aux_dtype = aux_dtype;
+  // mode 1 (D = alpha*acc * act'(aux)) has no pre-activation output; there the same argument carries the optional fp32
+  // column-sum accumulator (see Params::colsum and the header)
+  float* colsum = nullptr;
+  if (mode == 1 && preact_out) { colsum = reinterpret_cast<float*>(preact_out); preact_out = nullptr; }
   p.preact_out = preact_out;
+  p.colsum = colsum;
   HYP_REQUIRE(!preact_out || reinterpret_cast<uintptr_t>(preact_out) % 16 == 0, "hyp_gemm: preact_out must be 16B aligned");
   p.act = act; p.mode = mode; p.alpha = alpha; p.beta = beta;
   const int oes = (out_dtype == DT_F32) ? 4 : 2;
@@ -1205,6 +1223,8 @@ static int gemm_impl(const void* A, const void* B, void* D, int M, int N, int K,
   else if (vec && p.splits > 1) epi = 4;
   else if (vec && p.splits == 1 && beta != 0.f && mode == 0 && act == 0 && !bias && !aux && !preact_out) epi = 5;
   p.simple = epi;
+  HYP_REQUIRE(!colsum || (epi == 2 && out_dtype != DT_F32 && N % 32 == 0),
+              "hyp_gemm: the fused column sum needs the act' epilogue on aligned 16-bit tensors with N %% 32 == 0 (N=%d)", N);
 
   bool want_pair = pair_ok;
   bool pair128 = false;

@@ -296,14 +296,23 @@ class _MlpFn(torch.autograd.Function):
         dy2 = _as2d(dy)
         has_b1, has_b2, has_res = ctx.flags
         # dh = (dy @ W2) * act'(h): activation derivative applied in the GEMM epilogue
-        dh = native.gemm(dy2, w2, b_mn_major=True, aux=h, act=ctx.act, mode=1)
+        # the bias gradient of the first layer = column sums of dh: produced by the same epilogue when dh is final there
+        # (no dropout to re-apply afterwards) and the shape takes the staged epilogue for every tile
+        N1 = w2.shape[1]
+        fuse_db1 = (has_b1 and ctx.drop is None and dy2.dtype != torch.float32 and N1 % 256 == 0
+                    and os.environ.get("HYPERION_GEMM_COLSUM", "1") == "1")
+        cs1 = torch.zeros(N1, device=dy2.device, dtype=torch.float32) if fuse_db1 else None
+        dh = native.gemm(dy2, w2, b_mn_major=True, aux=h, act=ctx.act, mode=1, colsum=cs1)
         if ctx.drop is not None:
             native.dropout(dh, *ctx.drop, out=dh)
         s_w1, s_b1, s_w2, s_b2 = ctx.slots
         dw2 = _wgrad(dy2, a, w2.dtype, s_w2)
         dw1 = _wgrad(dh, x2, w1.dtype, s_w1)
         dx = native.gemm(dh, w1, b_mn_major=True).reshape(ctx.x_shape) if ctx.needs_input_grad[0] else None
-        db1 = _bias_grad(dh, dy.dtype, s_b1) if has_b1 else None
+        if fuse_db1:
+            db1 = native.cast(cs1, dy.dtype, out=gradslot.claim(s_b1, dy.dtype))
+        else:
+            db1 = _bias_grad(dh, dy.dtype, s_b1) if has_b1 else None
         db2 = _bias_grad(dy2, dy.dtype, s_b2, dy) if has_b2 else None
         return dx, dw1, db1, dw2, db2, (dy if has_res else None), None, None, None, None
 

@@ -22,8 +22,12 @@ def _ld(t: torch.Tensor) -> int:
 def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn_major: bool = False, b_mn_major: bool = False,
          out: torch.Tensor | None = None, out_dtype: torch.dtype | None = None, bias: torch.Tensor | None = None,
          aux: torch.Tensor | None = None, act: str | None = None, mode: int = 0, alpha: float = 1.0,
-         beta: float = 0.0, splits: int = 1, preact_out: torch.Tensor | None = None) -> torch.Tensor:
+         beta: float = 0.0, splits: int = 1, preact_out: torch.Tensor | None = None,
+         colsum: torch.Tensor | None = None) -> torch.Tensor:
     """D = epilogue(alpha * A @ B^T) on the tcgen05 GEMM.
+
+    ``colsum`` (``mode=1`` only): fp32 ``[N]`` accumulator; the epilogue adds the column sums of the rounded output to it
+    (bias gradient of the layer whose pre-activation gradient this GEMM produces).
 
     ``a`` is [M, K] (or [K, M] when ``a_mn_major``); ``b`` is [N, K] -- the
     ``nn.Linear.weight`` layout -- (or [K, N] when ``b_mn_major``).
@@ -50,6 +54,9 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn_major: bool = False, b_mn_maj
     assert out.shape == (M, N)
     if preact_out is not None:
         assert preact_out.shape == out.shape and preact_out.dtype == out.dtype and _ld(preact_out) == _ld(out)
+    if colsum is not None:
+        assert mode == 1 and preact_out is None and colsum.dtype == torch.float32 and colsum.numel() == N and colsum.is_contiguous()
+        preact_out = colsum   # the C ABI reuses the pre-activation argument for it in mode 1 (include/hyperion_b200.h)
     call("hyp_gemm", ptr(a), ptr(b), ptr(out), M, N, K, _ld(a), _ld(b), _ld(out), DT[a.dtype], DT[out.dtype],
          int(a_mn_major), int(b_mn_major), ptr(bias), DT[bias.dtype] if bias is not None else 0, ptr(aux),
          _ld(aux) if aux is not None else 0, DT[aux.dtype] if aux is not None else 0, ptr(preact_out), ACT[act], mode,

@@ -38,6 +38,9 @@ int hyp_device_supported(void); /* 1 iff the current device is compute capabilit
  * accumulate into), plain epilogue only.
  * Reference: torch.matmul (Phase 1/01_hardware_exploration.ipynb c1 L92), every
  * nn.Linear in 02_development/distributed_utils.py:75-88. */
+/* mode 1 (D = alpha*acc * act'(aux), the activation-backward epilogue) has no pre-activation output: there `preact_out`,
+ * when non-NULL, is an fp32 [N] accumulator to which the epilogue ADDS the column sums of the rounded 16-bit output (the bias
+ * gradient of the layer below), N % 32 == 0; the caller zeroes it. */
 int hyp_gemm(const void* A, const void* B, void* D, int M, int N, int K, long long lda, long long ldb, long long ldd,
              int in_dtype, int out_dtype, int a_mn_major, int b_mn_major, const void* bias, int bias_dtype,
              const void* aux, long long ld_aux, int aux_dtype, void* preact_out, int act, int mode, float alpha,

@@ -67,6 +67,26 @@ def test_mlp_op(ops, act):
         assert _rel(g, r) < 4e-2
 
 
+@pytest.mark.parametrize("rows", [1016, 256, 4097])
+def test_mlp_bias_grad_from_gemm_epilogue_matches_column_sum(ops, rows, monkeypatch):
+    """db1 produced by the act'-epilogue of the dgrad GEMM (fp32 atomics of the rounded tile's column sums) vs the stand-alone
+    column-sum kernel over the same dh, including row counts that leave partial M tiles."""
+    torch.manual_seed(5)
+    x, w1, b1, w2, b2 = _leaf(rows, 256), _leaf(1024, 256, scale=0.05), _leaf(1024), _leaf(256, 1024, scale=0.02), _leaf(256)
+    dy = torch.randn(rows, 256, device="cuda", dtype=x.dtype)
+    outs = {}
+    for mode in ("1", "0"):
+        monkeypatch.setenv("HYPERION_GEMM_COLSUM", mode)
+        y = ops.mlp(x, w1, b1, w2, b2, act="gelu_tanh")
+        outs[mode] = torch.autograd.grad(y, [x, w1, b1], dy)
+    for a, b in zip(outs["1"], outs["0"]):
+        assert _rel(a, b) < 5e-3, _rel(a, b)
+    xr, w1r, b1r, w2r, b2r = _ref_copy(x, w1, b1, w2, b2)
+    yr = F.linear(F.gelu(F.linear(xr, w1r, b1r), approximate="tanh"), w2r, b2r)
+    gb = torch.autograd.grad(yr, [b1r], dy.float())[0]
+    assert _rel(outs["1"][2], gb) < 3e-2
+
+
 @pytest.mark.parametrize("rms", [False, True])
 def test_norm_op(ops, rms):
     torch.manual_seed(2)
