@@ -100,3 +100,41 @@ def test_header_declares_every_exported_entry_point():
             if not re.search(r"\b" + m.group(1) + r"\s*\(", hdr):
                 missing.append(m.group(1))
     assert not missing, missing
+
+
+def test_reference_arm_environment_and_unavailable_line(tmp_path, capsys, monkeypatch):
+    """bench.py --impl reference: configs the reference cannot run print one `unavailable` JSON line and exit 0; for the
+    ones it can, the environment the unmodified trainers need (tokenizer dir, on-disk dataset, import stand-ins) is built
+    and the installed reference module imports from baseline/_ref."""
+    import json
+    import sys
+    import types
+
+    from baseline import reference_arm as ra
+
+    rc = ra.run(types.SimpleNamespace(config="gpt2_fsdp", steps=2, warmup=1))
+    line = json.loads(capsys.readouterr().out.strip().splitlines()[-1])
+    assert rc == 0 and line["impl"] == "reference" and "unavailable" in line and line["same_config"] is False
+    assert set(line["reference_configs"]) == {"lm_ddp", "lm_fsdp", "cifar_ddp"}
+    if not (ra.REF_DIR / "distributed_utils.py").exists():
+        pytest.skip("baseline/_ref not installed on this machine (baseline/install_reference.sh)")
+    monkeypatch.setenv("RANK", "0")
+    ra._prepare(tmp_path, "lm_ddp", 8, 128)
+    assert (tmp_path / "gpt2" / "tokenizer.json").exists() and (tmp_path / ".ready").exists()
+    assert (tmp_path / "data/processed/wikitext2_tokenized/dataset_dict.json").exists()
+    made = ra._shim_modules()
+    assert "peft" in sys.modules and "matplotlib.pyplot" in sys.modules
+    monkeypatch.syspath_prepend(str(ra.REF_DIR))
+    monkeypatch.setenv("HF_HUB_OFFLINE", "1")
+    import importlib
+
+    ref = importlib.import_module("distributed_utils")
+    assert {"train_language_model_ddp", "train_language_model_fsdp", "train_cifar_model_ddp"} <= set(dir(ref))
+    monkeypatch.chdir(tmp_path)
+    from transformers import AutoTokenizer
+
+    tok = AutoTokenizer.from_pretrained("gpt2", use_fast=True)
+    tok.pad_token = tok.pad_token or tok.eos_token
+    assert tok.vocab_size == 50257 and tok.pad_token_id == 50256
+    for name in made:
+        sys.modules.pop(name, None)
