@@ -58,7 +58,11 @@ def _unavailable(why: str, config: str) -> int:
     if int(os.environ.get("RANK", 0)) == 0:
         print(json.dumps({"impl": "reference", "unavailable": why, "config": {"name": config}, "same_config": False,
                           "operative_baseline": "bench.py --impl torch --config " + config,
-                          "reference_configs": sorted(JOBS)}), flush=True)
+                          "reference_configs": sorted(JOBS),
+                          "how_to_measure_the_reference": "python bench.py --impl reference --config lm_ddp|lm_fsdp|cifar_ddp "
+                                                          "(same flags for the product arm); committed runs of both arms at "
+                                                          "N=1/2/4/8: profiles/bench/r2/matrix_n<N>_<config>_{reference,hyperion}.json, "
+                                                          "table in BASELINE.md section 3"}), flush=True)
     return 0
 
 
