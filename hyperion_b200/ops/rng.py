@@ -21,12 +21,29 @@ _salt = 0
 _seed = 0x5EED_B200
 
 
+def _rank() -> int:
+    try:
+        import torch.distributed as dist
+
+        if dist.is_available() and dist.is_initialized():
+            return dist.get_rank()
+    except Exception:  # noqa: BLE001
+        pass
+    return 0
+
+
+def _seed_for(key: int) -> int:
+    # every rank (and every device of a process) draws its own masks
+    return _seed + 7919 * key + 104729 * _rank()
+
+
 def manual_seed(seed: int) -> None:
-    """Re-seed every device's dropout state (and restart the per-call salt)."""
+    """Re-seed every device's dropout state (and restart the per-call salt).  Written in place, so a captured CUDA graph
+    that reads the state keeps working."""
     global _seed, _salt
     _seed, _salt = int(seed), 0
-    for t in _state.values():
-        t[0] = _seed
+    for key, t in _state.items():
+        t[0] = _seed_for(key)
         t[1] = 0
 
 
@@ -35,7 +52,7 @@ def state(device) -> torch.Tensor:
     key = device.index if device.index is not None else torch.cuda.current_device()
     t = _state.get(key)
     if t is None:
-        t = torch.tensor([_seed + 7919 * key, 0], dtype=torch.int64, device=torch.device("cuda", key))
+        t = torch.tensor([_seed_for(key), 0], dtype=torch.int64, device=torch.device("cuda", key))
         _state[key] = t
     return t
 

@@ -49,6 +49,9 @@ def setup(rank: int, world_size: int, backend: str | None = None, timeout_min: f
         torch.manual_seed(seed)
         if dev.type == "cuda":
             torch.cuda.manual_seed_all(seed)
+            from ..ops import rng
+
+            rng.manual_seed(seed)   # the native dropout kernels' (seed, step) state; ranks differ through the device index
     if rank == 0:
         print(f"[Rank 0] PG ready on {os.environ['MASTER_ADDR']}:{os.environ['MASTER_PORT']} (backend={backend})")
     return dev
