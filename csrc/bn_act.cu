@@ -125,7 +125,16 @@ template <typename T, typename P = float>
 __global__ void __launch_bounds__(256)
 bwd_dx_kernel(const T* __restrict__ dy, const T* __restrict__ x, const T* __restrict__ y, const float* __restrict__ mean,
               const float* __restrict__ rstd, const P* __restrict__ gamma, const float* __restrict__ dsums,
-              T* __restrict__ dx, T* __restrict__ dres, long long rows, int C, int relu) {
+              T* __restrict__ dx, T* __restrict__ dres, long long rows, int C, int relu,
+              P* __restrict__ dgamma_out = nullptr, P* __restrict__ dbeta_out = nullptr) {
+  // the reductions are complete (previous kernel on the stream): block 0 also rounds them into the parameter-dtype
+  // gradient tensors, so the caller needs no cast launches (and can hand the kernel the flat-gradient slots directly)
+  if (blockIdx.x == 0 && dgamma_out != nullptr) {
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+      dgamma_out[c] = from_f32<P>(dsums[C + c]);
+      dbeta_out[c] = from_f32<P>(dsums[c]);
+    }
+  }
   const long long total = rows * C / 8;
   const float inv_n = 1.f / static_cast<float>(rows);
   const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
@@ -213,7 +222,8 @@ HYP_API int hyp_bn_act_bwd(const void* dy, const void* x, const void* y, const f
 
 
 // Same two entry points with gamma / beta in the activations' 16-bit dtype (the layout a mixed-precision module holds them
-// in), so the caller does not launch two cast kernels per layer and step.
+// in), so the caller does not launch two cast kernels per layer and step.  The backward also rounds dgamma / dbeta into
+// 16-bit outputs (dgamma16 / dbeta16, both or neither; e.g. the parameters' ranges of a flat gradient buffer).
 HYP_API int hyp_bn_act_fwd_p16(const void* x, const void* res, const void* gamma, const void* beta, void* y, float* sums,
                                float* mean, float* rstd, float* running_mean, float* running_var, long long rows, int C,
                                float eps, float momentum, int relu, int dtype, void* stream_) {
@@ -239,7 +249,7 @@ HYP_API int hyp_bn_act_fwd_p16(const void* x, const void* res, const void* gamma
 
 HYP_API int hyp_bn_act_bwd_p16(const void* dy, const void* x, const void* y, const float* mean, const float* rstd,
                                const void* gamma, float* dsums, void* dx, void* dres, long long rows, int C, int relu,
-                               int dtype, void* stream_) {
+                               int dtype, void* dgamma16, void* dbeta16, void* stream_) {
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream_);
   HYP_REQUIRE(dtype == DT_BF16 || dtype == DT_F16, "hyp_bn_act_bwd_p16: 16-bit dtypes only");
   HYP_REQUIRE(rows > 0 && C > 0 && C % 8 == 0, "hyp_bn_act_bwd_p16: need C %% 8 == 0 (C=%d)", C);
@@ -249,11 +259,11 @@ HYP_API int hyp_bn_act_bwd_p16(const void* dy, const void* x, const void* y, con
   if (dtype == DT_BF16) {
     using T = __nv_bfloat16;
     bn::bwd_reduce_kernel<T><<<grid, 256, 0, st>>>((const T*)dy, (const T*)x, (const T*)y, mean, rstd, dsums, rows, C, rpb, relu);
-    bn::bwd_dx_kernel<T, T><<<eg, 256, 0, st>>>((const T*)dy, (const T*)x, (const T*)y, mean, rstd, (const T*)gamma, dsums, (T*)dx, (T*)dres, rows, C, relu);
+    bn::bwd_dx_kernel<T, T><<<eg, 256, 0, st>>>((const T*)dy, (const T*)x, (const T*)y, mean, rstd, (const T*)gamma, dsums, (T*)dx, (T*)dres, rows, C, relu, (T*)dgamma16, (T*)dbeta16);
   } else {
     using T = __half;
     bn::bwd_reduce_kernel<T><<<grid, 256, 0, st>>>((const T*)dy, (const T*)x, (const T*)y, mean, rstd, dsums, rows, C, rpb, relu);
-    bn::bwd_dx_kernel<T, T><<<eg, 256, 0, st>>>((const T*)dy, (const T*)x, (const T*)y, mean, rstd, (const T*)gamma, dsums, (T*)dx, (T*)dres, rows, C, relu);
+    bn::bwd_dx_kernel<T, T><<<eg, 256, 0, st>>>((const T*)dy, (const T*)x, (const T*)y, mean, rstd, (const T*)gamma, dsums, (T*)dx, (T*)dres, rows, C, relu, (T*)dgamma16, (T*)dbeta16);
   }
   HYP_CHECK_CUDA(cudaGetLastError());
   return 0;

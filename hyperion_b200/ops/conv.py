@@ -157,7 +157,7 @@ def _declare_bn():
         _lib.declare("hyp_bn_act_bwd", "ppppppppp" + "li" + "ii" + "p")
         if hasattr(_lib.raw(), "hyp_bn_act_fwd_p16"):
             _lib.declare("hyp_bn_act_fwd_p16", "pppppppppp" + "li" + "ff" + "ii" + "p")
-            _lib.declare("hyp_bn_act_bwd_p16", "ppppppppp" + "li" + "ii" + "p")
+            _lib.declare("hyp_bn_act_bwd_p16", "ppppppppp" + "li" + "ii" + "pp" + "p")
         _bn_declared = True
 
 
@@ -203,6 +203,9 @@ class _BnActFn(torch.autograd.Function):
                   float(momentum), int(relu), _lib.DT[x.dtype], _lib.stream_ptr())
         ctx.save_for_backward(x, y, mean, rstd, gf)
         ctx.relu, ctx.has_res, ctx.pdtype = relu, residual is not None, gamma.dtype
+        from . import gradslot
+
+        ctx.slots = (gradslot.slot_of(gamma), gradslot.slot_of(beta))
         return y
 
     @staticmethod
@@ -213,7 +216,22 @@ class _BnActFn(torch.autograd.Function):
         dx = torch.empty_like(x, memory_format=torch.channels_last)
         dres = torch.empty_like(x, memory_format=torch.channels_last) if ctx.has_res else None
         dsums = ctx.dsums
-        _lib.call("hyp_bn_act_bwd_p16" if ctx.p16 else "hyp_bn_act_bwd", _lib.ptr(dy), _lib.ptr(x), _lib.ptr(y), _lib.ptr(mean), _lib.ptr(rstd), _lib.ptr(gf),
+        if ctx.p16:
+            # dgamma / dbeta are rounded by the dx kernel itself, straight into the parameters' slots of the flat gradient
+            # buffer when they can be claimed (no cast launches, no accumulate copies)
+            from . import gradslot
+
+            dg = gradslot.claim(ctx.slots[0], ctx.pdtype)
+            db = gradslot.claim(ctx.slots[1], ctx.pdtype)
+            if dg is None:
+                dg = torch.empty(C, device=x.device, dtype=ctx.pdtype)
+            if db is None:
+                db = torch.empty(C, device=x.device, dtype=ctx.pdtype)
+            _lib.call("hyp_bn_act_bwd_p16", _lib.ptr(dy), _lib.ptr(x), _lib.ptr(y), _lib.ptr(mean), _lib.ptr(rstd), _lib.ptr(gf),
+                      _lib.ptr(dsums), _lib.ptr(dx), _lib.ptr(dres), N * H * W, C, int(ctx.relu), _lib.DT[x.dtype],
+                      _lib.ptr(dg), _lib.ptr(db), _lib.stream_ptr())
+            return dx, dg, db, dres, None, None, None, None, None
+        _lib.call("hyp_bn_act_bwd", _lib.ptr(dy), _lib.ptr(x), _lib.ptr(y), _lib.ptr(mean), _lib.ptr(rstd), _lib.ptr(gf),
                   _lib.ptr(dsums), _lib.ptr(dx), _lib.ptr(dres), N * H * W, C, int(ctx.relu), _lib.DT[x.dtype], _lib.stream_ptr())
         return dx, dsums[C:].to(ctx.pdtype), dsums[:C].to(ctx.pdtype), dres, None, None, None, None, None
 

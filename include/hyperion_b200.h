@@ -270,7 +270,8 @@ int hyp_bn_act_fwd_p16(const void* x, const void* res, const void* gamma, const 
                        float* rstd, float* running_mean, float* running_var, long long rows, int C, float eps, float momentum,
                        int relu, int dtype, void* stream);
 int hyp_bn_act_bwd_p16(const void* dy, const void* x, const void* y, const float* mean, const float* rstd, const void* gamma,
-                       float* dsums, void* dx, void* dres, long long rows, int C, int relu, int dtype, void* stream);
+                       float* dsums, void* dx, void* dres, long long rows, int C, int relu, int dtype, void* dgamma16,
+                       void* dbeta16, void* stream);   /* dgamma16 / dbeta16: optional 16-bit [C] outputs (both or neither) */
 
 #ifdef __cplusplus
 }
