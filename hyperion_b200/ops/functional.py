@@ -50,6 +50,17 @@ def _native(*tensors) -> bool:
     return t0.dtype in _SUPPORTED
 
 
+def _ensure_gathered(*weights) -> None:
+    """Library fallback paths (CPU, misaligned K, disabled native library) read the weights directly: if one of them belongs
+    to an FSDP unit that was waiting to be gathered inside its first GEMM, gather it now with the stand-alone kernel --
+    otherwise the fallback would silently compute with last step's parameters."""
+    for w in weights:
+        h = getattr(w, "_hyp_ag", None) if w is not None else None
+        if h is not None and h.pending:
+            h.fsdp.sync_params()
+            return
+
+
 def _as2d(t: torch.Tensor) -> torch.Tensor:
     """2-D row-major view usable as a TMA operand (16-byte aligned rows), copying only if needed."""
     t2 = t.reshape(-1, t.shape[-1])
@@ -254,6 +265,7 @@ def linear(x, w, b=None, act: str | None = None, residual=None):
     """``act(x @ w.T + b) + residual`` with the bias / activation / residual fused into the GEMM epilogue."""
     if _native(x, w) and x.shape[-1] % (16 // x.element_size()) == 0:
         return _LinearFn.apply(x, w, b, residual, act, getattr(w, "_hyp_ag", None))
+    _ensure_gathered(w)
     y = _act_ref(F.linear(x, w, b), act)
     return y if residual is None else y + residual
 
@@ -327,6 +339,7 @@ def mlp(x, w1, b1, w2, b2, act: str = "relu", residual=None, dropout_p: float = 
             return linear(h, w2, b2, residual=residual)
         return _MlpFn.apply(x, w1, b1, w2, b2, residual, act, getattr(w1, "_hyp_ag", None), getattr(w2, "_hyp_ag", None),
                             dropout_p)
+    _ensure_gathered(w1, w2)
     h = _act_ref(F.linear(x, w1, b1), act)
     if dropout_p > 0.0:
         h = F.dropout(h, dropout_p, True)
@@ -577,6 +590,7 @@ def linear_cross_entropy(x, w, b, targets, ignore_index: int = -100, chunk_rows:
     """Mean cross-entropy of ``x @ w.T + b`` against ``targets`` (fp32 scalar)."""
     if _native(x, w) and x.shape[-1] % (16 // x.element_size()) == 0:
         return _LinearCEFn.apply(x, w, b, targets, ignore_index, chunk_rows)
+    _ensure_gathered(w)
     logits = F.linear(x, w, b)
     return F.cross_entropy(logits.reshape(-1, logits.shape[-1]).float(), targets.reshape(-1), ignore_index=ignore_index)
 
