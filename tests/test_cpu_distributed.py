@@ -179,3 +179,50 @@ def test_gloo_kill_and_resume_reproduces_the_loss_curve(tmp_path, strategy):
     resumed = torch.load(os.path.join(base, "hist_resume.pt"))
     assert len(full) == 3 and len(first) == 2 and len(resumed) == 1
     assert abs(full[2] - resumed[0]) < 1e-4 * max(1.0, abs(full[2])), (full, first, resumed)
+
+
+def _reshard_ckpt_worker(rank, world, port, reshard, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    from hyperion_b200.models import GPT2Config, GPT2LMHeadModel
+    from hyperion_b200.models.gpt2 import Block
+    from hyperion_b200.parallel.runtime import cleanup, setup
+    from hyperion_b200.train.engine import build_engine
+    from hyperion_b200.utils.checkpoint import full_state_dict
+
+    torch.set_num_threads(1)
+    dev = setup(rank, world, "gloo", seed=0)
+    torch.manual_seed(0)
+    model = GPT2LMHeadModel(GPT2Config(vocab_size=256, n_positions=32, n_embd=32, n_layer=3, n_head=2))
+    model.use_checkpoint = True            # every block is recomputed inside backward: gathers fire from the recompute too
+    eng = build_engine(model, strategy="fsdp", precision="fp32", lr=1e-2, clip=1.0, device=dev,
+                       fsdp_units=[m for m in model.modules() if isinstance(m, Block)], reshard_after_forward=reshard)
+    eng.model.train()
+    g = torch.Generator().manual_seed(3)
+    data = torch.randint(0, 256, (4, 2 * world, 24), generator=g)
+    losses = []
+    for step in range(4):
+        if step == 2:
+            # weights-only reload in the middle of training: shards / master (and, when resharded, the slots) must follow
+            sd = full_state_dict(eng.model)
+            eng.model.load_state_dict(sd)
+        loss = eng.model.loss(data[step, rank * 2:(rank + 1) * 2])
+        eng.backward_and_step(loss)
+        losses.append(float(loss.detach()))
+    sd = full_state_dict(eng.model)
+    if rank == 0:
+        torch.save({"sd": sd, "losses": losses}, out)
+    cleanup()
+
+
+def test_gloo_full_shard_with_activation_checkpointing_and_reload(tmp_path):
+    """FULL_SHARD slots + activation checkpointing (block forwards re-run inside backward) + a mid-run load_state_dict:
+    same losses and parameters as the params-resident mode."""
+    outs = []
+    for reshard in (False, True):
+        out = str(tmp_path / f"c{int(reshard)}.pt")
+        mp.spawn(_reshard_ckpt_worker, args=(2, _free_port(), reshard, out), nprocs=2, join=True)
+        outs.append(torch.load(out, weights_only=False))
+    a, b = outs
+    assert torch.allclose(torch.tensor(a["losses"]), torch.tensor(b["losses"]), atol=1e-5), (a["losses"], b["losses"])
+    for k in a["sd"]:
+        assert torch.allclose(a["sd"][k], b["sd"][k], atol=1e-5), k
