@@ -226,3 +226,54 @@ def test_gloo_full_shard_with_activation_checkpointing_and_reload(tmp_path):
     assert torch.allclose(torch.tensor(a["losses"]), torch.tensor(b["losses"]), atol=1e-5), (a["losses"], b["losses"])
     for k in a["sd"]:
         assert torch.allclose(a["sd"][k], b["sd"][k], atol=1e-5), k
+
+
+class _PartlyUsed(torch.nn.Module):
+    """Two branches; only `a` is used in forward, so `b` never receives a gradient."""
+
+    def __init__(self):
+        super().__init__()
+        self.a = torch.nn.Linear(16, 16)
+        self.b = torch.nn.Linear(16, 16)
+
+    def forward(self, x):
+        return self.a(x)
+
+
+def _unused_worker(rank, world, port, strategy, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    from hyperion_b200.parallel.runtime import cleanup, setup
+    from hyperion_b200.train.engine import build_engine
+
+    torch.set_num_threads(1)
+    dev = setup(rank, world, "gloo", seed=0)
+    torch.manual_seed(0)
+    model = _PartlyUsed()
+    # default 25 MB buckets / one root unit: the used and the unused branch share a bucket (unit), whose hook counter
+    # therefore never reaches zero on its own
+    eng = build_engine(model, strategy=strategy, precision="fp32", lr=1e-2, device=dev, fsdp_min_num_params=10 ** 6)
+    g = torch.Generator().manual_seed(10 + rank)          # different data per rank: only the all-reduce keeps them equal
+    for _ in range(3):
+        x = torch.randn(4, 16, generator=g)
+        eng.backward_and_step(eng.model(x).pow(2).mean())
+    from hyperion_b200.utils.checkpoint import full_state_dict
+
+    sd = full_state_dict(eng.model)
+    flat = torch.cat([v.reshape(-1) for v in sd.values()])
+    gathered = [torch.zeros_like(flat) for _ in range(world)]
+    torch.distributed.all_gather(gathered, flat)
+    if rank == 0:
+        torch.save({"same": bool(torch.allclose(gathered[0], gathered[1], atol=1e-6)),
+                    "unused": list(getattr(eng.model, "unused", [])), "moved": float((sd["a.weight"] - _PartlyUsed().a.weight).abs().sum())}, out)
+    cleanup()
+
+
+@pytest.mark.parametrize("strategy", ["ddp", "fsdp"])
+def test_gloo_parameters_without_gradient_do_not_desynchronise_the_ranks(tmp_path, strategy):
+    """A bucket / unit holding a parameter that got no gradient is still reduced at the end of backward (with zeros in the
+    missing slots): the ranks stay identical, the used branch trains, and the engine names the unused parameters."""
+    out = str(tmp_path / "u.pt")
+    mp.spawn(_unused_worker, args=(2, _free_port(), strategy, out), nprocs=2, join=True)
+    r = torch.load(out, weights_only=False)
+    assert r["same"], "ranks diverged"
+    assert any(n.startswith("b.") for n in r["unused"]), r["unused"]
