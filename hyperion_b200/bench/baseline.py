@@ -134,6 +134,44 @@ def test_batch_size_scaling(model_fn=create_resnet50, input_hw=(3, 224, 224), ou
     return df
 
 
+def visualize_baseline_results(results: pd.DataFrame, out_dir: str = "results") -> str | None:
+    """The notebook's 2x2 page (baseline_performance.ipynb c0 L236-288): time breakdown, memory, throughput, total time per
+    model -> ``<out_dir>/visualizations/baseline_benchmarks.svg`` (no matplotlib in this image, so SVG)."""
+    if results is None or len(results) == 0:
+        print("No results to visualize.")
+        return None
+    from ..utils.svgplot import bar_chart, compose
+
+    d = os.path.join(out_dir, "visualizations")
+    models = [str(m).split(" (")[0] for m in results["Model"]]
+    panels = [bar_chart(os.path.join(d, "_p0.svg"), models,
+                        {"Forward": list(results["Forward Time (ms)"]), "Backward": list(results["Backward Time (ms)"]),
+                         "Optimizer": list(results["Optimizer Time (ms)"])}, title="Time Breakdown by Model", ylabel="Time (ms)")]
+    for i, col in enumerate(("Memory Usage (MB)", "Throughput (samples/s)", "Total Time (ms)"), start=1):
+        panels.append(bar_chart(os.path.join(d, f"_p{i}.svg"), models, {col: list(results[col])},
+                                title=col.split(" (")[0] + " by Model", ylabel=col))
+    return str(compose(os.path.join(d, "baseline_benchmarks.svg"), panels))
+
+
+def visualize_batch_scaling(results: pd.DataFrame, model_name: str, out_dir: str = "results") -> str | None:
+    """The notebook's batch-scaling page (c0 L350-400): throughput, memory, total time and scaling efficiency (throughput over
+    linear scaling from the first batch size, in %) against batch size."""
+    if results is None or len(results) == 0:
+        print(f"No scaling results available for {model_name}.")
+        return None
+    from ..utils.svgplot import compose, line_chart
+
+    d = os.path.join(out_dir, "visualizations")
+    bs, thr = list(results["Batch Size"]), list(results["Throughput (samples/s)"])
+    eff = [t / (thr[0] * b / bs[0]) * 100 for t, b in zip(thr, bs)]
+    panels = []
+    for i, (ys, yl) in enumerate(((thr, "Throughput (samples/s)"), (list(results["Memory Usage (MB)"]), "Memory Usage (MB)"),
+                                  (list(results["Total Time (ms)"]), "Total Time (ms)"), (eff, "Scaling Efficiency (%)"))):
+        panels.append(line_chart(os.path.join(d, f"_p{i}.svg"), {model_name: (bs, ys)},
+                                 title=f"{model_name} {yl.split(' (')[0]} vs Batch Size", xlabel="Batch Size", ylabel=yl))
+    return str(compose(os.path.join(d, f"{model_name.lower().replace(' ', '_')}_batch_scaling.svg"), panels))
+
+
 def main(argv=None) -> int:
     ap = argparse.ArgumentParser(prog="hyperion baseline")
     ap.add_argument("--out", default="results/benchmarks")
@@ -145,9 +183,12 @@ def main(argv=None) -> int:
     a = ap.parse_args(argv)
     df = run_baseline_benchmarks(a.batch, a.precision, a.out, a.iters, a.warmup)
     print(df.to_string(index=False))
+    viz = os.path.dirname(os.path.normpath(a.out)) or "."          # results/benchmarks -> results/visualizations
+    print("Figure:", visualize_baseline_results(df, viz))
     if not a.no_scaling:
         sc = test_batch_size_scaling(precision=a.precision, out_dir=a.out)
         print(sc.to_string(index=False))
+        print("Figure:", visualize_batch_scaling(sc, "ResNet-50", viz))
     return 0
 
 

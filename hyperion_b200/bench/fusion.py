@@ -155,8 +155,15 @@ def run(base_dir: str = ".", dtype: str = "fp32", repeat: int = 50, variants=("e
         df.pivot(index="model", columns="variant", values="time_ms").plot.bar(ax=ax[0], title="time (ms)")
         df.pivot(index="model", columns="variant", values="mem_gb").plot.bar(ax=ax[1], title="peak memory (GB)")
         fig.savefig(os.path.join(out, "compilation_ckpt_speed_mem.png"), dpi=120)
-    except ImportError:
-        pass
+    except ImportError:  # no matplotlib in this image: the same two panels as SVG files
+        from ..utils.svgplot import bar_chart
+
+        if len(df):
+            models = list(df["model"].unique())
+            for col, stem, label in (("time_ms", "speed", "time (ms)"), ("mem_gb", "mem", "peak memory (GB)")):
+                piv = df.pivot(index="model", columns="variant", values=col)
+                bar_chart(os.path.join(out, f"compilation_ckpt_{stem}.svg"), models,
+                          {v: [piv.loc[m, v] for m in models] for v in piv.columns}, title=label, ylabel=label)
     return df
 
 

@@ -117,7 +117,44 @@ def main(argv=None) -> int:
     prec.to_csv(os.path.join(a.out, "precision_results.csv"), index=False)
     bw.to_csv(os.path.join(a.out, "bandwidth_results.csv"), index=False)
     print(f"CSVs written to {a.out}")
+    plot_results(prec, bw, a.out)
     return 0
+
+
+def plot_results(prec: pd.DataFrame, bw: pd.DataFrame, out: str) -> list[str]:
+    """The notebook's two figures (01_hardware_exploration.ipynb c1 L110-123, L165-176): TFLOPS per precision and matrix size,
+    bandwidth per vector size.  PNG with matplotlib when it exists, otherwise SVG from ``utils.svgplot``."""
+    sizes = sorted(prec["Size"].unique())
+    curves = {}
+    for name in prec["Precision"].unique():
+        sub = prec[prec.Precision == name].set_index("Size")
+        curves[name] = (sizes, [sub["TFLOPS"].get(s) for s in sizes])
+        if "TFLOPS tcgen05" in sub.columns and sub["TFLOPS tcgen05"].notna().any():
+            curves[f"{name} tcgen05"] = (sizes, [sub["TFLOPS tcgen05"].get(s) for s in sizes])
+    bws = {c.replace(" (GB/s)", ""): (list(bw["Size (M elements)"]), list(bw[c])) for c in bw.columns if c.endswith("(GB/s)")}
+    try:
+        import matplotlib
+
+        matplotlib.use("Agg")
+        import matplotlib.pyplot as plt
+
+        paths = [os.path.join(out, "precision_performance.png"), os.path.join(out, "memory_bandwidth.png")]
+        for path, data, xl, yl in ((paths[0], curves, "Matrix size", "TFLOPS"), (paths[1], bws, "Size (M elements)", "GB/s")):
+            fig, ax = plt.subplots(figsize=(10, 6))
+            for k, (xs, ys) in data.items():
+                ax.plot(xs, ys, "o-", label=k)
+            ax.set_xlabel(xl); ax.set_ylabel(yl); ax.grid(True); ax.legend()
+            fig.savefig(path, dpi=120)
+            plt.close(fig)
+    except ImportError:
+        from ..utils.svgplot import line_chart
+
+        paths = [str(line_chart(os.path.join(out, "precision_performance.svg"), curves,
+                                title="Performance across precision formats", xlabel="Matrix size", ylabel="TFLOPS")),
+                 str(line_chart(os.path.join(out, "memory_bandwidth.svg"), bws,
+                                title="Memory bandwidth vs data size", xlabel="Size (M elements)", ylabel="GB/s"))]
+    print("Figures: " + ", ".join(paths))
+    return paths
 
 
 if __name__ == "__main__":

@@ -104,6 +104,13 @@ def create_scaling_report(data_dir, plot: bool = True) -> pd.DataFrame | None:
             ax[0].set_xlabel("GPUs"); ax[0].set_ylabel("speedup"); ax[0].legend()
             ax[1].set_xlabel("GPUs"); ax[1].set_ylabel("efficiency")
             fig.savefig(data_dir / "scaling_analysis.png", dpi=120)
-        except ImportError:
-            pass  # matplotlib is optional; the CSV is the artefact of record
+        except ImportError:  # no matplotlib in this image: the same two panels as SVG files
+            from .svgplot import line_chart
+
+            g = list(table["gpus"])
+            line_chart(data_dir / "scaling_analysis.svg",
+                       {"ideal": (g, list(table["ideal"])), **{m: (g, list(table[f"{m}_speedup"])) for m in durations}},
+                       title="Speedup vs 1 GPU", xlabel="GPUs", ylabel="speedup")
+            line_chart(data_dir / "scaling_efficiency.svg", {m: (g, list(table[f"{m}_efficiency"])) for m in durations},
+                       title="Scaling efficiency", xlabel="GPUs", ylabel="speedup / GPUs")
     return table

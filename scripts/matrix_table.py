@@ -1,10 +1,17 @@
-"""matrix_table.py [dir]: markdown table of the bench matrix (profiles/bench/r2/matrix_n<N>_<config>_<impl>[_flags].json)."""
+"""matrix_table.py [dir] [--svg out.svg]: markdown table of the bench matrix
+(profiles/bench/r2/matrix_n<N>_<config>_<impl>[_flags].json); --svg also draws throughput relative to the same arm at N=1."""
 import json
 import re
 import sys
 from pathlib import Path
 
-d = Path(sys.argv[1] if len(sys.argv) > 1 else "profiles/bench/r2")
+argv = sys.argv[1:]
+svg = None
+if "--svg" in argv:
+    i = argv.index("--svg")
+    svg = argv[i + 1]
+    del argv[i:i + 2]
+d = Path(argv[0] if argv else "profiles/bench/r2")
 rows = {}
 for f in sorted(d.glob("matrix_n*_*.json")):
     m = re.match(r"matrix_n(\d+)_(.+?)_(hyperion|torch|reference)(?:_(.+))?$", f.stem)
@@ -47,3 +54,14 @@ for (cfg, arm), v in sorted(rows.items()):
             s += f"; {mem:.1f} GB" if mem else ""
             cells.append(s + ")")
     print(f"| {cfg} | {arm} | " + " | ".join(cells) + " |")
+
+if svg:
+    sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+    from hyperion_b200.utils.svgplot import line_chart
+
+    series = {"ideal": (ns, [float(n) for n in ns])}
+    for (cfg, arm), v in sorted(rows.items()):
+        pts = {n: c[0] for n, c in v.items() if c != "unavailable"}
+        if 1 in pts and len(pts) > 2 and "+" not in arm:
+            series[f"{cfg} {arm}"] = (sorted(pts), [pts[n] / pts[1] for n in sorted(pts)])
+    line_chart(svg, series, title="Weak scaling: throughput vs the same arm at N=1", xlabel="GPUs", ylabel="x N=1")

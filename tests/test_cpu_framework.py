@@ -112,7 +112,8 @@ def test_scaling_report_reproduces_reference_numbers(tmp_path):
 
     for f in (REF / "data/distributed").glob("*_metrics.csv"):
         shutil.copy(f, tmp_path / f.name)
-    table = create_scaling_report(tmp_path, plot=False)
+    table = create_scaling_report(tmp_path, plot=True)
+    assert (tmp_path / "scaling_analysis.png").exists() or (tmp_path / "scaling_analysis.svg").exists()
     row4 = table[table.gpus == 4].iloc[0]
     assert abs(row4["language_ddp_speedup"] - 3.4223) < 2e-3
     assert abs(row4["cifar_speedup"] - 2.9274) < 2e-3

@@ -21,6 +21,9 @@ def test_probe_csv_schemas(tmp_path):
     assert set(prec["Precision"]) == {"FP32", "TF32", "FP16", "BF16"}
     bw = pd.read_csv(tmp_path / "bandwidth_results.csv")
     assert list(bw.columns)[:2] == ["Size (M elements)", "Bandwidth (GB/s)"]
+    # the notebook's two figures (PNG with matplotlib, SVG without)
+    assert any((tmp_path / f"precision_performance.{e}").exists() for e in ("png", "svg"))
+    assert any((tmp_path / f"memory_bandwidth.{e}").exists() for e in ("png", "svg"))
 
 
 def test_benchmark_utils_return_keys(tmp_path):
@@ -58,6 +61,17 @@ def test_baseline_benchmark_columns(tmp_path):
     df = batch_scaling(tiny, (3, 8, 8), 10, batch_sizes=(1, 2), out_dir=str(tmp_path), iters=2, warmup=1)
     assert list(df.columns) == COLUMNS + ["Batch Size"]
     assert (tmp_path / "scaling" / "tiny_batch_scaling.csv").exists()
+    import xml.dom.minidom as minidom
+
+    from hyperion_b200.bench.baseline import visualize_baseline_results, visualize_batch_scaling
+
+    one = pd.DataFrame([r], columns=COLUMNS)
+    f1 = visualize_baseline_results(one, str(tmp_path))
+    f2 = visualize_batch_scaling(df, "Tiny Net", str(tmp_path))
+    assert f1.endswith("visualizations/baseline_benchmarks.svg") and f2.endswith("visualizations/tiny_net_batch_scaling.svg")
+    for f in (f1, f2):                                               # 2x2 page of nested charts, panel files removed
+        assert len(minidom.parse(f).documentElement.getElementsByTagName("svg")) == 4
+    assert sorted(x.name for x in (tmp_path / "visualizations").iterdir()) == ["baseline_benchmarks.svg", "tiny_net_batch_scaling.svg"]
 
 
 def test_fusion_bench_outputs(tmp_path):
@@ -70,6 +84,28 @@ def test_fusion_bench_outputs(tmp_path):
     assert (out / "compilation_ckpt_benchmark.csv").exists() and (out / "compilation_ckpt_analysis.txt").exists()
     rows = json.loads((out / "compilation_ckpt_benchmark.json").read_text())
     assert set(rows[0]) == {"model", "variant", "time_ms", "mem_gb"}
+    assert (out / "compilation_ckpt_speed_mem.png").exists() or (out / "compilation_ckpt_speed.svg").exists()
+
+
+def test_svg_charts_are_well_formed(tmp_path):
+    import xml.dom.minidom as minidom
+
+    from hyperion_b200.utils.svgplot import _ticks, bar_chart, line_chart
+
+    assert _ticks(0, 1800) == [0, 500, 1000, 1500] and _ticks(0, 0.9)[:3] == [0, 0.2, 0.4]
+    p = line_chart(tmp_path / "a" / "l.svg", {"ideal": ([1, 2, 4, 8], [1, 2, 4, 8]), "m<1>": ([1, 2, 4, 8], [1, 1.9, None, float("nan")]),
+                                               "empty": ([1], [None])}, title="t & t", xlabel="GPUs", ylabel="x")
+    d = minidom.parse(str(p))
+    assert len(d.getElementsByTagName("polyline")) == 2          # the all-None series is dropped
+    assert len(d.getElementsByTagName("circle")) == 4 + 2        # None / NaN points are skipped
+    assert "m&lt;1&gt;" in p.read_text() and "stroke-dasharray" in p.read_text()
+    b = bar_chart(tmp_path / "b.svg", ["x", "y"], {"eager": [1.0, 2.0], "hyperion": [0.5, None]}, title="ms")
+    d = minidom.parse(str(b))
+    bars = [r for r in d.getElementsByTagName("rect") if r.getAttribute("fill").startswith("#") and r.getAttribute("width") != "12"]
+    assert len(bars) == 3
+    assert max(float(r.getAttribute("height")) for r in bars) <= 310
+    line_chart(tmp_path / "e.svg", {})                               # degenerate inputs still give a valid file
+    minidom.parse(str(tmp_path / "e.svg"))
 
 
 def test_bench_reference_arm_reports_unavailable():
