@@ -145,25 +145,21 @@ def run(base_dir: str = ".", dtype: str = "fp32", repeat: int = 50, variants=("e
     with open(os.path.join(out, "compilation_ckpt_analysis.txt"), "w") as f:
         f.write("\n".join(lines) + "\n")
     print("\n".join(lines))
-    try:
-        import matplotlib
+    from ..utils.svgplot import bar_chart, pyplot
 
-        matplotlib.use("Agg")
-        import matplotlib.pyplot as plt
-
+    plt = pyplot()
+    if plt is not None and len(df):
         fig, ax = plt.subplots(1, 2, figsize=(10, 4))
         df.pivot(index="model", columns="variant", values="time_ms").plot.bar(ax=ax[0], title="time (ms)")
         df.pivot(index="model", columns="variant", values="mem_gb").plot.bar(ax=ax[1], title="peak memory (GB)")
         fig.savefig(os.path.join(out, "compilation_ckpt_speed_mem.png"), dpi=120)
-    except ImportError:  # no matplotlib in this image: the same two panels as SVG files
-        from ..utils.svgplot import bar_chart
-
-        if len(df):
-            models = list(df["model"].unique())
-            for col, stem, label in (("time_ms", "speed", "time (ms)"), ("mem_gb", "mem", "peak memory (GB)")):
-                piv = df.pivot(index="model", columns="variant", values=col)
-                bar_chart(os.path.join(out, f"compilation_ckpt_{stem}.svg"), models,
-                          {v: [piv.loc[m, v] for m in models] for v in piv.columns}, title=label, ylabel=label)
+    elif len(df):  # no matplotlib in this image: the same two panels as SVG files
+        models = list(df["model"].unique())
+        for col, stem, label in (("time_ms", "speed", "time (ms)"), ("mem_gb", "mem", "peak memory (GB)")):
+            piv = df.pivot(index="model", columns="variant", values=col)
+            bar_chart(os.path.join(out, f"compilation_ckpt_{stem}.svg"), models,
+                      {v: [piv.loc[m, v] if v in piv.columns and m in piv.index else None for m in models] for v in piv.columns},
+                      title=label, ylabel=label)
     return df
 
 

@@ -132,12 +132,10 @@ def plot_results(prec: pd.DataFrame, bw: pd.DataFrame, out: str) -> list[str]:
         if "TFLOPS tcgen05" in sub.columns and sub["TFLOPS tcgen05"].notna().any():
             curves[f"{name} tcgen05"] = (sizes, [sub["TFLOPS tcgen05"].get(s) for s in sizes])
     bws = {c.replace(" (GB/s)", ""): (list(bw["Size (M elements)"]), list(bw[c])) for c in bw.columns if c.endswith("(GB/s)")}
-    try:
-        import matplotlib
+    from ..utils.svgplot import line_chart, pyplot
 
-        matplotlib.use("Agg")
-        import matplotlib.pyplot as plt
-
+    plt = pyplot()
+    if plt is not None:
         paths = [os.path.join(out, "precision_performance.png"), os.path.join(out, "memory_bandwidth.png")]
         for path, data, xl, yl in ((paths[0], curves, "Matrix size", "TFLOPS"), (paths[1], bws, "Size (M elements)", "GB/s")):
             fig, ax = plt.subplots(figsize=(10, 6))
@@ -146,9 +144,7 @@ def plot_results(prec: pd.DataFrame, bw: pd.DataFrame, out: str) -> list[str]:
             ax.set_xlabel(xl); ax.set_ylabel(yl); ax.grid(True); ax.legend()
             fig.savefig(path, dpi=120)
             plt.close(fig)
-    except ImportError:
-        from ..utils.svgplot import line_chart
-
+    else:
         paths = [str(line_chart(os.path.join(out, "precision_performance.svg"), curves,
                                 title="Performance across precision formats", xlabel="Matrix size", ylabel="TFLOPS")),
                  str(line_chart(os.path.join(out, "memory_bandwidth.svg"), bws,

@@ -90,12 +90,10 @@ def create_scaling_report(data_dir, plot: bool = True) -> pd.DataFrame | None:
     print("\n=== Scaling analysis ===")
     print(table.to_string(index=False))
     if plot:
-        try:
-            import matplotlib
+        from .svgplot import line_chart, pyplot
 
-            matplotlib.use("Agg")
-            import matplotlib.pyplot as plt
-
+        plt = pyplot()
+        if plt is not None:
             fig, ax = plt.subplots(1, 2, figsize=(12, 5))
             ax[0].plot(table["gpus"], table["ideal"], "k--", label="ideal")
             for model in durations:
@@ -104,9 +102,7 @@ def create_scaling_report(data_dir, plot: bool = True) -> pd.DataFrame | None:
             ax[0].set_xlabel("GPUs"); ax[0].set_ylabel("speedup"); ax[0].legend()
             ax[1].set_xlabel("GPUs"); ax[1].set_ylabel("efficiency")
             fig.savefig(data_dir / "scaling_analysis.png", dpi=120)
-        except ImportError:  # no matplotlib in this image: the same two panels as SVG files
-            from .svgplot import line_chart
-
+        else:  # no matplotlib in this image: the same two panels as SVG files
             g = list(table["gpus"])
             line_chart(data_dir / "scaling_analysis.svg",
                        {"ideal": (g, list(table["ideal"])), **{m: (g, list(table[f"{m}_speedup"])) for m in durations}},

@@ -16,6 +16,20 @@ _COLORS = ["#1f77b4", "#ff7f0e", "#2ca02c", "#d62728", "#9467bd", "#8c564b", "#e
 _W, _H, _ML, _MR, _MT, _MB = 700, 400, 70, 190, 40, 50
 
 
+def pyplot():
+    """``matplotlib.pyplot`` on the Agg backend, or None when matplotlib is absent (or is a stand-in module without a backend, as
+    the reference arm installs for the reference's module-scope import)."""
+    try:
+        import matplotlib
+
+        matplotlib.use("Agg")
+        import matplotlib.pyplot as plt
+
+        return plt if hasattr(plt, "subplots") else None
+    except (ImportError, AttributeError):
+        return None
+
+
 def _esc(s) -> str:
     return str(s).replace("&", "&amp;").replace("<", "&lt;").replace(">", "&gt;")
 
