@@ -29,11 +29,33 @@ def main() -> int:
         from .data import synth
 
         ap = argparse.ArgumentParser(prog="hyperion data")
-        ap.add_argument("what", choices=["synth"])
+        ap.add_argument("what", choices=["synth", "prepare", "verify"],
+                        help="synth: seeded stand-ins in the real formats; prepare: the real corpora (data/raw or a download); "
+                             "verify: reload and print what is under data/processed")
         ap.add_argument("--base_dir", default=".")
         ap.add_argument("--seed", type=int, default=0)
-        ap.add_argument("--small", action="store_true", help="1/50 of the row counts (quick check)")
+        ap.add_argument("--small", action="store_true", help="synth: 1/50 of the row counts (quick check)")
+        ap.add_argument("--only", choices=["wikitext2", "cifar10"], default=None, help="prepare: one corpus instead of both")
+        ap.add_argument("--tokenizer", default="gpt2", help="prepare: tokenizer name or local directory")
+        ap.add_argument("--no-download", action="store_true", help="prepare: use data/raw only")
         a = ap.parse_args(argv)
+        if a.what == "verify":
+            from .data import prepare
+
+            return 0 if prepare.verify(a.base_dir) else 1
+        if a.what == "prepare":
+            from .data import prepare
+
+            try:
+                if a.only in (None, "wikitext2"):
+                    prepare.prepare_wikitext2(a.base_dir, tokenizer=a.tokenizer, download=not a.no_download)
+                if a.only in (None, "cifar10"):
+                    prepare.prepare_cifar10(a.base_dir, download=not a.no_download)
+            except prepare.DataUnavailable as e:
+                print(f"error: {e}", file=sys.stderr)
+                return 1
+            prepare.verify(a.base_dir)
+            return 0
         rows_w = {k: max(8, v // 50) for k, v in synth.WIKITEXT2_ROWS.items()} if a.small else None
         rows_c = {k: max(8, v // 50) for k, v in synth.CIFAR10_ROWS.items()} if a.small else None
         synth.write_wikitext2_like(f"{a.base_dir}/data/processed/wikitext2_tokenized", seed=a.seed, rows=rows_w)

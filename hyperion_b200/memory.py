@@ -73,6 +73,24 @@ def enable_checkpointing(model: torch.nn.Module, on: bool = True) -> int:
     return k
 
 
+def checkpoint_resnet_blocks(model: torch.nn.Module) -> torch.nn.Module:
+    """The reference's helper of that name (memory_optimization.ipynb c4 L1-14: it replaces ``forward`` by one that runs
+    ``[layer1..layer4]`` through ``checkpoint_sequential``).  The ResNets here carry the switch already, so this flips
+    ``use_checkpoint`` and returns the same module; a torchvision ResNet gets the wrapped forward."""
+    if hasattr(model, "use_checkpoint"):
+        model.use_checkpoint = True
+        return model
+    stages = [model.layer1, model.layer2, model.layer3, model.layer4]
+
+    def forward_with_ckpt(x):
+        x = model.maxpool(model.relu(model.bn1(model.conv1(x))))
+        x = checkpoint_sequential(stages, len(stages), x) if torch.is_grad_enabled() else torch.nn.Sequential(*stages)(x)
+        return model.fc(torch.flatten(model.avgpool(x), 1))
+
+    model.forward = forward_with_ckpt
+    return model
+
+
 @dataclass
 class MemorySample:
     allocated_mb: float

@@ -278,7 +278,13 @@ def conv_bn_act(x, conv: nn.Conv2d, bn: nn.BatchNorm2d, relu: bool = True, resid
     if bn.training:
         if bn.num_batches_tracked is not None:
             bn.num_batches_tracked.add_(1)
-    y = F.batch_norm(y, bn.running_mean, bn.running_var, bn.weight, bn.bias, bn.training, bn.momentum or 0.0, bn.eps)
+    if y.device.type == "cpu" and y.dtype != torch.float32:
+        # ATen's CPU batch norm wants one dtype for weight and running statistics; 16-bit modules keep fp32 statistics
+        w = bn.weight.float() if bn.weight is not None else None
+        b = bn.bias.float() if bn.bias is not None else None
+        y = F.batch_norm(y.float(), bn.running_mean, bn.running_var, w, b, bn.training, bn.momentum or 0.0, bn.eps).to(y.dtype)
+    else:
+        y = F.batch_norm(y, bn.running_mean, bn.running_var, bn.weight, bn.bias, bn.training, bn.momentum or 0.0, bn.eps)
     if residual is not None:
         y = y + residual
     return F.relu(y) if relu else y

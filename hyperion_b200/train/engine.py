@@ -93,8 +93,8 @@ def build_engine(model: nn.Module, *, strategy: str = "single", precision: str =
     rank, W = world()
     pol = policy(precision)
     device = torch.device(device) if device is not None else next(model.parameters()).device
-    if device.type != "cuda":
-        pol = policy("fp32") if precision != "fp32" and not torch.cuda.is_available() and precision == "fp16" else pol
+    if device.type != "cuda" and precision == "fp16" and not torch.cuda.is_available():
+        pol = policy("fp32")          # no fp16 arithmetic worth the name on a CPU-only machine
     model = model.to(device)
     cast_trainable(model, pol.dtype)
     scaler = DynamicLossScaler(device, enabled=True) if pol.needs_scaler else None

@@ -175,3 +175,39 @@ def test_reference_arm_environment_and_unavailable_line(tmp_path, capsys, monkey
     assert tok.vocab_size == 50257 and tok.pad_token_id == 50256
     for name in made:
         sys.modules.pop(name, None)
+
+
+def test_distributed_utils_drop_in_module():
+    """`import distributed_utils` of the reference keeps working: same twelve public names, the reference's argument order."""
+    import importlib.util
+    import inspect
+
+    spec = importlib.util.spec_from_file_location("hyperion_distributed_utils_dropin", ROOT / "distributed_utils.py")
+    du = importlib.util.module_from_spec(spec)            # by path: the reference arm imports the reference's module of that name
+    spec.loader.exec_module(du)
+    names = ["WikiText2TorchDataset", "CIFAR10TorchDataset", "SimpleTransformerLM", "_local_gpu", "setup", "cleanup",
+             "train_language_model_ddp", "train_cifar_model_ddp", "train_language_model_fsdp", "train_llama_fsdp",
+             "create_scaling_report", "run_scaling_experiment"]
+    assert sorted(du.__all__) == sorted(names) and all(callable(getattr(du, n)) for n in names)
+    for fn in ("train_language_model_ddp", "train_cifar_model_ddp", "train_language_model_fsdp"):
+        assert list(inspect.signature(getattr(du, fn)).parameters)[:4] == ["rank", "world_size", "epochs", "base_dir"]
+    p = inspect.signature(du.train_llama_fsdp).parameters
+    assert {"epochs", "base_dir", "hf_token", "model_id", "lora", "batch_size", "progress_every"} <= set(p)
+    assert list(inspect.signature(du.setup).parameters)[:3] == ["rank", "world_size", "backend"]
+    assert list(inspect.signature(du.run_scaling_experiment).parameters)[:5] == ["model_type", "gpu_counts", "epochs", "base_dir", "hf_token"]
+    cmds = du.run_scaling_experiment("llama", [1, 2], 1, "/tmp/x", "tok", dry_run=True)
+    assert len(cmds) == 2 and "--hf_token=tok" in cmds[1] and "--model=llama" in cmds[1] and "--nproc-per-node=2" in cmds[1]
+    m = du.SimpleTransformerLM(100, 32, 2, 1)             # positional like distributed_utils.py:76
+    assert m(torch.randint(0, 100, (2, 8))).shape == (2, 8, 100)
+    assert du._local_gpu(3) == 0 or torch.cuda.is_available()
+
+
+def test_benchmarking_drop_in_module():
+    import importlib.util
+
+    spec = importlib.util.spec_from_file_location("hyperion_benchmarking_dropin", ROOT / "benchmarking.py")
+    bm = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bm)
+    r = bm.benchmark_forward_pass(nn.Linear(8, 8), torch.rand(4, 8), num_iterations=2, warmup=1)
+    assert set(r) == {"total_time", "avg_time", "throughput", "memory_usage"}
+    assert sorted(bm.__all__) == ["benchmark_forward_pass", "benchmark_training_step", "compare_precision_formats", "save_benchmark_results"]
