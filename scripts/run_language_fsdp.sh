@@ -11,7 +11,7 @@ export TORCH_NCCL_HEARTBEAT_TIMEOUT_SEC=${TORCH_NCCL_HEARTBEAT_TIMEOUT_SEC:-600}
 export HYPERION_NVLS=${HYPERION_NVLS:-1}        # use multimem.* in the fused kernels when a multicast mapping exists
 NGPU=${NGPU:-4}
 EPOCHS=${EPOCHS:-25}
-BASE_DIR=${BASE_DIR:-$(cd "$(dirname "$0")/.." && pwd)}
-cd "$BASE_DIR"
+REPO=$(cd "$(dirname "$0")/.." && pwd)
+BASE_DIR=${BASE_DIR:-$REPO}                     # data/processed is read from, data/distributed written under it
 python -m torch.distributed.run --standalone --local-addr 127.0.0.1 --nproc-per-node "$NGPU" \
-  run_distributed.py --model language_fsdp --epochs "$EPOCHS" --base_dir "$BASE_DIR" "$@"
+  "$REPO/run_distributed.py" --model language_fsdp --epochs "$EPOCHS" --base_dir "$BASE_DIR" "$@"

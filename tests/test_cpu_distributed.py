@@ -277,3 +277,23 @@ def test_gloo_parameters_without_gradient_do_not_desynchronise_the_ranks(tmp_pat
     r = torch.load(out, weights_only=False)
     assert r["same"], "ranks diverged"
     assert any(n.startswith("b.") for n in r["unused"]), r["unused"]
+
+
+def test_launch_script_runs_the_fsdp_job_under_torchrun(tmp_path):
+    """scripts/run_language_fsdp.sh (reference: 02_development/run_language_fsdp.sh) end to end on gloo, 2 ranks: the launcher, the
+    environment preset, run_distributed.py, the FSDP trainer, the metrics CSV and the checkpoint."""
+    import subprocess
+    from pathlib import Path
+
+    import pandas as pd
+
+    root = Path(__file__).resolve().parent.parent
+    env = {**os.environ, "NGPU": "2", "EPOCHS": "2", "BASE_DIR": str(tmp_path), "CUDA_VISIBLE_DEVICES": ""}
+    r = subprocess.run(["bash", str(root / "scripts/run_language_fsdp.sh"), "--backend", "gloo", "--steps", "2", "--batch_size", "4"],
+                       env=env, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
+    csvs = [f for f in (tmp_path / "data/distributed").glob("language_fsdp_2gpus_*_metrics.csv") if "device_metrics" not in f.name]
+    assert len(csvs) == 1, list((tmp_path / "data/distributed").iterdir())
+    df = pd.read_csv(csvs[0])
+    assert list(df["epoch"]) == [1, 2] and set(df["gpus"]) == {2} and {"loss", "duration"} <= set(df.columns)
+    assert any((tmp_path / "data/distributed").glob("*.pt"))
