@@ -92,7 +92,7 @@ def train_cifar_model_ddp(rank: int, world_size: int, epochs: int = 5, base_dir:
     dev = setup(rank, world_size, backend, seed=seed)
     precision = precision or ("fp16" if dev.type == "cuda" else "fp32")
     out_dir = os.path.join(base_dir, "data/distributed")
-    logger = CsvLogger(out_dir, "cifar_ddp", world_size, rank)
+    logger = CsvLogger(out_dir, "cifar_ddp" if arch == "resnet18" else f"{arch}_ddp", world_size, rank)
     make, size, ncls = VISION_MODELS[arch]
     if size == 32:
         x_all, y_all = load_cifar_tensors(base_dir, dev, synthetic, rows, seed)

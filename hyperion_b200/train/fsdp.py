@@ -84,7 +84,7 @@ def train_gpt2_fsdp(rank: int, world_size: int, epochs: int = 1, base_dir: str =
     cfg = {"medium": GPT2Config.medium, "small": GPT2Config.small, "tiny": GPT2Config.tiny}[size]()
     seq_len = min(seq_len, cfg.n_positions)
     out_dir = os.path.join(base_dir, "data/distributed")
-    logger = CsvLogger(out_dir, "language_fsdp", world_size, rank, run_id=None)
+    logger = CsvLogger(out_dir, "gpt2_fsdp", world_size, rank, run_id=None)
     model = GPT2LMHeadModel(cfg)
     model.use_checkpoint = checkpointing
     units = [m for m in model.modules() if isinstance(m, GPT2Block)]

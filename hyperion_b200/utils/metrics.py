@@ -22,6 +22,10 @@ HEADERS = {
     "language_fsdp": ["epoch", "loss", "duration", "gpus"],
     "cifar_ddp": ["epoch", "loss", "accuracy", "duration", "gpus"],
     "llama": ["epoch", "loss", "duration_s", "gpus", "mode"],
+    # jobs the reference does not have get their own file-name prefix, so a scaling report never mixes two models
+    "gpt2_fsdp": ["epoch", "loss", "duration", "gpus"],
+    "resnet50_ddp": ["epoch", "loss", "accuracy", "duration", "gpus"],
+    "vit_ddp": ["epoch", "loss", "accuracy", "duration", "gpus"],
 }
 DEVICE_HEADER = ["epoch", "steps", "step_ms_max", "throughput", "unit", "peak_mem_mb", "gpus"]
 

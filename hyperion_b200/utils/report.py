@@ -4,12 +4,14 @@ Same inputs (``*_metrics.csv`` in a directory, classified by file-name substring
 ``max(1, n//3)`` epochs as warm-up, mean epoch duration, speedup vs the 1-GPU run, efficiency = speedup/gpus),
 same outputs (``scaling_analysis.csv`` with columns ``gpus, ideal, {model}_speedup, {model}_efficiency`` and an
 optional ``scaling_analysis.png`` when matplotlib exists).  Deviations, all listed in SURVEY.md appendix A:
-accepts ``duration_s`` (A-11), never fabricates sample curves when no CSVs exist (A-10).
+accepts ``duration_s`` (A-11), never fabricates sample curves when no CSVs exist (A-10), and files of other jobs
+(``gpt2_fsdp_*``, ``resnet50_ddp_*``, ``vit_ddp_*``) become columns of their own instead of being skipped.
 """
 from __future__ import annotations
 
 import glob
 import os
+import re
 from pathlib import Path
 
 import pandas as pd
@@ -27,7 +29,8 @@ def classify(filename: str) -> str | None:
         return "language_fsdp"
     if "llama" in base:
         return "llama"
-    return None
+    m = re.match(r"(.+?)_\d+gpus_", base)          # jobs beyond the reference's four: <kind>_<N>gpus_<stamp>_metrics.csv
+    return m.group(1) if m else None
 
 
 def steady_mean_duration(df: pd.DataFrame) -> float | None:

@@ -129,6 +129,25 @@ def test_scaling_report_never_fabricates(tmp_path):
     assert not list(tmp_path.glob("scaling_analysis*"))
 
 
+def test_scaling_report_keeps_other_jobs_apart(tmp_path):
+    import pandas as pd
+
+    from hyperion_b200.utils.metrics import HEADERS
+    from hyperion_b200.utils.report import classify, create_scaling_report
+
+    assert classify("language_fsdp_4gpus_20250427_085625_metrics.csv") == "language_fsdp"
+    assert classify("cifar_ddp_1gpus_x_metrics.csv") == "cifar" and classify("llama_1gpus_x_metrics.csv") == "llama"
+    assert classify("gpt2_fsdp_8gpus_20261107_000000_metrics.csv") == "gpt2_fsdp"
+    assert classify("vit_ddp_2gpus_20261107_000000_metrics.csv") == "vit_ddp" and classify("notes_metrics.csv") is None
+    assert HEADERS["gpt2_fsdp"] == HEADERS["language_fsdp"] and HEADERS["resnet50_ddp"] == HEADERS["cifar_ddp"]
+    for kind, g, d in (("gpt2_fsdp", 1, 8.0), ("gpt2_fsdp", 8, 1.25), ("language_fsdp", 1, 2.0), ("language_fsdp", 8, 1.0)):
+        pd.DataFrame({"epoch": [1, 2, 3], "loss": [1.0] * 3, "duration": [99.0, d, d], "gpus": [g] * 3}).to_csv(
+            tmp_path / f"{kind}_{g}gpus_20261107_00000{g}_metrics.csv", index=False)
+    t = create_scaling_report(tmp_path, plot=False)
+    row = t[t.gpus == 8].iloc[0]
+    assert abs(row["gpt2_fsdp_speedup"] - 6.4) < 1e-9 and abs(row["language_fsdp_speedup"] - 2.0) < 1e-9
+
+
 def test_scaling_orchestrator_commands():
     from hyperion_b200.utils.scaling import run_scaling_experiment
 
