@@ -37,6 +37,11 @@ def train_llama_fsdp(rank: int, world_size: int, epochs: int = 1, base_dir: str 
                      resume: str | None = None, graph: bool | None = None, reshard_after_forward: bool | None = None):
     dev = setup(rank, world_size, backend, seed=seed)
     cfg = config or CONFIGS[size]()
+    if dev.type != "cuda" and config is None and size == "7b" and os.environ.get("HYPERION_ALLOW_CPU_7B") != "1":
+        # fp32 weights + gradients + AdamW state of 6.7 B parameters per rank: > 100 GB of host memory, and the OOM killer's choice of
+        # victim is not ours to make.  The CPU / gloo path exists for the host-side logic; it has a model of its own size.
+        raise RuntimeError("Llama-2-7B on a machine without a GPU needs > 100 GB of host memory per rank; pass size='tiny' "
+                           "(--llama-size tiny) for CPU runs, or set HYPERION_ALLOW_CPU_7B=1 to go ahead")
     mode = "lora_bf16" if lora else "fsdp_bf16"
     out_dir = os.path.join(base_dir, "data/distributed")
     logger = CsvLogger(out_dir, "llama", world_size, rank)

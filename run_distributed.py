@@ -64,6 +64,25 @@ def build_parser() -> argparse.ArgumentParser:
     return p
 
 
+def forwarded_args(argv: list[str]) -> list[str]:
+    """What a scaling sweep hands down to every run it launches: the command line as given, minus the options the sweep sets itself
+    (``--model``, ``--epochs``, ``--base_dir``, ``--scaling_gpus``) -- so ``--backend``, ``--steps``, ``--batch_size``, ``--lora``,
+    ``--llama-size`` ... apply to the child runs too."""
+    own = ("--model", "--epochs", "--base_dir", "--scaling_gpus")
+    out, skip = [], False
+    for tok in argv:
+        if skip:
+            skip = False
+            continue
+        if tok in own:
+            skip = True
+            continue
+        if tok.split("=", 1)[0] in own:
+            continue
+        out.append(tok)
+    return out
+
+
 def run_selected(which: str, args, rank: int, world: int) -> None:
     from hyperion_b200 import train
 
@@ -119,7 +138,7 @@ def main(argv=None) -> int:
         from hyperion_b200.utils.scaling import run_scaling_experiment
 
         gpus = [int(x) for x in args.scaling_gpus.split(",")]
-        extra = ["--synthetic"] + ([f"--steps={args.steps}"] if args.steps else []) + (["--lora"] if args.lora else [])
+        extra = forwarded_args(sys.argv[1:] if argv is None else list(argv))
         for mdl in ["language_ddp", "cifar", "language_fsdp", "llama"]:
             run_scaling_experiment(mdl, gpus, epochs=args.epochs, base_dir=args.base_dir, extra_args=extra)
         create_scaling_report(os.path.join(args.base_dir, "data/distributed"))

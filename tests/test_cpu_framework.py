@@ -148,6 +148,16 @@ def test_scaling_report_keeps_other_jobs_apart(tmp_path):
     assert abs(row["gpt2_fsdp_speedup"] - 6.4) < 1e-9 and abs(row["language_fsdp_speedup"] - 2.0) < 1e-9
 
 
+def test_scaling_sweep_forwards_the_command_line():
+    import run_distributed
+
+    argv = ["--model", "scaling", "--scaling_gpus=1,2", "--epochs", "3", "--backend", "gloo", "--steps=2", "--lora", "--base_dir", "/x",
+            "--llama-size", "tiny", "--batch_size", "4"]
+    assert run_distributed.forwarded_args(argv) == ["--backend", "gloo", "--steps=2", "--lora", "--llama-size", "tiny", "--batch_size", "4"]
+    a = run_distributed.build_parser().parse_args(["--model", "llama"] + run_distributed.forwarded_args(argv))
+    assert a.backend == "gloo" and a.steps == 2 and a.lora and a.llama_size == "tiny" and a.batch_size == 4
+
+
 def test_scaling_orchestrator_commands():
     from hyperion_b200.utils.scaling import run_scaling_experiment
 
