@@ -19,6 +19,7 @@
 // Reference call sites: torchvision resnet18/50 Conv2d (02_development/distributed_utils.py:229; Phase 1
 // baseline_performance.ipynb c0 L23; Phase 5 compilation_optimization.py:89), SURVEY.md K-O7.
 #include "common/ptx.cuh"
+#include "common/tiling.cuh"
 #include "common/tmap.cuh"
 #include "common/util.cuh"
 #include <stdlib.h>
@@ -55,14 +56,9 @@ struct Cfg {
   static constexpr int TMEM_COLS = 2 * BN;
 };
 
-struct Tile { int kb, pw, ph, pn; };
+using Tile = hyp::tiling::ConvTile;   // tile order: common/tiling.cuh, host-testable
 __device__ __forceinline__ Tile decode(int t, const Params& p) {
-  Tile c;
-  c.kb = t % p.tiles_k; t /= p.tiles_k;   // output-channel blocks of one patch run back to back (input patch stays in L2)
-  c.pw = t % p.tiles_w; t /= p.tiles_w;
-  c.ph = t % p.tiles_h; t /= p.tiles_h;
-  c.pn = t;
-  return c;
+  return hyp::tiling::decode_conv_tile(t, p.tiles_k, p.tiles_w, p.tiles_h);
 }
 
 template <int BN>
@@ -342,17 +338,9 @@ struct WCfg {
   static constexpr int TMEM_COLS = 2 * BN;
 };
 
-struct WItem { int kb, tap, cb, pb0, pb1; };
+using WItem = hyp::tiling::WgradItem;
 __device__ __forceinline__ WItem wdecode(int t, const WParams& p) {
-  WItem w;
-  const int split = t % p.splits; t /= p.splits;
-  w.cb = t % p.cblocks; t /= p.cblocks;
-  w.tap = t % (p.R * p.S); t /= (p.R * p.S);
-  w.kb = t;
-  const int total_pb = p.tiles_w * p.tiles_h * p.tiles_n;
-  w.pb0 = split * p.pb_per_split;
-  w.pb1 = min(total_pb, w.pb0 + p.pb_per_split);
-  return w;
+  return hyp::tiling::decode_wgrad_item(t, p.splits, p.cblocks, p.R * p.S, p.tiles_w * p.tiles_h * p.tiles_n, p.pb_per_split);
 }
 
 template <int BN>

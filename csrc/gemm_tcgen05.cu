@@ -17,6 +17,7 @@
 // (Phase 1/01_hardware_exploration.ipynb c1 L92) and every nn.Linear inside
 // the models (02_development/distributed_utils.py:75-88).
 #include "common/ptx.cuh"
+#include "common/tiling.cuh"
 #include "common/tmap.cuh"
 #include "common/util.cuh"
 #include <stdlib.h>
@@ -214,26 +215,11 @@ __device__ __noinline__ void epilogue8(const Params* pp, float v0, float v1, flo
   }
 }
 
-struct TileCoord {
-  int m_blk, n_blk, kb0, kb1;
-};
+using TileCoord = hyp::tiling::TileCoord;
 
+// tile order (L2 grouping, split-K ranges): common/tiling.cuh, host-testable
 __device__ __forceinline__ TileCoord decode_tile(int tile, int tiles_m, int tiles_n, int nkb, int splits) {
-  const int per_split = tiles_m * tiles_n;
-  const int s = tile / per_split;
-  const int t = tile - s * per_split;
-  const int group_size = GROUP_M * tiles_n;
-  const int g = t / group_size;
-  const int first_m = g * GROUP_M;
-  const int gm = min(tiles_m - first_m, GROUP_M);
-  const int r = t - g * group_size;
-  TileCoord c;
-  c.m_blk = first_m + r % gm;
-  c.n_blk = r / gm;
-  const int per = (nkb + splits - 1) / splits;
-  c.kb0 = s * per;
-  c.kb1 = min(nkb, c.kb0 + per);
-  return c;
+  return hyp::tiling::decode_gemm_tile<GROUP_M>(tile, tiles_m, tiles_n, nkb, splits);
 }
 
 // 32 consecutive columns of one output row, compile-time epilogue kind:

@@ -99,3 +99,86 @@ def test_masks_differ_across_step_salt_and_plane(host_lib):
         a.update(kw)
         other, _ = reference_keep_mask(a["seed"], a["step"], a["salt"], a["plane"], 32, 128, 0.5)
         assert 0.35 < (other != base).mean() < 0.65, kw
+
+
+# ---------------------------------------------------------------------------------------------------------------------------------
+# csrc/common/tiling.cuh: the tile schedules of the persistent GEMM / convolution kernels, same source as the device code
+TILING_HARNESS = r"""
+#include "common/tiling.cuh"
+using namespace hyp::tiling;
+extern "C" void gemm_tile(int tile, int tiles_m, int tiles_n, int nkb, int splits, int* out) {
+  const TileCoord c = decode_gemm_tile<8>(tile, tiles_m, tiles_n, nkb, splits);
+  out[0] = c.m_blk; out[1] = c.n_blk; out[2] = c.kb0; out[3] = c.kb1;
+}
+extern "C" void conv_tile(int t, int tiles_k, int tiles_w, int tiles_h, int* out) {
+  const ConvTile c = decode_conv_tile(t, tiles_k, tiles_w, tiles_h);
+  out[0] = c.kb; out[1] = c.pw; out[2] = c.ph; out[3] = c.pn;
+}
+extern "C" void wgrad_item(int t, int splits, int cblocks, int taps, int total_pb, int pb_per_split, int* out) {
+  const WgradItem w = decode_wgrad_item(t, splits, cblocks, taps, total_pb, pb_per_split);
+  out[0] = w.kb; out[1] = w.tap; out[2] = w.cb; out[3] = w.pb0; out[4] = w.pb1;
+}
+"""
+
+
+@pytest.fixture(scope="module")
+def tiling_lib(tmp_path_factory):
+    gxx = shutil.which("g++")
+    if gxx is None:
+        pytest.skip("no g++ on this machine")
+    d = tmp_path_factory.mktemp("tilinglib")
+    (d / "harness.cpp").write_text(TILING_HARNESS)
+    so = d / "libtiling_host.so"
+    subprocess.run([gxx, "-O2", "-std=c++17", "-shared", "-fPIC", "-I", str(ROOT / "csrc"), str(d / "harness.cpp"), "-o", str(so)], check=True)
+    return ctypes.CDLL(str(so))
+
+
+@pytest.mark.parametrize("tiles_m,tiles_n,nkb,splits", [(1, 1, 1, 1), (8, 4, 16, 1), (13, 5, 7, 1), (3, 197, 12, 1), (2, 2, 64, 4),
+                                                          (1, 3, 10, 3), (17, 1, 5, 8), (32, 32, 32, 1)])
+def test_gemm_schedule_covers_every_tile_and_k_block_once(tiling_lib, tiles_m, tiles_n, nkb, splits):
+    out = (ctypes.c_int * 4)()
+    seen = np.zeros((tiles_m, tiles_n, nkb), dtype=np.int32)
+    order = []
+    for t in range(tiles_m * tiles_n * splits):
+        tiling_lib.gemm_tile(t, tiles_m, tiles_n, nkb, splits, out)
+        m, n, k0, k1 = list(out)
+        assert 0 <= m < tiles_m and 0 <= n < tiles_n and 0 <= k0 and k1 <= nkb
+        if k1 > k0:                                   # a trailing split may be empty when splits does not divide nkb
+            seen[m, n, k0:k1] += 1
+        order.append((m, n))
+    assert (seen == 1).all()
+    # L2 grouping: within the first split, any 8 consecutive tiles of a full group share one n block (one B panel)
+    if tiles_m >= 8 and splits == 1:
+        first_group = order[:8 * tiles_n]
+        for i in range(0, len(first_group), 8):
+            assert len({n for _, n in first_group[i:i + 8]}) == 1 and sorted(m for m, _ in first_group[i:i + 8]) == list(range(8))
+
+
+@pytest.mark.parametrize("tiles_k,tiles_w,tiles_h,tiles_n", [(1, 1, 1, 1), (4, 7, 7, 2), (2, 3, 5, 4), (16, 1, 2, 1)])
+def test_conv_forward_schedule(tiling_lib, tiles_k, tiles_w, tiles_h, tiles_n):
+    out = (ctypes.c_int * 4)()
+    seen = set()
+    prev = None
+    for t in range(tiles_k * tiles_w * tiles_h * tiles_n):
+        tiling_lib.conv_tile(t, tiles_k, tiles_w, tiles_h, out)
+        kb, pw, ph, pn = list(out)
+        assert 0 <= kb < tiles_k and 0 <= pw < tiles_w and 0 <= ph < tiles_h and 0 <= pn < tiles_n
+        seen.add((kb, pw, ph, pn))
+        if prev is not None and kb != 0:              # the output-channel blocks of one patch are consecutive (input patch stays in L2)
+            assert prev[1:] == (pw, ph, pn) and prev[0] == kb - 1
+        prev = (kb, pw, ph, pn)
+    assert len(seen) == tiles_k * tiles_w * tiles_h * tiles_n
+
+
+@pytest.mark.parametrize("kblocks,taps,cblocks,total_pb,splits", [(1, 1, 1, 1, 1), (2, 9, 2, 49, 4), (4, 9, 1, 10, 3), (1, 1, 4, 7, 7), (2, 49, 1, 5, 8)])
+def test_conv_wgrad_schedule(tiling_lib, kblocks, taps, cblocks, total_pb, splits):
+    per = (total_pb + splits - 1) // splits
+    out = (ctypes.c_int * 5)()
+    seen = np.zeros((kblocks, taps, cblocks, total_pb), dtype=np.int32)
+    for t in range(kblocks * taps * cblocks * splits):
+        tiling_lib.wgrad_item(t, splits, cblocks, taps, total_pb, per, out)
+        kb, tap, cb, pb0, pb1 = list(out)
+        assert 0 <= kb < kblocks and 0 <= tap < taps and 0 <= cb < cblocks and pb1 <= total_pb
+        if pb1 > pb0:
+            seen[kb, tap, cb, pb0:pb1] += 1
+    assert (seen == 1).all()                          # every (filter block, tap, channel block) sees every patch exactly once
