@@ -75,3 +75,38 @@ def test_checkpoint_resnet_blocks_on_a_torchvision_model():
     torch.testing.assert_close(net.conv1.weight.grad, g_ref)
     with torch.no_grad():
         torch.testing.assert_close(ck(x), ref)
+
+
+def test_notebooks_are_in_sync_and_run(tmp_path, monkeypatch, capsys):
+    """notebooks/*.ipynb (one per notebook of the reference): valid nbformat-4 JSON, equal to what scripts/make_notebooks.py writes, and
+    every code cell executes in order with HYPERION_NOTEBOOK_QUICK=1 on the CPU."""
+    import importlib.util
+    import json
+
+    spec = importlib.util.spec_from_file_location("make_notebooks", ROOT / "scripts/make_notebooks.py")
+    mk = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mk)
+    fresh = {p.name: p.read_text() for p in mk.write_all(tmp_path / "nb")}
+    names = ["01_hardware_exploration", "baseline_performance", "dataset_preparation", "core_framework", "mixed_precision",
+             "memory_optimization"]
+    assert sorted(fresh) == sorted(n + ".ipynb" for n in names)
+    monkeypatch.setenv("HYPERION_NOTEBOOK_QUICK", "1")
+    monkeypatch.setenv("HYPERION_BASE_DIR", str(tmp_path))
+    monkeypatch.setenv("HYPERION_REPO", str(ROOT))
+    for n in ["dataset_preparation", "core_framework", "mixed_precision", "memory_optimization", "01_hardware_exploration",
+              "baseline_performance"]:
+        committed = (ROOT / "notebooks" / f"{n}.ipynb").read_text()
+        assert committed == fresh[n + ".ipynb"], f"notebooks/{n}.ipynb is stale: run python scripts/make_notebooks.py"
+        nb = json.loads(committed)
+        assert nb["nbformat"] == 4 and nb["cells"][0]["cell_type"] == "markdown"
+        ns: dict = {"__name__": f"nb_{n}"}
+        for cell in nb["cells"]:
+            assert set(cell) >= {"cell_type", "metadata", "source"}
+            if cell["cell_type"] == "code":
+                assert cell["outputs"] == [] and cell["execution_count"] is None          # committed without outputs
+                exec(compile("".join(cell["source"]), f"{n}.ipynb", "exec"), ns)
+    out = capsys.readouterr().out
+    assert "Directory structure created" in out and "Models saved after 2 epochs." in out and "with checkpointing" in out
+    assert (tmp_path / "data/processed/simple_transformer_lm.pt").exists() and (tmp_path / "data/processed/resnet18_cifar10_amp.pt").exists()
+    assert (tmp_path / "results/benchmarks/hardware/precision_results.csv").exists()
+    assert (tmp_path / "results/visualizations/resnet-50_batch_scaling.svg").exists()
