@@ -9,7 +9,6 @@ from __future__ import annotations
 import torch
 
 from ..data import synth
-from ..parallel.runtime import world as _world
 from ..train.engine import build_engine
 
 

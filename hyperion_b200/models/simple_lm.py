@@ -17,7 +17,6 @@ the fused linear+cross-entropy op (loss and gradients in one pass over L2-sized 
 """
 from __future__ import annotations
 
-import torch
 import torch.nn as nn
 
 from .. import ops

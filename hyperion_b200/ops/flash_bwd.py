@@ -3,7 +3,7 @@ from __future__ import annotations
 
 import torch
 
-from ._lib import DT, call, ptr, stream_ptr
+from ._lib import DT, ptr
 from .flash import _declare, _strides_bhs, _tma_ok, bwd_call
 
 

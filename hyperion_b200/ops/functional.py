@@ -8,7 +8,6 @@ raises (see :func:`_native`).
 """
 from __future__ import annotations
 
-import math
 import os
 
 import torch

@@ -9,7 +9,7 @@ from pathlib import Path
 import torch
 import torch.distributed as dist
 
-from ..data import DeviceResidentLoader, synth
+from ..data import synth
 from ..parallel.runtime import max_over_ranks, world
 
 

@@ -14,7 +14,6 @@ from __future__ import annotations
 
 import csv
 import datetime
-import os
 from pathlib import Path
 
 HEADERS = {

@@ -6,7 +6,6 @@ SYNCS = mbarrier, LDGMC / multimem, RED/ATOM) and the register / spill line from
 """
 import re
 import subprocess
-import sys
 from pathlib import Path
 
 ROOT = Path(__file__).resolve().parent.parent

@@ -1,12 +1,10 @@
 """gloo world_size=2 integration tests on CPU (BASELINE config 1): the DDP and FSDP engines must produce the same
 parameters as a single process training on the concatenated batch (mean loss over equal-sized rank batches)."""
-import copy
 import os
 import socket
 
 import pytest
 import torch
-import torch.distributed as dist
 import torch.multiprocessing as mp
 
 

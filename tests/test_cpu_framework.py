@@ -4,7 +4,6 @@ parity.  Oracles are the PyTorch classes / numbers the reference itself uses."""
 import copy
 import csv
 import json
-import os
 from pathlib import Path
 
 import pytest

@@ -1,5 +1,4 @@
 """CPU tests of the benchmark tools and CLIs: output schemas must equal the reference's."""
-import csv
 import json
 import subprocess
 import sys
