@@ -295,3 +295,63 @@ def test_launch_script_runs_the_fsdp_job_under_torchrun(tmp_path):
     df = pd.read_csv(csvs[0])
     assert list(df["epoch"]) == [1, 2] and set(df["gpus"]) == {2} and {"loss", "duration"} <= set(df.columns)
     assert any((tmp_path / "data/distributed").glob("*.pt"))
+
+
+def _eval_between_worker(rank, world, port, strategy, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    from hyperion_b200.models import SimpleTransformerLM
+    from hyperion_b200.parallel.runtime import cleanup, setup
+    from hyperion_b200.train.engine import build_engine
+
+    torch.set_num_threads(1)
+    dev = setup(rank, world, "gloo", seed=0)
+    torch.manual_seed(0)
+    model = SimpleTransformerLM(300, 32, 2, 2, 64, dropout=0.0)
+    reshard = strategy == "fsdp_reshard"
+    eng = build_engine(model, strategy="fsdp" if reshard else strategy, precision="fp32", lr=1e-2, device=dev,
+                       fsdp_min_num_params=2000, reshard_after_forward=reshard, fsdp_units=list(model.tr.layers) if reshard else None)
+    data = torch.randint(0, 300, (4, 2 * world, 12), generator=torch.Generator().manual_seed(1))
+    val = []
+    for step in (0, 1, 2, 0):
+        b = data[step, rank * 2:(rank + 1) * 2]
+        eng.model.train()
+        if step == 0:
+            eng.model.loss(b[:, :-1].contiguous(), b[:, 1:].contiguous())      # a forward whose graph is dropped without a backward
+        eng.backward_and_step(eng.model.loss(b[:, :-1].contiguous(), b[:, 1:].contiguous()))
+        eng.model.eval()                                                       # validation between steps: no_grad, twice
+        with torch.no_grad():
+            v = data[3, :2]
+            l1 = float(eng.model.loss(v[:, :-1].contiguous(), v[:, 1:].contiguous()))
+            l2 = float(eng.model.loss(v[:, :-1].contiguous(), v[:, 1:].contiguous()))
+        assert l1 == l2
+        val.append(l1)
+    if rank == 0:
+        torch.save(val, out)
+    cleanup()
+
+
+@pytest.mark.parametrize("strategy", ["ddp", "fsdp", "fsdp_reshard"])
+def test_gloo_validation_passes_between_steps(tmp_path, strategy):
+    """eval()/no_grad forwards between optimizer steps (a validation loop) and a forward that is never backpropagated leave the engines
+    consistent: the validation loss after every step equals the single-process run's."""
+    from hyperion_b200.models import SimpleTransformerLM
+
+    torch.manual_seed(0)
+    model = SimpleTransformerLM(300, 32, 2, 2, 64, dropout=0.0)
+    opt = torch.optim.AdamW(model.parameters(), lr=1e-2, weight_decay=0.01)
+    data = torch.randint(0, 300, (4, 4, 12), generator=torch.Generator().manual_seed(1))
+    want = []
+    for step in (0, 1, 2, 0):
+        model.train()
+        b = data[step]
+        opt.zero_grad()
+        model.loss(b[:, :-1].contiguous(), b[:, 1:].contiguous()).backward()
+        opt.step()
+        model.eval()
+        with torch.no_grad():
+            v = data[3, :2]
+            want.append(float(model.loss(v[:, :-1].contiguous(), v[:, 1:].contiguous())))
+    out = tmp_path / "val.pt"
+    mp.spawn(_eval_between_worker, args=(2, _free_port(), strategy, str(out)), nprocs=2, join=True)
+    got = torch.load(out)
+    assert got == pytest.approx(want, rel=2e-5), (got, want)
