@@ -78,14 +78,25 @@ def train_gpt2_fsdp(rank: int, world_size: int, epochs: int = 1, base_dir: str =
                     precision: str = "bf16", size: str = "medium", seq_len: int = 1024, batch_size: int = 8,
                     steps_per_epoch: int = 20, fused_comm: bool | None = None, seed: int = 0, clip: float = 1.0,
                     save: bool = False, checkpointing: bool = False, resume: str | None = None, graph: bool | None = None,
-                    reshard_after_forward: bool | None = None):
-    """GPT-2 (medium by default) under HyperionFSDP on WikiText-2-shaped synthetic tokens, seq 1024 (config 4)."""
+                    reshard_after_forward: bool | None = None, model_id: str | None = None):
+    """GPT-2 (medium by default) under HyperionFSDP on WikiText-2-shaped synthetic tokens, seq 1024 (config 4).  ``model_id``: a local
+    Hugging Face GPT-2 checkpoint directory to start from (random weights of ``size`` otherwise)."""
     dev = setup(rank, world_size, backend, seed=seed)
+    from ..models.hf import gpt2_from_pretrained, is_checkpoint_dir, read_config
+
+    pretrained = is_checkpoint_dir(model_id) and read_config(model_id).get("model_type") == "gpt2"
     cfg = {"medium": GPT2Config.medium, "small": GPT2Config.small, "tiny": GPT2Config.tiny}[size]()
     seq_len = min(seq_len, cfg.n_positions)
     out_dir = os.path.join(base_dir, "data/distributed")
     logger = CsvLogger(out_dir, "gpt2_fsdp", world_size, rank, run_id=None)
-    model = GPT2LMHeadModel(cfg)
+    if pretrained:
+        model = gpt2_from_pretrained(model_id)
+        cfg = model.config
+        seq_len = min(seq_len, cfg.n_positions)
+        if rank == 0:
+            print(f"[GPT2-FSDP] weights read from {model_id}")
+    else:
+        model = GPT2LMHeadModel(cfg)
     model.use_checkpoint = checkpointing
     units = [m for m in model.modules() if isinstance(m, GPT2Block)]
     eng = build_engine(model, strategy="fsdp", precision=precision if dev.type == "cuda" else "fp32", lr=1e-4, clip=clip,

@@ -36,8 +36,11 @@ def train_llama_fsdp(rank: int, world_size: int, epochs: int = 1, base_dir: str 
                      seed: int = 0, save: bool = True, checkpointing: bool = False, config: LlamaConfig | None = None,
                      resume: str | None = None, graph: bool | None = None, reshard_after_forward: bool | None = None):
     dev = setup(rank, world_size, backend, seed=seed)
-    cfg = config or CONFIGS[size]()
-    if dev.type != "cuda" and config is None and size == "7b" and os.environ.get("HYPERION_ALLOW_CPU_7B") != "1":
+    from ..models.hf import is_checkpoint_dir, llama_config_from_hf, read_config
+
+    pretrained = config is None and is_checkpoint_dir(model_id)      # a local HF checkpoint directory: its weights, its config
+    cfg = config or (llama_config_from_hf(read_config(model_id)) if pretrained else CONFIGS[size]())
+    if dev.type != "cuda" and config is None and not pretrained and size == "7b" and os.environ.get("HYPERION_ALLOW_CPU_7B") != "1":
         # fp32 weights + gradients + AdamW state of 6.7 B parameters per rank: > 100 GB of host memory, and the OOM killer's choice of
         # victim is not ours to make.  The CPU / gloo path exists for the host-side logic; it has a model of its own size.
         raise RuntimeError("Llama-2-7B on a machine without a GPU needs > 100 GB of host memory per rank; pass size='tiny' "
@@ -55,6 +58,14 @@ def train_llama_fsdp(rank: int, world_size: int, epochs: int = 1, base_dir: str 
             model = LlamaForCausalLM(cfg)
     finally:
         torch.set_default_dtype(prev)
+    if pretrained:
+        from ..models.hf import _copy_in, iter_tensors
+
+        _copy_in(model, iter_tensors(model_id), lambda k, v: None if k.endswith("rotary_emb.inv_freq") else (k, v))
+        if rank == 0:
+            print(f"[Llama] weights read from {model_id} ({model.num_parameters():,} parameters)")
+    elif rank == 0 and model_id and os.path.sep in str(model_id) and not str(model_id).startswith("NousResearch/"):
+        print(f"[Llama] {model_id} is not a local checkpoint directory (no config.json): training from random weights")
     model.model.use_checkpoint = checkpointing
     if lora:
         inject_lora(model, r=16, alpha=32, dropout=0.05)

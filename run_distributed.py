@@ -30,7 +30,9 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--epochs", type=int, default=5)
     p.add_argument("--base_dir", type=str, default=os.environ.get("HYPERION_BASE_DIR", "."))
     p.add_argument("--hf_token", type=str, default=None, help="accepted for compatibility; nothing is downloaded")
-    p.add_argument("--model_id", type=str, default="NousResearch/Llama-2-7b-hf")
+    p.add_argument("--model_id", type=str, default="NousResearch/Llama-2-7b-hf",
+                   help="a local Hugging Face checkpoint directory (config.json + safetensors) to start from; a hub name is accepted "
+                        "for compatibility and means random weights of that architecture (nothing is downloaded)")
     p.add_argument("--lora", action="store_true", help="LoRA adapters (r=16, alpha=32, q/k/v/o) instead of full fine-tuning")
     p.add_argument("--batch_size", type=int, default=None, help="per-GPU batch size (Llama default 1)")
     p.add_argument("--progress_every", type=int, default=50)
@@ -107,7 +109,7 @@ def run_selected(which: str, args, rank: int, world: int) -> None:
                               precision=args.precision or "bf16", size=args.gpt2_size, seq_len=args.seq_len or 1024,
                               steps_per_epoch=args.steps or 20, fused_comm=args.fused_comm, seed=args.seed,
                               checkpointing=args.checkpointing, save=args.save_gpt2,
-                              resume=args.resume, graph=args.graph, reshard_after_forward=args.reshard, **bs)
+                              resume=args.resume, graph=args.graph, reshard_after_forward=args.reshard, model_id=args.model_id, **bs)
     elif which == "llama":
         train.train_llama_fsdp(rank, world, epochs=args.epochs, base_dir=args.base_dir, hf_token=args.hf_token,
                                model_id=args.model_id, lora=args.lora, batch_size=args.batch_size or 1,
