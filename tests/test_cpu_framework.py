@@ -410,3 +410,38 @@ def test_device_prefetcher_preserves_order_and_values():
     for i, (a, b) in enumerate(got):
         assert torch.equal(a, torch.arange(4) + i) and torch.equal(b, torch.ones(2) * i)
     assert list(DevicePrefetcher(iter([]), "cpu")) == []
+
+
+def test_vision_models_compute_what_torchvision_computes():
+    """Same weights -> same outputs as torchvision's resnet18 / resnet50 / vit_b_16 (the architectures the reference builds with
+    torchvision / torch.hub): a checkpoint of the reference gives the same predictions here.  CPU path; the kernels have GPU tests."""
+    import torchvision
+
+    from hyperion_b200 import models
+
+    torch.manual_seed(0)
+    cases = [(models.resnet18(10), torchvision.models.resnet18(num_classes=10), (4, 3, 32, 32)),
+             (models.resnet50(), torchvision.models.resnet50(), (2, 3, 64, 64)),
+             (models.vit_b_16(), torchvision.models.vit_b_16(), (1, 3, 224, 224))]
+    for ours, tv, shape in cases:
+        for p in tv.parameters():                      # torchvision zero-initialises the ViT head and the last BN gammas
+            if float(p.detach().abs().sum()) == 0.0:
+                torch.nn.init.normal_(p, std=0.05)
+        ours.load_state_dict(tv.state_dict())
+        x = torch.randn(*shape)
+        ours.eval(), tv.eval()
+        with torch.no_grad():
+            a, b = ours(x), tv(x)
+        assert float(b.abs().max()) > 1e-3
+        torch.testing.assert_close(a, b, rtol=1e-3, atol=1e-4)
+    ours, tv, shape = cases[0]                         # training mode: batch statistics, running buffers, gradients
+    ours.train(), tv.train()
+    x = torch.randn(8, 3, 32, 32)
+    a, b = ours(x), tv(x)
+    a.square().mean().backward()
+    b.square().mean().backward()
+    torch.testing.assert_close(a, b, rtol=1e-3, atol=1e-4)
+    torch.testing.assert_close(ours.bn1.running_var, tv.bn1.running_var, rtol=1e-5, atol=1e-7)
+    assert int(ours.bn1.num_batches_tracked) == int(tv.bn1.num_batches_tracked) == 1
+    g1, g2 = ours.layer3[0].conv1.weight.grad, tv.layer3[0].conv1.weight.grad
+    assert float((g1 - g2).norm() / g2.norm()) < 1e-3
