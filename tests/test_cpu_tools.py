@@ -210,3 +210,20 @@ def test_benchmarking_drop_in_module():
     r = bm.benchmark_forward_pass(nn.Linear(8, 8), torch.rand(4, 8), num_iterations=2, warmup=1)
     assert set(r) == {"total_time", "avg_time", "throughput", "memory_usage"}
     assert sorted(bm.__all__) == ["benchmark_forward_pass", "benchmark_training_step", "compare_precision_formats", "save_benchmark_results"]
+
+
+def test_every_environment_switch_is_documented():
+    """TROUBLESHOOTING.md (the reference README's section 9: environment knobs, common issues) lists every HYPERION_* variable the code reads."""
+    import re
+
+    doc = (ROOT / "TROUBLESHOOTING.md").read_text()
+    used = set()
+    files = [*ROOT.glob("*.py"), *(ROOT / "hyperion_b200").rglob("*.py"), *(ROOT / "csrc").rglob("*.cu*"), *(ROOT / "scripts").glob("*.sh"),
+             *(ROOT / "scripts").glob("*.py"), *(ROOT / "baseline").glob("*.py")]
+    for f in files:
+        used |= set(re.findall(r"HYPERION_[A-Z0-9_]+", f.read_text()))
+    used -= {"HYPERION_B200_H"}                      # include guard
+    missing = sorted(v for v in used if v not in doc)
+    assert not missing, f"undocumented environment switches: {missing}"
+    for section in ("## Environment switches", "## Common issues", "## Reproducibility"):
+        assert section in doc
