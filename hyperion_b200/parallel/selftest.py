@@ -29,6 +29,11 @@ def run(bench: bool = False, out_json: str | None = None) -> int:
     from hyperion_b200.parallel.symm import SymmetricArena
 
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    if not torch.cuda.is_available():
+        if rank == 0:
+            print("comm-check tests the peer-memory communication kernels and needs one CUDA GPU per rank; on a machine without GPUs "
+                  "`python test_nccl.py` under torchrun checks the process group over gloo", file=sys.stderr)
+        return 2
     dev = setup(rank, world, "nccl")
     torch.manual_seed(1234 + rank)
     arena = SymmetricArena(dev)
