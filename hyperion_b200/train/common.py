@@ -13,6 +13,17 @@ from ..data import synth
 from ..parallel.runtime import max_over_ranks, world
 
 
+def _warn_missing(path, what: str) -> None:
+    """``--real-data`` was asked for and the prepared files are not there: say so (once per process and dataset) before falling back."""
+    if str(path) not in _warned and world()[0] == 0:
+        print(f"WARNING: {path} not found -- training on synthetic {what}-shaped data instead "
+              f"(write the real files with `python -m hyperion_b200 data prepare --base_dir ...`)", flush=True)
+    _warned.add(str(path))
+
+
+_warned: set = set()
+
+
 def load_wikitext_tensors(base_dir, device, synthetic: bool, rows: int | None = None, seq_len: int = 128,
                           vocab: int = synth.GPT2_VOCAB, pad_id: int = synth.GPT2_PAD, seed: int = 0):
     """(input_ids, attention_mask) on ``device``: from ``data/processed/wikitext2_tokenized`` if it exists and
@@ -25,6 +36,8 @@ def load_wikitext_tensors(base_dir, device, synthetic: bool, rows: int | None = 
 
         ds = WikiText2TorchDataset(load_from_disk(str(path)), "train")
         return ds.ids.to(device), ds.mask.to(device)
+    if not synthetic:
+        _warn_missing(path, "WikiText-2")
     n = rows or synth.WIKITEXT2_ROWS["train"]
     ids, mask = synth.wikitext2_like_arrays(n, seq_len, vocab, pad_id, seed)
     return torch.from_numpy(ids).to(device), torch.from_numpy(mask).to(device)
@@ -37,6 +50,8 @@ def load_cifar_tensors(base_dir, device, synthetic: bool, rows: int | None = Non
         x = torch.stack([d[0] for d in data]).to(device)
         y = torch.tensor([d[1] for d in data], device=device)
         return x, y
+    if not synthetic:
+        _warn_missing(path, "CIFAR-10")
     n = rows or synth.CIFAR10_ROWS["train"]
     g = torch.Generator().manual_seed(seed)
     labels = torch.randint(0, 10, (n,), generator=g)
