@@ -57,10 +57,30 @@ def setup(rank: int, world_size: int, backend: str | None = None, timeout_min: f
     return dev
 
 
+_holds = 0
+
+
+def hold_process_group() -> None:
+    """Keep the process group alive across several trainers run in ONE process (``--model all``): until the matching
+    ``release_process_group()``, ``cleanup()`` only synchronises.  The reference tears the group down and re-creates it between
+    its four jobs (run_distributed.py:134-139 -> distributed_utils.py:101-125, SURVEY.md A-15); re-initialising ``env://`` in the same
+    process races the previous store's teardown (gloo refuses the connection), and the peer-memory arenas are tied to the group."""
+    global _holds
+    _holds += 1
+
+
+def release_process_group() -> None:
+    global _holds
+    _holds = max(0, _holds - 1)
+    if _holds == 0:
+        cleanup()
+
+
 def cleanup() -> None:
     if dist.is_initialized():
         dist.barrier()
-        dist.destroy_process_group()
+        if _holds == 0:
+            dist.destroy_process_group()
 
 
 def world() -> tuple[int, int]:

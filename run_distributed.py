@@ -157,10 +157,16 @@ def main(argv=None) -> int:
 
         print(f"torch {torch.__version__} | rank {rank}/{world} | GPU {local_rank} / node has {torch.cuda.device_count()} devices")
     if args.model == "all":
-        for mdl in ["language_ddp", "cifar", "language_fsdp", "llama"]:
-            if local_rank == 0:
-                print(f"\n=== [{mdl}] starting ===\n")
-            run_selected(mdl, args, rank, world)
+        from hyperion_b200.parallel.runtime import hold_process_group, release_process_group
+
+        hold_process_group()                # one process group for the four jobs (each trainer's cleanup() only synchronises)
+        try:
+            for mdl in ["language_ddp", "cifar", "language_fsdp", "llama"]:
+                if local_rank == 0:
+                    print(f"\n=== [{mdl}] starting ===\n")
+                run_selected(mdl, args, rank, world)
+        finally:
+            release_process_group()
     else:
         run_selected(args.model, args, rank, world)
     if rank == 0:

@@ -355,3 +355,40 @@ def test_gloo_validation_passes_between_steps(tmp_path, strategy):
     mp.spawn(_eval_between_worker, args=(2, _free_port(), strategy, str(out)), nprocs=2, join=True)
     got = torch.load(out)
     assert got == pytest.approx(want, rel=2e-5), (got, want)
+
+
+def test_model_all_runs_the_four_jobs_in_one_process_group(tmp_path):
+    """`run_distributed.py --model all` (reference: run_distributed.py:134-139): four trainers back to back in one torchrun launch.  The
+    process group is held across them (tearing it down and re-creating it in the same process fails on gloo)."""
+    import subprocess
+    import sys
+    from pathlib import Path
+
+    root = Path(__file__).resolve().parent.parent
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--standalone", "--local-addr", "127.0.0.1", "--nproc-per-node", "2",
+           str(root / "run_distributed.py"), "--model", "all", "--llama-size", "tiny", "--epochs", "1", "--steps", "2", "--batch_size", "2",
+           "--backend", "gloo", "--base_dir", str(tmp_path), "--no-save"]
+    r = subprocess.run(cmd, env={**os.environ, "CUDA_VISIBLE_DEVICES": ""}, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-3000:]
+    for tag in ("[LM-DDP] Epoch 1/1", "[CIFAR-DDP] Epoch 1/1", "[LM-FSDP] Epoch 1/1", "[Llama-fsdp_bf16] Epoch 1/1"):
+        assert tag in r.stdout, tag
+    kinds = sorted({f.name.split("_2gpus_")[0] for f in (tmp_path / "data/distributed").glob("*_metrics.csv")})
+    assert kinds == ["cifar_ddp", "language_ddp", "language_fsdp", "llama"]
+    assert (tmp_path / "data/distributed/scaling_analysis.csv").exists()
+
+
+def test_hold_and_release_of_the_process_group():
+    from hyperion_b200.parallel import runtime
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(_free_port()), RANK="0", WORLD_SIZE="1")
+    runtime.hold_process_group()
+    try:
+        runtime.setup(0, 1, "gloo")
+        runtime.cleanup()
+        assert torch.distributed.is_initialized()          # held: cleanup() only synchronised
+        runtime.setup(0, 1, "gloo")                        # a second trainer's setup() reuses the group
+        runtime.cleanup()
+        assert torch.distributed.is_initialized()
+    finally:
+        runtime.release_process_group()
+    assert not torch.distributed.is_initialized()
