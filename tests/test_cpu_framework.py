@@ -445,3 +445,24 @@ def test_vision_models_compute_what_torchvision_computes():
     assert int(ours.bn1.num_batches_tracked) == int(tv.bn1.num_batches_tracked) == 1
     g1, g2 = ours.layer3[0].conv1.weight.grad, tv.layer3[0].conv1.weight.grad
     assert float((g1 - g2).norm() / g2.norm()) < 1e-3
+
+
+def test_parameter_counts_of_every_model_family():
+    """exact parameter counts of the architectures the reference trains or benchmarks (+ GPT-2 medium of
+    BASELINE config 4).  The 7B model and GPT-2 medium are built on the meta device."""
+    from hyperion_b200 import models
+    from hyperion_b200.lora import inject_lora, trainable_parameters
+
+    n = lambda m: sum(p.numel() for p in m.parameters())
+    assert n(models.SimpleTransformerLM(50257)) == n(models.NotebookTransformerLM(50257)) == 28_411_985
+    assert n(models.CompileBenchLM()) == 105_596_497
+    assert n(models.resnet18(10)) == 11_181_642
+    assert n(models.resnet50()) == n(models.create_resnet50()) == 25_557_032
+    assert n(models.vit_b_16()) == n(models.create_vit_model()) == 86_567_656
+    with torch.device("meta"):
+        llama = models.LlamaForCausalLM(models.LlamaConfig.llama2_7b())
+        assert n(llama) == 6_738_415_616 and n(llama.model.layers[0]) == 202_383_360
+        inject_lora(llama, r=16, alpha=32, dropout=0.05)
+        assert trainable_parameters(llama) == 16_777_216
+        gpt2 = models.GPT2LMHeadModel(models.GPT2Config.medium())
+        assert n(gpt2) == 354_823_168 and n(gpt2.h[0]) == 12_596_224
