@@ -227,3 +227,26 @@ def test_every_environment_switch_is_documented():
     assert not missing, f"undocumented environment switches: {missing}"
     for section in ("## Environment switches", "## Common issues", "## Reproducibility"):
         assert section in doc
+
+
+def test_baseline_md_matrix_equals_the_committed_json_lines():
+    """Every row of the round-2 matrix in BASELINE.md is what scripts/matrix_table.py prints from profiles/bench/r2/*.json, and the
+    headline ratios quoted under it follow from the same files."""
+    r = subprocess.run([sys.executable, str(ROOT / "scripts/matrix_table.py"), str(ROOT / "profiles/bench/r2")], capture_output=True,
+                       text=True, timeout=120)
+    assert r.returncode == 0, r.stderr
+    doc = (ROOT / "BASELINE.md").read_text()
+    rows = r.stdout.strip().splitlines()
+    assert len(rows) > 20 and all(line in doc for line in rows)
+
+    def val(n, cfg, arm):
+        return json.loads((ROOT / f"profiles/bench/r2/matrix_n{n}_{cfg}_{arm}.json").read_text().splitlines()[0])["value"]
+
+    for cfg, base, n, quoted in (("lm_ddp", "reference", 1, "2.95x"), ("lm_ddp", "reference", 8, "3.06x"), ("lm_fsdp", "reference", 8, "4.46x"),
+                                 ("cifar_ddp", "reference", 1, "3.54x"), ("gpt2_fsdp", "torch", 1, "2.78x"), ("gpt2_fsdp", "torch", 8, "3.15x"),
+                                 ("resnet50_ddp", "torch", 1, "1.26x"), ("vit_ddp", "torch", 1, "1.84x"), ("llama_lora", "torch", 8, "4.22x")):
+        ratio = val(n, cfg, "hyperion") / val(n, cfg, base)
+        assert abs(ratio - float(quoted[:-1])) < 0.011 and quoted in doc, (cfg, n, ratio, quoted)
+    for f in (ROOT / "profiles/bench/r2").glob("matrix_n*_*.json"):           # every line carries a clocks record or says unavailable
+        j = json.loads(f.read_text().splitlines()[0])
+        assert "unavailable" in j or "clocks" in j, f.name
