@@ -466,3 +466,49 @@ def test_parameter_counts_of_every_model_family():
         assert trainable_parameters(llama) == 16_777_216
         gpt2 = models.GPT2LMHeadModel(models.GPT2Config.medium())
         assert n(gpt2) == 354_823_168 and n(gpt2.h[0]) == 12_596_224
+
+
+def test_flat_layout_invariants_property():
+    """FlatParams is what the communication kernels index: for random parameter shapes, dtypes, unit groupings and world sizes, every
+    parameter starts on a 256-byte boundary, ranges do not overlap, FSDP units tile the buffer and split evenly over the ranks in 16-byte
+    multiples, DDP buckets are whole-parameter ranges that cover the buffer once, and tied parameters are stored once."""
+    from hypothesis import given, settings, strategies as st
+
+    from hyperion_b200.parallel.flat import ALIGN_BYTES, FlatParams
+
+    shapes = st.lists(st.one_of(st.tuples(st.integers(1, 70)), st.tuples(st.integers(1, 33), st.integers(1, 40)),
+                                st.tuples(st.integers(1, 5), st.integers(1, 6), st.integers(1, 3), st.integers(1, 3))), min_size=1, max_size=9)
+
+    @settings(max_examples=60, deadline=None)
+    @given(shapes=shapes, dtype=st.sampled_from([torch.float32, torch.bfloat16]), world=st.sampled_from([1, 2, 4, 8]),
+           group=st.integers(1, 4), tie=st.booleans(), cap=st.integers(64, 4096))
+    def check(shapes, dtype, world, group, tie, cap):
+        params = [(f"u{i // group}.p{i}", nn.Parameter(torch.randn(*s).to(dtype))) for i, s in enumerate(shapes)]
+        if tie and len(params) > 1:
+            params.append(("tied.alias", params[0][1]))
+        frozen = nn.Parameter(torch.zeros(3), requires_grad=False)
+        values = {n: p.detach().clone() for n, p in params}
+        es = torch.empty((), dtype=dtype).element_size()
+        ua = world * 128
+        flat = FlatParams(params + [("frozen", frozen)], unit_key=lambda n: n.split(".")[0], unit_align=ua)
+        assert len(flat.specs) == len(shapes)                                   # tied alias and frozen parameter are not stored
+        spans = sorted((s.offset, s.offset + s.numel) for s in flat.specs)
+        assert all(o * es % ALIGN_BYTES == 0 for o, _ in spans)
+        assert all(a_end <= b_start for (_, a_end), (b_start, _) in zip(spans, spans[1:])) and spans[-1][1] <= flat.numel
+        assert flat.numel % ua == 0 and flat.data.numel() == flat.grad.numel() == flat.numel
+        units = flat.units
+        assert units[0][0] == 0 and units[-1][1] == flat.numel
+        assert all(a[1] == b[0] for a, b in zip(units, units[1:]))
+        for start, end, key in units:
+            assert start % ua == 0 and (end - start) % world == 0 and ((end - start) // world * es) % 16 == 0
+            assert all(start <= s.offset and s.offset + s.numel <= end for s in flat.specs if s.name.split(".")[0] == key)
+        for s in flat.specs:                                                    # values moved into the buffer, parameters are views of it
+            assert torch.equal(s.param.detach().reshape(-1), values[s.name].reshape(-1))
+            assert s.param.data_ptr() == flat.data.data_ptr() + s.offset * es
+        buckets = flat.buckets(cap)
+        assert buckets[0][0] == 0 and buckets[-1][1] == flat.numel and all(a[1] == b[0] for a, b in zip(buckets, buckets[1:]))
+        assert sorted(i for _, _, idx in buckets for i in idx) == list(range(len(flat.specs)))
+        for start, end, idx in buckets:
+            assert all(start <= flat.specs[i].offset and flat.specs[i].offset + flat.specs[i].numel <= end for i in idx)
+
+    check()
