@@ -250,3 +250,46 @@ def test_baseline_md_matrix_equals_the_committed_json_lines():
     for f in (ROOT / "profiles/bench/r2").glob("matrix_n*_*.json"):           # every line carries a clocks record or says unavailable
         j = json.loads(f.read_text().splitlines()[0])
         assert "unavailable" in j or "clocks" in j, f.name
+
+
+def test_ctypes_signatures_agree_with_the_c_header():
+    """Every entry point's ctypes signature (ops/_lib.py table + the declare() calls of flash.py / conv.py / symm.py) has the argument count
+    and the argument kinds (pointer, int, long long, float) of its prototype in include/hyperion_b200.h -- a drifted signature would
+    corrupt arguments silently at call time."""
+    import ast
+    import re
+
+    from hyperion_b200.ops import _lib
+
+    header = (ROOT / "include/hyperion_b200.h").read_text()
+    header = re.sub(r"/\*.*?\*/", " ", header, flags=re.S)
+    header = re.sub(r"//[^\n]*", " ", header)
+    protos = {}
+    for ret, name, args in re.findall(r"\b([A-Za-z_][\w\s\*]*?)\b(hyp_\w+)\s*\(([^;{]*?)\)\s*;", header):
+        codes = ""
+        for a in [x.strip() for x in args.split(",") if x.strip() and x.strip() != "void"]:
+            if "*" in a or "cudaStream_t" in a:
+                codes += "p"
+            elif "long long" in a or "size_t" in a or "int64_t" in a:
+                codes += "l"
+            elif "float" in a:
+                codes += "f"
+            elif re.search(r"\b(int|unsigned)\b", a):
+                codes += "i"
+            else:
+                raise AssertionError(f"{name}: cannot classify parameter {a!r}")
+        protos[name] = codes
+    assert len(protos) > 40
+
+    declared = dict(_lib._SIGS)
+    for rel in ("hyperion_b200/ops/flash.py", "hyperion_b200/ops/conv.py", "hyperion_b200/parallel/symm.py", "hyperion_b200/ops/native.py",
+                "hyperion_b200/ops/flash_bwd.py", "hyperion_b200/ops/functional.py", "hyperion_b200/optim.py", "hyperion_b200/amp.py"):
+        tree = ast.parse((ROOT / rel).read_text())
+        for node in ast.walk(tree):
+            if isinstance(node, ast.Call) and getattr(node.func, "attr", getattr(node.func, "id", "")) == "declare" and len(node.args) >= 2 \
+                    and isinstance(node.args[0], ast.Constant):
+                declared[node.args[0].value] = eval(compile(ast.Expression(node.args[1]), rel, "eval"), {})
+    assert len(declared) > 35
+    for name, sig in sorted(declared.items()):
+        assert name in protos, f"{name} is declared for ctypes but has no prototype in the header"
+        assert sig == protos[name], f"{name}: ctypes {sig} ({len(sig)} args) != header {protos[name]} ({len(protos[name])} args)"
