@@ -281,6 +281,24 @@ def test_ctypes_signatures_agree_with_the_c_header():
         protos[name] = codes
     assert len(protos) > 40
 
+    def classify(args: str) -> str:
+        codes = ""
+        for a in [x.strip() for x in args.split(",") if x.strip() and x.strip() != "void"]:
+            codes += ("p" if "*" in a or "cudaStream_t" in a else "l" if "long long" in a or "size_t" in a or "int64_t" in a
+                      else "f" if "float" in a else "i")
+        return codes
+
+    # the .cu files do not include the public header, so the compiler does not compare definition and prototype: do it here
+    defined = {}
+    for cu in (ROOT / "csrc").rglob("*.cu"):
+        src = re.sub(r"/\*.*?\*/", " ", cu.read_text(), flags=re.S)
+        src = re.sub(r"//[^\n]*", " ", src)
+        for name, args in re.findall(r"HYP_API\s+[\w\s\*]+?\b(hyp_\w+)\s*\(([^{;]*?)\)\s*\{", src):
+            defined[name] = classify(args)
+    assert len(defined) > 40
+    for name, codes in sorted(defined.items()):
+        assert name in protos and codes == protos[name], f"{name}: definition {codes} != header {protos.get(name)}"
+
     declared = dict(_lib._SIGS)
     for rel in ("hyperion_b200/ops/flash.py", "hyperion_b200/ops/conv.py", "hyperion_b200/parallel/symm.py", "hyperion_b200/ops/native.py",
                 "hyperion_b200/ops/flash_bwd.py", "hyperion_b200/ops/functional.py", "hyperion_b200/optim.py", "hyperion_b200/amp.py"):
