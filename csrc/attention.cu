@@ -328,6 +328,9 @@ static int make_qkv_map(CUtensorMap* tm, const void* ptr, int dtype, int B, int 
 template <typename T, int D, bool DROP>
 static int launch_fwd_t(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const FwdParams& p, cudaStream_t st) {
   using L = Smem<D>;
+  // D = 64 runs two CTAs per SM (each allocates 256 of the 512 TMEM columns): both shared-memory windows, plus the 1 KB the
+  // runtime reserves per CTA, must fit the 228 KB of an SM
+  static_assert(L::TOTAL <= kMaxSmemPerCta && (D != 64 || 2 * (L::TOTAL + 1024) <= 228 * 1024), "flash forward shared-memory layout");
   static bool attr_set[64] = {false};
   int dev = 0;
   cudaGetDevice(&dev);
@@ -1048,6 +1051,7 @@ template <typename T, bool DROP>
 static int launch_bwd64_t(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const CUtensorMap& tdo,
                           const BwdParams& p, cudaStream_t st) {
   using L = Bwd64Smem;
+  static_assert(L::TOTAL <= kMaxSmemPerCta, "flash backward (D = 64) shared-memory layout exceeds 227 KB");
   static bool attr_set[64] = {false};
   int dev = 0;
   cudaGetDevice(&dev);
@@ -1124,6 +1128,7 @@ template <typename T, int D, bool DROP>
 static int launch_bwd_t(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const CUtensorMap& tdo,
                       const BwdParams& p, cudaStream_t st) {
   using L = BwdSmem<D>;
+  static_assert(L::TOTAL <= kMaxSmemPerCta, "flash backward shared-memory layout exceeds 227 KB");
   static bool attr_set[64] = {false};
   int dev = 0;
   cudaGetDevice(&dev);

@@ -10,6 +10,11 @@
 
 namespace hyp {
 
+// Per-CTA budgets of sm_100a, checked at compile time wherever a kernel configuration is launched.
+constexpr int kMaxSmemPerCta = 227 * 1024;   // opt-in dynamic shared memory per CTA
+constexpr int kTmemColumns = 512;            // TMEM columns per SM (128 lanes x 512 x 32 bit = 256 KB)
+constexpr bool tmem_alloc_ok(int cols) { return cols >= 32 && cols <= kTmemColumns && (cols & (cols - 1)) == 0; }
+
 // dtype codes of the C ABI (include/hyperion_b200.h)
 enum : int { DT_F32 = 0, DT_F16 = 1, DT_BF16 = 2 };
 

@@ -244,6 +244,7 @@ static void pick_patch(int Ho, int Wo, int N, int* TW, int* TH, int* NB, int pix
 template <int BN>
 static int launch(const CUtensorMap& tx, const CUtensorMap& tw, const Params& p, cudaStream_t st) {
   using C = Cfg<BN>;
+  static_assert(C::SMEM_BYTES <= kMaxSmemPerCta && tmem_alloc_ok(C::TMEM_COLS), "conv forward tile exceeds the sm_100a CTA budget");
   static bool attr_set[64] = {false};
   int dev = 0;
   cudaGetDevice(&dev);
@@ -473,6 +474,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constan
 template <int BN>
 static int launch_wgrad(const CUtensorMap& tdy, const CUtensorMap& tx, const WParams& p, cudaStream_t st) {
   using C = WCfg<BN>;
+  static_assert(C::SMEM_BYTES <= kMaxSmemPerCta && tmem_alloc_ok(C::TMEM_COLS), "conv wgrad tile exceeds the sm_100a CTA budget");
   static bool attr_set[64] = {false};
   int dev = 0;
   cudaGetDevice(&dev);

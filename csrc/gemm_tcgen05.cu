@@ -1009,6 +1009,8 @@ int make_tmap_mn3(CUtensorMap* tm, const void* ptr, int dtype, long long mn, lon
 template <int BN, int EPI, int ACT, bool AG = false>
 static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const Params& p, cudaStream_t stream) {
   using C = Cfg<BN>;
+  static_assert(C::SMEM_BYTES <= kMaxSmemPerCta, "GEMM stage ring + staging exceeds the 227 KB shared memory of an sm_100a CTA");
+  static_assert(tmem_alloc_ok(C::TMEM_COLS), "TMEM allocations are powers of two between 32 and 512 columns");
   static bool attr_set[64] = {false};
   int dev = 0;
   cudaGetDevice(&dev);
@@ -1046,6 +1048,7 @@ static int launch2(const CUtensorMap& ta, const CUtensorMap& tb, const Params& p
   int dev = 0;
   cudaGetDevice(&dev);
   auto kernel = gemm2_kernel<EPI, ACT, BN>;
+  static_assert(G2Cfg<BN>::SMEM <= kMaxSmemPerCta, "pair-GEMM stage ring + staging exceeds the 227 KB shared memory of an sm_100a CTA");
   if (!attr_set[dev & 63]) {
     HYP_CHECK_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G2Cfg<BN>::SMEM));
     attr_set[dev & 63] = true;
