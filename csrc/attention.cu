@@ -14,6 +14,9 @@
 // CTAs fit per SM at D = 64 so one CTA's softmax overlaps the other's MMAs.
 // Masks: none / causal / causal + key padding (bool [B, Sk]); keys beyond Sk are masked, rows with no visible key
 // produce zeros.  The per-row log-sum-exp is saved for the backward.
+// Dropout (template DROP): the keep mask of P is drawn from Philox4x32-10 keyed by a device-side (seed, step) state and
+// addressed by (batch * H + head, query row, key column, per-call salt) -- common/philox.cuh; nothing is stored, the
+// backward kernels regenerate the same bits.
 //
 // Reference call sites: nn.MultiheadAttention inside nn.TransformerEncoderLayer (02_development/
 // distributed_utils.py:79; the reference ran the *math* SDPA path that materialises the scores)

@@ -11,7 +11,14 @@
 //   need -- no transposed copies are ever made.
 // * dtypes: bf16 / fp16 (kind::f16) and fp32 run as tf32 (kind::tf32).
 // * epilogue functors: +bias, ReLU / GELU(erf|tanh), +residual, activation
-//   derivative (D = acc * act'(aux)), beta-accumulate, split-K fp32 reduction.
+//   derivative (D = acc * act'(aux), optionally with the column sums of D = the
+//   bias gradient of the layer below), beta-accumulate, split-K fp32 reduction.
+// * gemm2_kernel: the same main loop on CTA PAIRS (tcgen05.mma cta_group::2,
+//   256 x BN tiles, each CTA stages half of B, two TMA producer warps) -- the
+//   default for shapes that fill the 74 pairs; gemm_kernel<..., AG> adds gather
+//   warps that pull the peers' slices of an FSDP unit into this GPU's buffer
+//   while the GEMM consumes the slices that have landed (hyp_gemm_ag).
+// * tile order and split-K ranges: common/tiling.cuh (host-testable).
 //
 // Replaces the reference's library GEMM call sites: torch.matmul in the probe
 // (Phase 1/01_hardware_exploration.ipynb c1 L92) and every nn.Linear inside
