@@ -7,8 +7,9 @@
 //
 // Replaces the three ATen launches per block tail (batch_norm, add, relu) of the torchvision ResNets the reference
 // trains (02_development/distributed_utils.py:229; Phase 1/baseline_performance.ipynb c0 L23) with two memory passes.
-// The convolution itself still runs in cuDNN (an implicit-GEMM tcgen05 convolution is not written yet); 1x1
-// convolutions go through gemm_tcgen05 (hyperion_b200/ops/conv.py).
+// The convolutions in front of it are conv_igemm.cu (forward and weight gradient; the data gradient defaults to cuDNN after
+// the per-part A/B in DESIGN.md); in eval mode BatchNorm is folded into the convolution epilogue instead (ops/conv.py).
+// gamma / beta may be 16-bit (the *_p16 entry points), and the backward then rounds dgamma / dbeta into the gradient slots.
 #include "common/ptx.cuh"
 #include "common/util.cuh"
 

@@ -6,10 +6,15 @@
 // zero gradient.  The row losses and the count of non-ignored rows are
 // accumulated into a device fp32[2] (sum, count); no host sync.
 //
-// Used by ops.fused_linear_cross_entropy, which runs the vocabulary projection
-// in row chunks through gemm_tcgen05 and calls this on each chunk, so the full
-// [tokens, vocab] logits tensor (817 MB fp32 for the reference LM) never
-// exists.  Reference call sites: nn.Linear(emb, vocab) + nn.CrossEntropyLoss(
+// Used by ops.linear_cross_entropy: the vocabulary projection writes 16-bit
+// logits through gemm_tcgen05 (one slice by default; HYPERION_CE_L2_ROWS=n
+// slices them by rows), this kernel turns them into the loss and, in place,
+// into d(loss)/d(logits), and the dgrad / wgrad GEMMs read that -- loss and all
+// gradients of the head in one op; no fp32 logits, no separate softmax or
+// backward pass (DESIGN.md has the numbers against the recompute variant).
+// The default kernel keeps a row in registers (1024 threads x 7 vectors);
+// rows equal to ignore_index store zeros without being read.
+// Reference call sites: nn.Linear(emb, vocab) + nn.CrossEntropyLoss(
 // ignore_index=pad) at 02_development/distributed_utils.py:81, 162, 177, 335, 348.
 #include "common/ptx.cuh"
 #include "common/util.cuh"

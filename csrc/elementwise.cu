@@ -1,5 +1,5 @@
 // Streaming elementwise kernels: the HBM bandwidth probe (z = x + y, copy),
-// column sums for bias gradients, SwiGLU, dtype casts.  All are 128-bit
+// column sums for bias gradients, SwiGLU, dtype casts, stand-alone Philox dropout.  All are 128-bit
 // vectorised grid-stride loops sized to a multiple of the SM count.
 //
 // Reference call sites: `z = x + y` in the bandwidth sweep

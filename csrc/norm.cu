@@ -4,8 +4,14 @@
 //   z = x (+ residual);  y = z * rsqrt(mean(z^2) + eps) * gamma      (RMSNorm)
 //
 // 16-bit or fp32 IO, fp32 math, one pass over the row held in registers.
+// Forward can drop elements of x before the residual add (hyp_norm_fwd_drop: the
+// Philox mask of common/philox.cuh, regenerated in backward -- the residual-branch
+// dropout of nn.TransformerEncoderLayer costs no extra pass).
 // Backward produces dz in the same pass and per-block partial dgamma/dbeta in a
-// caller-provided fp32 scratch, reduced by a second small kernel.
+// caller-provided fp32 scratch, reduced by a second small kernel (hyp_norm_bwd), or
+// by the last block to finish (hyp_norm_bwd_fused: one launch, also adds the
+// skip-connection gradient); hyp_norm_bwd_noalloc is the variant that allocates
+// nothing (scratch in a __device__ array of this library).
 //
 // Reference call sites: nn.LayerNorm inside nn.TransformerEncoderLayer
 // (02_development/distributed_utils.py:79; post-norm with residual) and the
