@@ -3,6 +3,7 @@
 // (alloc / mma / commit / ld), NVLS multimem and system-scope flags.
 // Everything is __device__ __forceinline__; no state lives here.
 #pragma once
+#include "desc.cuh"
 #include <cuda.h>
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
@@ -284,27 +285,7 @@ __device__ __forceinline__ void umma_commit_2sm(uint64_t* bar, uint16_t mask) {
       : "memory");
 }
 
-// Shared-memory matrix descriptor (SWIZZLE_128B, sm_100 version field = 1).
-// lbo/sbo are byte offsets (multiples of 16).
-__device__ __forceinline__ uint64_t make_smem_desc_sw128(uint32_t smem_addr, uint32_t lbo_bytes,
-                                                         uint32_t sbo_bytes) {
-  uint64_t d = 0;
-  d |= static_cast<uint64_t>((smem_addr & 0x3FFFFu) >> 4);
-  d |= static_cast<uint64_t>((lbo_bytes >> 4) & 0x3FFFu) << 16;
-  d |= static_cast<uint64_t>((sbo_bytes >> 4) & 0x3FFFu) << 32;
-  d |= 1ull << 46;  // descriptor version (Blackwell)
-  d |= 2ull << 61;  // LayoutType::SWIZZLE_128B
-  return d;
-}
-
-// Instruction descriptor for kind::f16 / kind::tf32 with fp32 accumulation.
-// fmt: 0 = f16, 1 = bf16, 2 = tf32.  *_mn_major: operand's non-reduction
-// dimension is the contiguous one in shared memory.
-__host__ __device__ constexpr uint32_t make_idesc(uint32_t fmt, uint32_t m, uint32_t n,
-                                                  bool a_mn_major, bool b_mn_major) {
-  return (1u << 4) | (fmt << 7) | (fmt << 10) | ((a_mn_major ? 1u : 0u) << 15) |
-         ((b_mn_major ? 1u : 0u) << 16) | ((n >> 3) << 17) | ((m >> 4) << 24);
-}
+// make_smem_desc_sw128 / make_idesc: common/desc.cuh (host-testable bit arithmetic)
 
 // ------------------------------------------------- NVLS multimem / sys flags
 __device__ __forceinline__ float4 multimem_ld_reduce_f32x4(const void* mc_ptr) {

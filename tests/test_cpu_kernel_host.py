@@ -182,3 +182,95 @@ def test_conv_wgrad_schedule(tiling_lib, kblocks, taps, cblocks, total_pb, split
         if pb1 > pb0:
             seen[kb, tap, cb, pb0:pb1] += 1
     assert (seen == 1).all()                          # every (filter block, tap, channel block) sees every patch exactly once
+
+
+# ---------------------------------------------------------------------------------------------------------------------------------
+# csrc/common/desc.cuh: tcgen05 instruction / shared-memory descriptors, same source as the device code
+DESC_HARNESS = r"""
+#include "common/desc.cuh"
+extern "C" unsigned idesc(unsigned fmt, unsigned m, unsigned n, int a_mn, int b_mn) { return hyp::make_idesc(fmt, m, n, a_mn != 0, b_mn != 0); }
+extern "C" unsigned long long smem_desc(unsigned addr, unsigned lbo, unsigned sbo) { return hyp::make_smem_desc_sw128(addr, lbo, sbo); }
+#ifdef WITH_CUTLASS
+#include <cute/arch/mma_sm100_desc.hpp>
+extern "C" unsigned cutlass_idesc(unsigned fmt, unsigned m, unsigned n, int a_mn, int b_mn) {
+  cute::UMMA::InstrDescriptor d = {};
+  d.a_format_ = fmt; d.b_format_ = fmt; d.c_format_ = 1;          // F32 accumulator
+  d.a_major_ = a_mn ? 1 : 0; d.b_major_ = b_mn ? 1 : 0;
+  d.n_dim_ = n >> 3; d.m_dim_ = m >> 4;
+  return d.desc_;
+}
+extern "C" unsigned long long cutlass_smem_desc(unsigned addr, unsigned lbo, unsigned sbo) {
+  cute::UMMA::SmemDescriptor d;
+  d.desc_ = 0;
+  d.start_address_ = (addr & 0x3FFFFu) >> 4; d.leading_byte_offset_ = lbo >> 4; d.stride_byte_offset_ = sbo >> 4;
+  d.version_ = 1; d.layout_type_ = 2;                              // Blackwell, SWIZZLE_128B
+  return d.desc_;
+}
+extern "C" int has_cutlass() { return 1; }
+#else
+extern "C" int has_cutlass() { return 0; }
+#endif
+"""
+
+
+def _cutlass_include():
+    try:
+        import flashinfer
+    except Exception:  # noqa: BLE001
+        return None
+    inc = Path(flashinfer.__file__).parent / "data/cutlass/include"
+    return inc if (inc / "cute/arch/mma_sm100_desc.hpp").exists() else None
+
+
+@pytest.fixture(scope="module")
+def desc_lib(tmp_path_factory):
+    gxx = shutil.which("g++")
+    if gxx is None:
+        pytest.skip("no g++ on this machine")
+    d = tmp_path_factory.mktemp("desclib")
+    (d / "harness.cpp").write_text(DESC_HARNESS)
+    base = [gxx, "-O1", "-std=c++17", "-shared", "-fPIC", "-I", str(ROOT / "csrc"), str(d / "harness.cpp")]
+    inc = _cutlass_include()
+    if inc is not None:
+        so = d / "libdesc_cutlass.so"
+        r = subprocess.run(base + ["-DWITH_CUTLASS", "-I", str(inc), "-I", "/usr/local/cuda/include", "-o", str(so)], capture_output=True, text=True)
+        if r.returncode == 0:
+            return ctypes.CDLL(str(so))
+    so = d / "libdesc.so"
+    subprocess.run(base + ["-o", str(so)], check=True)
+    return ctypes.CDLL(str(so))
+
+
+def test_instruction_descriptor_fields(desc_lib):
+    desc_lib.idesc.restype = ctypes.c_uint32
+    combos = [(fmt, m, n, a, b) for fmt in (0, 1, 2) for m in (64, 128, 256) for n in (8, 64, 128, 256) for a in (0, 1) for b in (0, 1)]
+    for fmt, m, n, a, b in combos:
+        v = desc_lib.idesc(fmt, m, n, a, b)
+        assert (v >> 4) & 0x3 == 1 and v & 0xF == 0                                    # fp32 accumulator, dense, no saturate
+        assert (v >> 7) & 0x7 == fmt and (v >> 10) & 0x7 == fmt                        # A / B format: 0 f16, 1 bf16, 2 tf32
+        assert (v >> 13) & 0x3 == 0                                                    # no negation
+        assert (v >> 15) & 1 == a and (v >> 16) & 1 == b                               # 0 = K-major, 1 = MN-major
+        assert (v >> 17) & 0x3F == n >> 3 and (v >> 23) & 1 == 0
+        assert (v >> 24) & 0x1F == m >> 4 and v >> 29 == 0
+    if desc_lib.has_cutlass():
+        desc_lib.cutlass_idesc.restype = ctypes.c_uint32
+        for c in combos:
+            assert desc_lib.idesc(*c) == desc_lib.cutlass_idesc(*c), c
+
+
+def test_shared_memory_descriptor_fields(desc_lib):
+    desc_lib.smem_desc.restype = ctypes.c_uint64
+    cases = [(0x0, 16, 1024), (0x400, 16, 1024), (0x23C00, 0, 1024), (0x3FFF0, 8192, 16), (0x8000, 2048, 512)]
+    for addr, lbo, sbo in cases:
+        v = desc_lib.smem_desc(addr, lbo, sbo)
+        assert v & 0x3FFF == addr >> 4 and (v >> 14) & 0x3 == 0
+        assert (v >> 16) & 0x3FFF == lbo >> 4 and (v >> 32) & 0x3FFF == sbo >> 4
+        assert (v >> 46) & 0x3 == 1                                                     # descriptor version: Blackwell
+        assert (v >> 48) & 0x1FFF == 0 and v >> 61 == 2                                 # base offset 0, SWIZZLE_128B
+    if desc_lib.has_cutlass():
+        desc_lib.cutlass_smem_desc.restype = ctypes.c_uint64
+        for c in cases:
+            assert desc_lib.smem_desc(*c) == desc_lib.cutlass_smem_desc(*c), c
+    # advancing the start address by k * 32 bytes (one UMMA_K step of 16-bit elements inside a 128-byte swizzle row) only touches the address field
+    a, b = desc_lib.smem_desc(0x400, 16, 1024), desc_lib.smem_desc(0x400 + 64, 16, 1024)
+    assert b - a == 64 >> 4
