@@ -95,6 +95,28 @@ def test_gpt2_checkpoint_dir_round_trip(tmp_path):
         assert float(back(input_ids=ids, labels=ids).loss) == pytest.approx(float(want.loss), rel=1e-5)
 
 
+def test_sharded_safetensors_and_bin_checkpoints(tmp_path):
+    """The 7B checkpoint comes as several shards; older ones as pytorch_model*.bin."""
+    from transformers import LlamaConfig as HC, LlamaForCausalLM as HM
+
+    from hyperion_b200.models import hf as H
+
+    torch.manual_seed(2)
+    ref = HM(HC(vocab_size=320, hidden_size=64, intermediate_size=176, num_hidden_layers=3, num_attention_heads=4, num_key_value_heads=4,
+                tie_word_embeddings=False, pad_token_id=2)).eval()
+    ref.save_pretrained(tmp_path / "sharded", safe_serialization=True, max_shard_size="100KB")
+    assert len(list((tmp_path / "sharded").glob("*.safetensors"))) > 2
+    (tmp_path / "bin").mkdir()
+    (tmp_path / "bin/config.json").write_text((tmp_path / "sharded/config.json").read_text())
+    torch.save(ref.state_dict(), tmp_path / "bin/pytorch_model.bin")
+    want = {k: v for k, v in ref.state_dict().items()}
+    for d in ("sharded", "bin"):
+        got = H.llama_from_pretrained(tmp_path / d, dtype=torch.bfloat16).state_dict()       # converted while copying
+        assert set(got) == set(want)
+        for k in want:
+            assert got[k].dtype == torch.bfloat16 and torch.equal(got[k], want[k].to(torch.bfloat16)), k
+
+
 def test_unsupported_checkpoints_are_refused(tmp_path):
     from hyperion_b200.models import hf as H
 
