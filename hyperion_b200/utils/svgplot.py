@@ -48,11 +48,11 @@ def _ticks(lo: float, hi: float, n: int = 5) -> list[float]:
     return out or [lo, hi]
 
 
-def _frame(title, xlabel, ylabel) -> list[str]:
-    return [f'<svg xmlns="http://www.w3.org/2000/svg" width="{_W}" height="{_H}" font-family="sans-serif" font-size="12">',
-            f'<rect width="{_W}" height="{_H}" fill="white"/>',
+def _frame(title, xlabel, ylabel, extra_bottom: int = 0) -> list[str]:
+    return [f'<svg xmlns="http://www.w3.org/2000/svg" width="{_W}" height="{_H + extra_bottom}" font-family="sans-serif" font-size="12">',
+            f'<rect width="{_W}" height="{_H + extra_bottom}" fill="white"/>',
             f'<text x="{(_ML + _W - _MR) / 2}" y="20" text-anchor="middle" font-size="14">{_esc(title)}</text>',
-            f'<text x="{(_ML + _W - _MR) / 2}" y="{_H - 10}" text-anchor="middle">{_esc(xlabel)}</text>',
+            f'<text x="{(_ML + _W - _MR) / 2}" y="{_H + extra_bottom - 10}" text-anchor="middle">{_esc(xlabel)}</text>',
             f'<text x="15" y="{(_MT + _H - _MB) / 2}" text-anchor="middle" transform="rotate(-90 15 {(_MT + _H - _MB) / 2})">{_esc(ylabel)}</text>',
             f'<rect x="{_ML}" y="{_MT}" width="{_W - _ML - _MR}" height="{_H - _MT - _MB}" fill="none" stroke="black"/>']
 
@@ -108,13 +108,18 @@ def bar_chart(path, categories: list, groups: dict, title: str = "", xlabel: str
     """Grouped bars: ``groups``: series name -> one value per category."""
     vals = [float(v) for g in groups.values() for v in g if v is not None and v == v] or [1.0]
     y1 = max(vals) * 1.05 or 1.0
-    out = _frame(title, xlabel, ylabel)
+    tilt = len(categories) > 6                      # many categories: slanted labels below the axis instead of overlapping ones
+    out = _frame(title, xlabel, ylabel, 70 if tilt else 0)
     ypix = _yaxis(out, 0.0, y1)
     n, k = max(1, len(categories)), max(1, len(groups))
     slot = (_W - _ML - _MR) / n
     bw = slot * 0.8 / k
     for ci, cat in enumerate(categories):
-        out.append(f'<text x="{_ML + slot * (ci + 0.5):.1f}" y="{_H - _MB + 16}" text-anchor="middle">{_esc(cat)}</text>')
+        x, y = _ML + slot * (ci + 0.5), _H - _MB + 16
+        if tilt:
+            out.append(f'<text x="{x:.1f}" y="{y - 4}" text-anchor="end" font-size="10" transform="rotate(-40 {x:.1f} {y - 4})">{_esc(cat)}</text>')
+        else:
+            out.append(f'<text x="{x:.1f}" y="{y}" text-anchor="middle">{_esc(cat)}</text>')
         for gi, (name, g) in enumerate(groups.items()):
             v = g[ci] if ci < len(g) else None
             if v is None or v != v:
